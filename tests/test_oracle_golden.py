@@ -1,0 +1,65 @@
+"""Pin the oracle against golden vectors produced by the live reference
+(tests/golden/make_golden.py).  CPU only."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from oracle import model as omodel
+from helpers import golden_files, load, render_case_inputs
+
+
+@pytest.mark.parametrize("path", golden_files("sampling_"))
+def test_sampling_bit_exact(path):
+    fx = load(path)
+    kc, lindisp = int(fx["n_coarse"]), bool(fx["lindisp"])
+    rays = torch.from_numpy(fx["rays"])
+    # torch restatement
+    z_c = oracle.sample_coarse(rays, kc, torch.from_numpy(fx["u_coarse"]), lindisp)
+    z_i, _ = oracle.sample_fine(rays, torch.from_numpy(fx["weights"]), kc, torch.from_numpy(fx["u_bin"]),
+                                torch.from_numpy(fx["u_in"]), lindisp)
+    z_d = oracle.sample_fine_depth(rays, torch.from_numpy(fx["depth"]), torch.from_numpy(fx["noise"]), 0.01)
+    assert np.array_equal(z_c.numpy(), fx["z_coarse"])
+    assert np.array_equal(z_i.numpy(), fx["z_imp"])
+    assert np.array_equal(z_d.numpy(), fx["z_depth"])
+    assert np.array_equal(oracle.merge_sorted([z_c, z_i, z_d]).numpy(), fx["z_sorted"])
+    # numpy emulation of the exact operation order (what the CUDA kernels implement)
+    assert np.array_equal(oracle.sample_coarse_np(fx["rays"], kc, fx["u_coarse"], lindisp, lin=fx["lin"]), fx["z_coarse"])
+    z_i_np, _ = oracle.sample_fine_np(fx["rays"], fx["weights"], kc, fx["u_bin"], fx["u_in"], lindisp)
+    assert np.array_equal(z_i_np, fx["z_imp"])
+    assert np.array_equal(oracle.sample_fine_depth_np(fx["rays"], fx["depth"], fx["noise"], 0.01), fx["z_depth"])
+
+
+def test_row_sum_matches_torch():
+    g = np.random.Generator(np.random.PCG64(5))
+    for k in (8, 24, 48, 64, 96, 100, 128):
+        x = (g.random((4096, k)) ** 6).astype(np.float32)
+        assert np.array_equal(oracle.aten_row_sum_f32(x), torch.sum(torch.from_numpy(x), -1).numpy())
+
+
+@pytest.mark.parametrize("path", golden_files("render_"))
+def test_render_matches_reference(path):
+    fx = load(path)
+    inp = render_case_inputs(fx)
+    sb, ns = inp["sb"], inp["ns"]
+    rays = inp["rays"].reshape(-1, 8)
+
+    def net_fn(xyz, dirs, coarse):
+        return omodel.net_forward(inp["wc"] if coarse else inp["wf"], inp["latent"], inp["cam"], ns, xyz, dirs)
+
+    with torch.no_grad():
+        probe_c = net_fn(torch.from_numpy(fx["probe_xyz"]), torch.from_numpy(fx["probe_dirs"]), True)
+        probe_f = net_fn(torch.from_numpy(fx["probe_xyz"]), torch.from_numpy(fx["probe_dirs"]), False)
+        out = oracle.render_rays(net_fn, rays, sb, 64, 32, 16, inp["draws"], depth_std=0.01,
+                                 white_bkgd=inp["white"], lindisp=inp["lindisp"])
+    # Same torch ops in the same order on the same machine class: expect (near) bit equality.
+    tol = dict(rtol=0, atol=2e-6)
+    np.testing.assert_allclose(probe_c.numpy(), fx["probe_coarse"], **tol)
+    np.testing.assert_allclose(probe_f.numpy(), fx["probe_fine"], **tol)
+    shp = fx["rgb_coarse"].shape[:2]
+    np.testing.assert_allclose(out["rgb_coarse"].reshape(*shp, 3).numpy(), fx["rgb_coarse"], **tol)
+    np.testing.assert_allclose(out["w_coarse"].reshape(*shp, -1).numpy(), fx["w_coarse"], **tol)
+    np.testing.assert_allclose(out["depth_coarse"].reshape(shp).numpy(), fx["depth_coarse"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(out["rgb_fine"].reshape(*shp, 3).numpy(), fx["rgb_fine"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(out["w_fine"].reshape(*shp, -1).numpy(), fx["w_fine"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(out["depth_fine"].reshape(shp).numpy(), fx["depth_fine"], rtol=0, atol=1e-5)
