@@ -1,0 +1,256 @@
+#!/usr/bin/env python
+"""Benchmark of the render hot path: rays/s for a full coarse+fine render.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--precision fp32|fp16]
+
+Workload (BASELINE.json configs[1]): SRN car 128x128, 1 source view, 64 coarse + 32 fine
+(16 importance + 16 depth) samples, whole frame per step (16 384 rays, 2.62 M MLP rows),
+synthetic scene and conditioned random weights (pixelnerf_b200.synthetic).  A step is one
+frame.  With N > 1 (torchrun) every rank renders its own frame of the same scene (rays are
+independent: weak scaling, no data-path collective except the 16 B/ray result all-gather).
+
+`--impl reference` times the CPU oracle port of the reference's torch path (oracle/, the
+reference is Python and cannot travel to the GPU box) on all host cores, same metric.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+SCENE = "srn_car"
+N_COARSE, N_FINE, N_DEPTH = 64, 32, 16
+MLP_FLOP_PER_POINT = {1: 2 * (1 * 2380800 + 1050624), 2: 2 * (2 * 2380800 + 1050624), 3: 2 * (3 * 2380800 + 1050624)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"],
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        mhz = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": int(self.samples[0][1]),
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def cpu_oracle_rays_per_s(sc, wc, wf, n_rays, repeats=1):
+    """The reference's torch-CPU path (oracle port) on a bounded ray sample."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import oracle_render
+    torch.set_num_threads(os.cpu_count())
+    idx = torch.linspace(0, sc["rays"].shape[0] - 1, n_rays).long()
+    rays = sc["rays"][idx]
+    draws = syn.draws(7, n_rays, N_COARSE, N_FINE - N_DEPTH, N_DEPTH)
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        oracle_render(sc, wc, wf, rays, draws, N_COARSE, N_FINE, N_DEPTH)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return n_rays / best, best
+
+
+def run_reference(args):
+    """--impl reference: CPU oracle port, all host threads, one bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from pixelnerf_b200 import synthetic as syn
+    sc = syn.scene(SCENE)
+    wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
+    sample = 512
+    for _ in range(args.warmup):
+        cpu_oracle_rays_per_s(sc, wc, wf, sample)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_oracle_rays_per_s(sc, wc, wf, sample)
+    dt = time.perf_counter() - t0
+    val = sample * args.steps / dt
+    cores = os.cpu_count()
+    line = {"impl": "reference", "metric": "rays/sec coarse+fine", "value": val, "unit": "rays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"SRN car 128x128 NS=1, {N_COARSE}+{N_FINE} samples; {sample}-ray sample per step "
+                                   "(CPU cost is linear in rays)"},
+            "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cores, "kind": "port",
+                             "sample": f"{sample} rays/step x {args.steps} steps, torch {torch.__version__} CPU, "
+                                       f"{cores} threads"},
+            "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_gpu(args):
+    import torch.distributed as dist
+    from pixelnerf_b200 import _lib, synthetic as syn
+    from pixelnerf_b200.testing import build_net
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback; see --impl reference)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    sc = syn.scene(SCENE, target_az=10.0 * rank)  # every rank: its own target frame, same scene
+    wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
+    net, ren = build_net(sc, wc, wf, dev, mlp_precision=args.precision)
+    if world > 1:  # encoder features come from rank 0 once per encode
+        lat = net.encoder.latent.contiguous()
+        dist.broadcast(lat, src=0)
+        net.encoder.latent = lat
+        net._refresh_camera()
+    par = ren.bind_parallel(net, [local], simple_output=True).eval()
+    n_rays = sc["rays"].shape[0]
+    rays_host = sc["rays"].reshape(1, n_rays, 8).contiguous().pin_memory()
+    rays_dev = rays_host.to(dev)
+    out_host = torch.empty(n_rays, 4).pin_memory()
+    gathered = torch.empty(world * n_rays, 4, device=dev) if world > 1 else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step(rays):
+        with torch.no_grad():
+            rgb, depth = par(rays)
+        res = torch.cat([rgb.reshape(-1, 3), depth.reshape(-1, 1)], -1)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, res)
+        return res
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """K steps, CUDA events on the launching stream, L2 flushed between steps (untimed)."""
+        total = 0.0
+        for _ in range(steps):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+            total += a.elapsed_time(b)
+        t = torch.tensor([total], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step(rays_dev)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    _lib.PROFILE = {}
+    launches0 = _lib.launch_count()
+    ms = timed(lambda: step(rays_dev), args.steps)
+    barrier()
+    launches = _lib.launch_count() - launches0
+    prof = {k: sum(a.elapsed_time(b) for a, b in v) for k, v in _lib.PROFILE.items()}
+    n_mlp = len(_lib.PROFILE.get("mlp", []))
+    _lib.PROFILE = None
+
+    def e2e_step():  # public API with HOST buffers: H2D of the rays, D2H of rgb+depth, inside the timed region
+        res = step(rays_host.to(dev, non_blocking=True))
+        out_host.copy_(res, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    e2e_step()
+    barrier()
+    ms_e2e = timed(e2e_step, args.steps)
+    barrier()
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    if rank == 0:
+        pk = peaks()
+        ns = sc["ns"]
+        rays_total = world * n_rays * args.steps
+        flop_step = n_rays * (N_COARSE + N_COARSE + N_FINE) * MLP_FLOP_PER_POINT[ns]
+        mlp_ms = prof.get("mlp", 0.0) / max(1, args.steps)
+        achieved = flop_step / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else 0.0
+        line = {
+            "metric": "rays/sec coarse+fine", "value": rays_total / (ms * 1e-3), "unit": "rays/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp32": "f32", "fp16": "f16", "bf16": "bf16"}[args.precision], "data": "synthetic",
+            "config": {"workload": f"SRN car 128x128 NS=1 full frame: {n_rays} rays/GPU/step, {N_COARSE} coarse + "
+                                   f"{N_FINE} fine ({N_DEPTH} depth) samples, ResnetFC 5x512 x2",
+                       "mlp_precision": args.precision, "parallelism": f"ray-sharded x{world}",
+                       "cache": "256 MiB L2 flush between steps; per-step intermediates (>=2.9 GB features) exceed L2"},
+            "e2e": {"value": rays_total / (ms_e2e * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": n_rays * 32,
+                    "d2h_bytes_per_step": n_rays * 16},
+            "gpu_launches": launches,
+            "clocks": sampler.summary(),
+            "roofline": {"bound": "tensor", "kernel": "ResnetFC chain (%s)" % args.precision, "achieved": achieved,
+                         "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
+                         "traffic": None, "peak_source": pk["source"] + ", sustained bf16",
+                         "launches_per_step": n_mlp // max(1, args.steps), "ms_per_step": mlp_ms},
+            "stage_ms_per_step": {k: v / args.steps for k, v in prof.items()},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            sample = 1024
+            v, secs = cpu_oracle_rays_per_s(sc, wc, wf, sample)
+            line["cpu_baseline"] = {"value": v, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"{sample} evenly spaced rays of the same frame, {secs:.1f} s, torch "
+                                              f"{torch.__version__} CPU"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp32"), choices=["fp32", "fp16", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

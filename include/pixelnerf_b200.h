@@ -1,0 +1,149 @@
+/* pixelnerf_b200 -- C ABI of the B200 (sm_100a) render hot path.
+ *
+ * The reference (etiiiR/pixel-nerf) is pure Python/PyTorch and has no FFI of its
+ * own; its boundary for this path is the Python API (make_model /
+ * PixelNeRFNet.encode / forward, NeRFRenderer.from_conf / bind_parallel).  The
+ * Python mirror of that API in pixelnerf_b200/{model,render} binds the entry
+ * points below with ctypes (pixelnerf_b200/_lib.py); INTEGRATION.md shows the
+ * stub.  Each entry point cites the reference code whose torch op sequence it
+ * replaces (paths are relative to the reference root).
+ *
+ * Conventions: every pointer is a DEVICE pointer unless named host_*; tensors are
+ * dense row-major fp32 unless stated; the library never allocates or frees device
+ * memory (outputs and workspaces are caller-owned); kernels are enqueued on
+ * `stream` and the call returns without synchronising; the return value is 0 on
+ * success, otherwise a PN_ERR_* code and pn_last_error() (thread-local) holds a
+ * message.  All functions are re-entrant and keep no per-process device state.
+ */
+#ifndef PIXELNERF_B200_H
+#define PIXELNERF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PN_OK 0
+#define PN_ERR_INVALID 1     /* bad argument / unsupported configuration */
+#define PN_ERR_CUDA 2        /* CUDA runtime error */
+#define PN_ERR_UNSUPPORTED 3 /* valid in the reference, deliberately not in this path */
+
+#define PN_DTYPE_F32 0
+#define PN_DTYPE_F16 1
+#define PN_DTYPE_BF16 2
+
+#define PN_D_HIDDEN 512  /* ResnetFC d_hidden of every shipped conf (conf/default_mv.conf:10,17) */
+#define PN_D_LATENT 512  /* ResNet34 4-level latent (src/model/encoder.py:70) */
+#define PN_D_CODE 42     /* 3 + 2*6*3 positional encoding + 3 view-dir (src/model/models.py:49-60) */
+#define PN_N_BLOCKS 5
+#define PN_COMBINE_LAYER 3
+
+typedef void* pn_stream_t; /* cudaStream_t */
+
+#if defined(__GNUC__)
+#define PN_API __attribute__((visibility("default")))
+#else
+#define PN_API
+#endif
+
+PN_API int pn_version(void);
+PN_API const char* pn_last_error(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+PN_API uint64_t pn_launch_count(void);
+
+/* ---- (1) ray sampling ---------------------------------------------------------------- */
+
+/* NeRFRenderer.sample_coarse, src/render/nerf.py:98-118.  rays (R,8) =
+ * [origin, dir, near, far]; host-made table lin = torch.linspace(0, 1-1/Kc, Kc);
+ * u (R,Kc) uniform draws or NULL to draw in-kernel from (seed).  Every fp32
+ * operation is rounded where torch rounds it (bit-exact with torch-CPU). */
+PN_API int pn_sample_coarse(const float* rays, const float* u, const float* lin, float* z,
+                     int64_t n_rays, int n_coarse, int lindisp, uint64_t seed, pn_stream_t stream);
+
+/* NeRFRenderer.sample_fine + sample_fine_depth + cat + sort,
+ * src/render/nerf.py:120-161, 285-295.  weights (R,Kc) and depth (R) are the coarse
+ * composite outputs; u_bin/u_in (R,Kf) and noise (R,Kd) are injected draws or NULL.
+ * z_sorted (R,Kc+Kf+Kd) is the merged ascending sample set; z_imp (R,Kf) and
+ * z_depth (R,Kd) are optional outputs (NULL to skip).  Kf or Kd may be 0. */
+PN_API int pn_sample_fine(const float* rays, const float* z_coarse, const float* weights, const float* depth,
+                   const float* u_bin, const float* u_in, const float* noise,
+                   float* z_sorted, float* z_imp, float* z_depth,
+                   int64_t n_rays, int n_coarse, int n_imp, int n_depth, float depth_std,
+                   int lindisp, uint64_t seed, pn_stream_t stream);
+
+/* ---- (2) point features ---------------------------------------------------------------- */
+
+/* NCHW fp32 encoder output (src/model/encoder.py:150-164) -> channels-last map
+ * (V,Hl,Wl,C) in fp32 or fp16, so one bilinear tap is one contiguous C-vector. */
+PN_API int pn_prepare_latent(const float* latent_nchw, void* latent_nhwc, int n_maps, int channels,
+                      int hl, int wl, int dtype, pn_stream_t stream);
+
+typedef struct pn_camera {
+  const float* poses;   /* (SB*NS,3,4) world->camera, as cached by encode(), models.py:112-114 */
+  const float* focal;   /* (SB*NS,2) [fx,-fy] already expanded per view, models.py:120-130 */
+  const float* c;       /* (SB*NS,2) principal points, models.py:132-141 */
+  float scale_x;        /* latent_scaling[0] / image_width,  encoder.py:98-99,161-163 */
+  float scale_y;        /* latent_scaling[1] / image_height */
+  int hl, wl;           /* latent map size */
+  int n_objects;        /* SB */
+  int n_views;          /* NS */
+} pn_camera_t;
+
+/* PixelNeRFNet.forward up to the MLP input, src/model/models.py:157-227 +
+ * SpatialEncoder.index src/model/encoder.py:80-109 + PositionalEncoding
+ * src/model/code.py:30-42.  Points come either from rays+z (renderer path:
+ * x = o + z d, viewdir = d, src/render/nerf.py:185,203-208; n_samples = K, P = rays
+ * per object * K) or from xyz/viewdirs (SB,P,3) when rays == NULL.
+ * Rows are ordered (object, view, point).  feat_z (N,512) and feat_x (N,ldx) are
+ * written in out_dtype; columns [42,ldx) of feat_x are zero. */
+PN_API int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc, int latent_dtype,
+                      const float* rays, const float* z, int n_samples,
+                      const float* xyz, const float* viewdirs,
+                      int64_t points_per_object, void* feat_z, void* feat_x, int ldx, int out_dtype,
+                      pn_stream_t stream);
+
+/* ---- (3) ResnetFC ---------------------------------------------------------------------- */
+
+typedef struct pn_mlp_weights {
+  const float* lin_in_w;  const float* lin_in_b;                 /* (512,42), (512)  resnetfc.py:88 */
+  const float* fc0_w[PN_N_BLOCKS]; const float* fc0_b[PN_N_BLOCKS]; /* (512,512)     resnetfc.py:32 */
+  const float* fc1_w[PN_N_BLOCKS]; const float* fc1_b[PN_N_BLOCKS]; /* (512,512)     resnetfc.py:33 */
+  const float* lin_z_w[PN_COMBINE_LAYER]; const float* lin_z_b[PN_COMBINE_LAYER]; /* resnetfc.py:112-114 */
+  const float* lin_out_w; const float* lin_out_b;                /* (4,512), (4)     resnetfc.py:92 */
+} pn_mlp_weights_t;
+
+/* Workspace for pn_mlp_forward_fp32 over n_rows = SB*NS*P feature rows. */
+PN_API size_t pn_mlp_fp32_workspace_bytes(int64_t n_rows);
+
+/* ResnetFC.forward (src/model/resnetfc.py:132-184) + output head
+ * (src/model/models.py:257-266) in fp32 on CUDA cores: the 1e-4 parity path.
+ * feat_z (N,512) fp32, feat_x (N,ldx>=42) fp32, rows ordered (object, view, point);
+ * out (SB*P,4) = [sigmoid(rgb), relu(sigma)].  If pre_act is not NULL the raw
+ * lin_out outputs (SB*P,4) are stored there too (needed by the backward). */
+PN_API int pn_mlp_forward_fp32(const pn_mlp_weights_t* w, const float* feat_z, const float* feat_x, int ldx,
+                        int n_objects, int n_views, int64_t points_per_object,
+                        float* out, float* pre_act, void* workspace, size_t workspace_bytes,
+                        pn_stream_t stream);
+
+/* ---- (4) compositing ------------------------------------------------------------------- */
+
+/* NeRFRenderer.composite after the model call, src/render/nerf.py:178-182, 228-249.
+ * rgb_sigma (R,K,4), z (R,K), rays (R,8) -> weights (R,K), rgb (R,3), depth (R). */
+PN_API int pn_composite_fwd(const float* rgb_sigma, const float* z, const float* rays,
+                     float* weights, float* rgb, float* depth,
+                     int64_t n_rays, int n_samples, int white_bkgd, pn_stream_t stream);
+
+/* Hand-written backward of the above (autograd of nerf.py:228-249; formulas in
+ * DESIGN.md): upstream g_rgb (R,3), g_depth (R) or NULL, g_weights (R,K) or NULL
+ * -> g_rgb_sigma (R,K,4) and, if not NULL, g_z (R,K). */
+PN_API int pn_composite_bwd(const float* rgb_sigma, const float* z, const float* rays,
+                     const float* g_rgb, const float* g_depth, const float* g_weights,
+                     float* g_rgb_sigma, float* g_z,
+                     int64_t n_rays, int n_samples, int white_bkgd, pn_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIXELNERF_B200_H */

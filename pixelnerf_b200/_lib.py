@@ -1,0 +1,235 @@
+"""ctypes binding of libpixelnerf_b200.so (the C ABI in include/pixelnerf_b200.h).
+
+There is deliberately no fallback: if the shared library is missing or a tensor is
+not on a CUDA device the call raises.  torch is used only to own device memory and
+to supply the current stream.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpixelnerf_b200.so")
+
+DTYPE_F32, DTYPE_F16 = 0, 1
+D_HIDDEN, D_LATENT, D_CODE, N_BLOCKS, COMBINE_LAYER = 512, 512, 42, 5, 3
+
+_vp, _i64, _int, _u64, _f32, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_float, C.c_size_t
+
+
+class Camera(C.Structure):
+    _fields_ = [("poses", _vp), ("focal", _vp), ("c", _vp), ("scale_x", _f32), ("scale_y", _f32),
+                ("hl", _int), ("wl", _int), ("n_objects", _int), ("n_views", _int)]
+
+
+class MlpWeights(C.Structure):
+    _fields_ = [("lin_in_w", _vp), ("lin_in_b", _vp),
+                ("fc0_w", _vp * N_BLOCKS), ("fc0_b", _vp * N_BLOCKS),
+                ("fc1_w", _vp * N_BLOCKS), ("fc1_b", _vp * N_BLOCKS),
+                ("lin_z_w", _vp * COMBINE_LAYER), ("lin_z_b", _vp * COMBINE_LAYER),
+                ("lin_out_w", _vp), ("lin_out_b", _vp)]
+
+
+_SIGNATURES = {
+    "pn_version": (_int, []),
+    "pn_last_error": (C.c_char_p, []),
+    "pn_launch_count": (_u64, []),
+    "pn_sample_coarse": (_int, [_vp, _vp, _vp, _vp, _i64, _int, _int, _u64, _vp]),
+    "pn_sample_fine": (_int, [_vp] * 10 + [_i64, _int, _int, _int, _f32, _int, _u64, _vp]),
+    "pn_prepare_latent": (_int, [_vp, _vp, _int, _int, _int, _int, _int, _vp]),
+    "pn_point_features": (_int, [C.POINTER(Camera), _vp, _int, _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp,
+                                 _int, _int, _vp]),
+    "pn_mlp_fp32_workspace_bytes": (_sz, [_i64]),
+    "pn_mlp_forward_fp32": (_int, [C.POINTER(MlpWeights), _vp, _vp, _int, _int, _int, _i64, _vp, _vp, _vp,
+                                   _sz, _vp]),
+    "pn_composite_fwd": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
+    "pn_composite_bwd": (_int, [_vp] * 8 + [_i64, _int, _int, _vp]),
+}
+
+_lib = None
+
+# bench.py sets PROFILE = {} to collect CUDA-event pairs per kernel family (recorded on the
+# launching stream, read after the step's final synchronise); None = no events.
+PROFILE = None
+
+
+class _Timed:
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            self.ev[0].record()
+
+    def __exit__(self, *exc):
+        if PROFILE is not None:
+            self.ev[1].record()
+            PROFILE.setdefault(self.name, []).append(self.ev)
+
+
+def exported_symbols():
+    return sorted(_SIGNATURES)
+
+
+def lib():
+    """Load the shared library once; raise (never fall back) if it is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(make -C pixelnerf_b200/csrc).  pixelnerf_b200 has no non-CUDA fallback.")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = handle
+    return _lib
+
+
+def launch_count():
+    return int(lib().pn_launch_count())
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"{what} failed ({rc}): {lib().pn_last_error().decode()}")
+
+
+def _ptr(t, dtype=torch.float32):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("pixelnerf_b200 kernels need CUDA tensors (there is no CPU path)")
+    if t.dtype != dtype or not t.is_contiguous():
+        raise RuntimeError(f"expected contiguous {dtype} tensor, got {t.dtype} contiguous={t.is_contiguous()}")
+    return t.data_ptr()
+
+
+def _f32c(t):
+    return None if t is None else t.detach().to(torch.float32).contiguous()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+_LIN_CACHE = {}
+
+
+def _linspace(n_coarse, device):
+    key = (n_coarse, str(device))
+    if key not in _LIN_CACHE:  # host-made table, see SURVEY 8a(a2): never re-derive torch.linspace
+        _LIN_CACHE[key] = torch.linspace(0, 1 - 1.0 / n_coarse, n_coarse).to(device)
+    return _LIN_CACHE[key]
+
+
+def sample_coarse(rays, n_coarse, lindisp=False, u=None, seed=0):
+    rays, u = _f32c(rays), _f32c(u)
+    z = torch.empty(rays.shape[0], n_coarse, device=rays.device, dtype=torch.float32)
+    _check(lib().pn_sample_coarse(_ptr(rays), _ptr(u), _ptr(_linspace(n_coarse, rays.device)), _ptr(z),
+                                  rays.shape[0], n_coarse, int(bool(lindisp)), seed, _stream()), "pn_sample_coarse")
+    return z
+
+
+def sample_fine(rays, z_coarse, weights, depth, n_imp, n_depth, depth_std, lindisp=False,
+                u_bin=None, u_in=None, noise=None, seed=0, want_parts=False):
+    rays, z_coarse, weights, depth = _f32c(rays), _f32c(z_coarse), _f32c(weights), _f32c(depth)
+    u_bin, u_in, noise = _f32c(u_bin), _f32c(u_in), _f32c(noise)
+    r, kc = z_coarse.shape
+    dev = rays.device
+    z_sorted = torch.empty(r, kc + n_imp + n_depth, device=dev, dtype=torch.float32)
+    z_imp = torch.empty(r, n_imp, device=dev, dtype=torch.float32) if want_parts else None
+    z_dep = torch.empty(r, n_depth, device=dev, dtype=torch.float32) if want_parts else None
+    _check(lib().pn_sample_fine(_ptr(rays), _ptr(z_coarse), _ptr(weights), _ptr(depth), _ptr(u_bin), _ptr(u_in),
+                                _ptr(noise), _ptr(z_sorted), _ptr(z_imp), _ptr(z_dep), r, kc, n_imp, n_depth,
+                                float(depth_std), int(bool(lindisp)), seed, _stream()), "pn_sample_fine")
+    return (z_sorted, z_imp, z_dep) if want_parts else z_sorted
+
+
+def prepare_latent(latent_nchw, dtype=torch.float32):
+    lat = _f32c(latent_nchw)
+    v, ch, hl, wl = lat.shape
+    if ch != D_LATENT:
+        raise NotImplementedError(f"latent size {ch} != {D_LATENT}: only the 4-level ResNet34 latent is supported")
+    out = torch.empty(v, hl, wl, ch, device=lat.device, dtype=dtype)
+    code = DTYPE_F32 if dtype == torch.float32 else DTYPE_F16
+    _check(lib().pn_prepare_latent(_ptr(lat), out.data_ptr(), v, ch, hl, wl, code, _stream()), "pn_prepare_latent")
+    return out
+
+
+def point_features(cam_bufs, latent_nhwc, ppo, *, rays=None, z=None, xyz=None, viewdirs=None, ldx=44):
+    """cam_bufs: dict(poses (V,3,4), focal (V,2), c (V,2), scale_x, scale_y, n_objects, n_views)."""
+    dt = latent_nhwc.dtype
+    code = DTYPE_F32 if dt == torch.float32 else DTYPE_F16
+    v, hl, wl, _ = latent_nhwc.shape
+    cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
+                 cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
+    if v != cam.n_objects * cam.n_views:
+        raise RuntimeError(f"latent holds {v} maps but camera state has {cam.n_objects}x{cam.n_views} views")
+    n_rows = v * ppo
+    dev = latent_nhwc.device
+    feat_z = torch.empty(n_rows, D_LATENT, device=dev, dtype=dt)
+    feat_x = torch.empty(n_rows, ldx, device=dev, dtype=dt)
+    rays, z, xyz, viewdirs = _f32c(rays), _f32c(z), _f32c(xyz), _f32c(viewdirs)
+    k = 0 if z is None else z.shape[-1]
+    with _Timed("features"):
+        _check(lib().pn_point_features(C.byref(cam), latent_nhwc.data_ptr(), code, _ptr(rays), _ptr(z), k,
+                                       _ptr(xyz), _ptr(viewdirs), ppo, feat_z.data_ptr(), feat_x.data_ptr(), ldx,
+                                       code, _stream()), "pn_point_features")
+    return feat_z, feat_x
+
+
+def pack_weights_fp32(w):
+    """dict of un-prefixed ResnetFC tensors (CUDA fp32 contiguous) -> (MlpWeights, keepalive)."""
+    keep = {k: _f32c(v) for k, v in w.items()}
+    s = MlpWeights()
+    s.lin_in_w, s.lin_in_b = _ptr(keep["lin_in.weight"]), _ptr(keep["lin_in.bias"])
+    for b in range(N_BLOCKS):
+        s.fc0_w[b], s.fc0_b[b] = _ptr(keep[f"blocks.{b}.fc_0.weight"]), _ptr(keep[f"blocks.{b}.fc_0.bias"])
+        s.fc1_w[b], s.fc1_b[b] = _ptr(keep[f"blocks.{b}.fc_1.weight"]), _ptr(keep[f"blocks.{b}.fc_1.bias"])
+    for b in range(COMBINE_LAYER):
+        s.lin_z_w[b], s.lin_z_b[b] = _ptr(keep[f"lin_z.{b}.weight"]), _ptr(keep[f"lin_z.{b}.bias"])
+    s.lin_out_w, s.lin_out_b = _ptr(keep["lin_out.weight"]), _ptr(keep["lin_out.bias"])
+    return s, keep
+
+
+def mlp_forward_fp32(packed, feat_z, feat_x, n_objects, n_views, ppo, want_pre=False):
+    s, _keep = packed
+    n_rows = n_objects * n_views * ppo
+    dev = feat_z.device
+    out = torch.empty(n_objects * ppo, 4, device=dev, dtype=torch.float32)
+    pre = torch.empty_like(out) if want_pre else None
+    nbytes = lib().pn_mlp_fp32_workspace_bytes(n_rows)
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    with _Timed("mlp"):
+        _check(lib().pn_mlp_forward_fp32(C.byref(s), _ptr(feat_z), _ptr(feat_x), feat_x.shape[1], n_objects,
+                                         n_views, ppo, _ptr(out), _ptr(pre), ws.data_ptr(), nbytes, _stream()),
+               "pn_mlp_forward_fp32")
+    return (out, pre) if want_pre else out
+
+
+def composite_fwd(rgb_sigma, z, rays, white_bkgd):
+    rgb_sigma, z, rays = _f32c(rgb_sigma), _f32c(z), _f32c(rays)
+    r, k = z.shape
+    dev = z.device
+    weights = torch.empty(r, k, device=dev, dtype=torch.float32)
+    rgb = torch.empty(r, 3, device=dev, dtype=torch.float32)
+    depth = torch.empty(r, device=dev, dtype=torch.float32)
+    with _Timed("composite"):
+        _check(lib().pn_composite_fwd(_ptr(rgb_sigma), _ptr(z), _ptr(rays), _ptr(weights), _ptr(rgb), _ptr(depth),
+                                      r, k, int(bool(white_bkgd)), _stream()), "pn_composite_fwd")
+    return weights, rgb, depth
+
+
+def composite_bwd(rgb_sigma, z, rays, white_bkgd, g_rgb, g_depth=None, g_weights=None, want_gz=True):
+    rgb_sigma, z, rays = _f32c(rgb_sigma), _f32c(z), _f32c(rays)
+    g_rgb, g_depth, g_weights = _f32c(g_rgb), _f32c(g_depth), _f32c(g_weights)
+    r, k = z.shape
+    g_rs = torch.empty(r, k, 4, device=z.device, dtype=torch.float32)
+    g_z = torch.empty(r, k, device=z.device, dtype=torch.float32) if want_gz else None
+    _check(lib().pn_composite_bwd(_ptr(rgb_sigma), _ptr(z), _ptr(rays), _ptr(g_rgb), _ptr(g_depth), _ptr(g_weights),
+                                  _ptr(g_rs), _ptr(g_z), r, k, int(bool(white_bkgd)), _stream()), "pn_composite_bwd")
+    return g_rs, g_z

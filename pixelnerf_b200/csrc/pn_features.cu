@@ -1,0 +1,200 @@
+// Point features: world->view transform, projection, bilinear latent gather and
+// positional encoding (reference src/model/models.py:157-227,
+// src/model/encoder.py:80-109, src/model/code.py:30-42, src/util/util.py:58-65).
+//
+// Layout: the latent is channels-last (V,Hl,Wl,C) so each of the four bilinear taps is
+// one contiguous C-vector; one warp produces one feature row, lanes stride the
+// channel axis in 16-byte vectors (512 B per warp load instruction, fully coalesced).
+// Rows are ordered (object, view, point) like the reference's repeat_interleave.
+#include "pn_common.cuh"
+
+namespace pn {
+
+// NCHW fp32 -> NHWC (fp32 or fp16) through a padded 32x32 shared tile.
+template <typename OutT>
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc_kernel(const float* __restrict__ src, OutT* __restrict__ dst, int channels, int hw) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z;
+  const int c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
+  const float* s = src + (size_t)n * channels * hw;
+  OutT* d = dst + (size_t)n * channels * hw;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int c = c0 + i, p = p0 + threadIdx.x;
+    tile[i][threadIdx.x] = (c < channels && p < hw) ? s[(size_t)c * hw + p] : 0.0f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int p = p0 + i, c = c0 + threadIdx.x;
+    if (p < hw && c < channels) d[(size_t)p * channels + c] = (OutT)tile[threadIdx.x][i];
+  }
+}
+
+struct CamView {
+  float r[9], t[3], fx, fy, cx, cy;
+};
+
+__device__ __forceinline__ void store_vec4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void store_vec4(__half* p, float4 v) {
+  __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&a);
+  u.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+__device__ __forceinline__ float4 load_vec4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 load_vec4(const __half* p) {
+  uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
+  float2 a = __half22float2(*reinterpret_cast<__half2*>(&u.x));
+  float2 b = __half22float2(*reinterpret_cast<__half2*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void store_one(float* p, float v) { *p = v; }
+__device__ __forceinline__ void store_one(__half* p, float v) { *p = __float2half_rn(v); }
+
+constexpr int kFeatWarps = 8;
+
+template <typename LatT, typename OutT>
+__global__ void __launch_bounds__(kFeatWarps * 32)
+point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
+                      const float* __restrict__ rays, const float* __restrict__ zs, int n_samples,
+                      const float* __restrict__ xyz_in, const float* __restrict__ dirs_in,
+                      int64_t ppo, OutT* __restrict__ feat_z, OutT* __restrict__ feat_x, int ldx,
+                      int64_t n_rows) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5);
+  if (row >= n_rows) return;
+  // row = (obj * NS + view) * P + p
+  const int64_t ov = row / ppo;
+  const int64_t p = row - ov * ppo;
+  const int view = (int)ov;
+  const int obj = view / cam.n_views;
+
+  float x, y, z, dx, dy, dz;
+  if (rays) {  // x = o + z d  (src/render/nerf.py:185), separate mul and add like torch
+    const int64_t ray = obj * (ppo / n_samples) + p / n_samples;
+    const float* rr = rays + ray * 8;
+    const float zz = zs[ray * n_samples + (p % n_samples)];
+    dx = rr[3]; dy = rr[4]; dz = rr[5];
+    x = __fadd_rn(rr[0], __fmul_rn(zz, dx));
+    y = __fadd_rn(rr[1], __fmul_rn(zz, dy));
+    z = __fadd_rn(rr[2], __fmul_rn(zz, dz));
+  } else {
+    const float* pp = xyz_in + ((int64_t)obj * ppo + p) * 3;
+    x = pp[0]; y = pp[1]; z = pp[2];
+    if (dirs_in) {
+      const float* dd = dirs_in + ((int64_t)obj * ppo + p) * 3;
+      dx = dd[0]; dy = dd[1]; dz = dd[2];
+    } else { dx = dy = dz = 0.0f; }
+  }
+  const float* P = cam.poses + (size_t)view * 12;  // (3,4) row-major [R | t]
+  const float r0 = P[0], r1 = P[1], r2 = P[2], t0 = P[3];
+  const float r3 = P[4], r4 = P[5], r5 = P[6], t1 = P[7];
+  const float r6 = P[8], r7 = P[9], r8 = P[10], t2 = P[11];
+  // xyz_rot = R x (models.py:162-164); xyz = xyz_rot + t (:165)
+  const float xr = r0 * x + r1 * y + r2 * z;
+  const float yr = r3 * x + r4 * y + r5 * z;
+  const float zr = r6 * x + r7 * y + r8 * z;
+  const float xc = xr + t0, yc = yr + t1, zc = zr + t2;
+  // uv = -xy/z * focal + c (models.py:206-212); focal = [fx, -fy]
+  const float fx = cam.focal[view * 2 + 0], fy = cam.focal[view * 2 + 1];
+  const float cx = cam.c[view * 2 + 0], cy = cam.c[view * 2 + 1];
+  const float u = (-xc / zc) * fx + cx;
+  const float v = (-yc / zc) * fy + cy;
+  // encoder.index (encoder.py:98-108): uv*scale - 1, then grid_sample(align_corners, border)
+  const float gx = u * cam.scale_x - 1.0f, gy = v * cam.scale_y - 1.0f;
+  float ix = ((gx + 1.0f) * 0.5f) * (float)(cam.wl - 1);
+  float iy = ((gy + 1.0f) * 0.5f) * (float)(cam.hl - 1);
+  ix = fminf(fmaxf(ix, 0.0f), (float)(cam.wl - 1));
+  iy = fminf(fmaxf(iy, 0.0f), (float)(cam.hl - 1));
+  // NaN (point on the camera plane) propagates through fminf/fmaxf as the clamp bound: texel 0
+  const float fx0 = floorf(ix), fy0 = floorf(iy);
+  const int x0 = (int)fx0, y0 = (int)fy0;
+  const int x1 = min(x0 + 1, cam.wl - 1), y1 = min(y0 + 1, cam.hl - 1);
+  const float ax = ix - fx0, ay = iy - fy0;  // weight of the +1 tap (0 when clamped at the border)
+  const float w00 = (1.0f - ax) * (1.0f - ay), w01 = ax * (1.0f - ay);
+  const float w10 = (1.0f - ax) * ay, w11 = ax * ay;
+  const LatT* base = latent + (size_t)view * cam.hl * cam.wl * PN_D_LATENT;
+  const LatT* p00 = base + ((size_t)y0 * cam.wl + x0) * PN_D_LATENT;
+  const LatT* p01 = base + ((size_t)y0 * cam.wl + x1) * PN_D_LATENT;
+  const LatT* p10 = base + ((size_t)y1 * cam.wl + x0) * PN_D_LATENT;
+  const LatT* p11 = base + ((size_t)y1 * cam.wl + x1) * PN_D_LATENT;
+  OutT* oz = feat_z + (size_t)row * PN_D_LATENT;
+#pragma unroll
+  for (int i = 0; i < PN_D_LATENT / 128; ++i) {
+    const int ch = i * 128 + lane * 4;
+    const float4 a = load_vec4(p00 + ch), b = load_vec4(p01 + ch);
+    const float4 c = load_vec4(p10 + ch), d = load_vec4(p11 + ch);
+    float4 o;
+    o.x = a.x * w00 + b.x * w01 + c.x * w10 + d.x * w11;
+    o.y = a.y * w00 + b.y * w01 + c.y * w10 + d.y * w11;
+    o.z = a.z * w00 + b.z * w01 + c.z * w10 + d.z * w11;
+    o.w = a.w * w00 + b.w * w01 + c.w * w10 + d.w * w11;
+    store_vec4(oz + ch, o);
+  }
+  // code: [x(3), sin(f_j x + phase_j)(36), R d (3)], zero pad to ldx
+  OutT* ox = feat_x + (size_t)row * ldx;
+  for (int e = lane; e < ldx; e += 32) {
+    float val = 0.0f;
+    if (e < 3) {
+      val = e == 0 ? xr : e == 1 ? yr : zr;
+    } else if (e < 39) {
+      const int j = (e - 3) / 3, d = (e - 3) % 3;
+      const float comp = d == 0 ? xr : d == 1 ? yr : zr;
+      const float freq = 1.5f * (float)(1 << (j >> 1));      // freq_factor * 2^k (conf/default.conf:19-23)
+      const float phase = (j & 1) ? 1.57079637050628662109375f : 0.0f;  // float32(pi/2) (code.py:24-28)
+      val = sinf(__fadd_rn(phase, __fmul_rn(comp, freq)));   // addcmul then sin (code.py:38)
+    } else if (e < 42) {
+      const int d = e - 39;
+      val = d == 0 ? (r0 * dx + r1 * dy + r2 * dz) : d == 1 ? (r3 * dx + r4 * dy + r5 * dz)
+                                                            : (r6 * dx + r7 * dy + r8 * dz);
+    }
+    store_one(ox + e, val);
+  }
+}
+
+}  // namespace pn
+
+extern "C" int pn_prepare_latent(const float* latent_nchw, void* latent_nhwc, int n_maps, int channels,
+                                 int hl, int wl, int dtype, pn_stream_t stream) {
+  PN_CHECK_ARG(latent_nchw && latent_nhwc, "pn_prepare_latent: null pointer");
+  PN_CHECK_ARG(n_maps > 0 && channels > 0 && hl > 0 && wl > 0, "pn_prepare_latent: bad sizes");
+  PN_CHECK_ARG(dtype == PN_DTYPE_F32 || dtype == PN_DTYPE_F16, "pn_prepare_latent: dtype must be f32 or f16");
+  const int hw = hl * wl;
+  dim3 grid(pn::ceil_div(hw, 32), pn::ceil_div(channels, 32), n_maps), block(32, 8);
+  if (dtype == PN_DTYPE_F32)
+    pn::nchw_to_nhwc_kernel<float><<<grid, block, 0, (cudaStream_t)stream>>>(latent_nchw, (float*)latent_nhwc, channels, hw);
+  else
+    pn::nchw_to_nhwc_kernel<__half><<<grid, block, 0, (cudaStream_t)stream>>>(latent_nchw, (__half*)latent_nhwc, channels, hw);
+  PN_LAUNCH_OK("nchw_to_nhwc_kernel");
+  pn::count_launch();
+  return PN_OK;
+}
+
+extern "C" int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc, int latent_dtype,
+                                 const float* rays, const float* z, int n_samples, const float* xyz,
+                                 const float* viewdirs, int64_t points_per_object, void* feat_z,
+                                 void* feat_x, int ldx, int out_dtype, pn_stream_t stream) {
+  PN_CHECK_ARG(cam && latent_nhwc && feat_z && feat_x, "pn_point_features: null pointer");
+  PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_features: camera buffers missing (call encode first)");
+  PN_CHECK_ARG((rays && z && n_samples > 0) || xyz, "pn_point_features: need rays+z or xyz");
+  PN_CHECK_ARG(!rays || points_per_object % n_samples == 0, "pn_point_features: P must be a multiple of K");
+  PN_CHECK_ARG(ldx >= PN_D_CODE, "pn_point_features: ldx=%d < %d", ldx, PN_D_CODE);
+  PN_CHECK_ARG(cam->hl > 1 && cam->wl > 1 && cam->n_objects > 0 && cam->n_views > 0, "pn_point_features: bad camera sizes");
+  PN_CHECK_ARG(latent_dtype == out_dtype && (out_dtype == PN_DTYPE_F32 || out_dtype == PN_DTYPE_F16),
+               "pn_point_features: latent/out dtype must both be f32 or both f16");
+  const int64_t n_rows = (int64_t)cam->n_objects * cam->n_views * points_per_object;
+  if (n_rows == 0) return PN_OK;
+  const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps);
+  if (out_dtype == PN_DTYPE_F32)
+    pn::point_features_kernel<float, float><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+        *cam, (const float*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
+        (float*)feat_z, (float*)feat_x, ldx, n_rows);
+  else
+    pn::point_features_kernel<__half, __half><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+        *cam, (const __half*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
+        (__half*)feat_z, (__half*)feat_x, ldx, n_rows);
+  PN_LAUNCH_OK("point_features_kernel");
+  pn::count_launch();
+  return PN_OK;
+}

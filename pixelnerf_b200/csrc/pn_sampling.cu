@@ -1,0 +1,187 @@
+// Ray sampling kernels: stratified coarse samples, inverse-CDF importance samples,
+// depth samples and the merge sort (reference src/render/nerf.py:98-161, 285-295).
+//
+// Bit-exactness contract (oracle/sampling_np.py is the executable statement of it):
+// every fp32 operation is a separately rounded IEEE op (__f*_rn intrinsics, which
+// the compiler never contracts into FMAs), the row sum follows ATen's CPU order
+// (8 lanes x 4 interleaved accumulators), the CDF is an fp64 running sum rounded to
+// fp32 per element, and searchsorted(right=True) is an upper-bound search.
+#include "pn_common.cuh"
+
+namespace pn {
+
+__device__ __forceinline__ float lerp_depth(float near, float far, float zs, bool lindisp) {
+  float a = __fsub_rn(1.0f, zs);
+  if (!lindisp) return __fadd_rn(__fmul_rn(near, a), __fmul_rn(far, zs));
+  float inv_n = __fdiv_rn(1.0f, near), inv_f = __fdiv_rn(1.0f, far);
+  return __fdiv_rn(1.0f, __fadd_rn(__fmul_rn(inv_n, a), __fmul_rn(inv_f, zs)));
+}
+
+// One thread per (ray, sample); consecutive threads write consecutive z: fully coalesced.
+__global__ void __launch_bounds__(256)
+sample_coarse_kernel(const float* __restrict__ rays, const float* __restrict__ u,
+                     const float* __restrict__ lin, float* __restrict__ z, int64_t total, int kc,
+                     float step, bool lindisp, uint64_t seed) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int64_t r = i / kc;
+  int k = (int)(i - r * kc);
+  float uu = u ? u[i] : rand_uniform(seed, PN_STREAM_COARSE, (uint64_t)i);
+  float zs = __fadd_rn(lin[k], __fmul_rn(uu, step));
+  float2 nf = *reinterpret_cast<const float2*>(rays + r * 8 + 6);
+  z[i] = lerp_depth(nf.x, nf.y, zs, lindisp);
+}
+
+// torch.sum(row) in ATen's CPU order, computed redundantly-free by one warp.
+// Thread (j = lane/8, l = lane%8) owns accumulator j of vector lane l.
+__device__ float aten_row_sum(const float* __restrict__ w, int k, int lane) {
+  const int nv = k >> 3, full = nv >> 2;
+  const int j = lane >> 3, l = lane & 7;
+  float acc = 0.0f;
+  for (int i = 0; i < full; ++i) acc = __fadd_rn(acc, w[((i << 2) + j) * 8 + l]);
+  if (j == 0)
+    for (int i = full << 2; i < nv; ++i) acc = __fadd_rn(acc, w[i * 8 + l]);
+  // A[l] = ((acc0 + acc1) + acc2) + acc3, held by threads j == 0
+  float a1 = __shfl_sync(0xffffffffu, acc, 8 + l);
+  float a2 = __shfl_sync(0xffffffffu, acc, 16 + l);
+  float a3 = __shfl_sync(0xffffffffu, acc, 24 + l);
+  float a = __fadd_rn(__fadd_rn(__fadd_rn(acc, a1), a2), a3);
+  // scalar tail (k % 8), same 4-way structure, summed first
+  float s = 0.0f;
+  const int nt = k & 7;
+  if (nt) {
+    const float* t = w + (nv << 3);
+    float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+    if (nt >= 4) { t0 = t[0]; t1 = t[1]; t2 = t[2]; t3 = t[3]; }
+    for (int i = (nt >> 2) << 2; i < nt; ++i) t0 = __fadd_rn(t0, t[i]);
+    s = __fadd_rn(__fadd_rn(__fadd_rn(t0, t1), t2), t3);
+  }
+#pragma unroll
+  for (int q = 0; q < 8; ++q) s = __fadd_rn(s, __shfl_sync(0xffffffffu, a, q));
+  return s;  // identical in every lane
+}
+
+constexpr int kFineWarps = 4;
+
+// One warp per ray.  Shared memory per warp: w/pdf (Kc) + cdf (Kc+1) + sort buffer (pow2 >= K2).
+__global__ void __launch_bounds__(kFineWarps * 32)
+sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_coarse,
+                   const float* __restrict__ weights, const float* __restrict__ depth,
+                   const float* __restrict__ u_bin, const float* __restrict__ u_in,
+                   const float* __restrict__ noise, float* __restrict__ z_sorted,
+                   float* __restrict__ z_imp, float* __restrict__ z_depth, int64_t n_rays, int kc,
+                   int kf, int kd, int sort_n, float depth_std, bool lindisp, uint64_t seed) {
+  extern __shared__ float smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per_warp = kc + (kc + 1) + sort_n;
+  float* w = smem + warp * per_warp;
+  float* cdf = w + kc;
+  float* srt = cdf + kc + 1;
+  const int k2 = kc + kf + kd;
+
+  for (int64_t r = (int64_t)blockIdx.x * kFineWarps + warp; r < n_rays; r += (int64_t)gridDim.x * kFineWarps) {
+    const float2 nf = *reinterpret_cast<const float2*>(rays + r * 8 + 6);
+    for (int k = lane; k < kc; k += 32) srt[k] = z_coarse[r * kc + k];
+    if (kf > 0) {
+      for (int k = lane; k < kc; k += 32) w[k] = __fadd_rn(weights[r * kc + k], 1e-5f);
+      __syncwarp();
+      const float s = aten_row_sum(w, kc, lane);
+      for (int k = lane; k < kc; k += 32) w[k] = __fdiv_rn(w[k], s);  // pdf
+      __syncwarp();
+      if (lane == 0) {  // torch.cumsum on CPU: fp64 accumulator, rounded per element
+        double run = 0.0;
+        cdf[0] = 0.0f;
+        for (int k = 0; k < kc; ++k) {
+          run += (double)w[k];
+          cdf[k + 1] = (float)run;
+        }
+      }
+      __syncwarp();
+      for (int q = lane; q < kf; q += 32) {
+        const int64_t di = r * kf + q;
+        const float ub = u_bin ? u_bin[di] : rand_uniform(seed, PN_STREAM_BIN, (uint64_t)di);
+        const float ui = u_in ? u_in[di] : rand_uniform(seed, PN_STREAM_IN, (uint64_t)di);
+        int lo = 0, hi = kc + 1;  // upper bound: first index with cdf > ub
+        while (lo < hi) {
+          int mid = (lo + hi) >> 1;
+          if (cdf[mid] <= ub) lo = mid + 1; else hi = mid;
+        }
+        const float ind = fmaxf(__fsub_rn((float)lo, 1.0f), 0.0f);
+        const float zs = __fdiv_rn(__fadd_rn(ind, ui), (float)kc);
+        const float zz = lerp_depth(nf.x, nf.y, zs, lindisp);
+        srt[kc + q] = zz;
+        if (z_imp) z_imp[di] = zz;
+      }
+    }
+    if (kd > 0) {
+      const float d = depth[r];
+      for (int q = lane; q < kd; q += 32) {
+        const int64_t di = r * kd + q;
+        const float nz = noise ? noise[di] : rand_normal(seed, PN_STREAM_NOISE, (uint64_t)di);
+        float zz = __fadd_rn(d, __fmul_rn(nz, depth_std));
+        zz = fmaxf(fminf(zz, nf.y), nf.x);
+        srt[kc + kf + q] = zz;
+        if (z_depth) z_depth[di] = zz;
+      }
+    }
+    for (int k = k2 + lane; k < sort_n; k += 32) srt[k] = __int_as_float(0x7f800000);  // +inf padding
+    __syncwarp();
+    // bitonic sort of sort_n (power of two) floats by one warp
+    for (int size = 2; size <= sort_n; size <<= 1) {
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        for (int t = lane; t < (sort_n >> 1); t += 32) {
+          const int lo = ((t / stride) * (stride << 1)) + (t % stride);
+          const int hi = lo + stride;
+          const bool up = ((lo & size) == 0);
+          const float a = srt[lo], b = srt[hi];
+          if ((a > b) == up) { srt[lo] = b; srt[hi] = a; }
+        }
+        __syncwarp();
+      }
+    }
+    for (int k = lane; k < k2; k += 32) z_sorted[r * k2 + k] = srt[k];
+    __syncwarp();
+  }
+}
+
+}  // namespace pn
+
+extern "C" int pn_sample_coarse(const float* rays, const float* u, const float* lin, float* z,
+                                int64_t n_rays, int n_coarse, int lindisp, uint64_t seed,
+                                pn_stream_t stream) {
+  PN_CHECK_ARG(rays && lin && z, "pn_sample_coarse: null pointer");
+  PN_CHECK_ARG(n_rays >= 0 && n_coarse > 0, "pn_sample_coarse: bad sizes R=%lld Kc=%d", (long long)n_rays, n_coarse);
+  if (n_rays == 0) return PN_OK;
+  const int64_t total = n_rays * n_coarse;
+  const float step = (float)(1.0 / (double)n_coarse);
+  pn::sample_coarse_kernel<<<pn::ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      rays, u, lin, z, total, n_coarse, step, lindisp != 0, seed);
+  PN_LAUNCH_OK("sample_coarse_kernel");
+  pn::count_launch();
+  return PN_OK;
+}
+
+extern "C" int pn_sample_fine(const float* rays, const float* z_coarse, const float* weights,
+                              const float* depth, const float* u_bin, const float* u_in,
+                              const float* noise, float* z_sorted, float* z_imp, float* z_depth,
+                              int64_t n_rays, int n_coarse, int n_imp, int n_depth, float depth_std,
+                              int lindisp, uint64_t seed, pn_stream_t stream) {
+  PN_CHECK_ARG(rays && z_coarse && z_sorted, "pn_sample_fine: null pointer");
+  PN_CHECK_ARG(n_imp == 0 || weights, "pn_sample_fine: importance samples need coarse weights");
+  PN_CHECK_ARG(n_depth == 0 || depth, "pn_sample_fine: depth samples need coarse depth");
+  PN_CHECK_ARG(n_rays >= 0 && n_coarse > 0 && n_imp >= 0 && n_depth >= 0, "pn_sample_fine: bad sizes");
+  PN_CHECK_ARG(n_coarse < 512, "pn_sample_fine: Kc=%d >= 512 is outside the emulated ATen row-sum regime", n_coarse);
+  if (n_rays == 0) return PN_OK;
+  const int k2 = n_coarse + n_imp + n_depth;
+  int sort_n = 2;
+  while (sort_n < k2) sort_n <<= 1;
+  const size_t smem = (size_t)pn::kFineWarps * (n_coarse + n_coarse + 1 + sort_n) * sizeof(float);
+  PN_CHECK_ARG(smem <= 48 * 1024, "pn_sample_fine: K too large for shared memory");
+  const int blocks = (int)((n_rays + pn::kFineWarps - 1) / pn::kFineWarps);
+  pn::sample_fine_kernel<<<blocks < 148 * 16 ? blocks : 148 * 16, pn::kFineWarps * 32, smem, (cudaStream_t)stream>>>(
+      rays, z_coarse, weights, depth, u_bin, u_in, noise, z_sorted, z_imp, z_depth, n_rays, n_coarse,
+      n_imp, n_depth, sort_n, depth_std, lindisp != 0, seed);
+  PN_LAUNCH_OK("sample_fine_kernel");
+  pn::count_launch();
+  return PN_OK;
+}

@@ -1,0 +1,78 @@
+"""Spatial image encoder -- stays in torch by design (BASELINE.json north_star).
+
+Same constructor keys, attributes (``latent``, ``latent_scaling``, ``latent_size``)
+and state_dict names (``model.*`` = torchvision resnet) as the reference's
+SpatialEncoder (src/model/encoder.py:13-177).  The feature lookup
+(``SpatialEncoder.index``, encoder.py:80-109) is NOT here: it is part of the hot path
+and lives in csrc/pn_features.cu.
+"""
+import torch
+import torch.nn.functional as F
+import torchvision
+from torch import nn
+
+from .. import util
+
+
+class SpatialEncoder(nn.Module):
+    def __init__(self, backbone="resnet34", pretrained=True, num_layers=4, index_interp="bilinear",
+                 index_padding="border", upsample_interp="bilinear", feature_scale=1.0,
+                 use_first_pool=True, norm_type="batch"):
+        super().__init__()
+        if backbone == "custom":
+            raise NotImplementedError("backbone=custom (experimental ConvEncoder) is outside the B200 hot path")
+        if index_interp != "bilinear" or index_padding != "border":
+            raise NotImplementedError("the gather kernel implements index_interp=bilinear, index_padding=border only")
+        if norm_type != "batch":
+            assert not pretrained
+        self.feature_scale, self.use_first_pool = feature_scale, use_first_pool
+        weights = "IMAGENET1K_V1" if pretrained else None
+        self.model = getattr(torchvision.models, backbone)(weights=weights, norm_layer=util.get_norm_layer(norm_type))
+        self.model.fc = nn.Sequential()
+        self.model.avgpool = nn.Sequential()
+        self.latent_size = [0, 64, 128, 256, 512, 1024][num_layers]
+        self.num_layers = num_layers
+        self.index_interp, self.index_padding, self.upsample_interp = index_interp, index_padding, upsample_interp
+        self.register_buffer("latent", torch.empty(1, 1, 1, 1), persistent=False)
+        self.register_buffer("latent_scaling", torch.empty(2, dtype=torch.float32), persistent=False)
+
+    def index(self, uv, cam_z=None, image_size=(), z_bounds=None):
+        raise NotImplementedError("latent lookup is fused into pn_point_features; call PixelNeRFNet.forward")
+
+    def forward(self, x):
+        """(B,3,H,W) image -> latent (B, latent_size, H/2, W/2), cached in ``self.latent``."""
+        if self.feature_scale != 1.0:
+            up = self.feature_scale > 1.0
+            x = F.interpolate(x, scale_factor=self.feature_scale, mode="bilinear" if up else "area",
+                              align_corners=True if up else None, recompute_scale_factor=True)
+        x = x.to(device=self.latent.device)
+        m = self.model
+        x = m.relu(m.bn1(m.conv1(x)))
+        latents = [x]
+        if self.num_layers > 1:
+            if self.use_first_pool:
+                x = m.maxpool(x)
+            x = m.layer1(x)
+            latents.append(x)
+        for i, layer in enumerate((m.layer2, m.layer3, m.layer4)):
+            if self.num_layers > i + 2:
+                x = layer(x)
+                latents.append(x)
+        self.latents = latents
+        size = latents[0].shape[-2:]
+        latents = [F.interpolate(l, size, mode=self.upsample_interp, align_corners=True) for l in latents]
+        self.latent = torch.cat(latents, dim=1)
+        ls = torch.tensor([self.latent.shape[-1], self.latent.shape[-2]], dtype=torch.float32,
+                          device=self.latent.device)
+        self.latent_scaling = ls / (ls - 1) * 2.0
+        return self.latent
+
+    @classmethod
+    def from_conf(cls, conf):
+        return cls(conf.get_string("backbone"), pretrained=conf.get_bool("pretrained", True),
+                   num_layers=conf.get_int("num_layers", 4),
+                   index_interp=conf.get_string("index_interp", "bilinear"),
+                   index_padding=conf.get_string("index_padding", "border"),
+                   upsample_interp=conf.get_string("upsample_interp", "bilinear"),
+                   feature_scale=conf.get_float("feature_scale", 1.0),
+                   use_first_pool=conf.get_bool("use_first_pool", True))

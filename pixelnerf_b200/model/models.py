@@ -1,0 +1,182 @@
+"""PixelNeRFNet -- same constructor keys, attributes, encode()/forward() contracts
+and checkpoint format as the reference's src/model/models.py, with forward()
+running on the sm_100a kernels (point features -> ResnetFC -> head).
+"""
+import os
+import os.path as osp
+import warnings
+
+import torch
+
+from .. import _lib
+from .code import PositionalEncoding
+from .model_util import make_encoder, make_mlp
+
+_PRECISIONS = ("fp32", "fp16", "bf16")
+
+
+class PixelNeRFNet(torch.nn.Module):
+    def __init__(self, conf, stop_encoder_grad=False):
+        super().__init__()
+        self.encoder = make_encoder(conf["encoder"])
+        self.use_encoder = conf.get_bool("use_encoder", True)
+        self.use_xyz = conf.get_bool("use_xyz", False)
+        assert self.use_encoder or self.use_xyz
+        self.normalize_z = conf.get_bool("normalize_z", True)
+        self.stop_encoder_grad = stop_encoder_grad
+        self.use_code = conf.get_bool("use_code", False)
+        self.use_code_viewdirs = conf.get_bool("use_code_viewdirs", True)
+        self.use_viewdirs = conf.get_bool("use_viewdirs", False)
+        self.use_global_encoder = conf.get_bool("use_global_encoder", False)
+        # The kernels implement the configuration every shipped conf resolves to
+        # (conf/default.conf:5-29); other switch settings raise instead of falling back.
+        bad = [n for n, ok in (("use_encoder=False", self.use_encoder), ("use_xyz=False", self.use_xyz),
+                               ("normalize_z=False", self.normalize_z), ("use_code=False", self.use_code),
+                               ("use_code_viewdirs=True", not self.use_code_viewdirs),
+                               ("use_viewdirs=False", self.use_viewdirs),
+                               ("use_global_encoder=True", not self.use_global_encoder)) if not ok]
+        if bad:
+            raise NotImplementedError("model switches outside the B200 hot path: " + ", ".join(bad))
+        d_latent = self.encoder.latent_size
+        self.code = PositionalEncoding.from_conf(conf["code"], d_in=3)
+        if self.code.num_freqs != 6 or abs(self.code.freq_factor - 1.5) > 1e-12 or not self.code.include_input:
+            raise NotImplementedError("positional encoding other than num_freqs=6, freq_factor=1.5, include_input")
+        d_in = self.code.d_out + 3
+        d_out = 4
+        self.latent_size = self.encoder.latent_size
+        self.mlp_coarse = make_mlp(conf["mlp_coarse"], d_in, d_latent, d_out=d_out)
+        self.mlp_fine = make_mlp(conf["mlp_fine"], d_in, d_latent, d_out=d_out, allow_empty=True)
+        self.register_buffer("poses", torch.empty(1, 3, 4), persistent=False)
+        self.register_buffer("image_shape", torch.empty(2), persistent=False)
+        self.d_in, self.d_out, self.d_latent = d_in, d_out, d_latent
+        self.register_buffer("focal", torch.empty(1, 2), persistent=False)
+        self.register_buffer("c", torch.empty(1, 2), persistent=False)
+        self.num_objs = 0
+        self.num_views_per_obj = 1
+        # "fp32": CUDA-core path, 1e-4 parity.  "fp16"/"bf16": tcgen05 chain, 2e-3 parity.
+        self.mlp_precision = conf.get_string("mlp_precision", os.environ.get("PIXELNERF_B200_MLP", "fp32"))
+        assert self.mlp_precision in _PRECISIONS, self.mlp_precision
+        self._cam = None
+        self._latent_nhwc = {}
+
+    # ------------------------------------------------------------------ encode
+    def encode(self, images, poses, focal, z_bounds=None, c=None):
+        """Cache the encoder latent and per-view cameras.  Reference models.py:89-144.
+
+        images (NS,3,H,W) or (SB,NS,3,H,W); poses camera-to-world (...,4,4); focal (), (SB) or
+        (SB,2); c None, (), (SB) or (SB,2).
+        """
+        self.num_objs = images.size(0)
+        if len(images.shape) == 5:
+            assert len(poses.shape) == 4
+            assert poses.size(1) == images.size(1)
+            self.num_views_per_obj = images.size(1)
+            images = images.reshape(-1, *images.shape[2:])
+            poses = poses.reshape(-1, 4, 4)
+        else:
+            self.num_views_per_obj = 1
+        self.encoder(images)
+        rot = poses[:, :3, :3].transpose(1, 2)
+        trans = -torch.bmm(rot, poses[:, :3, 3:])
+        self.poses = torch.cat((rot, trans), dim=-1)
+        self.image_shape[0] = images.shape[-1]
+        self.image_shape[1] = images.shape[-2]
+        if len(focal.shape) == 0:
+            focal = focal[None, None].repeat((1, 2))
+        elif len(focal.shape) == 1:
+            focal = focal.unsqueeze(-1).repeat((1, 2))
+        else:
+            focal = focal.clone()
+        self.focal = focal.float()
+        self.focal[..., 1] *= -1.0
+        if c is None:
+            c = (self.image_shape * 0.5).unsqueeze(0)
+        elif len(c.shape) == 0:
+            c = c[None, None].repeat((1, 2))
+        elif len(c.shape) == 1:
+            c = c.unsqueeze(-1).repeat((1, 2))
+        self.c = c
+        self._refresh_camera()
+
+    def _refresh_camera(self):
+        """Kernel-side camera block: per-view expanded focal / c and the uv -> texel scale."""
+        n_views_total = self.poses.shape[0]
+        ns = self.num_views_per_obj
+        dev = self.poses.device
+
+        def per_view(t):  # (SB or 1, 2) -> (SB*NS, 2), the repeat_interleave of models.py:207-212
+            t = t.to(device=dev, dtype=torch.float32)
+            if t.shape[0] == 1:
+                return t.expand(n_views_total, 2).contiguous()
+            return t.unsqueeze(1).expand(-1, ns, 2).reshape(-1, 2).contiguous()
+
+        ls = self.encoder.latent_scaling.float().cpu()
+        img = self.image_shape.float().cpu()
+        scale = ls / img  # encoder.py:98: latent_scaling / image_size, fp32 like the reference
+        self._cam = dict(poses=self.poses.float().contiguous(), focal=per_view(self.focal), c=per_view(self.c),
+                         scale_x=float(scale[0]), scale_y=float(scale[1]),
+                         n_objects=n_views_total // ns, n_views=ns)
+        self._latent_nhwc = {}
+
+    def latent_nhwc(self, dtype):
+        """Channels-last copy of encoder.latent in `dtype`, made once per encode()."""
+        lat = self.encoder.latent
+        key = (dtype, lat.data_ptr(), lat._version)
+        if self._latent_nhwc.get("key") != key:
+            src = lat.detach() if self.stop_encoder_grad or not lat.requires_grad else lat.detach()
+            self._latent_nhwc = {"key": key, "t": _lib.prepare_latent(src, dtype)}
+        return self._latent_nhwc["t"]
+
+    # ----------------------------------------------------------------- forward
+    def _mlp(self, coarse):
+        return self.mlp_coarse if coarse or self.mlp_fine is None else self.mlp_fine
+
+    def run_points(self, coarse, ppo, *, rays=None, z=None, xyz=None, viewdirs=None):
+        """Feature gather + MLP + head for SB*ppo points -> (SB*ppo, 4) [rgb, sigma]."""
+        if self._cam is None:
+            raise RuntimeError("call encode() before forward()")
+        prec = self.mlp_precision
+        mlp = self._mlp(coarse)
+        cam = self._cam
+        if prec == "fp32":
+            fz, fx = _lib.point_features(cam, self.latent_nhwc(torch.float32), ppo, rays=rays, z=z, xyz=xyz,
+                                         viewdirs=viewdirs, ldx=44)
+            return _lib.mlp_forward_fp32(mlp.packed("fp32"), fz, fx, cam["n_objects"], cam["n_views"], ppo)
+        fz, fx = _lib.point_features(cam, self.latent_nhwc(torch.float16), ppo, rays=rays, z=z, xyz=xyz,
+                                     viewdirs=viewdirs, ldx=64)
+        return _lib.mlp_forward_tc(mlp.packed(prec), fz, fx, cam["n_objects"], cam["n_views"], ppo)
+
+    def forward(self, xyz, coarse=True, viewdirs=None, far=False):
+        """(SB,B,3) world points -> (SB,B,4) [sigmoid rgb, relu sigma].  Reference models.py:146-266."""
+        sb, b, _ = xyz.shape
+        assert viewdirs is not None, "use_viewdirs=True needs viewdirs (reference models.py:186)"
+        assert sb == self._cam["n_objects"], "xyz batch must match the encoded objects"
+        out = self.run_points(coarse, b, xyz=xyz.reshape(sb, b, 3), viewdirs=viewdirs.reshape(sb, b, 3))
+        return out.reshape(sb, b, 4)
+
+    # -------------------------------------------------------------- checkpoints
+    def load_weights(self, args, opt_init=False, strict=True, device=None):
+        """Reference models.py:268-298: <checkpoints_path>/<name>/pixel_nerf_{init,latest}."""
+        if opt_init and not args.resume:
+            return
+        ckpt_name = "pixel_nerf_init" if opt_init or not args.resume else "pixel_nerf_latest"
+        model_path = "%s/%s/%s" % (args.checkpoints_path, args.name, ckpt_name)
+        if device is None:
+            device = self.poses.device
+        if os.path.exists(model_path):
+            print("Load", model_path)
+            self.load_state_dict(torch.load(model_path, map_location=device), strict=strict)
+        elif not opt_init:
+            warnings.warn("WARNING: {} does not exist, not loaded!! Model will be re-initialized.".format(model_path))
+        return self
+
+    def save_weights(self, args, opt_init=False):
+        """Reference models.py:300-316 (keeps one backup copy)."""
+        from shutil import copyfile
+        ckpt_name = "pixel_nerf_init" if opt_init else "pixel_nerf_latest"
+        backup_name = "pixel_nerf_init_backup" if opt_init else "pixel_nerf_backup"
+        ckpt_path = osp.join(args.checkpoints_path, args.name, ckpt_name)
+        if osp.exists(ckpt_path):
+            copyfile(ckpt_path, osp.join(args.checkpoints_path, args.name, backup_name))
+        torch.save(self.state_dict(), ckpt_path)
+        return self

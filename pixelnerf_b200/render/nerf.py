@@ -1,0 +1,201 @@
+"""NeRFRenderer -- drop-in for the reference's src/render/nerf.py on sm_100a kernels.
+
+Same constructor / from_conf keys, mutable ``n_coarse`` / ``n_fine`` / ``using_fine``
+read at call time, persistent buffers ``iter_idx`` / ``last_sched``, ``sched_step``,
+``bind_parallel`` and output structure.  Per ray chunk the forward is
+    pn_sample_coarse -> pn_point_features -> MLP -> pn_composite_fwd
+    -> pn_sample_fine (importance + depth + merge sort) -> features -> MLP -> composite
+with no host synchronisation in between.
+"""
+import torch
+
+from .. import _lib
+
+
+class DotMap(dict):
+    """Attribute dict with auto-vivification and toDict(): the slice of dotmap.DotMap the
+    reference's callers rely on (``outputs.fine`` exists and is empty when n_fine == 0)."""
+
+    def __getattr__(self, k):
+        if k.startswith("__"):
+            raise AttributeError(k)
+        if k not in self:
+            self[k] = DotMap()
+        return self[k]
+
+    def __setattr__(self, k, v):
+        self[k] = v
+
+    def toDict(self):
+        return {k: (v.toDict() if isinstance(v, DotMap) else v) for k, v in self.items()}
+
+
+class _RenderWrapper(torch.nn.Module):
+    """Reference nerf.py:15-42."""
+
+    def __init__(self, net, renderer, simple_output):
+        super().__init__()
+        self.net, self.renderer, self.simple_output = net, renderer, simple_output
+
+    def forward(self, rays, want_weights=False):
+        if rays.shape[0] == 0:
+            return torch.zeros(0, 3, device=rays.device), torch.zeros(0, device=rays.device)
+        outputs = self.renderer(self.net, rays, want_weights=want_weights and not self.simple_output)
+        if self.simple_output:
+            part = outputs.fine if self.renderer.using_fine else outputs.coarse
+            return part.rgb, part.depth
+        return outputs.toDict()
+
+
+class NeRFRenderer(torch.nn.Module):
+    def __init__(self, n_coarse=128, n_fine=0, n_fine_depth=0, noise_std=0.0, depth_std=0.01,
+                 eval_batch_size=100000, white_bkgd=False, lindisp=False, sched=None):
+        super().__init__()
+        self.n_coarse, self.n_fine, self.n_fine_depth = n_coarse, n_fine, n_fine_depth
+        self.noise_std, self.depth_std = noise_std, depth_std
+        self.eval_batch_size = eval_batch_size
+        self.white_bkgd, self.lindisp = white_bkgd, lindisp
+        if lindisp:
+            print("Using linear displacement rays")
+        self.using_fine = n_fine > 0
+        self.sched = sched if sched is not None and len(sched) > 0 else None
+        self.register_buffer("iter_idx", torch.tensor(0, dtype=torch.long), persistent=True)
+        self.register_buffer("last_sched", torch.tensor(0, dtype=torch.long), persistent=True)
+        # Test hook: dict(u_coarse, u_bin, u_in, noise) consumed by the next forward() instead of
+        # in-kernel draws (the reference's four torch.rand* calls, nerf.py:111,135,141,158).
+        self.injected_draws = None
+        self.injected_z = None  # teacher forcing: dict(z_coarse=..., z_fine=...)
+        self.max_rows_per_launch = 1 << 21
+
+    # ---------------------------------------------------------------- sampling
+    @staticmethod
+    def _seed():
+        # one 63-bit seed per call from torch's CPU generator (honours torch.manual_seed)
+        return int(torch.empty((), dtype=torch.int64).random_().item())
+
+    def sample_coarse(self, rays, u=None, seed=None):
+        """Stratified samples (B,8) -> (B,Kc).  Reference nerf.py:98-118."""
+        return _lib.sample_coarse(rays, self.n_coarse, self.lindisp, u=u,
+                                  seed=self._seed() if seed is None and u is None else (seed or 0))
+
+    def sample_fine(self, rays, weights, u_bin=None, u_in=None, seed=None):
+        """Importance samples (B, Kf-Kfd).  Reference nerf.py:120-148."""
+        n_imp = self.n_fine - self.n_fine_depth
+        z0 = torch.zeros(rays.shape[0], self.n_coarse, device=rays.device)
+        _, z_imp, _ = _lib.sample_fine(rays, z0, weights, None, n_imp, 0, self.depth_std, self.lindisp, u_bin=u_bin,
+                                       u_in=u_in, seed=self._seed() if seed is None else seed, want_parts=True)
+        return z_imp
+
+    def sample_fine_depth(self, rays, depth, noise=None, seed=None):
+        """Samples around the coarse depth (B, Kfd).  Reference nerf.py:150-161."""
+        z0 = torch.zeros(rays.shape[0], 1, device=rays.device)
+        _, _, z_dep = _lib.sample_fine(rays, z0, None, depth, 0, self.n_fine_depth, self.depth_std, self.lindisp,
+                                       noise=noise, seed=self._seed() if seed is None else seed, want_parts=True)
+        return z_dep
+
+    # --------------------------------------------------------------- composite
+    def composite(self, model, rays, z_samp, coarse=True, sb=0):
+        """Model evaluation + alpha compositing.  Reference nerf.py:163-249.
+        rays (B,8), z_samp (B,K) -> weights (B,K), rgb (B,3), depth (B)."""
+        if self.training and self.noise_std > 0.0:
+            raise NotImplementedError("sigma noise (noise_std > 0) is unused by every shipped conf")
+        b, k = z_samp.shape
+        n_obj = max(sb, 1)
+        rgbs = model.run_points(coarse, (b // n_obj) * k, rays=rays, z=z_samp)
+        return _lib.composite_fwd(rgbs.reshape(b, k, 4), z_samp, rays, self.white_bkgd)
+
+    # ----------------------------------------------------------------- forward
+    def _render_chunk(self, model, rays, sb, draws, forced, want_weights, seed):
+        d = draws or {}
+        z_c = forced.get("z_coarse")
+        if z_c is None:
+            z_c = _lib.sample_coarse(rays, self.n_coarse, self.lindisp, u=d.get("u_coarse"), seed=seed)
+        coarse = self.composite(model, rays, z_c, coarse=True, sb=sb)
+        fine = None
+        if self.using_fine:
+            n_dep = self.n_fine_depth
+            n_imp = self.n_fine - n_dep
+            z_f = forced.get("z_fine")
+            if z_f is None:
+                z_f = _lib.sample_fine(rays, z_c, forced.get("w_coarse", coarse[0]),
+                                       forced.get("depth_coarse", coarse[2]), n_imp, n_dep, self.depth_std,
+                                       self.lindisp, u_bin=d.get("u_bin"), u_in=d.get("u_in"), noise=d.get("noise"),
+                                       seed=seed)
+            fine = self.composite(model, rays, z_f, coarse=False, sb=sb) + (z_f,)
+        return coarse + (z_c,), fine
+
+    def forward(self, model, rays, want_weights=False):
+        """rays (SB,B,8) -> DotMap{coarse:{rgb,depth[,weights]}, fine:{...}}.  Reference nerf.py:251-303."""
+        if self.sched is not None and self.last_sched.item() > 0:
+            self.n_coarse = self.sched[1][self.last_sched.item() - 1]
+            self.n_fine = self.sched[2][self.last_sched.item() - 1]
+        assert len(rays.shape) == 3
+        sb, b = rays.shape[0], rays.shape[1]
+        if not rays.is_cuda:
+            raise RuntimeError("pixelnerf_b200 renders on CUDA devices only (no CPU fallback)")
+        rays = rays.reshape(-1, 8).float().contiguous()
+        draws, forced = self.injected_draws, self.injected_z or {}
+        self.injected_draws, self.injected_z = None, None
+        seed = 0 if draws else self._seed()
+        ns = getattr(model, "num_views_per_obj", 1)
+        k_max = self.n_coarse + (self.n_fine if self.using_fine else 0)
+        # chunk along the per-object ray axis so every launch keeps (object, view, point) row order
+        chunk = max(1, self.max_rows_per_launch // max(1, sb * ns * k_max))
+        if chunk >= b:
+            parts = [self._render_chunk(model, rays, sb, draws, forced, want_weights, seed)]
+        else:
+            def cut(t, s, e):  # (SB*B, ...) -> (SB*(e-s), ...), keeping object-major order
+                return t.reshape(sb, b, *t.shape[1:])[:, s:e].reshape(sb * (e - s), *t.shape[1:]).contiguous()
+
+            parts = []
+            for s in range(0, b, chunk):
+                e = min(b, s + chunk)
+                dr = {k: cut(v, s, e) for k, v in draws.items()} if draws else None
+                fz = {k: cut(v, s, e) for k, v in forced.items()}
+                parts.append(self._render_chunk(model, cut(rays, s, e), sb, dr, fz, want_weights, seed + s))
+
+        def gather(which, idx):  # chunk outputs -> (SB, B, ...)
+            ts = [p[which][idx] for p in parts]
+            return torch.cat([t.reshape(sb, -1, *t.shape[1:]) for t in ts], dim=1)
+
+        def fmt(which):
+            ret = DotMap(rgb=gather(which, 1), depth=gather(which, 2))
+            if want_weights:
+                ret.weights = gather(which, 0)
+            return ret
+
+        outputs = DotMap(coarse=fmt(0))
+        if self.using_fine:
+            outputs.fine = fmt(1)
+        # sample positions of the last call, for the stage-wise parity tests
+        self.last_z = (gather(0, 3), gather(1, 3) if self.using_fine else None)
+        return outputs
+
+    def sched_step(self, steps=1):
+        """Reference nerf.py:318-338."""
+        if self.sched is None:
+            return
+        self.iter_idx += steps
+        while self.last_sched.item() < len(self.sched[0]) and self.iter_idx.item() >= self.sched[0][self.last_sched.item()]:
+            self.n_coarse = self.sched[1][self.last_sched.item()]
+            self.n_fine = self.sched[2][self.last_sched.item()]
+            print("INFO: NeRF sampling resolution changed on schedule ==> c", self.n_coarse, "f", self.n_fine)
+            self.last_sched += 1
+
+    @classmethod
+    def from_conf(cls, conf, white_bkgd=False, lindisp=False, eval_batch_size=100000):
+        """Reference nerf.py:340-352 (white_bkgd is read with get_float there; kept)."""
+        return cls(conf.get_int("n_coarse", 128), conf.get_int("n_fine", 0),
+                   n_fine_depth=conf.get_int("n_fine_depth", 0), noise_std=conf.get_float("noise_std", 0.0),
+                   depth_std=conf.get_float("depth_std", 0.01), white_bkgd=conf.get_float("white_bkgd", white_bkgd),
+                   lindisp=lindisp, eval_batch_size=conf.get_int("eval_batch_size", eval_batch_size),
+                   sched=conf.get_list("sched", None))
+
+    def bind_parallel(self, net, gpus=None, simple_output=False):
+        """Reference nerf.py:354-371.  With more than one GPU the reference wraps the module in
+        DataParallel; here multi-GPU is one process per GPU (pixelnerf_b200.parallel)."""
+        wrapped = _RenderWrapper(net, self, simple_output=simple_output)
+        if gpus is not None and len(gpus) > 1:
+            from ..parallel import RaySharded
+            wrapped = RaySharded(wrapped)
+        return wrapped

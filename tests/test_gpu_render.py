@@ -1,0 +1,89 @@
+"""Whole renderer through the public API (make_model / NeRFRenderer) vs golden vectors of the
+live reference, stage-wise with teacher forcing (hard part 12):
+  (i)   coarse pass on injected draws            -> rgb/depth/weights within 1e-4
+  (ii)  fine sampling fed the REFERENCE's coarse weights/depth -> sample positions bit-exact
+  (iii) fine pass on the reference's sorted z    -> rgb/depth/weights within 1e-4
+and one end-to-end run with a quantile criterion (the fine pass is chaotic w.r.t. the coarse one)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from oracle import model as omodel
+from helpers import golden_files, load, render_case_inputs
+from test_gpu_model import _net_for
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+@pytest.mark.parametrize("path", golden_files("render_"))
+def test_render_stagewise(path):
+    fx = load(path)
+    inp = render_case_inputs(fx)
+    sb, ns = inp["sb"], inp["ns"]
+    net, ren = _net_for(fx, inp)
+    rays = inp["rays"]
+    draws = {k: v.cuda() for k, v in inp["draws"].items()}
+    shp = fx["rgb_coarse"].shape[:2]
+
+    # oracle run (pinned to the reference by test_oracle_golden) for the intermediates
+    def net_fn(xyz, dirs, coarse):
+        return omodel.net_forward(inp["wc"] if coarse else inp["wf"], inp["latent"], inp["cam"], ns, xyz, dirs)
+    with torch.no_grad():
+        ref = oracle.render_rays(net_fn, rays.reshape(-1, 8), sb, 64, 32, 16, inp["draws"], white_bkgd=inp["white"],
+                                 lindisp=inp["lindisp"])
+
+    # (ii)+(iii): teacher-forced fine sampling and fine pass
+    ren.injected_draws = draws
+    ren.injected_z = dict(w_coarse=ref["w_coarse"].cuda(), depth_coarse=ref["depth_coarse"].cuda())
+    with torch.no_grad():
+        out = ren(net, rays.cuda(), want_weights=True)
+    z_c, z_f = ren.last_z
+    assert np.array_equal(z_c.reshape(-1, 64).cpu().numpy(), ref["z_coarse"].numpy())      # bit-exact
+    assert np.array_equal(z_f.reshape(-1, 96).cpu().numpy(), ref["z_fine"].numpy())        # bit-exact
+    # (i) coarse vs the live reference's golden outputs
+    assert np.abs(out.coarse.rgb.cpu().numpy() - fx["rgb_coarse"]).max() < TOL
+    assert np.abs(out.coarse.weights.cpu().numpy() - fx["w_coarse"]).max() < TOL
+    assert np.abs(out.coarse.depth.cpu().numpy() - fx["depth_coarse"]).max() < TOL * 4  # world units up to ~4
+    # (iii) fine
+    assert np.abs(out.fine.rgb.cpu().numpy() - fx["rgb_fine"]).max() < TOL
+    assert np.abs(out.fine.weights.cpu().numpy() - fx["w_fine"]).max() < TOL
+    assert np.abs(out.fine.depth.cpu().numpy() - fx["depth_fine"]).max() < TOL * 4
+    assert out.fine.rgb.shape == (*shp, 3) and out.fine.depth.shape == shp
+
+
+@pytest.mark.parametrize("path", golden_files("render_"))
+def test_render_end_to_end_quantile(path):
+    fx = load(path)
+    inp = render_case_inputs(fx)
+    net, ren = _net_for(fx, inp)
+    ren.injected_draws = {k: v.cuda() for k, v in inp["draws"].items()}
+    par = ren.bind_parallel(net, [0], simple_output=True).eval()
+    with torch.no_grad():
+        rgb, depth = par(inp["rays"].cuda())
+    err = np.abs(rgb.cpu().numpy() - fx["rgb_fine"]).max(-1).reshape(-1)
+    assert np.quantile(err, 0.9) < TOL, np.sort(err)[-5:]
+
+
+def test_chunked_equals_unchunked_and_wrapper_contract():
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import build_net
+    sc = syn.scene("sn64")
+    net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), torch.device("cuda"))
+    rays = sc["rays"][:600].cuda()[None]
+    d = {k: v.cuda() for k, v in syn.draws(3, 600, 64, 16, 16).items()}
+    ren.injected_draws = dict(d)
+    with torch.no_grad():
+        a = ren(net, rays, want_weights=True)
+        ren.max_rows_per_launch = 96 * 100
+        ren.injected_draws = dict(d)
+        b = ren(net, rays, want_weights=True)
+    assert torch.equal(a.fine.rgb, b.fine.rgb) and torch.equal(a.coarse.weights, b.coarse.weights)
+    par = ren.bind_parallel(net, [0], simple_output=False)
+    empty = par(torch.zeros(0, 0, 8, device="cuda"))
+    assert empty[0].shape == (0, 3)
+    ren.n_fine, ren.using_fine = 0, False  # callers mutate these after construction
+    with torch.no_grad():
+        o = par(rays, want_weights=True)
+    assert set(o) == {"coarse"} and set(o["coarse"]) == {"rgb", "depth", "weights"}

@@ -1,0 +1,104 @@
+"""CPU-only checks: the C-ABI library loads and exports what include/*.h declares, the HOCON
+subset reader, the API mirror's construction-time contracts, and the no-fallback rule."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="session")
+def built_lib():
+    from pixelnerf_b200 import _lib
+    if not os.path.exists(_lib.LIB_PATH):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "pixelnerf_b200", "csrc"), "-j8"])
+    return _lib
+
+
+def test_library_exports_every_declared_symbol(built_lib):
+    header = open(os.path.join(ROOT, "include", "pixelnerf_b200.h")).read()
+    declared = set(re.findall(r"PN_API\s+[\w\s\*]+?\b(pn_\w+)\s*\(", header))
+    assert len(declared) >= 11
+    handle = ctypes.CDLL(built_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(handle, name), f"{name} declared in the header but not exported"
+    assert declared == set(built_lib.exported_symbols()), "ctypes table and header disagree"
+    assert built_lib.lib().pn_version() >= 100  # no compute call: there is no GPU here
+
+
+def test_no_cpu_fallback(built_lib):
+    with pytest.raises(RuntimeError, match="CUDA"):
+        built_lib.sample_coarse(torch.zeros(4, 8), 64)
+    from pixelnerf_b200.render import NeRFRenderer
+    with pytest.raises(RuntimeError, match="CUDA"):
+        NeRFRenderer(n_coarse=8)(None, torch.zeros(1, 4, 8))
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "pixelnerf_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py") and f != "testing.py":
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(import|from)\s+oracle", src, re.M), f
+
+
+def test_conf_reader(tmp_path):
+    from pixelnerf_b200.conf import ConfigFactory
+    (tmp_path / "base.conf").write_text("""
+# base
+model { mlp_coarse { type = resnet  # trailing comment
+    n_blocks = 3
+    d_hidden=512 }
+  use_xyz = True }
+renderer { n_coarse = 64
+  sched = []
+  white_bkgd = True }
+""")
+    (tmp_path / "exp").mkdir()
+    (tmp_path / "exp" / "child.conf").write_text("""
+include required("../base.conf")
+model { mlp_coarse { n_blocks = 5, combine_type = average } encoder { use_first_pool=False } }
+renderer { white_bkgd = False }
+data { format = dvr_dtu, ban = [3, 4, 5] }
+""")
+    c = ConfigFactory.parse_file(str(tmp_path / "exp" / "child.conf"))
+    assert c.get_int("model.mlp_coarse.n_blocks") == 5 and c["model"]["mlp_coarse"].get_int("d_hidden") == 512
+    assert c["model.mlp_coarse"].get_string("type") == "resnet" and c.get_bool("model.use_xyz") is True
+    assert c.get_float("renderer.white_bkgd") == 0.0 and c.get_list("renderer.sched") == []
+    assert c.get_bool("model.encoder.use_first_pool") is False and c.get_list("data.ban") == [3, 4, 5]
+    assert c.get_string("data.nope", "dflt") == "dflt" and c.get_list("renderer.nope", None) is None
+    with pytest.raises(KeyError):
+        c.get_int("renderer.nope")
+
+
+def test_api_mirror_construction():
+    import pixelnerf_b200
+    from pixelnerf_b200.testing import default_conf
+    model, render, util = pixelnerf_b200.install()
+    import model as m2
+    assert m2 is model
+    conf = default_conf()
+    net = model.make_model(conf["model"])
+    keys = set(net.state_dict())
+    assert len(keys) == 278  # reference checkpoints load unchanged
+    for k in ("mlp_coarse.lin_in.weight", "mlp_fine.blocks.4.fc_1.bias", "mlp_coarse.lin_z.2.weight",
+              "mlp_fine.lin_out.weight", "code._freqs", "code._phases", "encoder.model.conv1.weight"):
+        assert k in keys
+    assert net.state_dict()["mlp_coarse.lin_in.weight"].shape == (512, 42)
+    assert float(net.mlp_coarse.blocks[0].fc_1.weight.abs().max()) == 0.0  # reference init: zero fc_1
+    ren = render.NeRFRenderer.from_conf(conf["renderer"], lindisp=False, eval_batch_size=50000)
+    assert (ren.n_coarse, ren.n_fine, ren.n_fine_depth, ren.using_fine) == (64, 32, 16, True)
+    assert set(ren.state_dict()) == {"iter_idx", "last_sched"}
+    ren2 = render.NeRFRenderer(n_coarse=8, sched=[[2, 4], [16, 32], [8, 16]])
+    ren2.sched_step(3)
+    assert (ren2.n_coarse, ren2.n_fine, int(ren2.last_sched)) == (16, 8, 1)
+    with pytest.raises(NotImplementedError):
+        model.make_model(type("C", (), {"get_string": lambda self, k, d=None: "other"})())
+    x = torch.arange(6.0).reshape(3, 2)
+    assert util.repeat_interleave(x, 2).shape == (6, 2) and torch.equal(util.repeat_interleave(x, 2)[1], x[0])
+    assert torch.allclose(util.combine_interleaved(torch.ones(2 * 3 * 4, 5), (3, 4)), torch.ones(2, 4, 5))
