@@ -202,6 +202,7 @@ static int composite_args_ok(int64_t n_rays, int k) {
 extern "C" int pn_composite_fwd(const float* rgb_sigma, const float* z, const float* rays,
                                 float* weights, float* rgb, float* depth, int64_t n_rays,
                                 int n_samples, int white_bkgd, pn_stream_t stream) {
+  if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers
   PN_CHECK_ARG(rgb_sigma && z && rays && weights && rgb && depth, "pn_composite_fwd: null pointer");
   PN_CHECK_ARG(composite_args_ok(n_rays, n_samples), "pn_composite_fwd: need 1 <= K <= %d, got K=%d",
                32 * pn::kMaxPerLane, n_samples);
@@ -219,6 +220,7 @@ extern "C" int pn_composite_bwd(const float* rgb_sigma, const float* z, const fl
                                 const float* g_rgb, const float* g_depth, const float* g_weights,
                                 float* g_rgb_sigma, float* g_z, int64_t n_rays, int n_samples,
                                 int white_bkgd, pn_stream_t stream) {
+  if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers
   PN_CHECK_ARG(rgb_sigma && z && rays && g_rgb && g_rgb_sigma, "pn_composite_bwd: null pointer");
   PN_CHECK_ARG(composite_args_ok(n_rays, n_samples), "pn_composite_bwd: need 1 <= K <= %d, got K=%d",
                32 * pn::kMaxPerLane, n_samples);

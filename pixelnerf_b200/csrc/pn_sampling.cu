@@ -149,6 +149,7 @@ sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_c
 extern "C" int pn_sample_coarse(const float* rays, const float* u, const float* lin, float* z,
                                 int64_t n_rays, int n_coarse, int lindisp, uint64_t seed,
                                 pn_stream_t stream) {
+  if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers
   PN_CHECK_ARG(rays && lin && z, "pn_sample_coarse: null pointer");
   PN_CHECK_ARG(n_rays >= 0 && n_coarse > 0, "pn_sample_coarse: bad sizes R=%lld Kc=%d", (long long)n_rays, n_coarse);
   if (n_rays == 0) return PN_OK;
@@ -166,6 +167,7 @@ extern "C" int pn_sample_fine(const float* rays, const float* z_coarse, const fl
                               const float* noise, float* z_sorted, float* z_imp, float* z_depth,
                               int64_t n_rays, int n_coarse, int n_imp, int n_depth, float depth_std,
                               int lindisp, uint64_t seed, pn_stream_t stream) {
+  if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers
   PN_CHECK_ARG(rays && z_coarse && z_sorted, "pn_sample_fine: null pointer");
   PN_CHECK_ARG(n_imp == 0 || weights, "pn_sample_fine: importance samples need coarse weights");
   PN_CHECK_ARG(n_depth == 0 || depth, "pn_sample_fine: depth samples need coarse depth");
