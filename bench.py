@@ -243,7 +243,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp32"), choices=["fp32", "fp16", "bf16"])
+    ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp16"), choices=["fp32", "fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

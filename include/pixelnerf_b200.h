@@ -127,6 +127,32 @@ PN_API int pn_mlp_forward_fp32(const pn_mlp_weights_t* w, const float* feat_z, c
                         float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                         pn_stream_t stream);
 
+/* Tensor-core ResnetFC (tcgen05 / TMEM / TMA chain kernel, csrc/pn_mlp_tc.cu): fp16 GEMM
+ * operands, fp32 accumulation and an fp32 residual stream held in tensor memory.
+ * pn_prepare_weights converts one MLP's fp32 state_dict tensors once into the packed form
+ * (15 zero-padded [512][512] fp16 layers + fp32 bias tables); `packed` is a caller-owned
+ * 256-byte-aligned device buffer of pn_mlp_tc_packed_bytes(). */
+PN_API size_t pn_mlp_tc_packed_bytes(void);
+PN_API int pn_prepare_weights(const pn_mlp_weights_t* w, void* packed, size_t packed_bytes, pn_stream_t stream);
+
+typedef struct pn_mlp_tc_debug {
+  float* h;   /* (rows, 512) fp32: residual stream h as read at `stage`, biases included */
+  int stage;  /* 0..5: h before block `stage` (5 = input of lin_out) */
+} pn_mlp_tc_debug_t;
+
+PN_API size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views);
+
+/* ResnetFC.forward + head like pn_mlp_forward_fp32, on the tensor cores.  feat_z (N,512)
+ * and feat_x (N,64) are fp16 (pn_point_features with out_dtype PN_DTYPE_F16, ldx 64), rows
+ * ordered (object, view, point).  With n_views > 1 the per-view blocks 0-2 and the merged
+ * blocks 3-4 run as two launches with the fp32 view mean in between (workspace).  dbg may
+ * be NULL.  The first 4 bytes of workspace receive a nonzero code if a device-side wait
+ * timed out (the launch then fails with a CUDA error instead of hanging). */
+PN_API int pn_mlp_forward_tc(const void* packed, const void* feat_z, const void* feat_x,
+                      int n_objects, int n_views, int64_t points_per_object,
+                      float* out, float* pre_act, void* workspace, size_t workspace_bytes,
+                      const pn_mlp_tc_debug_t* dbg, pn_stream_t stream);
+
 /* ---- (4) compositing ------------------------------------------------------------------- */
 
 /* NeRFRenderer.composite after the model call, src/render/nerf.py:178-182, 228-249.

@@ -23,6 +23,10 @@ class Camera(C.Structure):
                 ("hl", _int), ("wl", _int), ("n_objects", _int), ("n_views", _int)]
 
 
+class MlpTcDebug(C.Structure):
+    _fields_ = [("h", _vp), ("stage", _int)]
+
+
 class MlpWeights(C.Structure):
     _fields_ = [("lin_in_w", _vp), ("lin_in_b", _vp),
                 ("fc0_w", _vp * N_BLOCKS), ("fc0_b", _vp * N_BLOCKS),
@@ -43,6 +47,10 @@ _SIGNATURES = {
     "pn_mlp_fp32_workspace_bytes": (_sz, [_i64]),
     "pn_mlp_forward_fp32": (_int, [C.POINTER(MlpWeights), _vp, _vp, _int, _int, _int, _i64, _vp, _vp, _vp,
                                    _sz, _vp]),
+    "pn_mlp_tc_packed_bytes": (_sz, []),
+    "pn_prepare_weights": (_int, [C.POINTER(MlpWeights), _vp, _sz, _vp]),
+    "pn_mlp_tc_workspace_bytes": (_sz, [_i64, _int]),
+    "pn_mlp_forward_tc": (_int, [_vp, _vp, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp, _vp]),
     "pn_composite_fwd": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "pn_composite_bwd": (_int, [_vp] * 8 + [_i64, _int, _int, _vp]),
 }
@@ -209,6 +217,41 @@ def mlp_forward_fp32(packed, feat_z, feat_x, n_objects, n_views, ppo, want_pre=F
                                          n_views, ppo, _ptr(out), _ptr(pre), ws.data_ptr(), nbytes, _stream()),
                "pn_mlp_forward_fp32")
     return (out, pre) if want_pre else out
+
+
+def pack_weights_tc(w, precision="fp16"):
+    """dict of un-prefixed ResnetFC tensors -> packed fp16 layers + bias tables (one device buffer)."""
+    if precision != "fp16":
+        raise NotImplementedError(f"tensor-core MLP operand format {precision!r}: only fp16 is implemented")
+    s, keep = pack_weights_fp32(w)
+    dev = keep["lin_in.weight"].device
+    nbytes = lib().pn_mlp_tc_packed_bytes()
+    packed = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    _check(lib().pn_prepare_weights(C.byref(s), packed.data_ptr(), nbytes, _stream()), "pn_prepare_weights")
+    return packed
+
+
+def mlp_forward_tc(packed, feat_z, feat_x, n_objects, n_views, ppo, want_pre=False, debug_stage=None):
+    """fp16 feat_z (N,512) / feat_x (N,64) -> (SB*ppo, 4) [sigmoid rgb, relu sigma] on the tensor cores."""
+    n_rows = n_objects * n_views * ppo
+    dev = feat_z.device
+    if feat_x.shape[1] != 64:
+        raise RuntimeError("tensor-core MLP needs feat_x with ldx=64")
+    out = torch.empty(n_objects * ppo, 4, device=dev, dtype=torch.float32)
+    pre = torch.empty_like(out) if want_pre else None
+    nbytes = lib().pn_mlp_tc_workspace_bytes(n_rows, n_views)
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    dbg, dbg_h = None, None
+    if debug_stage is not None:
+        rows = n_rows if debug_stage < COMBINE_LAYER or n_views == 1 else n_objects * ppo
+        dbg_h = torch.zeros(rows, D_HIDDEN, device=dev, dtype=torch.float32)
+        dbg = C.byref(MlpTcDebug(dbg_h.data_ptr(), int(debug_stage)))
+    with _Timed("mlp"):
+        _check(lib().pn_mlp_forward_tc(packed.data_ptr(), _ptr(feat_z, torch.float16), _ptr(feat_x, torch.float16),
+                                       n_objects, n_views, ppo, _ptr(out), _ptr(pre), ws.data_ptr(), nbytes, dbg,
+                                       _stream()), "pn_mlp_forward_tc")
+    ret = (out, pre) if want_pre else out
+    return (ret, dbg_h) if debug_stage is not None else ret
 
 
 def composite_fwd(rgb_sigma, z, rays, white_bkgd):

@@ -1,0 +1,578 @@
+// ResnetFC chain on the 5th-generation tensor cores (reference src/model/resnetfc.py:132-184,
+// block :53-62, head src/model/models.py:257-266): one persistent kernel runs
+//   lin_in, 3 x lin_z, 5 x (fc_0, fc_1), lin_out
+// for a tile of rows with every activation resident on chip.
+//
+// Work decomposition.  A CTA pair (2-CTA cluster, tcgen05 cta_group::2) owns a tile of 128
+// feature rows, 64 per CTA.  Every GEMM is issued as M=128 x N=256 x K=16 tcgen05.mma
+// instructions by one thread of the leader CTA; each CTA supplies its 64 rows of A and its
+// 128-row half of the 256-wide weight block B from its own shared memory.
+//
+// Tensor memory (512 columns per CTA, all used).  In the M=128 pair layout a 64 x 256 fp32
+// accumulator takes 128 columns: lanes 0-63 hold output features [0,128) of the block, lanes
+// 64-127 features [128,256).  Columns [0,256) hold the fp32 residual stream h (two 256-wide
+// blocks), columns [256,512) hold t = fc_0(relu(h)) (and lin_out's result).  h is never
+// rounded: lin_z and fc_1 accumulate into it in place (tcgen05.mma accumulate), biases are
+// added as a cumulative per-column vector whenever h is read.
+//
+// Shared memory per CTA: ACT (relu'd fp16 operand of the next GEMM, 8 K-chunks of
+// [64 rows x 64 fp16], 128-byte swizzled, 64 KB), Z (latent features of the tile, same
+// layout, 64 KB), X (positional code, 8 KB) and a 5-stage ring of weight tiles
+// [128 features x 64 K] (16 KB each) filled by TMA.
+//
+// Overlap.  A GEMM is issued in four quarters (block0,K-lo) (block1,K-lo) (block0,K-hi)
+// (block1,K-hi): block 0's accumulator is complete after the third quarter, so the epilogue
+// warps convert it to the next operand's K-chunks 0-3 while the fourth quarter runs, and
+// the next GEMM's first two quarters only need chunks 0-3.  lin_z of the next block is
+// issued between fc_0 and fc_1.  The tensor pipe therefore never waits for an epilogue in
+// steady state, and the next tile's X/Z are prefetched during blocks 2-4.
+#include "pn_common.cuh"
+#include "pn_tc_ptx.cuh"
+
+namespace pn {
+namespace tc {
+
+constexpr int kThreads = 384;          // warp 0 TMA, warp 1 MMA issue, warp 2 TMEM alloc, warps 4-11 epilogue
+constexpr int kEpiWarp0 = 4;
+constexpr int kRows = 64;              // rows per CTA
+constexpr int kTileRows = 128;         // rows per CTA pair
+constexpr int kChunkBytes = kRows * 128;   // [64 rows x 64 fp16]
+constexpr int kWStageBytes = 128 * 128;    // [128 features x 64 fp16]
+constexpr int kStages = 5;
+constexpr int kOffAct = 0;
+constexpr int kOffZ = 8 * kChunkBytes;
+constexpr int kOffX = 16 * kChunkBytes;
+constexpr int kOffW = 17 * kChunkBytes;
+constexpr int kOffBar = kOffW + kStages * kWStageBytes;
+enum {
+  BAR_W_FULL = 0,
+  BAR_W_EMPTY = kStages,
+  BAR_X_FULL = 2 * kStages,
+  BAR_X_EMPTY,
+  BAR_Z_FULL,
+  BAR_Z_EMPTY,
+  BAR_ACT,                  // 8: operand chunk c of the current generation is in shared memory
+  BAR_ACC = BAR_ACT + 8,    // 4: accumulator (region, block) complete
+  BAR_COUNT = BAR_ACC + 4
+};
+constexpr int kOffTmemPtr = kOffBar + BAR_COUNT * 8;
+constexpr int kSmemBytes = kOffTmemPtr + 16;
+constexpr int kSmemAlloc = kSmemBytes + 1024;  // slack for the manual 1024-byte alignment
+static_assert(kSmemAlloc <= 227 * 1024, "shared memory budget");
+
+constexpr uint32_t kColH = 0, kColT = 256;  // TMEM column bases
+constexpr uint32_t kIdesc = idesc_f16(128, 256);
+
+// Packed weights: 15 layers of [512 features][512 K] fp16 (lin_in and lin_out zero padded).
+constexpr int kLayers = 15;
+constexpr int L_IN = 0, L_Z0 = 1, L_FC = 4, L_OUT = 14;
+constexpr size_t kPackedWeightBytes = (size_t)kLayers * 512 * 512 * 2;
+// Bias table: rows 0-5 cumulative residual bias cb_0..cb_5, rows 6-10 fc_0 biases, then b_out[4].
+constexpr int kBiasFloats = 11 * 512 + 4;
+constexpr size_t kBiasBytes = ((size_t)kBiasFloats * 4 + 255) / 256 * 256;
+
+struct ChainParams {
+  const float* bias;     // table of the segment being run
+  float4* out;           // (rows, 4) [sigmoid rgb, relu sigma], segments ending in lin_out
+  float4* pre;           // optional raw lin_out outputs
+  float* h_io;           // segment [0,3): fp32 h written here; segment [3,5]: view-mean of it read
+  float* debug_h;        // optional (rows, 512) dump of h at stage debug_stage
+  unsigned int* err;     // device word set before a watchdog trap
+  int64_t n_rows;        // rows this launch processes
+  int64_t ppo;           // points per object (view-mean gather)
+  int n_tiles;
+  int first_block, last_block;   // [0,5] full chain, [0,3) and [3,5] when NS > 1
+  int n_views;
+  int debug_stage;
+};
+
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Bounded wait: a protocol bug must become a CUDA error, never a hung GPU.
+template <bool kCluster>
+__device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned int* err, unsigned int code) {
+  uint32_t spins = 0;
+  uint64_t t0 = 0;
+  while (!(kCluster ? mbar_try_wait_cluster(bar, parity) : mbar_try_wait(bar, parity))) {
+    if ((++spins & 0xFFFu) == 0) {
+      const uint64_t t = globaltimer_ns();
+      if (t0 == 0) t0 = t;
+      else if (t - t0 > 4000000000ull) {
+        if (err) atomicExch(err, code);
+        __trap();
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
+  __half2 h = __floats2half2_rn(fmaxf(a, 0.0f), fmaxf(b, 0.0f));
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_z,
+                 const __grid_constant__ CUtensorMap map_x, const ChainParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int n_clusters = gridDim.x >> 1;
+  const int cluster_id = blockIdx.x >> 1;
+  auto bar = [&](int i) { return smem_base + kOffBar + i * 8; };
+  const bool full_front = p.first_block == 0;      // lin_in / lin_z present (needs X, Z)
+  const bool has_head = p.last_block == 5;         // lin_out present
+
+  cluster_sync_all();
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_w);
+    prefetch_tensormap(&map_z);
+    prefetch_tensormap(&map_x);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bar(BAR_W_FULL + s), 2);   // leader's expect_tx arrive + peer's arrive
+      mbar_init(bar(BAR_W_EMPTY + s), 1);  // one multicast commit
+    }
+    mbar_init(bar(BAR_X_FULL), 2);
+    mbar_init(bar(BAR_X_EMPTY), 1);
+    mbar_init(bar(BAR_Z_FULL), 2);
+    mbar_init(bar(BAR_Z_EMPTY), 1);
+    for (int c = 0; c < 8; ++c) mbar_init(bar(BAR_ACT + c), 4);  // 2 warps per chunk per CTA
+    for (int a = 0; a < 4; ++a) mbar_init(bar(BAR_ACC + a), 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc_pair(smem_base + kOffTmemPtr, 512);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_base + kOffTmemPtr));
+
+  if (warp == 0 && lane == 0) {
+    // =============================== TMA producer (both CTAs) ===============================
+    uint32_t it = 0;
+    auto load_w = [&](int layer, int nb, int kc) {
+      const uint32_t s = it % kStages, use = it / kStages;
+      wait_bar<false>(bar(BAR_W_EMPTY + s), (use & 1) ^ 1, p.err, 0x100 + s);
+      const uint32_t full = bar(BAR_W_FULL + s);
+      if (rank == 0) mbar_arrive_expect_tx(full, 2 * kWStageBytes);
+      else mbar_arrive_cluster(full, 0);
+      tma_load_2d_pair(smem_base + kOffW + s * kWStageBytes, &map_w, full, kc * 64,
+                       layer * 512 + nb * 256 + (int)rank * 128);
+      ++it;
+    };
+    auto load_gemm = [&](int layer) {
+      for (int q = 0; q < 4; ++q)
+        for (int kk = 0; kk < 4; ++kk) load_w(layer, q & 1, (q >> 1) * 4 + kk);
+    };
+    auto load_xz = [&](int tile, uint32_t ti) {
+      const int row0 = tile * kTileRows + (int)rank * kRows;
+      wait_bar<false>(bar(BAR_X_EMPTY), (ti & 1) ^ 1, p.err, 0x110);
+      if (rank == 0) mbar_arrive_expect_tx(bar(BAR_X_FULL), 2 * kChunkBytes);
+      else mbar_arrive_cluster(bar(BAR_X_FULL), 0);
+      tma_load_2d_pair(smem_base + kOffX, &map_x, bar(BAR_X_FULL), 0, row0);
+      wait_bar<false>(bar(BAR_Z_EMPTY), (ti & 1) ^ 1, p.err, 0x111);
+      if (rank == 0) mbar_arrive_expect_tx(bar(BAR_Z_FULL), 2 * 8 * kChunkBytes);
+      else mbar_arrive_cluster(bar(BAR_Z_FULL), 0);
+      for (int c = 0; c < 8; ++c)
+        tma_load_2d_pair(smem_base + kOffZ + c * kChunkBytes, &map_z, bar(BAR_Z_FULL), c * 64, row0);
+    };
+    uint32_t ti = 0;
+    if (full_front && cluster_id < p.n_tiles) load_xz(cluster_id, 0);
+    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters, ++ti) {
+      if (full_front) {
+        load_w(L_IN, 0, 0);
+        load_w(L_IN, 1, 0);
+        load_gemm(L_Z0);
+      }
+      for (int b = p.first_block; b < p.last_block; ++b) {
+        load_gemm(L_FC + 2 * b);
+        if (b < 2) load_gemm(L_Z0 + b + 1);
+        load_gemm(L_FC + 2 * b + 1);
+        // next tile's X/Z: their buffers were released after lin_in / lin_z[2] of this tile
+        if (b == 1 && full_front && tile + n_clusters < p.n_tiles) load_xz(tile + n_clusters, ti + 1);
+      }
+      if (has_head)
+        for (int kc = 0; kc < 8; ++kc) load_w(L_OUT, 0, kc);
+    }
+  } else if (warp == 1 && lane == 0 && rank == 0) {
+    // =============================== MMA issuer (leader CTA) ================================
+    uint32_t it = 0, gen = 0, ti = 0;
+    auto item = [&](uint32_t a_addr, uint32_t d_col, bool clear, int ksteps) {
+      const uint32_t s = it % kStages, use = it / kStages;
+      wait_bar<false>(bar(BAR_W_FULL + s), use & 1, p.err, 0x200 + s);
+      tc_fence_after();
+      const uint32_t b_addr = smem_base + kOffW + s * kWStageBytes;
+      for (int j = 0; j < ksteps; ++j)
+        umma_f16_pair(tmem_base + d_col, smem_desc_k128(a_addr + 32 * j), smem_desc_k128(b_addr + 32 * j),
+                      kIdesc, (clear && j == 0) ? 0u : 1u);
+      umma_commit_pair(bar(BAR_W_EMPTY + s), 3);
+      ++it;
+    };
+    auto wait_act = [&](int c0) {
+      for (int c = c0; c < c0 + 4; ++c) wait_bar<true>(bar(BAR_ACT + c), gen & 1, p.err, 0x210 + c);
+      tc_fence_after();
+    };
+    // One 512x512 GEMM: A = 8 K-chunks at a_base, D = 2 blocks at d_col.
+    auto gemm = [&](uint32_t a_base, uint32_t d_col, bool clear, bool from_act, int commit_region) {
+      for (int q = 0; q < 4; ++q) {
+        const int nb = q & 1, kg = q >> 1;
+        if (from_act && nb == 0) wait_act(kg * 4);
+        for (int kk = 0; kk < 4; ++kk)
+          item(a_base + (kg * 4 + kk) * kChunkBytes, d_col + nb * 128, clear && kg == 0 && kk == 0, 4);
+        if (kg == 1 && commit_region >= 0) umma_commit_pair(bar(BAR_ACC + commit_region * 2 + nb), 3);
+      }
+      if (from_act) ++gen;
+    };
+    const uint32_t act = smem_base + kOffAct, zb = smem_base + kOffZ, xb = smem_base + kOffX;
+    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters, ++ti) {
+      if (full_front) {
+        wait_bar<false>(bar(BAR_X_FULL), ti & 1, p.err, 0x220);
+        wait_bar<false>(bar(BAR_Z_FULL), ti & 1, p.err, 0x221);
+        tc_fence_after();
+        item(xb, kColH, true, 3);          // lin_in: K = 48 of the zero-padded 64
+        item(xb, kColH + 128, true, 3);
+        umma_commit_pair(bar(BAR_X_EMPTY), 3);
+        gemm(zb, kColH, false, false, 0);  // lin_z[0] completes h_0
+      }
+      for (int b = p.first_block; b < p.last_block; ++b) {
+        gemm(act, kColT, true, true, 1);   // t = fc_0(relu(h))
+        if (b < 2) {
+          gemm(zb, kColH, false, false, -1);  // h += lin_z[b+1](z), overlaps the epilogue of t
+          if (b == 1) umma_commit_pair(bar(BAR_Z_EMPTY), 3);
+        }
+        gemm(act, kColH, false, true, 0);  // h += fc_1(relu(t))
+      }
+      if (has_head) {
+        wait_act(0);
+        for (int kc = 0; kc < 4; ++kc) item(act + kc * kChunkBytes, kColT, kc == 0, 4);
+        wait_act(4);
+        for (int kc = 4; kc < 8; ++kc) item(act + kc * kChunkBytes, kColT, false, 4);
+        umma_commit_pair(bar(BAR_ACC + 2), 3);
+        ++gen;
+      } else {
+        // the epilogue is still reading h out of tensor memory: wait for its drain signal
+        wait_act(0);
+        wait_act(4);
+        ++gen;
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    // =============================== epilogue warps (both CTAs) =============================
+    const int lq = warp & 3;             // TMEM lane quarter this warp may touch
+    const int ch = (warp - kEpiWarp0) >> 2;  // which 64 of the 128 accumulator columns
+    const int hf = lq >> 1;              // lanes 64-127 hold features [128,256) of a block
+    const int r = (lq & 1) * 32 + lane;  // row within the CTA
+    const uint32_t lane_addr = ((uint32_t)(lq * 32)) << 16;
+    const uint32_t sw = (uint32_t)(r & 7);
+    const uint32_t row_off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
+    uint32_t n_acc[4] = {0, 0, 0, 0};    // completed waits per (region, block) barrier
+
+    // mode 0: relu -> ACT operand; mode 1: dump fp32 to h_io (segment end)
+    auto epi = [&](int region, const float* bias_vec, int mode, int64_t grow, bool dbg) {
+      for (int nb = 0; nb < 2; ++nb) {
+        const int a = region * 2 + nb;
+        wait_bar<false>(bar(BAR_ACC + a), n_acc[a] & 1, p.err, 0x300 + a);
+        ++n_acc[a];
+        tc_fence_after();
+        const int n0 = 256 * nb + 128 * hf + 64 * ch;
+        const int c = n0 >> 6;
+        const uint32_t chunk = smem_base + kOffAct + c * kChunkBytes + row_off;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + lane_addr + (region ? kColT : kColH) + nb * 128 + ch * 64 + half * 32, v);
+          tmem_wait_ld();
+          const float4* bp = reinterpret_cast<const float4*>(bias_vec + n0 + half * 32);
+          float x[32];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 bv = __ldg(bp + i);
+            x[4 * i + 0] = __uint_as_float(v[4 * i + 0]) + bv.x;
+            x[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + bv.y;
+            x[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + bv.z;
+            x[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + bv.w;
+          }
+          if (dbg && grow < p.n_rows) {
+            float4* d = reinterpret_cast<float4*>(p.debug_h + grow * 512 + n0 + half * 32);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) d[i] = make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
+          }
+          if (mode == 1) {
+            if (grow < p.n_rows) {
+              float4* d = reinterpret_cast<float4*>(p.h_io + grow * 512 + n0 + half * 32);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) d[i] = make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t piece = (uint32_t)(half * 4 + i);
+              st_shared_v4(chunk + ((piece ^ sw) << 4), pack_relu_h2(x[8 * i + 0], x[8 * i + 1]),
+                           pack_relu_h2(x[8 * i + 2], x[8 * i + 3]), pack_relu_h2(x[8 * i + 4], x[8 * i + 5]),
+                           pack_relu_h2(x[8 * i + 6], x[8 * i + 7]));
+            }
+          }
+        }
+        if (mode == 0) fence_proxy_async_smem();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), 0);
+      }
+    };
+    // Segment [3,5] entry: h = mean over views of the fp32 h the first segment wrote.
+    auto epi_load = [&](int64_t grow) {
+      const bool valid = grow < p.n_rows;
+      const int64_t obj = valid ? grow / p.ppo : 0, pt = valid ? grow - obj * p.ppo : 0;
+      const float* src = p.h_io + ((obj * p.n_views) * p.ppo + pt) * 512;
+      const float inv = (float)p.n_views;
+      for (int nb = 0; nb < 2; ++nb) {
+        const int n0 = 256 * nb + 128 * hf + 64 * ch;
+        const int c = n0 >> 6;
+        const uint32_t chunk = smem_base + kOffAct + c * kChunkBytes + row_off;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          float x[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) x[i] = 0.0f;
+          if (valid) {
+            for (int v = 0; v < p.n_views; ++v) {
+              const float4* s4 = reinterpret_cast<const float4*>(src + (int64_t)v * p.ppo * 512 + n0 + half * 32);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float4 t = s4[i];
+                x[4 * i] += t.x; x[4 * i + 1] += t.y; x[4 * i + 2] += t.z; x[4 * i + 3] += t.w;
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) x[i] = x[i] / inv;   // torch.mean: sum in view order, then divide
+          }
+          uint32_t v[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(x[i]);
+          tmem_st_32x32(tmem_base + lane_addr + kColH + nb * 128 + ch * 64 + half * 32, v);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t piece = (uint32_t)(half * 4 + i);
+            st_shared_v4(chunk + ((piece ^ sw) << 4), pack_relu_h2(x[8 * i + 0], x[8 * i + 1]),
+                         pack_relu_h2(x[8 * i + 2], x[8 * i + 3]), pack_relu_h2(x[8 * i + 4], x[8 * i + 5]),
+                         pack_relu_h2(x[8 * i + 6], x[8 * i + 7]));
+          }
+        }
+        tmem_wait_st();
+        fence_proxy_async_smem();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), 0);
+      }
+    };
+
+    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters) {
+      const int64_t grow = (int64_t)tile * kTileRows + rank * kRows + r;
+      if (!full_front) epi_load(grow);
+      for (int b = p.first_block; b < p.last_block; ++b) {
+        if (b > p.first_block || full_front)
+          epi(0, p.bias + b * 512, 0, grow, p.debug_h != nullptr && p.debug_stage == b);
+        epi(1, p.bias + (6 + b) * 512, 0, grow, false);
+      }
+      if (has_head) {
+        epi(0, p.bias + 5 * 512, 0, grow, p.debug_h != nullptr && p.debug_stage == 5);
+        // lin_out result: features 0-3 of block 0 = lanes 0-63, columns kColT..+3
+        wait_bar<false>(bar(BAR_ACC + 2), n_acc[2] & 1, p.err, 0x310);
+        ++n_acc[2];
+        tc_fence_after();
+        if (hf == 0 && ch == 0) {
+          uint32_t v[4];
+          tmem_ld_32x4(tmem_base + lane_addr + kColT, v);
+          tmem_wait_ld();
+          if (grow < p.n_rows) {
+            const float4 bo = __ldg(reinterpret_cast<const float4*>(p.bias + 11 * 512));
+            const float s0 = __uint_as_float(v[0]) + bo.x, s1 = __uint_as_float(v[1]) + bo.y;
+            const float s2 = __uint_as_float(v[2]) + bo.z, s3 = __uint_as_float(v[3]) + bo.w;
+            if (p.pre) p.pre[grow] = make_float4(s0, s1, s2, s3);
+            p.out[grow] = make_float4(1.0f / (1.0f + expf(-s0)), 1.0f / (1.0f + expf(-s1)),
+                                      1.0f / (1.0f + expf(-s2)), fmaxf(s3, 0.0f));
+          }
+        }
+        tc_fence_before();
+      } else {
+        epi(0, p.bias + p.last_block * 512, 1, grow, false);
+      }
+    }
+  }
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc_pair(tmem_base, 512);
+}
+
+// ---- weight packing -----------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+pack_weights_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)kLayers * 512 * 512) return;
+  const int layer = (int)(i / (512 * 512));
+  const int n = (int)((i / 512) % 512), k = (int)(i % 512);
+  float v = 0.0f;
+  if (layer == L_IN) {
+    if (k < PN_D_CODE) v = w.lin_in_w[n * PN_D_CODE + k];
+  } else if (layer < L_FC) {
+    v = w.lin_z_w[layer - L_Z0][n * 512 + k];
+  } else if (layer < L_OUT) {
+    const int b = (layer - L_FC) >> 1;
+    v = ((layer - L_FC) & 1) ? w.fc1_w[b][n * 512 + k] : w.fc0_w[b][n * 512 + k];
+  } else if (n < 4) {
+    v = w.lin_out_w[n * 512 + k];
+  }
+  dst[i] = __float2half_rn(v);
+}
+
+// table A: cumulative from lin_in; table B: cumulative from block 3 (h handed over with biases in).
+__global__ void __launch_bounds__(512)
+pack_bias_kernel(pn_mlp_weights_t w, float* __restrict__ ta, float* __restrict__ tb) {
+  const int n = threadIdx.x;
+  float cb = w.lin_in_b[n] + w.lin_z_b[0][n];
+  ta[0 * 512 + n] = cb;
+  for (int b = 0; b < 5; ++b) {
+    cb += w.fc1_b[b][n];
+    if (b + 1 < PN_COMBINE_LAYER) cb += w.lin_z_b[b + 1][n];
+    ta[(b + 1) * 512 + n] = cb;
+  }
+  tb[0 * 512 + n] = tb[1 * 512 + n] = tb[2 * 512 + n] = tb[3 * 512 + n] = 0.0f;
+  tb[4 * 512 + n] = w.fc1_b[3][n];
+  tb[5 * 512 + n] = w.fc1_b[3][n] + w.fc1_b[4][n];
+  for (int b = 0; b < 5; ++b) ta[(6 + b) * 512 + n] = tb[(6 + b) * 512 + n] = w.fc0_b[b][n];
+  if (n < 4) ta[11 * 512 + n] = tb[11 * 512 + n] = w.lin_out_b[n];
+}
+
+// ---- host side ----------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)ptr;
+  }
+  return fn;
+}
+
+// fp16 matrix (rows, cols) with `pitch` bytes per row -> boxes of [box_rows x 64 columns], 128-byte swizzle.
+static int make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled entry point unavailable"); return PN_ERR_CUDA; }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {pitch};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return PN_ERR_CUDA; }
+  return PN_OK;
+}
+
+static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mz, const CUtensorMap& mx, ChainParams p,
+                        cudaStream_t st) {
+  static bool attr_set = false;  // idempotent; a benign race at worst repeats the call
+  if (!attr_set) {
+    PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
+    attr_set = true;
+  }
+  int dev = 0, sms = 0;
+  PN_CUDA_OK(cudaGetDevice(&dev));
+  PN_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  p.n_tiles = (int)((p.n_rows + kTileRows - 1) / kTileRows);
+  const int clusters = p.n_tiles < sms / 2 ? p.n_tiles : sms / 2;
+  mlp_chain_kernel<<<2 * clusters, kThreads, kSmemAlloc, st>>>(mw, mz, mx, p);
+  PN_LAUNCH_OK("mlp_chain_kernel");
+  count_launch();
+  return PN_OK;
+}
+
+}  // namespace tc
+}  // namespace pn
+
+extern "C" size_t pn_mlp_tc_packed_bytes(void) {
+  return pn::tc::kPackedWeightBytes + 2 * pn::tc::kBiasBytes;
+}
+
+extern "C" int pn_prepare_weights(const pn_mlp_weights_t* w, void* packed, size_t packed_bytes, pn_stream_t stream) {
+  using namespace pn::tc;
+  PN_CHECK_ARG(w && packed, "pn_prepare_weights: null pointer");
+  PN_CHECK_ARG(packed_bytes >= pn_mlp_tc_packed_bytes(), "pn_prepare_weights: buffer too small");
+  PN_CHECK_ARG(((uintptr_t)packed & 255) == 0, "pn_prepare_weights: buffer must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t total = (int64_t)kLayers * 512 * 512;
+  pack_weights_kernel<<<pn::ceil_div(total, 256), 256, 0, st>>>(*w, (__half*)packed);
+  PN_LAUNCH_OK("pack_weights_kernel");
+  float* ta = (float*)((char*)packed + kPackedWeightBytes);
+  float* tb = (float*)((char*)packed + kPackedWeightBytes + kBiasBytes);
+  pack_bias_kernel<<<1, 512, 0, st>>>(*w, ta, tb);
+  PN_LAUNCH_OK("pack_bias_kernel");
+  pn::count_launch(2);
+  return PN_OK;
+}
+
+extern "C" size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views) {
+  // fp32 h of every (view, point) row handed from the per-view segment to the merged one, + error word
+  return 256 + (n_views > 1 && n_rows > 0 ? (size_t)n_rows * 512 * sizeof(float) : 0);
+}
+
+extern "C" int pn_mlp_forward_tc(const void* packed, const void* feat_z, const void* feat_x, int n_objects,
+                                 int n_views, int64_t points_per_object, float* out, float* pre_act,
+                                 void* workspace, size_t workspace_bytes, const pn_mlp_tc_debug_t* dbg,
+                                 pn_stream_t stream) {
+  using namespace pn::tc;
+  PN_CHECK_ARG(packed && feat_z && feat_x && out && workspace, "pn_mlp_forward_tc: null pointer");
+  PN_CHECK_ARG(n_objects > 0 && n_views > 0 && points_per_object >= 0, "pn_mlp_forward_tc: bad sizes");
+  const int64_t n_rows = (int64_t)n_objects * n_views * points_per_object;
+  const int64_t n_pts = (int64_t)n_objects * points_per_object;
+  if (n_rows == 0) return PN_OK;
+  PN_CHECK_ARG(n_rows < (1ll << 31) - 256, "pn_mlp_forward_tc: too many rows for one launch");
+  PN_CHECK_ARG(workspace_bytes >= pn_mlp_tc_workspace_bytes(n_rows, n_views), "pn_mlp_forward_tc: workspace too small");
+  PN_CHECK_ARG(((uintptr_t)workspace & 255) == 0 && ((uintptr_t)feat_z & 15) == 0 && ((uintptr_t)feat_x & 15) == 0,
+               "pn_mlp_forward_tc: misaligned buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUtensorMap mw, mz, mx;
+  int rc;
+  if ((rc = make_map(&mw, packed, (uint64_t)kLayers * 512, 512, 1024, 128))) return rc;
+  if ((rc = make_map(&mz, feat_z, (uint64_t)n_rows, 512, 1024, kRows))) return rc;
+  if ((rc = make_map(&mx, feat_x, (uint64_t)n_rows, 64, 128, kRows))) return rc;
+  unsigned int* err = (unsigned int*)workspace;
+  PN_CUDA_OK(cudaMemsetAsync(err, 0, 4, st));
+  ChainParams p = {};
+  p.out = (float4*)out;
+  p.pre = (float4*)pre_act;
+  p.err = err;
+  p.ppo = points_per_object;
+  p.n_views = n_views;
+  p.debug_h = dbg ? dbg->h : nullptr;
+  p.debug_stage = dbg ? dbg->stage : -1;
+  const float* ta = (const float*)((const char*)packed + kPackedWeightBytes);
+  const float* tb = (const float*)((const char*)packed + kPackedWeightBytes + kBiasBytes);
+  if (n_views == 1) {
+    p.bias = ta; p.n_rows = n_rows; p.first_block = 0; p.last_block = 5;
+    return launch_chain(mw, mz, mx, p, st);
+  }
+  // NS > 1: blocks 0-2 per (view, point) row, then the view mean (resnetfc.py:152-172) feeds blocks 3-4
+  p.h_io = (float*)((char*)workspace + 256);
+  p.bias = ta; p.n_rows = n_rows; p.first_block = 0; p.last_block = 3;
+  if ((rc = launch_chain(mw, mz, mx, p, st))) return rc;
+  p.bias = tb; p.n_rows = n_pts; p.first_block = 3; p.last_block = 5;
+  p.debug_h = (dbg && dbg->stage >= 4) ? dbg->h : nullptr;
+  return launch_chain(mw, mz, mx, p, st);
+}

@@ -35,3 +35,33 @@ def render_case_inputs(fx):
         rays=torch.from_numpy(fx["rays"]),
         sb=sb, ns=ns, white=bool(fx["white"]), lindisp=bool(fx["lindisp"]),
     )
+
+
+def emulate_tc_chain(w, feat_z, feat_x, ns, ppo):
+    """float64 restatement of the tensor-core ResnetFC chain with its operand rounding: weights and
+    GEMM inputs rounded to fp16, exact accumulation, fp32-exact residual stream and biases.
+    feat_z (N,512), feat_x (N,>=42) are the (already fp16-valued) kernel inputs.
+    Returns (list of h at stages 0..5 incl. biases, raw lin_out outputs (N/ns, 4))."""
+    def W(k):
+        return w[k + ".weight"].half().double()
+
+    def B(k):
+        return w[k + ".bias"].double()
+
+    def q(t):
+        return torch.relu(t).half().double()
+
+    z, x = feat_z.double(), feat_x[:, :42].double()
+    h = x @ W("lin_in").T + B("lin_in")
+    stages = []
+    for b in range(5):
+        if b == 3 and ns > 1:
+            h = h.reshape(-1, ns, ppo, 512).sum(1).div(ns).reshape(-1, 512)
+        if b < 3:
+            h = h + z @ W(f"lin_z.{b}").T + B(f"lin_z.{b}")
+        stages.append(h)
+        t = q(h) @ W(f"blocks.{b}.fc_0").T + B(f"blocks.{b}.fc_0")
+        h = h + q(t) @ W(f"blocks.{b}.fc_1").T + B(f"blocks.{b}.fc_1")
+    stages.append(h)
+    pre = q(h) @ W("lin_out").T + B("lin_out")
+    return stages, pre
