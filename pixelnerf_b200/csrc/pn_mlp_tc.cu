@@ -138,12 +138,12 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(bar(BAR_W_FULL + s), 2);   // leader's expect_tx arrive + peer's arrive
+      mbar_init(bar(BAR_W_FULL + s), 1);   // the leader's expect_tx arrive (both CTAs' bytes)
       mbar_init(bar(BAR_W_EMPTY + s), 1);  // one multicast commit
     }
-    mbar_init(bar(BAR_X_FULL), 2);
+    mbar_init(bar(BAR_X_FULL), 1);
     mbar_init(bar(BAR_X_EMPTY), 1);
-    mbar_init(bar(BAR_Z_FULL), 2);
+    mbar_init(bar(BAR_Z_FULL), 1);
     mbar_init(bar(BAR_Z_EMPTY), 1);
     for (int c = 0; c < 8; ++c) mbar_init(bar(BAR_ACT + c), 4);  // 2 warps per chunk per CTA
     for (int a = 0; a < 4; ++a) mbar_init(bar(BAR_ACC + a), 1);
@@ -156,43 +156,52 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_base + kOffTmemPtr));
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0) {
     // =============================== TMA producer (both CTAs) ===============================
-    uint32_t it = 0;
+    // The whole warp walks the schedule (warp-uniform control flow keeps addresses and
+    // parities in uniform registers); one elected lane issues the copies.
+    uint32_t stage = 0, phase = 0;
     auto load_w = [&](int layer, int nb, int kc) {
-      const uint32_t s = it % kStages, use = it / kStages;
-      wait_bar<false>(bar(BAR_W_EMPTY + s), (use & 1) ^ 1, p.err, 0x100 + s);
-      const uint32_t full = bar(BAR_W_FULL + s);
-      if (rank == 0) mbar_arrive_expect_tx(full, 2 * kWStageBytes);
-      else mbar_arrive_cluster(full, 0);
-      tma_load_2d_pair(smem_base + kOffW + s * kWStageBytes, &map_w, full, kc * 64,
-                       layer * 512 + nb * 256 + (int)rank * 128);
-      ++it;
+      wait_bar<false>(bar(BAR_W_EMPTY + stage), phase ^ 1, p.err, 0x100 + stage);
+      if (elect_one()) {
+        const uint32_t full = bar(BAR_W_FULL + stage);
+        // the leader expects both CTAs' bytes; the peer's copy credits the leader's barrier
+        if (rank == 0) mbar_arrive_expect_tx(full, 2 * kWStageBytes);
+        tma_load_2d_pair(smem_base + kOffW + stage * kWStageBytes, &map_w, full, kc * 64,
+                         layer * 512 + nb * 256 + (int)rank * 128);
+      }
+      __syncwarp();
+      if (++stage == kStages) { stage = 0; phase ^= 1; }
     };
     auto load_gemm = [&](int layer) {
+#pragma unroll 1
       for (int q = 0; q < 4; ++q)
+#pragma unroll 1
         for (int kk = 0; kk < 4; ++kk) load_w(layer, q & 1, (q >> 1) * 4 + kk);
     };
     auto load_xz = [&](int tile, uint32_t ti) {
       const int row0 = tile * kTileRows + (int)rank * kRows;
       wait_bar<false>(bar(BAR_X_EMPTY), (ti & 1) ^ 1, p.err, 0x110);
-      if (rank == 0) mbar_arrive_expect_tx(bar(BAR_X_FULL), 2 * kChunkBytes);
-      else mbar_arrive_cluster(bar(BAR_X_FULL), 0);
-      tma_load_2d_pair(smem_base + kOffX, &map_x, bar(BAR_X_FULL), 0, row0);
       wait_bar<false>(bar(BAR_Z_EMPTY), (ti & 1) ^ 1, p.err, 0x111);
-      if (rank == 0) mbar_arrive_expect_tx(bar(BAR_Z_FULL), 2 * 8 * kChunkBytes);
-      else mbar_arrive_cluster(bar(BAR_Z_FULL), 0);
-      for (int c = 0; c < 8; ++c)
-        tma_load_2d_pair(smem_base + kOffZ + c * kChunkBytes, &map_z, bar(BAR_Z_FULL), c * 64, row0);
+      if (elect_one()) {
+        if (rank == 0) mbar_arrive_expect_tx(bar(BAR_X_FULL), 2 * kChunkBytes);
+        tma_load_2d_pair(smem_base + kOffX, &map_x, bar(BAR_X_FULL), 0, row0);
+        if (rank == 0) mbar_arrive_expect_tx(bar(BAR_Z_FULL), 2 * 8 * kChunkBytes);
+        for (int c = 0; c < 8; ++c)
+          tma_load_2d_pair(smem_base + kOffZ + c * kChunkBytes, &map_z, bar(BAR_Z_FULL), c * 64, row0);
+      }
+      __syncwarp();
     };
     uint32_t ti = 0;
     if (full_front && cluster_id < p.n_tiles) load_xz(cluster_id, 0);
+#pragma unroll 1
     for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters, ++ti) {
       if (full_front) {
         load_w(L_IN, 0, 0);
         load_w(L_IN, 1, 0);
         load_gemm(L_Z0);
       }
+#pragma unroll 1
       for (int b = p.first_block; b < p.last_block; ++b) {
         load_gemm(L_FC + 2 * b);
         if (b < 2) load_gemm(L_Z0 + b + 1);
@@ -200,39 +209,57 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         // next tile's X/Z: their buffers were released after lin_in / lin_z[2] of this tile
         if (b == 1 && full_front && tile + n_clusters < p.n_tiles) load_xz(tile + n_clusters, ti + 1);
       }
-      if (has_head)
+      if (has_head) {
+#pragma unroll 1
         for (int kc = 0; kc < 8; ++kc) load_w(L_OUT, 0, kc);
+      }
     }
-  } else if (warp == 1 && lane == 0 && rank == 0) {
+  } else if (warp == 1 && rank == 0) {
     // =============================== MMA issuer (leader CTA) ================================
-    uint32_t it = 0, gen = 0, ti = 0;
+    // Warp-uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit.
+    uint32_t stage = 0, phase = 0, gen = 0, ti = 0;
+    const uint32_t w0 = smem_base + kOffW;
+    // descriptor = constant high word | (address >> 4): only the low word changes per MMA
+    const uint64_t desc_hi = smem_desc_k128(0);
     auto item = [&](uint32_t a_addr, uint32_t d_col, bool clear, int ksteps) {
-      const uint32_t s = it % kStages, use = it / kStages;
-      wait_bar<false>(bar(BAR_W_FULL + s), use & 1, p.err, 0x200 + s);
+      wait_bar<false>(bar(BAR_W_FULL + stage), phase, p.err, 0x200 + stage);
       tc_fence_after();
-      const uint32_t b_addr = smem_base + kOffW + s * kWStageBytes;
-      for (int j = 0; j < ksteps; ++j)
-        umma_f16_pair(tmem_base + d_col, smem_desc_k128(a_addr + 32 * j), smem_desc_k128(b_addr + 32 * j),
-                      kIdesc, (clear && j == 0) ? 0u : 1u);
-      umma_commit_pair(bar(BAR_W_EMPTY + s), 3);
-      ++it;
+      if (elect_one()) {
+        const uint32_t a_lo = a_addr >> 4, b_lo = (w0 + stage * kWStageBytes) >> 4;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (j < ksteps)
+            umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)(a_lo + 2 * j), desc_hi | (uint64_t)(b_lo + 2 * j),
+                          kIdesc, (clear && j == 0) ? 0u : 1u);
+        umma_commit_pair(bar(BAR_W_EMPTY + stage), 3);
+      }
+      __syncwarp();
+      if (++stage == kStages) { stage = 0; phase ^= 1; }
+    };
+    auto commit = [&](int b) {
+      if (elect_one()) umma_commit_pair(bar(b), 3);
+      __syncwarp();
     };
     auto wait_act = [&](int c0) {
+#pragma unroll 1
       for (int c = c0; c < c0 + 4; ++c) wait_bar<true>(bar(BAR_ACT + c), gen & 1, p.err, 0x210 + c);
       tc_fence_after();
     };
     // One 512x512 GEMM: A = 8 K-chunks at a_base, D = 2 blocks at d_col.
     auto gemm = [&](uint32_t a_base, uint32_t d_col, bool clear, bool from_act, int commit_region) {
+#pragma unroll 1
       for (int q = 0; q < 4; ++q) {
         const int nb = q & 1, kg = q >> 1;
         if (from_act && nb == 0) wait_act(kg * 4);
+#pragma unroll 1
         for (int kk = 0; kk < 4; ++kk)
           item(a_base + (kg * 4 + kk) * kChunkBytes, d_col + nb * 128, clear && kg == 0 && kk == 0, 4);
-        if (kg == 1 && commit_region >= 0) umma_commit_pair(bar(BAR_ACC + commit_region * 2 + nb), 3);
+        if (kg == 1 && commit_region >= 0) commit(BAR_ACC + commit_region * 2 + nb);
       }
       if (from_act) ++gen;
     };
     const uint32_t act = smem_base + kOffAct, zb = smem_base + kOffZ, xb = smem_base + kOffX;
+#pragma unroll 1
     for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters, ++ti) {
       if (full_front) {
         wait_bar<false>(bar(BAR_X_FULL), ti & 1, p.err, 0x220);
@@ -240,23 +267,26 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         tc_fence_after();
         item(xb, kColH, true, 3);          // lin_in: K = 48 of the zero-padded 64
         item(xb, kColH + 128, true, 3);
-        umma_commit_pair(bar(BAR_X_EMPTY), 3);
+        commit(BAR_X_EMPTY);
         gemm(zb, kColH, false, false, 0);  // lin_z[0] completes h_0
       }
+#pragma unroll 1
       for (int b = p.first_block; b < p.last_block; ++b) {
         gemm(act, kColT, true, true, 1);   // t = fc_0(relu(h))
         if (b < 2) {
           gemm(zb, kColH, false, false, -1);  // h += lin_z[b+1](z), overlaps the epilogue of t
-          if (b == 1) umma_commit_pair(bar(BAR_Z_EMPTY), 3);
+          if (b == 1) commit(BAR_Z_EMPTY);
         }
         gemm(act, kColH, false, true, 0);  // h += fc_1(relu(t))
       }
       if (has_head) {
         wait_act(0);
+#pragma unroll 1
         for (int kc = 0; kc < 4; ++kc) item(act + kc * kChunkBytes, kColT, kc == 0, 4);
         wait_act(4);
+#pragma unroll 1
         for (int kc = 4; kc < 8; ++kc) item(act + kc * kChunkBytes, kColT, false, 4);
-        umma_commit_pair(bar(BAR_ACC + 2), 3);
+        commit(BAR_ACC + 2);
         ++gen;
       } else {
         // the epilogue is still reading h out of tensor memory: wait for its drain signal

@@ -1,0 +1,116 @@
+"""Tensor-core (tcgen05) ResnetFC chain on the GPU.
+
+Two oracles:
+  * the float64 emulation of the chain's own arithmetic (fp16-rounded GEMM operands, exact sums,
+    fp32-exact residual and biases; helpers.emulate_tc_chain) -- checks the kernel does what it
+    claims, layer by layer, tightly;
+  * the reference's fp32 path (golden vectors of the live reference / the oracle) -- checks the
+    fp16-operand path against north_star's reduced-precision tolerance: 2e-3 max-abs on
+    rgb / weights, depth read relative to the ray span.
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from oracle import model as omodel
+from helpers import emulate_tc_chain, golden_files, load, render_case_inputs
+from test_gpu_model import _net_for
+
+pytestmark = pytest.mark.gpu
+
+TC_TOL = 2e-3  # north_star: "2e-3 in the bf16/TF32 MLP path"
+
+
+def _inputs(n, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    fz = torch.rand(n, 512, generator=g).half()
+    fx = torch.zeros(n, 64)
+    fx[:, :42] = torch.randn(n, 42, generator=g)
+    return fz, fx.half()
+
+
+@pytest.mark.parametrize("ns,ppo,sb", [(1, 1, 1), (1, 300, 1), (2, 130, 2), (3, 77, 1), (1, 128 * 150 + 5, 1)])
+def test_chain_vs_emulation(ns, ppo, sb):
+    """Ragged row counts, more tiles than CTA pairs, NS = 1..3: final pre-activations and outputs."""
+    from pixelnerf_b200 import _lib, synthetic as syn
+    w = syn.mlp_weights(42)
+    packed = _lib.pack_weights_tc({k: v.cuda() for k, v in w.items()})
+    n = sb * ns * ppo
+    fz, fx = _inputs(n)
+    out, pre = _lib.mlp_forward_tc(packed, fz.cuda(), fx.cuda(), sb, ns, ppo, want_pre=True)
+    torch.cuda.synchronize()
+    # emulate object by object (the view mean is per object)
+    refs = []
+    for o in range(sb):
+        sl = slice(o * ns * ppo, (o + 1) * ns * ppo)
+        refs.append(emulate_tc_chain(w, fz[sl].float(), fx[sl].float(), ns, ppo)[1])
+    ref = torch.cat(refs)
+    scale = max(1.0, ref.abs().max().item())
+    # the kernel accumulates in fp32 and rounds operands like the emulation; what is left are rare
+    # fp16 rounding-boundary flips of single activations
+    assert (pre.cpu().double() - ref).abs().max().item() < 1.5e-3 * scale
+    assert (out.cpu()[:, :3].double() - torch.sigmoid(ref[:, :3])).abs().max().item() < 1e-3
+
+
+@pytest.mark.parametrize("stage", [0, 2, 5])
+def test_residual_stream_stages(stage):
+    """h as held in tensor memory (plus cumulative bias) at the start, middle and end of the chain."""
+    from pixelnerf_b200 import _lib, synthetic as syn
+    w = syn.mlp_weights(7)
+    packed = _lib.pack_weights_tc({k: v.cuda() for k, v in w.items()})
+    fz, fx = _inputs(200, seed=3)
+    _, dbg = _lib.mlp_forward_tc(packed, fz.cuda(), fx.cuda(), 1, 1, 200, debug_stage=stage)
+    ref = emulate_tc_chain(w, fz.float(), fx.float(), 1, 200)[0][stage]
+    tol = 1e-4 if stage == 0 else 5e-3   # stage 0 has no rounded activations upstream
+    assert (dbg.cpu().double() - ref).abs().max().item() < tol
+
+
+@pytest.mark.parametrize("path", golden_files("render_"))
+def test_net_forward_fp16_vs_golden(path):
+    fx = load(path)
+    inp = render_case_inputs(fx)
+    net, _ = _net_for(fx, inp, precision="fp16")
+    xyz, dirs = torch.from_numpy(fx["probe_xyz"]).cuda(), torch.from_numpy(fx["probe_dirs"]).cuda()
+    with torch.no_grad():
+        out_c = net(xyz, coarse=True, viewdirs=dirs).cpu().numpy()
+        out_f = net(xyz, coarse=False, viewdirs=dirs).cpu().numpy()
+    for out, ref in ((out_c, fx["probe_coarse"]), (out_f, fx["probe_fine"])):
+        assert np.abs(out[..., :3] - ref[..., :3]).max() < TC_TOL
+        assert np.abs(out[..., 3] - ref[..., 3]).max() < TC_TOL * max(1.0, np.abs(ref[..., 3]).max())
+
+
+@pytest.mark.parametrize("path", golden_files("render_"))
+def test_render_stagewise_fp16(path):
+    """Teacher-forced stage-wise render (see test_gpu_render.py) with the tensor-core MLP."""
+    fx = load(path)
+    inp = render_case_inputs(fx)
+    sb, ns = inp["sb"], inp["ns"]
+    net, ren = _net_for(fx, inp, precision="fp16")
+    rays = inp["rays"]
+    draws = {k: v.cuda() for k, v in inp["draws"].items()}
+
+    def net_fn(xyz, dirs, coarse):
+        return omodel.net_forward(inp["wc"] if coarse else inp["wf"], inp["latent"], inp["cam"], ns, xyz, dirs)
+    with torch.no_grad():
+        ref = oracle.render_rays(net_fn, rays.reshape(-1, 8), sb, 64, 32, 16, inp["draws"], white_bkgd=inp["white"],
+                                 lindisp=inp["lindisp"])
+    ren.injected_draws = draws
+    ren.injected_z = dict(w_coarse=ref["w_coarse"].cuda(), depth_coarse=ref["depth_coarse"].cuda())
+    with torch.no_grad():
+        out = ren(net, rays.cuda(), want_weights=True)
+    z_c, z_f = ren.last_z
+    # sampling does not depend on the MLP precision when teacher-forced: still bit-exact
+    assert np.array_equal(z_c.reshape(-1, 64).cpu().numpy(), ref["z_coarse"].numpy())
+    assert np.array_equal(z_f.reshape(-1, 96).cpu().numpy(), ref["z_fine"].numpy())
+    span = float((rays[..., 7] - rays[..., 6]).max())
+    for part, tag in ((out.coarse, "coarse"), (out.fine, "fine")):
+        assert np.abs(part.rgb.cpu().numpy() - fx["rgb_" + tag]).max() < TC_TOL, tag
+        assert np.abs(part.weights.cpu().numpy() - fx["w_" + tag]).max() < TC_TOL, tag
+        assert np.abs(part.depth.cpu().numpy() - fx["depth_" + tag]).max() < TC_TOL * max(1.0, span), tag
+
+
+def test_unimplemented_operand_format_raises():
+    from pixelnerf_b200 import _lib, synthetic as syn
+    with pytest.raises(NotImplementedError):
+        _lib.pack_weights_tc({k: v.cuda() for k, v in syn.mlp_weights(1).items()}, precision="bf16")
