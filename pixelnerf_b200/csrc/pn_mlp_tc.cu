@@ -15,17 +15,19 @@
 // rounded: lin_z and fc_1 accumulate into it in place (tcgen05.mma accumulate), biases are
 // added as a cumulative per-column vector whenever h is read.
 //
-// Shared memory per CTA: ACT (relu'd fp16 operand of the next GEMM, 8 K-chunks of
-// [64 rows x 64 fp16], 128-byte swizzled, 64 KB), Z (latent features of the tile, same
-// layout, 64 KB), X (positional code, 8 KB) and a 5-stage ring of weight tiles
-// [128 features x 64 K] (16 KB each) filled by TMA.
+// Shared memory per CTA (225 KB): ACT (relu'd fp16 operand of the next GEMM, 8 K-chunks of
+// [64 rows x 64 fp16], 128-byte swizzled, 64 KB), a 4-slot ring of operand chunks through
+// which the tile's x and z stream by TMA (8 KB each; z is re-read from L2 for each of the
+// three lin_z, K-outer, so it never needs 64 KB of residency) and a 4-stage ring of weight
+// tiles [128 features x 128 K] (32 KB each, two TMA boxes).  128 KB of weights in flight per
+// CTA is what covers the L2 round trip; one stage = 8 tcgen05.mma = 512 tensor-pipe clocks.
 //
 // Overlap.  A GEMM is issued in four quarters (block0,K-lo) (block1,K-lo) (block0,K-hi)
 // (block1,K-hi): block 0's accumulator is complete after the third quarter, so the epilogue
 // warps convert it to the next operand's K-chunks 0-3 while the fourth quarter runs, and
 // the next GEMM's first two quarters only need chunks 0-3.  lin_z of the next block is
 // issued between fc_0 and fc_1.  The tensor pipe therefore never waits for an epilogue in
-// steady state, and the next tile's X/Z are prefetched during blocks 2-4.
+// steady state; the next tile's x/z rows are pulled into L2 a tile ahead.
 #include "pn_common.cuh"
 #include "pn_tc_ptx.cuh"
 
@@ -37,22 +39,21 @@ constexpr int kEpiWarp0 = 4;
 constexpr int kRows = 64;              // rows per CTA
 constexpr int kTileRows = 128;         // rows per CTA pair
 constexpr int kChunkBytes = kRows * 128;   // [64 rows x 64 fp16]
-constexpr int kWStageBytes = 128 * 128;    // [128 features x 64 fp16]
-constexpr int kStages = 5;
+constexpr int kWBoxBytes = 128 * 128;      // TMA box [128 features x 64 fp16]
+constexpr int kWStageBytes = 2 * kWBoxBytes;   // one ring stage = K 128 = two boxes
+constexpr int kStages = 4;
+constexpr int kASlots = 4;                 // operand-chunk ring (x and z stream through it)
 constexpr int kOffAct = 0;
-constexpr int kOffZ = 8 * kChunkBytes;
-constexpr int kOffX = 16 * kChunkBytes;
-constexpr int kOffW = 17 * kChunkBytes;
+constexpr int kOffA = 8 * kChunkBytes;
+constexpr int kOffW = kOffA + kASlots * kChunkBytes;
 constexpr int kOffBar = kOffW + kStages * kWStageBytes;
 enum {
   BAR_W_FULL = 0,
   BAR_W_EMPTY = kStages,
-  BAR_X_FULL = 2 * kStages,
-  BAR_X_EMPTY,
-  BAR_Z_FULL,
-  BAR_Z_EMPTY,
-  BAR_ACT,                  // 8: operand chunk c of the current generation is in shared memory
-  BAR_ACC = BAR_ACT + 8,    // 4: accumulator (region, block) complete
+  BAR_A_FULL = 2 * kStages,
+  BAR_A_EMPTY = 2 * kStages + kASlots,
+  BAR_ACT = 2 * kStages + 2 * kASlots,   // 8: operand chunk c of the current generation is in shared memory
+  BAR_ACC = BAR_ACT + 8,                 // 4: accumulator (region, block) complete
   BAR_COUNT = BAR_ACC + 4
 };
 constexpr int kOffTmemPtr = kOffBar + BAR_COUNT * 8;
@@ -141,10 +142,10 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       mbar_init(bar(BAR_W_FULL + s), 1);   // the leader's expect_tx arrive (both CTAs' bytes)
       mbar_init(bar(BAR_W_EMPTY + s), 1);  // one multicast commit
     }
-    mbar_init(bar(BAR_X_FULL), 1);
-    mbar_init(bar(BAR_X_EMPTY), 1);
-    mbar_init(bar(BAR_Z_FULL), 1);
-    mbar_init(bar(BAR_Z_EMPTY), 1);
+    for (int a = 0; a < kASlots; ++a) {
+      mbar_init(bar(BAR_A_FULL + a), 1);
+      mbar_init(bar(BAR_A_EMPTY + a), 1);
+    }
     for (int c = 0; c < 8; ++c) mbar_init(bar(BAR_ACT + c), 4);  // 2 warps per chunk per CTA
     for (int a = 0; a < 4; ++a) mbar_init(bar(BAR_ACC + a), 1);
     fence_mbar_init();
@@ -159,82 +160,105 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   if (warp == 0) {
     // =============================== TMA producer (both CTAs) ===============================
     // The whole warp walks the schedule (warp-uniform control flow keeps addresses and
-    // parities in uniform registers); one elected lane issues the copies.
-    uint32_t stage = 0, phase = 0;
-    auto load_w = [&](int layer, int nb, int kc) {
-      wait_bar<false>(bar(BAR_W_EMPTY + stage), phase ^ 1, p.err, 0x100 + stage);
+    // parities in uniform registers); one elected lane issues the copies.  Loads are issued
+    // in exactly the order the MMA issuer consumes them, so the two rings cannot deadlock.
+    uint32_t ws = 0, wph = 0;   // weight ring stage / phase
+    uint32_t as = 0, aph = 0;   // operand-chunk ring slot / phase
+    // Weight tile for K-chunks [kc, kc+nkc) of block nb of `layer`: nkc boxes of [128 out x 64 in].
+    auto load_w = [&](int layer, int nb, int kc, int nkc) {
+      wait_bar<false>(bar(BAR_W_EMPTY + ws), wph ^ 1, p.err, 0x100 + ws);
       if (elect_one()) {
-        const uint32_t full = bar(BAR_W_FULL + stage);
-        // the leader expects both CTAs' bytes; the peer's copy credits the leader's barrier
-        if (rank == 0) mbar_arrive_expect_tx(full, 2 * kWStageBytes);
-        tma_load_2d_pair(smem_base + kOffW + stage * kWStageBytes, &map_w, full, kc * 64,
-                         layer * 512 + nb * 256 + (int)rank * 128);
+        const uint32_t full = bar(BAR_W_FULL + ws);
+        // the leader expects both CTAs' bytes; the peer's copies credit the leader's barrier
+        if (rank == 0) mbar_arrive_expect_tx(full, 2 * nkc * kWBoxBytes);
+        const int row = layer * 512 + nb * 256 + (int)rank * 128;
+        for (int i = 0; i < nkc; ++i)
+          tma_load_2d_pair(smem_base + kOffW + ws * kWStageBytes + i * kWBoxBytes, &map_w, full, (kc + i) * 64, row);
       }
       __syncwarp();
-      if (++stage == kStages) { stage = 0; phase ^= 1; }
+      if (++ws == kStages) { ws = 0; wph ^= 1; }
     };
-    auto load_gemm = [&](int layer) {
+    // One [64 rows x 64] operand chunk (x, or K-chunk c of z) of this CTA's rows.
+    auto load_a = [&](const CUtensorMap* map, int col, int row0) {
+      wait_bar<false>(bar(BAR_A_EMPTY + as), aph ^ 1, p.err, 0x110 + as);
+      if (elect_one()) {
+        const uint32_t full = bar(BAR_A_FULL + as);
+        if (rank == 0) mbar_arrive_expect_tx(full, 2 * kChunkBytes);
+        tma_load_2d_pair(smem_base + kOffA + as * kChunkBytes, map, full, col, row0);
+      }
+      __syncwarp();
+      if (++as == kASlots) { as = 0; aph ^= 1; }
+    };
+    auto load_fc = [&](int layer) {   // quarter order, two K=128 items per quarter
 #pragma unroll 1
       for (int q = 0; q < 4; ++q)
 #pragma unroll 1
-        for (int kk = 0; kk < 4; ++kk) load_w(layer, q & 1, (q >> 1) * 4 + kk);
+        for (int h = 0; h < 2; ++h) load_w(layer, q & 1, (q >> 1) * 4 + h * 2, 2);
     };
-    auto load_xz = [&](int tile, uint32_t ti) {
-      const int row0 = tile * kTileRows + (int)rank * kRows;
-      wait_bar<false>(bar(BAR_X_EMPTY), (ti & 1) ^ 1, p.err, 0x110);
-      wait_bar<false>(bar(BAR_Z_EMPTY), (ti & 1) ^ 1, p.err, 0x111);
+    auto load_lin_z = [&](int layer, int row0) {   // K-outer: z chunk pair, then both blocks' weights
+#pragma unroll 1
+      for (int kp = 0; kp < 4; ++kp) {
+        load_a(&map_z, (2 * kp) * 64, row0);
+        load_a(&map_z, (2 * kp + 1) * 64, row0);
+        load_w(layer, 0, 2 * kp, 2);
+        load_w(layer, 1, 2 * kp, 2);
+      }
+    };
+    auto prefetch_l2 = [&](int tile) {   // next tile's x / z rows: DRAM -> L2 ahead of the operand ring
       if (elect_one()) {
-        if (rank == 0) mbar_arrive_expect_tx(bar(BAR_X_FULL), 2 * kChunkBytes);
-        tma_load_2d_pair(smem_base + kOffX, &map_x, bar(BAR_X_FULL), 0, row0);
-        if (rank == 0) mbar_arrive_expect_tx(bar(BAR_Z_FULL), 2 * 8 * kChunkBytes);
-        for (int c = 0; c < 8; ++c)
-          tma_load_2d_pair(smem_base + kOffZ + c * kChunkBytes, &map_z, bar(BAR_Z_FULL), c * 64, row0);
+        const int row0 = tile * kTileRows + (int)rank * kRows;
+        tma_prefetch_2d(&map_x, 0, row0);
+        for (int c = 0; c < 8; ++c) tma_prefetch_2d(&map_z, c * 64, row0);
       }
       __syncwarp();
     };
-    uint32_t ti = 0;
-    if (full_front && cluster_id < p.n_tiles) load_xz(cluster_id, 0);
 #pragma unroll 1
-    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters, ++ti) {
+    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters) {
+      const int row0 = tile * kTileRows + (int)rank * kRows;
       if (full_front) {
-        load_w(L_IN, 0, 0);
-        load_w(L_IN, 1, 0);
-        load_gemm(L_Z0);
+        if (tile + n_clusters < p.n_tiles) prefetch_l2(tile + n_clusters);
+        load_a(&map_x, 0, row0);
+        load_w(L_IN, 0, 0, 1);
+        load_w(L_IN, 1, 0, 1);
+        load_lin_z(L_Z0, row0);
       }
 #pragma unroll 1
       for (int b = p.first_block; b < p.last_block; ++b) {
-        load_gemm(L_FC + 2 * b);
-        if (b < 2) load_gemm(L_Z0 + b + 1);
-        load_gemm(L_FC + 2 * b + 1);
-        // next tile's X/Z: their buffers were released after lin_in / lin_z[2] of this tile
-        if (b == 1 && full_front && tile + n_clusters < p.n_tiles) load_xz(tile + n_clusters, ti + 1);
+        load_fc(L_FC + 2 * b);
+        if (b < 2) load_lin_z(L_Z0 + b + 1, row0);
+        load_fc(L_FC + 2 * b + 1);
       }
       if (has_head) {
 #pragma unroll 1
-        for (int kc = 0; kc < 8; ++kc) load_w(L_OUT, 0, kc);
+        for (int kp = 0; kp < 4; ++kp) load_w(L_OUT, 0, 2 * kp, 2);
       }
     }
   } else if (warp == 1 && rank == 0) {
     // =============================== MMA issuer (leader CTA) ================================
     // Warp-uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit.
-    uint32_t stage = 0, phase = 0, gen = 0, ti = 0;
+    uint32_t ws = 0, wph = 0, as = 0, aph = 0, gen = 0;
     const uint32_t w0 = smem_base + kOffW;
     // descriptor = constant high word | (address >> 4): only the low word changes per MMA
     const uint64_t desc_hi = smem_desc_k128(0);
-    auto item = [&](uint32_t a_addr, uint32_t d_col, bool clear, int ksteps) {
-      wait_bar<false>(bar(BAR_W_FULL + stage), phase, p.err, 0x200 + stage);
+    // One weight stage: nk K=16 steps; A steps [0,4) come from a0, [4,8) from a1 (64-wide chunks).
+    auto item = [&](uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, int nk) {
+      wait_bar<false>(bar(BAR_W_FULL + ws), wph, p.err, 0x200 + ws);
       tc_fence_after();
       if (elect_one()) {
-        const uint32_t a_lo = a_addr >> 4, b_lo = (w0 + stage * kWStageBytes) >> 4;
+        const uint32_t b_lo = (w0 + ws * kWStageBytes) >> 4;
+        const uint32_t a0_lo = a0 >> 4, a1_lo = a1 >> 4;
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (j < ksteps)
-            umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)(a_lo + 2 * j), desc_hi | (uint64_t)(b_lo + 2 * j),
-                          kIdesc, (clear && j == 0) ? 0u : 1u);
-        umma_commit_pair(bar(BAR_W_EMPTY + stage), 3);
+        for (int j = 0; j < 8; ++j)
+          if (j < nk) {
+            const uint32_t a_lo = (j < 4 ? a0_lo : a1_lo) + 2 * (j & 3);
+            const uint32_t bj = b_lo + (j < 4 ? 0 : (kWBoxBytes >> 4)) + 2 * (j & 3);
+            umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)a_lo, desc_hi | (uint64_t)bj, kIdesc,
+                          (clear && j == 0) ? 0u : 1u);
+          }
+        umma_commit_pair(bar(BAR_W_EMPTY + ws), 3);
       }
       __syncwarp();
-      if (++stage == kStages) { stage = 0; phase ^= 1; }
+      if (++ws == kStages) { ws = 0; wph ^= 1; }
     };
     auto commit = [&](int b) {
       if (elect_one()) umma_commit_pair(bar(b), 3);
@@ -242,50 +266,69 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     };
     auto wait_act = [&](int c0) {
 #pragma unroll 1
-      for (int c = c0; c < c0 + 4; ++c) wait_bar<true>(bar(BAR_ACT + c), gen & 1, p.err, 0x210 + c);
+      for (int c = c0; c < c0 + 4; ++c) wait_bar<false>(bar(BAR_ACT + c), gen & 1, p.err, 0x210 + c);
       tc_fence_after();
     };
-    // One 512x512 GEMM: A = 8 K-chunks at a_base, D = 2 blocks at d_col.
-    auto gemm = [&](uint32_t a_base, uint32_t d_col, bool clear, bool from_act, int commit_region) {
+    // operand-chunk ring: wait for the next slot, return its address
+    auto take_a = [&]() {
+      wait_bar<false>(bar(BAR_A_FULL + as), aph, p.err, 0x220 + as);
+      const uint32_t addr = smem_base + kOffA + as * kChunkBytes;
+      if (++as == kASlots) { as = 0; aph ^= 1; }
+      return addr;
+    };
+    auto release_a = [&](uint32_t addr) { commit(BAR_A_EMPTY + (int)((addr - (smem_base + kOffA)) / kChunkBytes)); };
+    const uint32_t act = smem_base + kOffAct;
+    // 512x512 GEMM from the ACT operand, quarter order (see header), D = 2 blocks at d_col.
+    auto gemm_act = [&](uint32_t d_col, bool clear, int commit_region) {
 #pragma unroll 1
       for (int q = 0; q < 4; ++q) {
         const int nb = q & 1, kg = q >> 1;
-        if (from_act && nb == 0) wait_act(kg * 4);
+        if (nb == 0) wait_act(kg * 4);
 #pragma unroll 1
-        for (int kk = 0; kk < 4; ++kk)
-          item(a_base + (kg * 4 + kk) * kChunkBytes, d_col + nb * 128, clear && kg == 0 && kk == 0, 4);
-        if (kg == 1 && commit_region >= 0) commit(BAR_ACC + commit_region * 2 + nb);
+        for (int h = 0; h < 2; ++h) {
+          const uint32_t a = act + (kg * 4 + h * 2) * kChunkBytes;
+          item(a, a + kChunkBytes, d_col + nb * 128, clear && kg == 0 && h == 0, 8);
+        }
+        if (kg == 1) commit(BAR_ACC + commit_region * 2 + nb);
       }
-      if (from_act) ++gen;
+      ++gen;
     };
-    const uint32_t act = smem_base + kOffAct, zb = smem_base + kOffZ, xb = smem_base + kOffX;
+    // h += lin_z(z): z streams through the operand ring, K-outer
+    auto gemm_z = [&](bool completes_h) {
 #pragma unroll 1
-    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters, ++ti) {
-      if (full_front) {
-        wait_bar<false>(bar(BAR_X_FULL), ti & 1, p.err, 0x220);
-        wait_bar<false>(bar(BAR_Z_FULL), ti & 1, p.err, 0x221);
+      for (int kp = 0; kp < 4; ++kp) {
+        const uint32_t a0 = take_a(), a1 = take_a();
         tc_fence_after();
-        item(xb, kColH, true, 3);          // lin_in: K = 48 of the zero-padded 64
-        item(xb, kColH + 128, true, 3);
-        commit(BAR_X_EMPTY);
-        gemm(zb, kColH, false, false, 0);  // lin_z[0] completes h_0
+        item(a0, a1, kColH, false, 8);
+        item(a0, a1, kColH + 128, false, 8);
+        release_a(a0);
+        release_a(a1);
+      }
+      if (completes_h) { commit(BAR_ACC + 0); commit(BAR_ACC + 1); }
+    };
+#pragma unroll 1
+    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters) {
+      if (full_front) {
+        const uint32_t xa = take_a();
+        tc_fence_after();
+        item(xa, xa, kColH, true, 3);          // lin_in: K = 48 of the zero-padded 64
+        item(xa, xa, kColH + 128, true, 3);
+        release_a(xa);
+        gemm_z(true);                          // lin_z[0] completes h_0
       }
 #pragma unroll 1
       for (int b = p.first_block; b < p.last_block; ++b) {
-        gemm(act, kColT, true, true, 1);   // t = fc_0(relu(h))
-        if (b < 2) {
-          gemm(zb, kColH, false, false, -1);  // h += lin_z[b+1](z), overlaps the epilogue of t
-          if (b == 1) commit(BAR_Z_EMPTY);
-        }
-        gemm(act, kColH, false, true, 0);  // h += fc_1(relu(t))
+        gemm_act(kColT, true, 1);              // t = fc_0(relu(h))
+        if (b < 2) gemm_z(false);              // h += lin_z[b+1](z), overlaps the epilogue of t
+        gemm_act(kColH, false, 0);             // h += fc_1(relu(t))
       }
       if (has_head) {
         wait_act(0);
-#pragma unroll 1
-        for (int kc = 0; kc < 4; ++kc) item(act + kc * kChunkBytes, kColT, kc == 0, 4);
+        item(act, act + kChunkBytes, kColT, true, 8);
+        item(act + 2 * kChunkBytes, act + 3 * kChunkBytes, kColT, false, 8);
         wait_act(4);
-#pragma unroll 1
-        for (int kc = 4; kc < 8; ++kc) item(act + kc * kChunkBytes, kColT, false, 4);
+        item(act + 4 * kChunkBytes, act + 5 * kChunkBytes, kColT, false, 8);
+        item(act + 6 * kChunkBytes, act + 7 * kChunkBytes, kColT, false, 8);
         commit(BAR_ACC + 2);
         ++gen;
       } else {
