@@ -104,6 +104,14 @@ PN_API int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc, in
                       int64_t points_per_object, void* feat_z, void* feat_x, int ldx, int out_dtype,
                       pn_stream_t stream);
 
+/* Backward of the latent gather (grid_sample backward w.r.t. its input, encoder.py:102-108):
+ * g_latent_nhwc (V,Hl,Wl,512) fp32 += scatter of g_feat_z (N,512) with the bilinear weights.
+ * Same point addressing as pn_point_features.  The caller zeroes g_latent_nhwc first and hands
+ * its NCHW view to torch autograd for the ResNet encoder. */
+PN_API int pn_point_features_bwd(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
+                          const float* xyz, int64_t points_per_object, const float* g_feat_z,
+                          float* g_latent_nhwc, pn_stream_t stream);
+
 /* ---- (3) ResnetFC ---------------------------------------------------------------------- */
 
 typedef struct pn_mlp_weights {
@@ -126,6 +134,33 @@ PN_API int pn_mlp_forward_fp32(const pn_mlp_weights_t* w, const float* feat_z, c
                         int n_objects, int n_views, int64_t points_per_object,
                         float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                         pn_stream_t stream);
+
+/* ---- (3b) ResnetFC training: forward keeping activations + hand-written backward ----------
+ * (autograd of src/model/resnetfc.py:132-184 and the head src/model/models.py:257-266; driven by
+ * loss.backward() in train/train.py:271-281).  fp32 on CUDA cores. */
+typedef struct pn_mlp_grads {
+  float* lin_in_w;  float* lin_in_b;
+  float* fc0_w[PN_N_BLOCKS]; float* fc0_b[PN_N_BLOCKS];
+  float* fc1_w[PN_N_BLOCKS]; float* fc1_b[PN_N_BLOCKS];
+  float* lin_z_w[PN_COMBINE_LAYER]; float* lin_z_b[PN_COMBINE_LAYER];
+  float* lin_out_w; float* lin_out_b;
+} pn_mlp_grads_t;
+
+PN_API size_t pn_mlp_train_acts_bytes(int64_t n_rows);
+/* Same arithmetic as pn_mlp_forward_fp32; `acts` (pn_mlp_train_acts_bytes) receives the 11
+ * activation tensors the backward needs. */
+PN_API int pn_mlp_forward_fp32_train(const pn_mlp_weights_t* w, const float* feat_z, const float* feat_x, int ldx,
+                              int n_objects, int n_views, int64_t points_per_object,
+                              float* out, float* pre_act, void* acts, size_t acts_bytes, pn_stream_t stream);
+PN_API size_t pn_mlp_backward_workspace_bytes(int64_t n_rows);
+/* g_out (P,4) = dL/d[rgb, sigma] (the model outputs `out`).  Weight and bias gradients are
+ * ACCUMULATED (+=) into `grads` (same shapes as the weights); wt holds the transposed fc_0 / fc_1 /
+ * lin_z matrices ([in][out] row-major) for the data-gradient GEMMs.  If g_feat_z (N,512) is not NULL
+ * it receives dL/d feat_z (the latent rows), for pn_point_features_bwd. */
+PN_API int pn_mlp_backward_fp32(const pn_mlp_weights_t* w, const pn_mlp_weights_t* wt, const float* feat_z,
+                         const float* feat_x, int ldx, int n_objects, int n_views, int64_t points_per_object,
+                         const void* acts, const float* out, const float* g_out, const pn_mlp_grads_t* grads,
+                         float* g_feat_z, void* workspace, size_t workspace_bytes, pn_stream_t stream);
 
 /* Tensor-core ResnetFC (tcgen05 / TMEM / TMA chain kernel, csrc/pn_mlp_tc.cu): fp16 GEMM
  * operands, fp32 accumulation and an fp32 residual stream held in tensor memory.

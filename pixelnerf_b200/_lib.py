@@ -35,6 +35,10 @@ class MlpWeights(C.Structure):
                 ("lin_out_w", _vp), ("lin_out_b", _vp)]
 
 
+class MlpGrads(C.Structure):
+    _fields_ = MlpWeights._fields_
+
+
 _SIGNATURES = {
     "pn_version": (_int, []),
     "pn_last_error": (C.c_char_p, []),
@@ -47,6 +51,13 @@ _SIGNATURES = {
     "pn_mlp_fp32_workspace_bytes": (_sz, [_i64]),
     "pn_mlp_forward_fp32": (_int, [C.POINTER(MlpWeights), _vp, _vp, _int, _int, _int, _i64, _vp, _vp, _vp,
                                    _sz, _vp]),
+    "pn_point_features_bwd": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _i64, _vp, _vp, _vp]),
+    "pn_mlp_train_acts_bytes": (_sz, [_i64]),
+    "pn_mlp_forward_fp32_train": (_int, [C.POINTER(MlpWeights), _vp, _vp, _int, _int, _int, _i64, _vp, _vp, _vp,
+                                         _sz, _vp]),
+    "pn_mlp_backward_workspace_bytes": (_sz, [_i64]),
+    "pn_mlp_backward_fp32": (_int, [C.POINTER(MlpWeights), C.POINTER(MlpWeights), _vp, _vp, _int, _int, _int, _i64,
+                                    _vp, _vp, _vp, C.POINTER(MlpGrads), _vp, _vp, _sz, _vp]),
     "pn_mlp_tc_packed_bytes": (_sz, []),
     "pn_prepare_weights": (_int, [C.POINTER(MlpWeights), _vp, _sz, _vp]),
     "pn_mlp_tc_workspace_bytes": (_sz, [_i64, _int]),
@@ -217,6 +228,71 @@ def mlp_forward_fp32(packed, feat_z, feat_x, n_objects, n_views, ppo, want_pre=F
                                          n_views, ppo, _ptr(out), _ptr(pre), ws.data_ptr(), nbytes, _stream()),
                "pn_mlp_forward_fp32")
     return (out, pre) if want_pre else out
+
+
+_WEIGHT_NAMES = (["lin_in.weight", "lin_in.bias"]
+                 + [f"blocks.{b}.fc_{i}.{k}" for b in range(N_BLOCKS) for i in (0, 1) for k in ("weight", "bias")]
+                 + [f"lin_z.{b}.{k}" for b in range(COMBINE_LAYER) for k in ("weight", "bias")]
+                 + ["lin_out.weight", "lin_out.bias"])
+
+
+def weight_names():
+    """Un-prefixed ResnetFC state_dict names, the order used for flat parameter / gradient lists."""
+    return list(_WEIGHT_NAMES)
+
+
+def _fill_struct(s, t):
+    s.lin_in_w, s.lin_in_b = _ptr(t["lin_in.weight"]), _ptr(t["lin_in.bias"])
+    for b in range(N_BLOCKS):
+        s.fc0_w[b], s.fc0_b[b] = _ptr(t[f"blocks.{b}.fc_0.weight"]), _ptr(t[f"blocks.{b}.fc_0.bias"])
+        s.fc1_w[b], s.fc1_b[b] = _ptr(t[f"blocks.{b}.fc_1.weight"]), _ptr(t[f"blocks.{b}.fc_1.bias"])
+    for b in range(COMBINE_LAYER):
+        s.lin_z_w[b], s.lin_z_b[b] = _ptr(t[f"lin_z.{b}.weight"]), _ptr(t[f"lin_z.{b}.bias"])
+    s.lin_out_w, s.lin_out_b = _ptr(t["lin_out.weight"]), _ptr(t["lin_out.bias"])
+    return s
+
+
+def mlp_forward_fp32_train(packed, feat_z, feat_x, n_objects, n_views, ppo):
+    """fp32 forward that keeps the activations: returns (out (P,4), acts buffer)."""
+    s, _keep = packed
+    n_rows = n_objects * n_views * ppo
+    dev = feat_z.device
+    out = torch.empty(n_objects * ppo, 4, device=dev, dtype=torch.float32)
+    nbytes = lib().pn_mlp_train_acts_bytes(n_rows)
+    acts = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    _check(lib().pn_mlp_forward_fp32_train(C.byref(s), _ptr(feat_z), _ptr(feat_x), feat_x.shape[1], n_objects, n_views,
+                                           ppo, _ptr(out), None, acts.data_ptr(), nbytes, _stream()),
+           "pn_mlp_forward_fp32_train")
+    return out, acts
+
+
+def mlp_backward_fp32(packed, weights, feat_z, feat_x, n_objects, n_views, ppo, acts, out, g_out, grads,
+                      want_g_feat_z):
+    """weights / grads: dicts keyed by weight_names(); grads are accumulated into (+=)."""
+    s, _keep = packed
+    wt = {k: (v.detach().t().contiguous() if v.dim() == 2 and v.shape[0] == v.shape[1] else v.detach().contiguous())
+          for k, v in weights.items()}
+    st = _fill_struct(MlpWeights(), wt)
+    sg = _fill_struct(MlpGrads(), grads)
+    n_rows = n_objects * n_views * ppo
+    dev = feat_z.device
+    g_fz = torch.empty(n_rows, D_LATENT, device=dev, dtype=torch.float32) if want_g_feat_z else None
+    nbytes = lib().pn_mlp_backward_workspace_bytes(n_rows)
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    _check(lib().pn_mlp_backward_fp32(C.byref(s), C.byref(st), _ptr(feat_z), _ptr(feat_x), feat_x.shape[1], n_objects,
+                                      n_views, ppo, acts.data_ptr(), _ptr(out), _ptr(_f32c(g_out)), C.byref(sg),
+                                      _ptr(g_fz), ws.data_ptr(), nbytes, _stream()), "pn_mlp_backward_fp32")
+    return g_fz
+
+
+def point_features_bwd(cam_bufs, g_latent_nhwc, ppo, g_feat_z, *, rays=None, z=None, xyz=None):
+    v, hl, wl, _ = g_latent_nhwc.shape
+    cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
+                 cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
+    rays, z, xyz = _f32c(rays), _f32c(z), _f32c(xyz)
+    k = 0 if z is None else z.shape[-1]
+    _check(lib().pn_point_features_bwd(C.byref(cam), _ptr(rays), _ptr(z), k, _ptr(xyz), ppo, _ptr(g_feat_z),
+                                       _ptr(g_latent_nhwc), _stream()), "pn_point_features_bwd")
 
 
 def pack_weights_tc(w, precision="fp16"):

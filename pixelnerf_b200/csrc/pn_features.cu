@@ -153,7 +153,85 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
   }
 }
 
+// Backward of the bilinear gather w.r.t. the latent (encoder.py:102-108 = grid_sample backward for
+// its input): g_latent[view, tap] += w_tap * g_feat_z[row].  One warp per row, 16-byte vector
+// atomics (red.global.add.v4.f32) on the channels-last fp32 gradient map.  Sample positions carry
+// no gradient here ("detached sample positions").
+__global__ void __launch_bounds__(kFeatWarps * 32)
+point_features_bwd_kernel(pn_camera_t cam, const float* __restrict__ rays, const float* __restrict__ zs,
+                          int n_samples, const float* __restrict__ xyz_in, int64_t ppo,
+                          const float* __restrict__ g_feat_z, float* __restrict__ g_latent, int64_t n_rows) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5);
+  if (row >= n_rows) return;
+  const int64_t ov = row / ppo;
+  const int64_t p = row - ov * ppo;
+  const int view = (int)ov;
+  const int obj = view / cam.n_views;
+  float x, y, z;
+  if (rays) {
+    const int64_t ray = obj * (ppo / n_samples) + p / n_samples;
+    const float* rr = rays + ray * 8;
+    const float zz = zs[ray * n_samples + (p % n_samples)];
+    x = __fadd_rn(rr[0], __fmul_rn(zz, rr[3]));
+    y = __fadd_rn(rr[1], __fmul_rn(zz, rr[4]));
+    z = __fadd_rn(rr[2], __fmul_rn(zz, rr[5]));
+  } else {
+    const float* pp = xyz_in + ((int64_t)obj * ppo + p) * 3;
+    x = pp[0]; y = pp[1]; z = pp[2];
+  }
+  const float* P = cam.poses + (size_t)view * 12;
+  const float xc = P[0] * x + P[1] * y + P[2] * z + P[3];
+  const float yc = P[4] * x + P[5] * y + P[6] * z + P[7];
+  const float zc = P[8] * x + P[9] * y + P[10] * z + P[11];
+  const float u = (-xc / zc) * cam.focal[view * 2 + 0] + cam.c[view * 2 + 0];
+  const float v = (-yc / zc) * cam.focal[view * 2 + 1] + cam.c[view * 2 + 1];
+  const float gx = u * cam.scale_x - 1.0f, gy = v * cam.scale_y - 1.0f;
+  float ix = ((gx + 1.0f) * 0.5f) * (float)(cam.wl - 1);
+  float iy = ((gy + 1.0f) * 0.5f) * (float)(cam.hl - 1);
+  ix = fminf(fmaxf(ix, 0.0f), (float)(cam.wl - 1));
+  iy = fminf(fmaxf(iy, 0.0f), (float)(cam.hl - 1));
+  const float fx0 = floorf(ix), fy0 = floorf(iy);
+  const int x0 = (int)fx0, y0 = (int)fy0;
+  const int x1 = min(x0 + 1, cam.wl - 1), y1 = min(y0 + 1, cam.hl - 1);
+  const float ax = ix - fx0, ay = iy - fy0;
+  const float w00 = (1.0f - ax) * (1.0f - ay), w01 = ax * (1.0f - ay);
+  const float w10 = (1.0f - ax) * ay, w11 = ax * ay;
+  float* base = g_latent + (size_t)view * cam.hl * cam.wl * PN_D_LATENT;
+  float* p00 = base + ((size_t)y0 * cam.wl + x0) * PN_D_LATENT;
+  float* p01 = base + ((size_t)y0 * cam.wl + x1) * PN_D_LATENT;
+  float* p10 = base + ((size_t)y1 * cam.wl + x0) * PN_D_LATENT;
+  float* p11 = base + ((size_t)y1 * cam.wl + x1) * PN_D_LATENT;
+  const float* g = g_feat_z + (size_t)row * PN_D_LATENT;
+#pragma unroll
+  for (int i = 0; i < PN_D_LATENT / 128; ++i) {
+    const int ch = i * 128 + lane * 4;
+    const float4 gv = *reinterpret_cast<const float4*>(g + ch);
+    atomicAdd(reinterpret_cast<float4*>(p00 + ch), make_float4(gv.x * w00, gv.y * w00, gv.z * w00, gv.w * w00));
+    if (w01 != 0.0f) atomicAdd(reinterpret_cast<float4*>(p01 + ch), make_float4(gv.x * w01, gv.y * w01, gv.z * w01, gv.w * w01));
+    if (w10 != 0.0f) atomicAdd(reinterpret_cast<float4*>(p10 + ch), make_float4(gv.x * w10, gv.y * w10, gv.z * w10, gv.w * w10));
+    if (w11 != 0.0f) atomicAdd(reinterpret_cast<float4*>(p11 + ch), make_float4(gv.x * w11, gv.y * w11, gv.z * w11, gv.w * w11));
+  }
+}
+
 }  // namespace pn
+
+extern "C" int pn_point_features_bwd(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
+                                     const float* xyz, int64_t points_per_object, const float* g_feat_z,
+                                     float* g_latent_nhwc, pn_stream_t stream) {
+  PN_CHECK_ARG(cam && g_feat_z && g_latent_nhwc, "pn_point_features_bwd: null pointer");
+  PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_features_bwd: camera buffers missing");
+  PN_CHECK_ARG((rays && z && n_samples > 0) || xyz, "pn_point_features_bwd: need rays+z or xyz");
+  PN_CHECK_ARG(!rays || points_per_object % n_samples == 0, "pn_point_features_bwd: P must be a multiple of K");
+  const int64_t n_rows = (int64_t)cam->n_objects * cam->n_views * points_per_object;
+  if (n_rows == 0) return PN_OK;
+  pn::point_features_bwd_kernel<<<pn::ceil_div(n_rows, pn::kFeatWarps), pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+      *cam, rays, z, n_samples, xyz, points_per_object, g_feat_z, g_latent_nhwc, n_rows);
+  PN_LAUNCH_OK("point_features_bwd_kernel");
+  pn::count_launch();
+  return PN_OK;
+}
+
 
 extern "C" int pn_prepare_latent(const float* latent_nchw, void* latent_nhwc, int n_maps, int channels,
                                  int hl, int wl, int dtype, pn_stream_t stream) {

@@ -26,10 +26,13 @@ __device__ __forceinline__ float4 load4(const float* p, int remain) {
   return v;
 }
 
+// C[M,512] = [resid +] [mask > 0 ?] (act(A)[M,K] * W[512,K]^T [+ bias]).  resid may alias C (in-place
+// accumulate); mask zeroes the product where mask[m,n] <= 0 (relu backward).
 template <bool kReluA, bool kAccum>
 __global__ void __launch_bounds__(kGemmThreads)
 linear512_kernel(const float* __restrict__ A, int lda, const float* __restrict__ W, int ldw,
-                 const float* __restrict__ bias, float* __restrict__ C, int64_t M, int K) {
+                 const float* __restrict__ bias, float* C, int64_t M, int K,
+                 const float* resid = nullptr, const float* __restrict__ mask = nullptr) {
   __shared__ __align__(16) float As[2][BK][BM + 4];
   __shared__ __align__(16) float Ws[2][BK][BN + 4];
   const int tid = threadIdx.x;
@@ -105,11 +108,18 @@ linear512_kernel(const float* __restrict__ A, int lda, const float* __restrict__
     for (int jh = 0; jh < 2; ++jh) {
       const int gn = n0 + jh * 64 + tx * 4;
       float4 o = make_float4(acc[i][jh * 4 + 0], acc[i][jh * 4 + 1], acc[i][jh * 4 + 2], acc[i][jh * 4 + 3]);
-      const float4 bv = *reinterpret_cast<const float4*>(bias + gn);
-      o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+      if (bias) {
+        const float4 bv = *reinterpret_cast<const float4*>(bias + gn);
+        o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+      }
+      if (mask) {
+        const float4 mv = *reinterpret_cast<const float4*>(mask + gm * PN_D_HIDDEN + gn);
+        o.x = mv.x > 0.f ? o.x : 0.f; o.y = mv.y > 0.f ? o.y : 0.f;
+        o.z = mv.z > 0.f ? o.z : 0.f; o.w = mv.w > 0.f ? o.w : 0.f;
+      }
       float* dst = C + gm * PN_D_HIDDEN + gn;
       if (kAccum) {
-        const float4 c = *reinterpret_cast<const float4*>(dst);
+        const float4 c = *reinterpret_cast<const float4*>((resid ? resid : C) + gm * PN_D_HIDDEN + gn);
         o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
       }
       *reinterpret_cast<float4*>(dst) = o;
@@ -171,11 +181,202 @@ head_kernel(const float* __restrict__ h, const float* __restrict__ w, const floa
 }
 
 template <bool kReluA, bool kAccum>
-static int launch_linear(const float* A, int lda, const float* W, int ldw, const float* bias, float* C,
-                         int64_t M, int K, cudaStream_t st) {
+int launch_linear(const float* A, int lda, const float* W, int ldw, const float* bias, float* C,
+                  int64_t M, int K, cudaStream_t st, const float* resid = nullptr, const float* mask = nullptr) {
   dim3 grid(ceil_div(M, BM), PN_D_HIDDEN / BN);
-  linear512_kernel<kReluA, kAccum><<<grid, kGemmThreads, 0, st>>>(A, lda, W, ldw, bias, C, M, K);
+  linear512_kernel<kReluA, kAccum><<<grid, kGemmThreads, 0, st>>>(A, lda, W, ldw, bias, C, M, K, resid, mask);
   PN_LAUNCH_OK("linear512_kernel");
+  count_launch();
+  return PN_OK;
+}
+
+
+// ---- backward kernels (training; reference: autograd of resnetfc.py:132-184) -----------------
+
+// dW[512, Ki] += G[M,512]^T * act(A)[M, Ki]   (split over row ranges, fp32 atomics)
+// Both operands are row-major with the reduction index m slowest, so tiles load coalesced with
+// no transpose: Gs[m][o], As[m][i].
+constexpr int WK = 16;
+template <bool kReluA>
+__global__ void __launch_bounds__(kGemmThreads)
+wgrad512_kernel(const float* __restrict__ G, const float* __restrict__ A, int lda, int ki,
+                float* __restrict__ dW, int ldw, int64_t M, int64_t rows_per_split) {
+  __shared__ __align__(16) float Gs[2][WK][BM + 4];
+  __shared__ __align__(16) float As[2][WK][BN + 4];
+  const int tid = threadIdx.x;
+  const int o0 = blockIdx.x * BM, i0 = blockIdx.y * BN;
+  const int64_t m_begin = (int64_t)blockIdx.z * rows_per_split;
+  const int64_t m_end = m_begin + rows_per_split < M ? m_begin + rows_per_split : M;
+  if (m_begin >= m_end) return;
+  const int lm = tid >> 5;          // 0..7 (+8): row of the 16-row slab
+  const int lc = (tid & 31) * 4;    // column within the 128-wide tile
+  const int tx = tid & 15, ty = tid >> 4;
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.0f;
+  float4 rg[2], ra[2];
+  auto load_tiles = [&](int64_t m0) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int64_t m = m0 + lm + h * 8;
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f), a = g;
+      if (m < m_end) {
+        g = *reinterpret_cast<const float4*>(G + m * PN_D_HIDDEN + o0 + lc);
+        a = load4(A + m * lda + i0 + lc, ki - (i0 + lc));
+        if (kReluA) { a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f); }
+      }
+      rg[h] = g; ra[h] = a;
+    }
+  };
+  auto store_tiles = [&](int buf) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      *reinterpret_cast<float4*>(&Gs[buf][lm + h * 8][lc]) = rg[h];
+      *reinterpret_cast<float4*>(&As[buf][lm + h * 8][lc]) = ra[h];
+    }
+  };
+  const int nk = (int)((m_end - m_begin + WK - 1) / WK);
+  load_tiles(m_begin);
+  store_tiles(0);
+  __syncthreads();
+  for (int kt = 0; kt < nk; ++kt) {
+    const int buf = kt & 1;
+    if (kt + 1 < nk) load_tiles(m_begin + (int64_t)(kt + 1) * WK);
+#pragma unroll
+    for (int kk = 0; kk < WK; ++kk) {
+      float a[TM], b[TN];
+      const float4 a0 = *reinterpret_cast<const float4*>(&Gs[buf][kk][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&Gs[buf][kk][64 + ty * 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&As[buf][kk][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&As[buf][kk][64 + tx * 4]);
+      a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+      b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (kt + 1 < nk) store_tiles(buf ^ 1);
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int o = o0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int c = i0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+      if (c < ki) atomicAdd(dW + (size_t)o * ldw + c, acc[i][j]);
+    }
+  }
+}
+
+// db[512] += column sums of G[M,512]
+__global__ void __launch_bounds__(256)
+colsum512_kernel(const float* __restrict__ G, float* __restrict__ db, int64_t M, int64_t rows_per_block) {
+  const int64_t m0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t m1 = m0 + rows_per_block < M ? m0 + rows_per_block : M;
+  float s0 = 0.f, s1 = 0.f;
+  for (int64_t m = m0; m < m1; ++m) {
+    s0 += G[m * PN_D_HIDDEN + threadIdx.x];
+    s1 += G[m * PN_D_HIDDEN + 256 + threadIdx.x];
+  }
+  atomicAdd(db + threadIdx.x, s0);
+  atomicAdd(db + 256 + threadIdx.x, s1);
+}
+
+// Head + lin_out backward.  out = [sigmoid(pre_rgb), relu(pre_sigma)]; g_out = dL/d out (P,4).
+//   g_pre = [c(1-c) g_c, [pre_sigma > 0] g_sigma]
+//   g_h[p,:] = [h5 > 0] * (g_pre[p] . W_out)          dW_out += g_pre^T relu(h5), db_out += sum g_pre
+// One warp per row; weight-gradient partials are reduced per block in shared memory first.
+__global__ void __launch_bounds__(256)
+head_bwd_kernel(const float* __restrict__ h5, const float4* __restrict__ out, const float4* __restrict__ g_out,
+                const float* __restrict__ w_out, float* __restrict__ g_h, float* __restrict__ dw_out,
+                float* __restrict__ db_out, int64_t rows, int rows_per_block) {
+  __shared__ float sdw[4][PN_D_HIDDEN];
+  __shared__ float sdb[4];
+  for (int i = threadIdx.x; i < 4 * PN_D_HIDDEN; i += 256) (&sdw[0][0])[i] = 0.0f;
+  if (threadIdx.x < 4) sdb[threadIdx.x] = 0.0f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  float4 wv[4][4];  // this lane's 16 columns (4 chunks of 4) of the 4 weight rows
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) wv[k][i] = __ldg(reinterpret_cast<const float4*>(w_out + k * PN_D_HIDDEN + i * 128 + lane * 4));
+  float dwl[4][16];
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int j = 0; j < 16; ++j) dwl[k][j] = 0.0f;
+  float dbl[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int64_t r = r0 + warp; r < r0 + rows_per_block && r < rows; r += 8) {
+    const float4 o = out[r], go = g_out[r];
+    const float gp[4] = {o.x * (1.0f - o.x) * go.x, o.y * (1.0f - o.y) * go.y, o.z * (1.0f - o.z) * go.z,
+                         o.w > 0.0f ? go.w : 0.0f};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) dbl[k] += gp[k];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = i * 128 + lane * 4;
+      const float4 hv = *reinterpret_cast<const float4*>(h5 + r * PN_D_HIDDEN + c);
+      const float hh[4] = {hv.x, hv.y, hv.z, hv.w};
+      float gh[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float w0 = (&wv[0][i].x)[e], w1 = (&wv[1][i].x)[e], w2 = (&wv[2][i].x)[e], w3 = (&wv[3][i].x)[e];
+        const float g = gp[0] * w0 + gp[1] * w1 + gp[2] * w2 + gp[3] * w3;
+        const bool on = hh[e] > 0.0f;
+        gh[e] = on ? g : 0.0f;
+        const float a = on ? hh[e] : 0.0f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) dwl[k][i * 4 + e] += gp[k] * a;
+      }
+      *reinterpret_cast<float4*>(g_h + r * PN_D_HIDDEN + c) = make_float4(gh[0], gh[1], gh[2], gh[3]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int j = 0; j < 16; ++j) atomicAdd(&sdw[k][(j >> 2) * 128 + lane * 4 + (j & 3)], dwl[k][j]);
+  if (lane == 0)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) atomicAdd(&sdb[k], dbl[k]);
+  __syncthreads();
+  for (int i = threadIdx.x; i < 4 * PN_D_HIDDEN; i += 256) atomicAdd(dw_out + i, (&sdw[0][0])[i]);
+  if (threadIdx.x < 4) atomicAdd(db_out + threadIdx.x, sdb[threadIdx.x]);
+}
+
+// backward of combine_interleaved(average): g (SB,P,512) -> (SB,NS,P,512), each view gets g / NS
+__global__ void __launch_bounds__(256)
+view_mean_bwd_kernel(const float4* __restrict__ g, float4* __restrict__ out, int ns, int64_t ppo4, int64_t total4) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total4) return;
+  const int64_t ov = i / ppo4, rem = i - ov * ppo4;
+  const float4 v = g[(ov / ns) * ppo4 + rem];
+  const float d = (float)ns;
+  out[i] = make_float4(v.x / d, v.y / d, v.z / d, v.w / d);
+}
+
+template <bool kReluA>
+int launch_wgrad(const float* G, const float* A, int lda, int ki, float* dW, int ldw, int64_t M, cudaStream_t st) {
+  int splits = (int)((M + 4095) / 4096);
+  if (splits > 64) splits = 64;
+  if (splits < 1) splits = 1;
+  int64_t rps = (M + splits - 1) / splits;
+  rps = (rps + WK - 1) / WK * WK;
+  dim3 grid(PN_D_HIDDEN / BM, ceil_div(ki, BN), splits);
+  wgrad512_kernel<kReluA><<<grid, kGemmThreads, 0, st>>>(G, A, lda, ki, dW, ldw, M, rps);
+  PN_LAUNCH_OK("wgrad512_kernel");
+  count_launch();
+  return PN_OK;
+}
+static int launch_colsum(const float* G, float* db, int64_t M, cudaStream_t st) {
+  const int64_t rpb = 256;
+  colsum512_kernel<<<ceil_div(M, rpb), 256, 0, st>>>(G, db, M, rpb);
+  PN_LAUNCH_OK("colsum512_kernel");
   count_launch();
   return PN_OK;
 }
@@ -224,5 +425,116 @@ extern "C" int pn_mlp_forward_fp32(const pn_mlp_weights_t* w, const float* feat_
   head_kernel<<<ceil_div(n_pts, 8), 256, 0, st>>>(h, w->lin_out_w, w->lin_out_b, (float4*)out, (float4*)pre_act, n_pts);
   PN_LAUNCH_OK("head_kernel");
   count_launch();
+  return PN_OK;
+}
+
+// ---- training: forward that keeps every activation, and the hand-written backward ------------
+// Activation slots (each n_rows x 512 fp32): slot 2b = H_b (input of block b: residual stream after
+// lin_z[b] / the view mean), slot 2b+1 = T_b (fc_0 output, pre-relu), slot 10 = H_5 (input of lin_out).
+static inline float* act_slot(void* acts, int64_t n_rows, int i) {
+  return (float*)acts + (size_t)i * n_rows * PN_D_HIDDEN;
+}
+
+extern "C" size_t pn_mlp_train_acts_bytes(int64_t n_rows) {
+  return (size_t)(n_rows > 0 ? n_rows : 0) * PN_D_HIDDEN * sizeof(float) * 11 + 256;
+}
+
+extern "C" int pn_mlp_forward_fp32_train(const pn_mlp_weights_t* w, const float* feat_z, const float* feat_x,
+                                         int ldx, int n_objects, int n_views, int64_t points_per_object,
+                                         float* out, float* pre_act, void* acts, size_t acts_bytes,
+                                         pn_stream_t stream) {
+  using namespace pn;
+  PN_CHECK_ARG(w && feat_z && feat_x && out && acts, "pn_mlp_forward_fp32_train: null pointer");
+  PN_CHECK_ARG(n_objects > 0 && n_views > 0 && points_per_object >= 0, "pn_mlp_forward_fp32_train: bad sizes");
+  PN_CHECK_ARG(ldx >= PN_D_CODE && ldx % 4 == 0, "pn_mlp_forward_fp32_train: ldx=%d", ldx);
+  const int64_t n_rows = (int64_t)n_objects * n_views * points_per_object;
+  const int64_t n_pts = (int64_t)n_objects * points_per_object;
+  if (n_rows == 0) return PN_OK;
+  PN_CHECK_ARG(acts_bytes >= pn_mlp_train_acts_bytes(n_rows), "pn_mlp_forward_fp32_train: activation buffer too small");
+  PN_CHECK_ARG(((uintptr_t)acts & 15) == 0, "pn_mlp_forward_fp32_train: activation buffer must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  auto S = [&](int i) { return act_slot(acts, n_rows, i); };
+  if ((rc = launch_linear<false, false>(feat_x, ldx, w->lin_in_w, PN_D_CODE, w->lin_in_b, S(0), n_rows, PN_D_CODE, st))) return rc;
+  if ((rc = launch_linear<false, true>(feat_z, PN_D_LATENT, w->lin_z_w[0], PN_D_LATENT, w->lin_z_b[0], S(0), n_rows, PN_D_LATENT, st))) return rc;
+  int64_t m = n_rows;
+  for (int b = 0; b < PN_N_BLOCKS; ++b) {
+    if ((rc = launch_linear<true, false>(S(2 * b), PN_D_HIDDEN, w->fc0_w[b], PN_D_HIDDEN, w->fc0_b[b], S(2 * b + 1), m, PN_D_HIDDEN, st))) return rc;
+    const bool mean_next = (b + 1 == PN_COMBINE_LAYER) && n_views > 1;
+    float* target = (b + 1 < PN_N_BLOCKS && !mean_next) ? S(2 * b + 2) : S(10);
+    if ((rc = launch_linear<true, true>(S(2 * b + 1), PN_D_HIDDEN, w->fc1_w[b], PN_D_HIDDEN, w->fc1_b[b], target, m, PN_D_HIDDEN, st, S(2 * b)))) return rc;
+    if (mean_next) {  // resnetfc.py:152-172
+      const int64_t ppo4 = points_per_object * (PN_D_HIDDEN / 4), total4 = n_pts * (PN_D_HIDDEN / 4);
+      view_mean_kernel<<<ceil_div(total4, 256), 256, 0, st>>>((const float4*)S(10), (float4*)S(2 * b + 2), n_views, ppo4, total4);
+      PN_LAUNCH_OK("view_mean_kernel");
+      count_launch();
+      m = n_pts;
+    } else if (b + 1 < PN_COMBINE_LAYER) {
+      if ((rc = launch_linear<false, true>(feat_z, PN_D_LATENT, w->lin_z_w[b + 1], PN_D_LATENT, w->lin_z_b[b + 1], target, m, PN_D_LATENT, st))) return rc;
+    }
+  }
+  head_kernel<<<ceil_div(n_pts, 8), 256, 0, st>>>(S(10), w->lin_out_w, w->lin_out_b, (float4*)out, (float4*)pre_act, n_pts);
+  PN_LAUNCH_OK("head_kernel");
+  count_launch();
+  return PN_OK;
+}
+
+extern "C" size_t pn_mlp_backward_workspace_bytes(int64_t n_rows) {
+  return (size_t)(n_rows > 0 ? n_rows : 0) * PN_D_HIDDEN * sizeof(float) * 2 + 256;
+}
+
+extern "C" int pn_mlp_backward_fp32(const pn_mlp_weights_t* w, const pn_mlp_weights_t* wt, const float* feat_z,
+                                    const float* feat_x, int ldx, int n_objects, int n_views,
+                                    int64_t points_per_object, const void* acts, const float* out,
+                                    const float* g_out, const pn_mlp_grads_t* grads, float* g_feat_z,
+                                    void* workspace, size_t workspace_bytes, pn_stream_t stream) {
+  using namespace pn;
+  PN_CHECK_ARG(w && wt && feat_z && feat_x && acts && out && g_out && grads && workspace, "pn_mlp_backward_fp32: null pointer");
+  PN_CHECK_ARG(n_objects > 0 && n_views > 0 && points_per_object >= 0, "pn_mlp_backward_fp32: bad sizes");
+  const int64_t n_rows = (int64_t)n_objects * n_views * points_per_object;
+  const int64_t n_pts = (int64_t)n_objects * points_per_object;
+  if (n_rows == 0) return PN_OK;
+  PN_CHECK_ARG(workspace_bytes >= pn_mlp_backward_workspace_bytes(n_rows), "pn_mlp_backward_fp32: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  auto S = [&](int i) { return (const float*)act_slot(const_cast<void*>(acts), n_rows, i); };
+  float* GA = (float*)workspace;
+  float* GB = GA + (size_t)n_rows * PN_D_HIDDEN;
+  {
+    const int rpb = 64;
+    head_bwd_kernel<<<ceil_div(n_pts, rpb), 256, 0, st>>>(S(10), (const float4*)out, (const float4*)g_out, w->lin_out_w,
+                                                          GA, grads->lin_out_w, grads->lin_out_b, n_pts, rpb);
+    PN_LAUNCH_OK("head_bwd_kernel");
+    count_launch();
+  }
+  int64_t m = n_pts;
+  for (int b = PN_N_BLOCKS - 1; b >= 0; --b) {
+    if (b == PN_COMBINE_LAYER - 1 && n_views > 1) {  // backward of the view mean: every view gets g / NS
+      const int64_t ppo4 = points_per_object * (PN_D_HIDDEN / 4), total4 = n_rows * (PN_D_HIDDEN / 4);
+      view_mean_bwd_kernel<<<ceil_div(total4, 256), 256, 0, st>>>((const float4*)GA, (float4*)GB, n_views, ppo4, total4);
+      PN_LAUNCH_OK("view_mean_bwd_kernel");
+      count_launch();
+      float* tmp = GA; GA = GB; GB = tmp;
+      m = n_rows;
+    }
+    // h_out = H_b + fc_1(relu(T_b)),  T_b = fc_0(relu(H_b))
+    if ((rc = launch_wgrad<true>(GA, S(2 * b + 1), PN_D_HIDDEN, PN_D_HIDDEN, grads->fc1_w[b], PN_D_HIDDEN, m, st))) return rc;
+    if ((rc = launch_colsum(GA, grads->fc1_b[b], m, st))) return rc;
+    if ((rc = launch_linear<false, false>(GA, PN_D_HIDDEN, wt->fc1_w[b], PN_D_HIDDEN, nullptr, GB, m, PN_D_HIDDEN, st, nullptr, S(2 * b + 1)))) return rc;
+    if ((rc = launch_wgrad<true>(GB, S(2 * b), PN_D_HIDDEN, PN_D_HIDDEN, grads->fc0_w[b], PN_D_HIDDEN, m, st))) return rc;
+    if ((rc = launch_colsum(GB, grads->fc0_b[b], m, st))) return rc;
+    if ((rc = launch_linear<false, true>(GB, PN_D_HIDDEN, wt->fc0_w[b], PN_D_HIDDEN, nullptr, GA, m, PN_D_HIDDEN, st, nullptr, S(2 * b)))) return rc;
+    if (b < PN_COMBINE_LAYER) {  // H_b = ... + lin_z[b](z)
+      if ((rc = launch_wgrad<false>(GA, feat_z, PN_D_LATENT, PN_D_LATENT, grads->lin_z_w[b], PN_D_LATENT, m, st))) return rc;
+      if ((rc = launch_colsum(GA, grads->lin_z_b[b], m, st))) return rc;
+      if (g_feat_z) {
+        if (b == PN_COMBINE_LAYER - 1) rc = launch_linear<false, false>(GA, PN_D_HIDDEN, wt->lin_z_w[b], PN_D_HIDDEN, nullptr, g_feat_z, m, PN_D_HIDDEN, st);
+        else rc = launch_linear<false, true>(GA, PN_D_HIDDEN, wt->lin_z_w[b], PN_D_HIDDEN, nullptr, g_feat_z, m, PN_D_HIDDEN, st);
+        if (rc) return rc;
+      }
+    }
+  }
+  if ((rc = launch_wgrad<false>(GA, feat_x, ldx, PN_D_CODE, grads->lin_in_w, PN_D_CODE, m, st))) return rc;
+  if ((rc = launch_colsum(GA, grads->lin_in_b, m, st))) return rc;
   return PN_OK;
 }

@@ -1,0 +1,111 @@
+"""Training path: one torch.autograd.Function around the render kernels.
+
+The reference trains by autograd over its whole torch op graph (train/train.py:264-281:
+``render_par(all_rays, want_weights=True)`` -> MSE on coarse/fine rgb -> ``loss.backward()``).
+Here the forward is the ordinary kernel path and the backward is hand written:
+
+    upstream (g_rgb, g_depth, g_weights) per pass
+      -> pn_composite_bwd                    dL/d(rgb, sigma) per sample
+      -> pn_mlp_backward_fp32                head + 15 linears: weight/bias grads, dL/d feat_z
+      -> pn_point_features_bwd               bilinear scatter-add into the latent gradient
+      -> returned to torch autograd          the ResNet34 encoder's backward stays in torch
+
+Activations are not kept from the forward: the backward re-runs the fp32 forward chunk by chunk
+(pn_mlp_forward_fp32_train keeps the 11 activation tensors of one chunk), so memory is bounded for
+any ray count (config 5's sweep goes to 2^22 rays).
+
+Deviation from the reference, on purpose and documented in DESIGN.md: sample positions are treated
+as constants.  In the reference the 16 depth samples of the fine pass depend differentiably on the
+coarse depth (src/render/nerf.py:150-161, 290-293), a second-order path from the fine loss into the
+coarse MLP; every other sample position is detached there too (``weights.detach()``, :130, :288).
+"""
+import torch
+
+from .. import _lib
+
+
+def _flat_params(model):
+    """(coarse tensors, fine tensors or []) in _lib.weight_names() order."""
+    names = _lib.weight_names()
+    wc = model.mlp_coarse.weight_dict()
+    coarse = [wc[k] for k in names]
+    fine = []
+    if model.mlp_fine is not None:
+        wf = model.mlp_fine.weight_dict()
+        fine = [wf[k] for k in names]
+    return coarse, fine
+
+
+class RenderFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, renderer, model, rays, sb, draws, forced, seed, latent, *params):
+        with torch.no_grad():
+            coarse, fine = renderer._render_all(model, rays, sb, draws, forced, seed)
+        ctx.renderer, ctx.model, ctx.sb = renderer, model, sb
+        ctx.n_params = len(params)
+        ctx.has_fine = fine is not None
+        ctx.latent_shape = latent.shape
+        z_f = fine[3] if fine is not None else coarse[3].new_zeros(0)
+        ctx.save_for_backward(rays, coarse[3], z_f)
+        outs = tuple(coarse) + (tuple(fine) if fine is not None else ())
+        ctx.mark_non_differentiable(coarse[3], *((fine[3],) if fine is not None else ()))
+        return outs
+
+    @staticmethod
+    def backward(ctx, *g):
+        renderer, model, sb = ctx.renderer, ctx.model, ctx.sb
+        rays, z_c, z_f = ctx.saved_tensors
+        names = _lib.weight_names()
+        coarse_p, fine_p = _flat_params(model)
+        dev = rays.device
+        want_latent = ctx.needs_input_grad[7]
+        g_lat = None
+        if want_latent:
+            v, ch, hl, wl = ctx.latent_shape
+            g_lat = torch.zeros(v, hl, wl, ch, device=dev, dtype=torch.float32)
+
+        def zero_grads(ps):
+            return {k: torch.zeros_like(p, dtype=torch.float32) for k, p in zip(names, ps)}
+
+        grads_c = zero_grads(coarse_p)
+        grads_f = zero_grads(fine_p) if fine_p else grads_c
+        _backward_pass(renderer, model, True, rays, z_c, sb, g[0], g[1], g[2], grads_c, g_lat)
+        if ctx.has_fine:
+            _backward_pass(renderer, model, False, rays, z_f, sb, g[4], g[5], g[6], grads_f, g_lat)
+        flat = [grads_c[k] for k in names] + ([grads_f[k] for k in names] if fine_p else [])
+        g_latent = g_lat.permute(0, 3, 1, 2) if want_latent else None
+        return (None, None, None, None, None, None, None, g_latent, *flat)
+
+
+def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, grads, g_lat):
+    r_total, k = z.shape
+    if g_w is None and g_rgb is None and g_depth is None:
+        return
+    b = r_total // sb
+    ns = model.num_views_per_obj
+    cam = model._cam
+    mlp = model.mlp_coarse if coarse or model.mlp_fine is None else model.mlp_fine
+    weights = {n: p.detach() for n, p in mlp.weight_dict().items()}
+    packed = mlp.packed("fp32")
+    latent = model.latent_nhwc(torch.float32)
+    if g_rgb is None:
+        g_rgb = torch.zeros(r_total, 3, device=z.device)
+    chunk = max(1, renderer.max_rows_train // max(1, sb * ns * k))
+
+    def cut(t, s, e):
+        if t is None:
+            return None
+        return t.reshape(sb, b, *t.shape[1:])[:, s:e].reshape(sb * (e - s), *t.shape[1:]).contiguous()
+
+    for s in range(0, b, chunk):
+        e = min(b, s + chunk)
+        rr, zz = cut(rays, s, e), cut(z, s, e)
+        ppo = (e - s) * k
+        fz, fx = _lib.point_features(cam, latent, ppo, rays=rr, z=zz, ldx=44)
+        out, acts = _lib.mlp_forward_fp32_train(packed, fz, fx, sb, ns, ppo)
+        g_rs, _ = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
+                                     cut(g_depth, s, e), cut(g_w, s, e), want_gz=False)
+        g_fz = _lib.mlp_backward_fp32(packed, weights, fz, fx, sb, ns, ppo, acts, out, g_rs.reshape(-1, 4), grads,
+                                      want_g_feat_z=g_lat is not None)
+        if g_lat is not None:
+            _lib.point_features_bwd(cam, g_lat, ppo, g_fz, rays=rr, z=zz)

@@ -66,6 +66,7 @@ class NeRFRenderer(torch.nn.Module):
         self.injected_draws = None
         self.injected_z = None  # teacher forcing: dict(z_coarse=..., z_fine=...)
         self.max_rows_per_launch = 1 << 21
+        self.max_rows_train = 1 << 16  # rows whose 11 fp32 activation tensors are kept at once (1.4 GB)
 
     # ---------------------------------------------------------------- sampling
     @staticmethod
@@ -124,6 +125,33 @@ class NeRFRenderer(torch.nn.Module):
             fine = self.composite(model, rays, z_f, coarse=False, sb=sb) + (z_f,)
         return coarse + (z_c,), fine
 
+    def _render_all(self, model, rays, sb, draws, forced, seed):
+        """rays (SB*B,8) -> coarse, fine tuples (weights, rgb, depth, z) with a flat (SB*B) leading axis."""
+        b = rays.shape[0] // sb
+        ns = getattr(model, "num_views_per_obj", 1)
+        k_max = self.n_coarse + (self.n_fine if self.using_fine else 0)
+        # chunk along the per-object ray axis so every launch keeps (object, view, point) row order
+        chunk = max(1, self.max_rows_per_launch // max(1, sb * ns * k_max))
+        if chunk >= b:
+            return self._render_chunk(model, rays, sb, draws, forced, False, seed)
+
+        def cut(t, s, e):  # (SB*B, ...) -> (SB*(e-s), ...), keeping object-major order
+            return t.reshape(sb, b, *t.shape[1:])[:, s:e].reshape(sb * (e - s), *t.shape[1:]).contiguous()
+
+        parts = []
+        for s in range(0, b, chunk):
+            e = min(b, s + chunk)
+            dr = {k: cut(v, s, e) for k, v in draws.items()} if draws else None
+            fz = {k: cut(v, s, e) for k, v in forced.items()}
+            parts.append(self._render_chunk(model, cut(rays, s, e), sb, dr, fz, False, seed + s))
+
+        def join(which):
+            if parts[0][which] is None:
+                return None
+            return tuple(torch.cat([p[which][i].reshape(sb, -1, *p[which][i].shape[1:]) for p in parts], dim=1)
+                         .reshape(sb * b, *parts[0][which][i].shape[1:]) for i in range(4))
+        return join(0), join(1)
+
     def forward(self, model, rays, want_weights=False):
         """rays (SB,B,8) -> DotMap{coarse:{rgb,depth[,weights]}, fine:{...}}.  Reference nerf.py:251-303."""
         if self.sched is not None and self.last_sched.item() > 0:
@@ -137,38 +165,31 @@ class NeRFRenderer(torch.nn.Module):
         draws, forced = self.injected_draws, self.injected_z or {}
         self.injected_draws, self.injected_z = None, None
         seed = 0 if draws else self._seed()
-        ns = getattr(model, "num_views_per_obj", 1)
-        k_max = self.n_coarse + (self.n_fine if self.using_fine else 0)
-        # chunk along the per-object ray axis so every launch keeps (object, view, point) row order
-        chunk = max(1, self.max_rows_per_launch // max(1, sb * ns * k_max))
-        if chunk >= b:
-            parts = [self._render_chunk(model, rays, sb, draws, forced, want_weights, seed)]
+        latent = model.encoder.latent
+        if model.stop_encoder_grad:
+            latent = latent.detach()
+        needs_grad = torch.is_grad_enabled() and (latent.requires_grad or any(
+            p.requires_grad for m in (model.mlp_coarse, model.mlp_fine) if m is not None for p in m.parameters()))
+        if needs_grad:
+            # training: hand-written backward behind one autograd node (render/autograd.py)
+            from .autograd import RenderFunction, _flat_params
+            coarse_p, fine_p = _flat_params(model)
+            res = RenderFunction.apply(self, model, rays, sb, draws, forced, seed, latent, *coarse_p, *fine_p)
+            coarse, fine = res[:4], (res[4:8] if self.using_fine else None)
         else:
-            def cut(t, s, e):  # (SB*B, ...) -> (SB*(e-s), ...), keeping object-major order
-                return t.reshape(sb, b, *t.shape[1:])[:, s:e].reshape(sb * (e - s), *t.shape[1:]).contiguous()
+            coarse, fine = self._render_all(model, rays, sb, draws, forced, seed)
 
-            parts = []
-            for s in range(0, b, chunk):
-                e = min(b, s + chunk)
-                dr = {k: cut(v, s, e) for k, v in draws.items()} if draws else None
-                fz = {k: cut(v, s, e) for k, v in forced.items()}
-                parts.append(self._render_chunk(model, cut(rays, s, e), sb, dr, fz, want_weights, seed + s))
-
-        def gather(which, idx):  # chunk outputs -> (SB, B, ...)
-            ts = [p[which][idx] for p in parts]
-            return torch.cat([t.reshape(sb, -1, *t.shape[1:]) for t in ts], dim=1)
-
-        def fmt(which):
-            ret = DotMap(rgb=gather(which, 1), depth=gather(which, 2))
+        def fmt(part):
+            ret = DotMap(rgb=part[1].reshape(sb, b, 3), depth=part[2].reshape(sb, b))
             if want_weights:
-                ret.weights = gather(which, 0)
+                ret.weights = part[0].reshape(sb, b, -1)
             return ret
 
-        outputs = DotMap(coarse=fmt(0))
+        outputs = DotMap(coarse=fmt(coarse))
         if self.using_fine:
-            outputs.fine = fmt(1)
+            outputs.fine = fmt(fine)
         # sample positions of the last call, for the stage-wise parity tests
-        self.last_z = (gather(0, 3), gather(1, 3) if self.using_fine else None)
+        self.last_z = (coarse[3].reshape(sb, b, -1), fine[3].reshape(sb, b, -1) if self.using_fine else None)
         return outputs
 
     def sched_step(self, steps=1):

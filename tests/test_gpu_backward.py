@@ -1,0 +1,138 @@
+"""Hand-written backward (composite -> head -> ResnetFC -> latent gather) against torch autograd
+over the CPU oracle, i.e. against what the reference's ``loss.backward()`` computes
+(train/train.py:271-281) on identical inputs.  Sample positions are teacher-forced constants on both
+sides (render/autograd.py explains the one deliberate deviation).  Tolerance: 1e-3 of the largest
+gradient entry of each tensor (fp32 sums of up to ~10^5 terms in a different order, atomics)."""
+import pytest
+import torch
+
+import oracle
+from oracle import model as omodel
+from pixelnerf_b200 import _lib, synthetic as syn
+from pixelnerf_b200.testing import build_net, scene_camera
+
+pytestmark = pytest.mark.gpu
+REL = 1e-3
+
+
+def _close(got, ref, what, rel=REL):
+    scale = ref.abs().max().item()
+    err = (got.cpu().double() - ref.double()).abs().max().item()
+    assert err <= rel * max(scale, 1e-6), f"{what}: max err {err:.3e} vs scale {scale:.3e}"
+
+
+@pytest.mark.parametrize("ns,ppo,sb", [(1, 300, 1), (2, 130, 2), (3, 77, 1)])
+def test_mlp_backward_vs_autograd(ns, ppo, sb):
+    w = syn.mlp_weights(11)
+    n = sb * ns * ppo
+    g = torch.Generator().manual_seed(1)
+    zx = torch.cat([torch.rand(n, 512, generator=g), torch.randn(n, 42, generator=g)], -1)
+    g_out = torch.randn(sb * ppo, 4, generator=g)
+    # reference: autograd through the oracle MLP + head, object by object (the mean is per object)
+    wr = {k: v.clone().requires_grad_(True) for k, v in w.items()}
+    zr = zx[:, :512].clone().requires_grad_(True)
+    outs = []
+    for o in range(sb):
+        sl = slice(o * ns * ppo, (o + 1) * ns * ppo)
+        wd = dict(wr)
+        wd["_points_per_obj"] = ppo
+        pre = omodel.resnetfc_forward(wd, torch.cat([zr[sl], zx[sl, 512:]], -1), ns)
+        outs.append(torch.cat([torch.sigmoid(pre[:, :3]), torch.relu(pre[:, 3:4])], -1))
+    out_ref = torch.cat(outs)
+    (out_ref * g_out).sum().backward()
+    # kernels
+    wd = {k: v.cuda() for k, v in w.items()}
+    packed = _lib.pack_weights_fp32(wd)
+    fz = zx[:, :512].contiguous().cuda()
+    fx = torch.nn.functional.pad(zx[:, 512:], (0, 2)).contiguous().cuda()
+    out, acts = _lib.mlp_forward_fp32_train(packed, fz, fx, sb, ns, ppo)
+    assert (out.cpu() - out_ref.detach()).abs().max() < 1e-4 * max(1.0, out_ref.abs().max().item())
+    grads = {k: torch.zeros_like(v) for k, v in wd.items()}
+    g_fz = _lib.mlp_backward_fp32(packed, wd, fz, fx, sb, ns, ppo, acts, out, g_out.cuda(), grads, True)
+    torch.cuda.synchronize()
+    for k in _lib.weight_names():
+        _close(grads[k], wr[k].grad, k)
+    _close(g_fz, zr.grad, "g_feat_z")
+
+
+@pytest.mark.parametrize("scene,n_rays", [("sn64", 96), ("srn_chair", 64)])
+def test_render_backward_vs_oracle(scene, n_rays):
+    """loss = <coarse rgb, Gc> + <fine rgb, Gf> + <coarse weights, Gw>: gradients w.r.t. both MLPs' parameters
+    and the encoder latent, through the public NeRFRenderer API."""
+    dev = torch.device("cuda")
+    sc = syn.scene(scene)
+    wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
+    net, ren = build_net(sc, wc, wf, dev)
+    ren.max_rows_train = 96 * 40 * sc["ns"]      # force several backward chunks
+    rays = sc["rays"][torch.linspace(0, sc["rays"].shape[0] - 1, n_rays).long()]
+    draws = syn.draws(9, n_rays, 64, 16, 16)
+    g = torch.Generator().manual_seed(3)
+    gc, gf = torch.randn(n_rays, 3, generator=g), torch.randn(n_rays, 3, generator=g)
+    gw = torch.randn(n_rays, 64, generator=g) * 0.1
+    # kernels: parameters and latent require grad
+    lat = sc["latent"].to(dev).clone().requires_grad_(True)
+    net.encoder.latent = lat
+    net._refresh_camera()
+    for p in net.parameters():
+        p.requires_grad_(True)
+    ren.injected_draws = {k: v.to(dev) for k, v in draws.items()}
+    out = ren(net, rays[None].to(dev), want_weights=True)
+    loss = (out.coarse.rgb[0] * gc.to(dev)).sum() + (out.fine.rgb[0] * gf.to(dev)).sum() \
+        + (out.coarse.weights[0] * gw.to(dev)).sum()
+    loss.backward()
+    z_c, z_f = ren.last_z
+    # oracle: same sample positions as constants, autograd for everything else.  Evaluated in float64:
+    # the fp32 torch-CPU oracle is itself up to 5e-3 (of a tensor's largest entry) away from its own
+    # float64 evaluation on these scenes (a few dominant samples per ray, relu decisions of near-zero
+    # activations), so float64 is the ground truth and the bar is that distance: 6e-3 (measured here:
+    # kernels 3.8e-3, fp32 CPU oracle 5.2e-3 on the coarse lin_z weights; the fine MLP and the latent
+    # agree to < 1e-3).
+    cam = {k: v.double() for k, v in scene_camera(sc).items()}
+    wcr = {k: v.double().requires_grad_(True) for k, v in wc.items()}
+    wfr = {k: v.double().requires_grad_(True) for k, v in wf.items()}
+    latr = sc["latent"].double().requires_grad_(True)
+
+    def net_fn(xyz, dirs, coarse):
+        return omodel.net_forward(wcr if coarse else wfr, latr, cam, sc["ns"], xyz, dirs)
+    torch.set_default_dtype(torch.float64)
+    try:
+        ref = oracle.render_rays(net_fn, rays.double(), 1, 64, 32, 16, {k: v.double() for k, v in draws.items()},
+                                 white_bkgd=sc["white"],
+                                 force=dict(z_coarse=z_c[0].cpu().double(), z_fine=z_f[0].cpu().double()))
+        loss_ref = (ref["rgb_coarse"] * gc).sum() + (ref["rgb_fine"] * gf).sum() + (ref["w_coarse"] * gw).sum()
+        loss_ref.backward()
+    finally:
+        torch.set_default_dtype(torch.float32)
+    assert abs(loss.item() - loss_ref.item()) < 1e-3 * max(1.0, abs(loss_ref.item()))
+    sd = dict(net.named_parameters())
+    worst = {}
+    for prefix, wr in (("mlp_coarse.", wcr), ("mlp_fine.", wfr)):
+        for k in _lib.weight_names():
+            ref_g, got = wr[k].grad, sd[prefix + k].grad
+            worst[prefix + k] = (got.cpu().double() - ref_g).abs().max().item() / max(ref_g.abs().max().item(), 1e-9)
+    worst["latent"] = (lat.grad.cpu().double() - latr.grad).abs().max().item() / latr.grad.abs().max().item()
+    print({k: f"{v:.1e}" for k, v in sorted(worst.items(), key=lambda kv: -kv[1])[:6]})
+    # A single relu decision of a near-zero activation that differs between fp32 and float64 moves one
+    # layer's gradient by a finite amount (measured: 8.5e-3 on mlp_fine.blocks.3.fc_0 of the NS=2 scene, and
+    # the fp32 CPU oracle shows the identical 8.5e-3 against float64), so: every tensor within 1e-2 of its
+    # largest entry, and the typical tensor within 1e-3.
+    vals = sorted(worst.values())
+    assert vals[-1] < 1e-2, worst
+    assert vals[len(vals) // 2] < REL, worst
+
+
+def test_stop_encoder_grad_and_eval_need_no_graph():
+    dev = torch.device("cuda")
+    sc = syn.scene("sn64")
+    net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), dev)
+    net.stop_encoder_grad = True
+    lat = sc["latent"].to(dev).clone().requires_grad_(True)
+    net.encoder.latent = lat
+    net._refresh_camera()
+    rays = sc["rays"][:32].to(dev)[None]
+    out = ren(net, rays)
+    out.fine.rgb.sum().backward()
+    assert lat.grad is None and net.mlp_fine.lin_out.weight.grad is not None
+    with torch.no_grad():
+        out = ren(net, rays)
+    assert not out.fine.rgb.requires_grad
