@@ -40,34 +40,40 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons while the timed region runs."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons while the timed region runs (NVML, ~5 ms period; the
+    nvidia-smi CLI takes longer per query than a whole frame)."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag = index, [], False
+        self.max_mhz = None
 
     def run(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in out.strip().split(",")]
-                if len(f) >= 6:
-                    self.samples.append(f)
-            except Exception:
-                pass
-            time.sleep(0.1)
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(visible.split(",")[self.index]) if visible and visible.split(",")[self.index].isdigit() else self.index
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            while not self.stop_flag:
+                self.samples.append((nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM),
+                                     nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)))
+                time.sleep(0.005)
+        except Exception as e:  # noqa: BLE001
+            self.error = repr(e)
 
     def summary(self):
         if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        mhz = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
-        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": int(self.samples[0][1]),
-                "reasons": reasons, "samples": len(self.samples)}
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unsampled: " + getattr(self, "error", "")]}
+        mhz = sorted(s[0] for s in self.samples)
+        bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                "hw_power_brake_slowdown": 0x80}
+        seen = 0
+        for s in self.samples:
+            seen |= s[1]
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_min_mhz": mhz[0], "sm_max_mhz": self.max_mhz,
+                "reasons": [n for n, b in bits.items() if seen & b], "samples": len(self.samples)}
 
 
 def cpu_oracle_rays_per_s(sc, wc, wf, n_rays, repeats=1):
@@ -114,6 +120,64 @@ def run_reference(args):
                                        f"{cores} threads"},
             "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def run_kernels(args):
+    """--kernels: every HBM-bound kernel of the path alone at a size that exceeds L2, as achieved GB/s of
+    its ALGORITHMIC bytes against the measured copy bandwidth."""
+    from pixelnerf_b200 import _lib, synthetic as syn
+    from pixelnerf_b200.testing import build_net
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    pk = peaks()
+    r = 1 << 20
+    g = torch.Generator(device="cpu").manual_seed(0)
+    rays = torch.zeros(r, 8, device=dev)
+    rays[:, 3:6] = torch.nn.functional.normalize(torch.randn(r, 3, device=dev), dim=-1)
+    rays[:, 2] = 1.3
+    rays[:, 6], rays[:, 7] = 0.8, 1.8
+    res = {}
+
+    def timeit(name, fn, nbytes, iters=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        b.synchronize()
+        ms = a.elapsed_time(b) / iters
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        res[name] = {"ms": ms, "algorithmic_bytes": nbytes, "GB/s": gbs, "frac_of_measured_hbm": gbs / pk["hbm"]}
+
+    kc, kf, kd = N_COARSE, N_FINE - N_DEPTH, N_DEPTH
+    k2 = kc + N_FINE
+    timeit("sample_coarse", lambda: _lib.sample_coarse(rays, kc, False, seed=1), r * (8 + 4 * kc))
+    z_c = _lib.sample_coarse(rays, kc, False, seed=1)
+    w_c = torch.rand(r, kc, device=dev)
+    d_c = torch.full((r,), 1.3, device=dev)
+    timeit("sample_fine", lambda: _lib.sample_fine(rays, z_c, w_c, d_c, kf, kd, 0.01, seed=2),
+           r * (4 * kc + 4 * kc + 4 + 8 + 4 * k2))
+    z_f = _lib.sample_fine(rays, z_c, w_c, d_c, kf, kd, 0.01, seed=2)
+    for k, z, tag in ((kc, z_c, "coarse"), (k2, z_f, "fine")):
+        rs = torch.rand(r, k, 4, device=dev)
+        timeit(f"composite_fwd_{tag}", lambda: _lib.composite_fwd(rs, z, rays, True), r * (k * 20 + 4 + k * 4 + 16))
+        g_rgb = torch.rand(r, 3, device=dev)
+        timeit(f"composite_bwd_{tag}", lambda: _lib.composite_bwd(rs, z, rays, True, g_rgb, want_gz=False),
+               r * (k * 20 + 4 + 12 + k * 16))
+        del rs
+    # point features at the bench frame's size (rows = 16384 rays x 96 samples), fp16 out
+    sc = syn.scene(SCENE)
+    net, _ = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), dev, mlp_precision="fp16")
+    fr = sc["rays"].to(dev)
+    zf = z_f[: fr.shape[0]].contiguous()
+    lat = net.latent_nhwc(torch.float16)
+    rows = fr.shape[0] * k2
+    timeit("point_features_fp16", lambda: _lib.point_features(net._cam, lat, rows, rays=fr, z=zf, ldx=64),
+           rows * (512 + 64) * 2 + fr.shape[0] * (32 + 4 * k2) + lat.numel() * 2)
+    print(json.dumps({"kernels": res, "hbm_peak_GB/s": pk["hbm"], "peak_source": pk["source"], "rays": r}))
 
 
 def run_gpu(args):
@@ -245,8 +309,11 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp16"), choices=["fp32", "fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernels", action="store_true", help="per-kernel HBM roofline of the memory-bound kernels")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.kernels:
+        run_kernels(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)

@@ -54,6 +54,45 @@ __device__ __forceinline__ void store_one(__half* p, float v) { *p = __float2hal
 
 constexpr int kFeatWarps = 8;
 
+// 16-byte vector of latent / feature elements as floats
+template <typename T> struct Vec16;
+template <> struct Vec16<float> {
+  static constexpr int N = 4;
+  static __device__ __forceinline__ void load(const float* p, float (&v)[4]) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  static __device__ __forceinline__ void store(float* p, const float (&v)[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+template <> struct Vec16<__half> {
+  static constexpr int N = 8;
+  static __device__ __forceinline__ void load(const __half* p, float (&v)[8]) {
+    const uint4 t = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+      v[2 * i] = f.x; v[2 * i + 1] = f.y;
+    }
+  }
+  static __device__ __forceinline__ void store(__half* p, const float (&v)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __half2 h = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+
+// Each warp produces 32 consecutive feature rows.  Phase 1: lane l projects row l (camera
+// transform, uv, the four tap offsets and bilinear weights) and writes that row's positional code
+// (its own 36 sinf) -- per-row scalar work is done once, not 32 times.  Phase 2: for each of the
+// 32 rows the tap offsets / weights are broadcast by shuffle and the whole warp blends the four
+// contiguous channels-last taps with 16-byte loads and stores (512 B per warp request).
 template <typename LatT, typename OutT>
 __global__ void __launch_bounds__(kFeatWarps * 32)
 point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
@@ -62,94 +101,125 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
                       int64_t ppo, OutT* __restrict__ feat_z, OutT* __restrict__ feat_x, int ldx,
                       int64_t n_rows) {
   const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5);
-  if (row >= n_rows) return;
-  // row = (obj * NS + view) * P + p
-  const int64_t ov = row / ppo;
-  const int64_t p = row - ov * ppo;
-  const int view = (int)ov;
-  const int obj = view / cam.n_views;
-
-  float x, y, z, dx, dy, dz;
-  if (rays) {  // x = o + z d  (src/render/nerf.py:185), separate mul and add like torch
-    const int64_t ray = obj * (ppo / n_samples) + p / n_samples;
-    const float* rr = rays + ray * 8;
-    const float zz = zs[ray * n_samples + (p % n_samples)];
-    dx = rr[3]; dy = rr[4]; dz = rr[5];
-    x = __fadd_rn(rr[0], __fmul_rn(zz, dx));
-    y = __fadd_rn(rr[1], __fmul_rn(zz, dy));
-    z = __fadd_rn(rr[2], __fmul_rn(zz, dz));
-  } else {
-    const float* pp = xyz_in + ((int64_t)obj * ppo + p) * 3;
-    x = pp[0]; y = pp[1]; z = pp[2];
-    if (dirs_in) {
-      const float* dd = dirs_in + ((int64_t)obj * ppo + p) * 3;
-      dx = dd[0]; dy = dd[1]; dz = dd[2];
-    } else { dx = dy = dz = 0.0f; }
-  }
-  const float* P = cam.poses + (size_t)view * 12;  // (3,4) row-major [R | t]
-  const float r0 = P[0], r1 = P[1], r2 = P[2], t0 = P[3];
-  const float r3 = P[4], r4 = P[5], r5 = P[6], t1 = P[7];
-  const float r6 = P[8], r7 = P[9], r8 = P[10], t2 = P[11];
-  // xyz_rot = R x (models.py:162-164); xyz = xyz_rot + t (:165)
-  const float xr = r0 * x + r1 * y + r2 * z;
-  const float yr = r3 * x + r4 * y + r5 * z;
-  const float zr = r6 * x + r7 * y + r8 * z;
-  const float xc = xr + t0, yc = yr + t1, zc = zr + t2;
-  // uv = -xy/z * focal + c (models.py:206-212); focal = [fx, -fy]
-  const float fx = cam.focal[view * 2 + 0], fy = cam.focal[view * 2 + 1];
-  const float cx = cam.c[view * 2 + 0], cy = cam.c[view * 2 + 1];
-  const float u = (-xc / zc) * fx + cx;
-  const float v = (-yc / zc) * fy + cy;
-  // encoder.index (encoder.py:98-108): uv*scale - 1, then grid_sample(align_corners, border)
-  const float gx = u * cam.scale_x - 1.0f, gy = v * cam.scale_y - 1.0f;
-  float ix = ((gx + 1.0f) * 0.5f) * (float)(cam.wl - 1);
-  float iy = ((gy + 1.0f) * 0.5f) * (float)(cam.hl - 1);
-  ix = fminf(fmaxf(ix, 0.0f), (float)(cam.wl - 1));
-  iy = fminf(fmaxf(iy, 0.0f), (float)(cam.hl - 1));
-  // NaN (point on the camera plane) propagates through fminf/fmaxf as the clamp bound: texel 0
-  const float fx0 = floorf(ix), fy0 = floorf(iy);
-  const int x0 = (int)fx0, y0 = (int)fy0;
-  const int x1 = min(x0 + 1, cam.wl - 1), y1 = min(y0 + 1, cam.hl - 1);
-  const float ax = ix - fx0, ay = iy - fy0;  // weight of the +1 tap (0 when clamped at the border)
-  const float w00 = (1.0f - ax) * (1.0f - ay), w01 = ax * (1.0f - ay);
-  const float w10 = (1.0f - ax) * ay, w11 = ax * ay;
-  const LatT* base = latent + (size_t)view * cam.hl * cam.wl * PN_D_LATENT;
-  const LatT* p00 = base + ((size_t)y0 * cam.wl + x0) * PN_D_LATENT;
-  const LatT* p01 = base + ((size_t)y0 * cam.wl + x1) * PN_D_LATENT;
-  const LatT* p10 = base + ((size_t)y1 * cam.wl + x0) * PN_D_LATENT;
-  const LatT* p11 = base + ((size_t)y1 * cam.wl + x1) * PN_D_LATENT;
-  OutT* oz = feat_z + (size_t)row * PN_D_LATENT;
-#pragma unroll
-  for (int i = 0; i < PN_D_LATENT / 128; ++i) {
-    const int ch = i * 128 + lane * 4;
-    const float4 a = load_vec4(p00 + ch), b = load_vec4(p01 + ch);
-    const float4 c = load_vec4(p10 + ch), d = load_vec4(p11 + ch);
-    float4 o;
-    o.x = a.x * w00 + b.x * w01 + c.x * w10 + d.x * w11;
-    o.y = a.y * w00 + b.y * w01 + c.y * w10 + d.y * w11;
-    o.z = a.z * w00 + b.z * w01 + c.z * w10 + d.z * w11;
-    o.w = a.w * w00 + b.w * w01 + c.w * w10 + d.w * w11;
-    store_vec4(oz + ch, o);
-  }
-  // code: [x(3), sin(f_j x + phase_j)(36), R d (3)], zero pad to ldx
-  OutT* ox = feat_x + (size_t)row * ldx;
-  for (int e = lane; e < ldx; e += 32) {
-    float val = 0.0f;
-    if (e < 3) {
-      val = e == 0 ? xr : e == 1 ? yr : zr;
-    } else if (e < 39) {
-      const int j = (e - 3) / 3, d = (e - 3) % 3;
-      const float comp = d == 0 ? xr : d == 1 ? yr : zr;
-      const float freq = 1.5f * (float)(1 << (j >> 1));      // freq_factor * 2^k (conf/default.conf:19-23)
-      const float phase = (j & 1) ? 1.57079637050628662109375f : 0.0f;  // float32(pi/2) (code.py:24-28)
-      val = sinf(__fadd_rn(phase, __fmul_rn(comp, freq)));   // addcmul then sin (code.py:38)
-    } else if (e < 42) {
-      const int d = e - 39;
-      val = d == 0 ? (r0 * dx + r1 * dy + r2 * dz) : d == 1 ? (r3 * dx + r4 * dy + r5 * dz)
-                                                            : (r6 * dx + r7 * dy + r8 * dz);
+  const int64_t row0 = ((int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5)) * 32;
+  if (row0 >= n_rows) return;
+  const int64_t row = row0 + lane;
+  const bool valid = row < n_rows;
+  uint32_t o00 = 0, o01 = 0, o10 = 0, o11 = 0;
+  float w00 = 0.f, w01 = 0.f, w10 = 0.f, w11 = 0.f;
+  if (valid) {
+    // row = (obj * NS + view) * P + p
+    const int64_t ov = row / ppo;
+    const int64_t p = row - ov * ppo;
+    const int view = (int)ov;
+    const int obj = view / cam.n_views;
+    float x, y, z, dx, dy, dz;
+    if (rays) {  // x = o + z d  (src/render/nerf.py:185), separate mul and add like torch
+      const int64_t ray = obj * (ppo / n_samples) + p / n_samples;
+      const float4 r0 = __ldg(reinterpret_cast<const float4*>(rays + ray * 8));
+      const float4 r1 = __ldg(reinterpret_cast<const float4*>(rays + ray * 8 + 4));
+      const float zz = zs[ray * n_samples + (p % n_samples)];
+      dx = r0.w; dy = r1.x; dz = r1.y;
+      x = __fadd_rn(r0.x, __fmul_rn(zz, dx));
+      y = __fadd_rn(r0.y, __fmul_rn(zz, dy));
+      z = __fadd_rn(r0.z, __fmul_rn(zz, dz));
+    } else {
+      const float* pp = xyz_in + ((int64_t)obj * ppo + p) * 3;
+      x = pp[0]; y = pp[1]; z = pp[2];
+      if (dirs_in) {
+        const float* dd = dirs_in + ((int64_t)obj * ppo + p) * 3;
+        dx = dd[0]; dy = dd[1]; dz = dd[2];
+      } else { dx = dy = dz = 0.0f; }
     }
-    store_one(ox + e, val);
+    const float* P = cam.poses + (size_t)view * 12;  // (3,4) row-major [R | t]
+    const float r0 = P[0], r1 = P[1], r2 = P[2], t0 = P[3];
+    const float r3 = P[4], r4 = P[5], r5 = P[6], t1 = P[7];
+    const float r6 = P[8], r7 = P[9], r8 = P[10], t2 = P[11];
+    // xyz_rot = R x (models.py:162-164); xyz = xyz_rot + t (:165)
+    const float xr = r0 * x + r1 * y + r2 * z;
+    const float yr = r3 * x + r4 * y + r5 * z;
+    const float zr = r6 * x + r7 * y + r8 * z;
+    const float xc = xr + t0, yc = yr + t1, zc = zr + t2;
+    // uv = -xy/z * focal + c (models.py:206-212); focal = [fx, -fy]
+    const float u = (-xc / zc) * cam.focal[view * 2 + 0] + cam.c[view * 2 + 0];
+    const float v = (-yc / zc) * cam.focal[view * 2 + 1] + cam.c[view * 2 + 1];
+    // encoder.index (encoder.py:98-108): uv*scale - 1, then grid_sample(align_corners, border)
+    const float gx = u * cam.scale_x - 1.0f, gy = v * cam.scale_y - 1.0f;
+    float ix = ((gx + 1.0f) * 0.5f) * (float)(cam.wl - 1);
+    float iy = ((gy + 1.0f) * 0.5f) * (float)(cam.hl - 1);
+    ix = fminf(fmaxf(ix, 0.0f), (float)(cam.wl - 1));
+    iy = fminf(fmaxf(iy, 0.0f), (float)(cam.hl - 1));
+    // NaN (point on the camera plane) propagates through fminf/fmaxf as the clamp bound: texel 0
+    const float fx0 = floorf(ix), fy0 = floorf(iy);
+    const int x0 = (int)fx0, y0 = (int)fy0;
+    const int x1 = min(x0 + 1, cam.wl - 1), y1 = min(y0 + 1, cam.hl - 1);
+    const float ax = ix - fx0, ay = iy - fy0;  // weight of the +1 tap (0 when clamped at the border)
+    w00 = (1.0f - ax) * (1.0f - ay); w01 = ax * (1.0f - ay);
+    w10 = (1.0f - ax) * ay; w11 = ax * ay;
+    const uint32_t vbase = (uint32_t)view * (uint32_t)(cam.hl * cam.wl);
+    o00 = (vbase + (uint32_t)(y0 * cam.wl + x0)) * PN_D_LATENT;
+    o01 = (vbase + (uint32_t)(y0 * cam.wl + x1)) * PN_D_LATENT;
+    o10 = (vbase + (uint32_t)(y1 * cam.wl + x0)) * PN_D_LATENT;
+    o11 = (vbase + (uint32_t)(y1 * cam.wl + x1)) * PN_D_LATENT;
+    // code: [x(3), sin(f_j x + phase_j)(36), R d (3)], zero pad to ldx; 4 elements at a time
+    OutT* ox = feat_x + (size_t)row * ldx;
+    const float comp[3] = {xr, yr, zr};
+    const float rd[3] = {r0 * dx + r1 * dy + r2 * dz, r3 * dx + r4 * dy + r5 * dz, r6 * dx + r7 * dy + r8 * dz};
+#pragma unroll
+    for (int e0 = 0; e0 < 44; e0 += 4) {   // 42 real entries; fully unrolled so every index is constant
+      float q[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int e = e0 + i;
+        float val = 0.0f;
+        if (e < 3) {
+          val = comp[e];
+        } else if (e < 39) {
+          const int j = (e - 3) / 3, d = (e - 3) - j * 3;
+          const float freq = 1.5f * (float)(1 << (j >> 1));      // freq_factor * 2^k (conf/default.conf:19-23)
+          const float phase = (j & 1) ? 1.57079637050628662109375f : 0.0f;  // float32(pi/2) (code.py:24-28)
+          val = sinf(__fadd_rn(phase, __fmul_rn(comp[d], freq)));  // addcmul then sin (code.py:38)
+        } else if (e < 42) {
+          val = rd[e - 39];
+        }
+        q[i] = val;
+      }
+      if (sizeof(OutT) == 4) {
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(q[0], q[1], q[2], q[3]);
+      } else {
+        const __half2 a = __floats2half2_rn(q[0], q[1]), b = __floats2half2_rn(q[2], q[3]);
+        *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ox) + e0) =
+            make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+      }
+    }
+    for (int e0 = 44; e0 < ldx; e0 += 4) {  // zero padding up to ldx
+      if (sizeof(OutT) == 4) *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(0.f, 0.f, 0.f, 0.f);
+      else *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ox) + e0) = make_uint2(0u, 0u);
+    }
+  }
+  // phase 2: the warp blends the taps of each of its rows
+  constexpr int N = Vec16<LatT>::N;
+  constexpr int kIters = PN_D_LATENT / (32 * N);
+  const int n_here = (int)((n_rows - row0) < 32 ? (n_rows - row0) : 32);
+#pragma unroll 2
+  for (int r = 0; r < n_here; ++r) {
+    const uint32_t a00 = __shfl_sync(0xffffffffu, o00, r), a01 = __shfl_sync(0xffffffffu, o01, r);
+    const uint32_t a10 = __shfl_sync(0xffffffffu, o10, r), a11 = __shfl_sync(0xffffffffu, o11, r);
+    const float b00 = __shfl_sync(0xffffffffu, w00, r), b01 = __shfl_sync(0xffffffffu, w01, r);
+    const float b10 = __shfl_sync(0xffffffffu, w10, r), b11 = __shfl_sync(0xffffffffu, w11, r);
+    OutT* oz = feat_z + (size_t)(row0 + r) * PN_D_LATENT;
+#pragma unroll
+    for (int it = 0; it < kIters; ++it) {
+      const int ch = (it * 32 + lane) * N;
+      float ta[N], tb[N], tc[N], td[N], o[N];
+      Vec16<LatT>::load(latent + a00 + ch, ta);
+      Vec16<LatT>::load(latent + a01 + ch, tb);
+      Vec16<LatT>::load(latent + a10 + ch, tc);
+      Vec16<LatT>::load(latent + a11 + ch, td);
+#pragma unroll
+      for (int i = 0; i < N; ++i) o[i] = ta[i] * b00 + tb[i] * b01 + tc[i] * b10 + td[i] * b11;
+      Vec16<OutT>::store(oz + ch, o);
+    }
   }
 }
 
@@ -257,13 +327,13 @@ extern "C" int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc
   PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_features: camera buffers missing (call encode first)");
   PN_CHECK_ARG((rays && z && n_samples > 0) || xyz, "pn_point_features: need rays+z or xyz");
   PN_CHECK_ARG(!rays || points_per_object % n_samples == 0, "pn_point_features: P must be a multiple of K");
-  PN_CHECK_ARG(ldx >= PN_D_CODE, "pn_point_features: ldx=%d < %d", ldx, PN_D_CODE);
+  PN_CHECK_ARG(ldx >= 44 && ldx % 4 == 0, "pn_point_features: ldx=%d must be a multiple of 4 and >= 44", ldx);
   PN_CHECK_ARG(cam->hl > 1 && cam->wl > 1 && cam->n_objects > 0 && cam->n_views > 0, "pn_point_features: bad camera sizes");
   PN_CHECK_ARG(latent_dtype == out_dtype && (out_dtype == PN_DTYPE_F32 || out_dtype == PN_DTYPE_F16),
                "pn_point_features: latent/out dtype must both be f32 or both f16");
   const int64_t n_rows = (int64_t)cam->n_objects * cam->n_views * points_per_object;
   if (n_rows == 0) return PN_OK;
-  const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps);
+  const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
   if (out_dtype == PN_DTYPE_F32)
     pn::point_features_kernel<float, float><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
         *cam, (const float*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
