@@ -17,7 +17,35 @@ __device__ __forceinline__ float lerp_depth(float near, float far, float zs, boo
   return __fdiv_rn(1.0f, __fadd_rn(__fmul_rn(inv_n, a), __fmul_rn(inv_f, zs)));
 }
 
-// One thread per (ray, sample); consecutive threads write consecutive z: fully coalesced.
+// One thread per 4 consecutive samples (one Philox call yields their 4 draws, one 16-byte store);
+// consecutive threads write consecutive z: fully coalesced.  Kc % 4 == 0 takes this path.
+__global__ void __launch_bounds__(256)
+sample_coarse4_kernel(const float* __restrict__ rays, const float* __restrict__ u,
+                      const float* __restrict__ lin, float* __restrict__ z, int64_t total4, int kc,
+                      float step, bool lindisp, uint64_t seed) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= total4) return;
+  const int64_t i = q * 4;
+  const int64_t r = i / kc;
+  const int k = (int)(i - r * kc);
+  float4 uu;
+  if (u) {
+    uu = *reinterpret_cast<const float4*>(u + i);
+  } else {
+    const uint4 rnd = Philox(seed)((uint64_t)q, (uint64_t)PN_STREAM_COARSE);  // same draws as rand_uniform(i..i+3)
+    uu = make_float4(u01(rnd.x), u01(rnd.y), u01(rnd.z), u01(rnd.w));
+  }
+  const float4 ln = *reinterpret_cast<const float4*>(lin + k);
+  const float2 nf = *reinterpret_cast<const float2*>(rays + r * 8 + 6);
+  float4 o;
+  o.x = lerp_depth(nf.x, nf.y, __fadd_rn(ln.x, __fmul_rn(uu.x, step)), lindisp);
+  o.y = lerp_depth(nf.x, nf.y, __fadd_rn(ln.y, __fmul_rn(uu.y, step)), lindisp);
+  o.z = lerp_depth(nf.x, nf.y, __fadd_rn(ln.z, __fmul_rn(uu.z, step)), lindisp);
+  o.w = lerp_depth(nf.x, nf.y, __fadd_rn(ln.w, __fmul_rn(uu.w, step)), lindisp);
+  *reinterpret_cast<float4*>(z + i) = o;
+}
+
+// General Kc: one thread per sample.
 __global__ void __launch_bounds__(256)
 sample_coarse_kernel(const float* __restrict__ rays, const float* __restrict__ u,
                      const float* __restrict__ lin, float* __restrict__ z, int64_t total, int kc,
@@ -61,6 +89,50 @@ __device__ float aten_row_sum(const float* __restrict__ w, int k, int lane) {
   return s;  // identical in every lane
 }
 
+template <int EPL>
+__device__ __forceinline__ void sort_store(const float* __restrict__ srt, float* __restrict__ dst, int k2, int lane) {
+  constexpr int N = 32 * EPL;
+  float v[EPL];
+#pragma unroll
+  for (int j = 0; j < EPL; ++j) v[j] = srt[lane * EPL + j];
+#pragma unroll
+  for (int size = 2; size <= N; size <<= 1) {
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      if (stride >= EPL) {
+        const int e = lane * EPL;   // bits >= log2(EPL) of the element index are the lane's
+        const bool keep_min = ((e & stride) == 0) == ((e & size) == 0);
+#pragma unroll
+        for (int j = 0; j < EPL; ++j) {
+          const float p = __shfl_xor_sync(0xffffffffu, v[j], stride / EPL);
+          v[j] = keep_min ? fminf(v[j], p) : fmaxf(v[j], p);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < EPL; ++j) {
+          if ((j & stride) == 0) {
+            const int e = lane * EPL + j;
+            const bool up = (e & size) == 0;
+            const float a = v[j], b = v[j | stride];
+            v[j] = up ? fminf(a, b) : fmaxf(a, b);
+            v[j | stride] = up ? fmaxf(a, b) : fminf(a, b);
+          }
+        }
+      }
+    }
+  }
+  const int e0 = lane * EPL;
+  if (EPL >= 4 && (k2 % 4) == 0 && ((uintptr_t)dst & 15) == 0) {
+#pragma unroll
+    for (int j = 0; j < EPL; j += 4)
+      if (e0 + j < k2) *reinterpret_cast<float4*>(dst + e0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < EPL; ++j)
+      if (e0 + j < k2) dst[e0 + j] = v[j];
+  }
+}
+
 constexpr int kFineWarps = 4;
 
 // One warp per ray.  Shared memory per warp: w/pdf (Kc) + cdf (Kc+1) + sort buffer (pow2 >= K2).
@@ -88,13 +160,27 @@ sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_c
       const float s = aten_row_sum(w, kc, lane);
       for (int k = lane; k < kc; k += 32) w[k] = __fdiv_rn(w[k], s);  // pdf
       __syncwarp();
-      if (lane == 0) {  // torch.cumsum on CPU: fp64 accumulator, rounded per element
+      // torch.cumsum on CPU: fp64 running sum, rounded to fp32 per element.  Done as a warp scan:
+      // every pdf is a 24-bit value >= 2^-23 (w >= 1e-5, S < 2^7) and the sums stay < 2, so all
+      // partial sums fit in fp64's 53 bits exactly and the order of additions cannot matter.
+      {
+        const int per = (kc + 31) >> 5, e0 = lane * per;
         double run = 0.0;
-        cdf[0] = 0.0f;
-        for (int k = 0; k < kc; ++k) {
-          run += (double)w[k];
-          cdf[k + 1] = (float)run;
+        for (int i = 0; i < per; ++i)
+          if (e0 + i < kc) run += (double)w[e0 + i];
+        double incl = run;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const double y = __shfl_up_sync(0xffffffffu, incl, d);
+          if (lane >= d) incl += y;
         }
+        double acc = incl - run;   // sum of the elements owned by lower lanes
+        if (lane == 0) cdf[0] = 0.0f;
+        for (int i = 0; i < per; ++i)
+          if (e0 + i < kc) {
+            acc += (double)w[e0 + i];
+            cdf[e0 + i + 1] = (float)acc;
+          }
       }
       __syncwarp();
       for (int q = lane; q < kf; q += 32) {
@@ -126,20 +212,13 @@ sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_c
     }
     for (int k = k2 + lane; k < sort_n; k += 32) srt[k] = __int_as_float(0x7f800000);  // +inf padding
     __syncwarp();
-    // bitonic sort of sort_n (power of two) floats by one warp
-    for (int size = 2; size <= sort_n; size <<= 1) {
-      for (int stride = size >> 1; stride > 0; stride >>= 1) {
-        for (int t = lane; t < (sort_n >> 1); t += 32) {
-          const int lo = ((t / stride) * (stride << 1)) + (t % stride);
-          const int hi = lo + stride;
-          const bool up = ((lo & size) == 0);
-          const float a = srt[lo], b = srt[hi];
-          if ((a > b) == up) { srt[lo] = b; srt[hi] = a; }
-        }
-        __syncwarp();
-      }
-    }
-    for (int k = lane; k < k2; k += 32) z_sorted[r * k2 + k] = srt[k];
+    // bitonic sort of sort_n = 32*EPL floats: lane l holds elements [l*EPL, (l+1)*EPL) in registers;
+    // strides >= EPL exchange through shuffles, smaller strides compare within the lane
+    if (sort_n == 128) sort_store<4>(srt, z_sorted + r * k2, k2, lane);
+    else if (sort_n == 64) sort_store<2>(srt, z_sorted + r * k2, k2, lane);
+    else if (sort_n == 256) sort_store<8>(srt, z_sorted + r * k2, k2, lane);
+    else if (sort_n == 512) sort_store<16>(srt, z_sorted + r * k2, k2, lane);
+    else sort_store<1>(srt, z_sorted + r * k2, k2, lane);
     __syncwarp();
   }
 }
@@ -155,8 +234,14 @@ extern "C" int pn_sample_coarse(const float* rays, const float* u, const float* 
   if (n_rays == 0) return PN_OK;
   const int64_t total = n_rays * n_coarse;
   const float step = (float)(1.0 / (double)n_coarse);
-  pn::sample_coarse_kernel<<<pn::ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
-      rays, u, lin, z, total, n_coarse, step, lindisp != 0, seed);
+  const bool vec = n_coarse % 4 == 0 && ((uintptr_t)z & 15) == 0 && ((uintptr_t)lin & 15) == 0 &&
+                   (!u || ((uintptr_t)u & 15) == 0);
+  if (vec)
+    pn::sample_coarse4_kernel<<<pn::ceil_div(total / 4, 256), 256, 0, (cudaStream_t)stream>>>(
+        rays, u, lin, z, total / 4, n_coarse, step, lindisp != 0, seed);
+  else
+    pn::sample_coarse_kernel<<<pn::ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        rays, u, lin, z, total, n_coarse, step, lindisp != 0, seed);
   PN_LAUNCH_OK("sample_coarse_kernel");
   pn::count_launch();
   return PN_OK;
@@ -175,8 +260,9 @@ extern "C" int pn_sample_fine(const float* rays, const float* z_coarse, const fl
   PN_CHECK_ARG(n_coarse < 512, "pn_sample_fine: Kc=%d >= 512 is outside the emulated ATen row-sum regime", n_coarse);
   if (n_rays == 0) return PN_OK;
   const int k2 = n_coarse + n_imp + n_depth;
-  int sort_n = 2;
+  int sort_n = 32;
   while (sort_n < k2) sort_n <<= 1;
+  PN_CHECK_ARG(sort_n <= 512, "pn_sample_fine: more than 512 samples per ray");
   const size_t smem = (size_t)pn::kFineWarps * (n_coarse + n_coarse + 1 + sort_n) * sizeof(float);
   PN_CHECK_ARG(smem <= 48 * 1024, "pn_sample_fine: K too large for shared memory");
   const int blocks = (int)((n_rays + pn::kFineWarps - 1) / pn::kFineWarps);
