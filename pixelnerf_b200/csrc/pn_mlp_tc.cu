@@ -113,9 +113,11 @@ __device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+// relu + round-to-nearest fp16 pair in one instruction (a in the low half)
 __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
-  __half2 h = __floats2half2_rn(fmaxf(a, 0.0f), fmaxf(b, 0.0f));
-  return *reinterpret_cast<uint32_t*>(&h);
+  uint32_t d;
+  asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  return d;
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
@@ -146,7 +148,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       mbar_init(bar(BAR_A_FULL + a), 1);
       mbar_init(bar(BAR_A_EMPTY + a), 1);
     }
-    for (int c = 0; c < 8; ++c) mbar_init(bar(BAR_ACT + c), 4);  // 2 warps per chunk per CTA
+    for (int c = 0; c < 8; ++c) mbar_init(bar(BAR_ACT + c), 8);  // 4 warps per chunk per CTA
     for (int a = 0; a < 4; ++a) mbar_init(bar(BAR_ACC + a), 1);
     fence_mbar_init();
   }
@@ -164,16 +166,17 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // in exactly the order the MMA issuer consumes them, so the two rings cannot deadlock.
     uint32_t ws = 0, wph = 0;   // weight ring stage / phase
     uint32_t as = 0, aph = 0;   // operand-chunk ring slot / phase
-    // Weight tile for K-chunks [kc, kc+nkc) of block nb of `layer`: nkc boxes of [128 out x 64 in].
-    auto load_w = [&](int layer, int nb, int kc, int nkc) {
+    // Weight tile for K-chunks kc0 and kc1 (kc1 < 0: kc0 only) of block nb of `layer`: boxes of [128 out x 64 in].
+    auto load_w = [&](int layer, int nb, int kc0, int kc1) {
+      const int nkc = kc1 < 0 ? 1 : 2;
       wait_bar<false>(bar(BAR_W_EMPTY + ws), wph ^ 1, p.err, 0x100 + ws);
       if (elect_one()) {
         const uint32_t full = bar(BAR_W_FULL + ws);
         // the leader expects both CTAs' bytes; the peer's copies credit the leader's barrier
         if (rank == 0) mbar_arrive_expect_tx(full, 2 * nkc * kWBoxBytes);
         const int row = layer * 512 + nb * 256 + (int)rank * 128;
-        for (int i = 0; i < nkc; ++i)
-          tma_load_2d_pair(smem_base + kOffW + ws * kWStageBytes + i * kWBoxBytes, &map_w, full, (kc + i) * 64, row);
+        tma_load_2d_pair(smem_base + kOffW + ws * kWStageBytes, &map_w, full, kc0 * 64, row);
+        if (kc1 >= 0) tma_load_2d_pair(smem_base + kOffW + ws * kWStageBytes + kWBoxBytes, &map_w, full, kc1 * 64, row);
       }
       __syncwarp();
       if (++ws == kStages) { ws = 0; wph ^= 1; }
@@ -189,19 +192,19 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       __syncwarp();
       if (++as == kASlots) { as = 0; aph ^= 1; }
     };
-    auto load_fc = [&](int layer) {   // quarter order, two K=128 items per quarter
+    auto load_fc = [&](int layer) {   // quarter order, two K=128 items per quarter: K-chunks (h, h+2) of the group
 #pragma unroll 1
       for (int q = 0; q < 4; ++q)
 #pragma unroll 1
-        for (int h = 0; h < 2; ++h) load_w(layer, q & 1, (q >> 1) * 4 + h * 2, 2);
+        for (int h = 0; h < 2; ++h) load_w(layer, q & 1, (q >> 1) * 4 + h, (q >> 1) * 4 + h + 2);
     };
     auto load_lin_z = [&](int layer, int row0) {   // K-outer: z chunk pair, then both blocks' weights
 #pragma unroll 1
       for (int kp = 0; kp < 4; ++kp) {
         load_a(&map_z, (2 * kp) * 64, row0);
         load_a(&map_z, (2 * kp + 1) * 64, row0);
-        load_w(layer, 0, 2 * kp, 2);
-        load_w(layer, 1, 2 * kp, 2);
+        load_w(layer, 0, 2 * kp, 2 * kp + 1);
+        load_w(layer, 1, 2 * kp, 2 * kp + 1);
       }
     };
     auto prefetch_l2 = [&](int tile) {   // next tile's x / z rows: DRAM -> L2 ahead of the operand ring
@@ -218,7 +221,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       if (full_front) {
         if (tile + n_clusters < p.n_tiles) prefetch_l2(tile + n_clusters);
         load_a(&map_x, 0, row0);
-        load_w(L_IN, 0, 0, 1);
+        load_w(L_IN, 0, 0, 1);                 // hi and lo halves of lin_in
         load_w(L_IN, 1, 0, 1);
         load_lin_z(L_Z0, row0);
       }
@@ -230,7 +233,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       if (has_head) {
 #pragma unroll 1
-        for (int kp = 0; kp < 4; ++kp) load_w(L_OUT, 0, 2 * kp, 2);
+        for (int kp = 0; kp < 4; ++kp) load_w(L_OUT, 0, 2 * kp, 2 * kp + 1);
       }
     }
   } else if (warp == 1 && rank == 0) {
@@ -241,7 +244,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // descriptor = constant high word | (address >> 4): only the low word changes per MMA
     const uint64_t desc_hi = smem_desc_k128(0);
     // One weight stage: nk K=16 steps; A steps [0,4) come from a0, [4,8) from a1 (64-wide chunks).
-    auto item = [&](uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, int nk) {
+    auto item = [&](uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask) {
       wait_bar<false>(bar(BAR_W_FULL + ws), wph, p.err, 0x200 + ws);
       tc_fence_after();
       if (elect_one()) {
@@ -249,7 +252,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         const uint32_t a0_lo = a0 >> 4, a1_lo = a1 >> 4;
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          if (j < nk) {
+          if ((kmask >> j) & 1u) {
             const uint32_t a_lo = (j < 4 ? a0_lo : a1_lo) + 2 * (j & 3);
             const uint32_t bj = b_lo + (j < 4 ? 0 : (kWBoxBytes >> 4)) + 2 * (j & 3);
             umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)a_lo, desc_hi | (uint64_t)bj, kIdesc,
@@ -264,9 +267,10 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       if (elect_one()) umma_commit_pair(bar(b), 3);
       __syncwarp();
     };
+    auto wait_chunk = [&](int c) { wait_bar<false>(bar(BAR_ACT + c), gen & 1, p.err, 0x210 + c); };
     auto wait_act = [&](int c0) {
 #pragma unroll 1
-      for (int c = c0; c < c0 + 4; ++c) wait_bar<false>(bar(BAR_ACT + c), gen & 1, p.err, 0x210 + c);
+      for (int c = c0; c < c0 + 4; ++c) wait_chunk(c);
       tc_fence_after();
     };
     // operand-chunk ring: wait for the next slot, return its address
@@ -283,11 +287,17 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll 1
       for (int q = 0; q < 4; ++q) {
         const int nb = q & 1, kg = q >> 1;
-        if (nb == 0) wait_act(kg * 4);
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {
-          const uint32_t a = act + (kg * 4 + h * 2) * kChunkBytes;
-          item(a, a + kChunkBytes, d_col + nb * 128, clear && kg == 0 && h == 0, 8);
+          // K-chunks (h, h+2) of the group: the epilogue finishes chunks 0 and 2 of a block first
+          const int c = kg * 4 + h;
+          if (nb == 0) {
+            wait_chunk(c);
+            wait_chunk(c + 2);
+            tc_fence_after();
+          }
+          const uint32_t a = act + c * kChunkBytes;
+          item(a, a + 2 * kChunkBytes, d_col + nb * 128, clear && kg == 0 && h == 0, 0xFFu);
         }
         if (kg == 1) commit(BAR_ACC + commit_region * 2 + nb);
       }
@@ -299,8 +309,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       for (int kp = 0; kp < 4; ++kp) {
         const uint32_t a0 = take_a(), a1 = take_a();
         tc_fence_after();
-        item(a0, a1, kColH, false, 8);
-        item(a0, a1, kColH + 128, false, 8);
+        item(a0, a1, kColH, false, 0xFFu);
+        item(a0, a1, kColH + 128, false, 0xFFu);
         release_a(a0);
         release_a(a1);
       }
@@ -311,8 +321,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       if (full_front) {
         const uint32_t xa = take_a();
         tc_fence_after();
-        item(xa, xa, kColH, true, 3);          // lin_in: K = 48 of the zero-padded 64
-        item(xa, xa, kColH + 128, true, 3);
+        item(xa, xa, kColH, true, 0x77u);      // lin_in: x (K = 48 of the zero-padded 64) times W_hi, then W_lo
+        item(xa, xa, kColH + 128, true, 0x77u);
         release_a(xa);
         gemm_z(true);                          // lin_z[0] completes h_0
       }
@@ -324,11 +334,11 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       if (has_head) {
         wait_act(0);
-        item(act, act + kChunkBytes, kColT, true, 8);
-        item(act + 2 * kChunkBytes, act + 3 * kChunkBytes, kColT, false, 8);
+        item(act, act + kChunkBytes, kColT, true, 0xFFu);
+        item(act + 2 * kChunkBytes, act + 3 * kChunkBytes, kColT, false, 0xFFu);
         wait_act(4);
-        item(act + 4 * kChunkBytes, act + 5 * kChunkBytes, kColT, false, 8);
-        item(act + 6 * kChunkBytes, act + 7 * kChunkBytes, kColT, false, 8);
+        item(act + 4 * kChunkBytes, act + 5 * kChunkBytes, kColT, false, 0xFFu);
+        item(act + 6 * kChunkBytes, act + 7 * kChunkBytes, kColT, false, 0xFFu);
         commit(BAR_ACC + 2);
         ++gen;
       } else {
@@ -349,56 +359,90 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     const uint32_t row_off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
     uint32_t n_acc[4] = {0, 0, 0, 0};    // completed waits per (region, block) barrier
 
-    // mode 0: relu -> ACT operand; mode 1: dump fp32 to h_io (segment end)
-    auto epi = [&](int region, const float* bias_vec, int mode, int64_t grow, bool dbg) {
-      for (int nb = 0; nb < 2; ++nb) {
-        const int a = region * 2 + nb;
-        wait_bar<false>(bar(BAR_ACC + a), n_acc[a] & 1, p.err, 0x300 + a);
-        ++n_acc[a];
-        tc_fence_after();
-        const int n0 = 256 * nb + 128 * hf + 64 * ch;
-        const int c = n0 >> 6;
-        const uint32_t chunk = smem_base + kOffAct + c * kChunkBytes + row_off;
+    // This warp's share of one accumulator block (64 rows x 256 features per CTA): rows r, and of each
+    // of the two 64-feature K-chunks its lane half holds (chunk = nb*4 + 2*hf + half) the 32 features
+    // [32*ch, 32*ch+32).  Both warps of a lane quarter work on the same chunk, so chunks 2*hf of a block
+    // are complete after half of the epilogue: the issuer consumes K in the order (0,2),(1,3).
+    auto ld_bias8 = [&](const float* src, float4 (&bv)[8]) {
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_base + lane_addr + (region ? kColT : kColH) + nb * 128 + ch * 64 + half * 32, v);
-          tmem_wait_ld();
-          const float4* bp = reinterpret_cast<const float4*>(bias_vec + n0 + half * 32);
-          float x[32];
+      for (int i = 0; i < 8; ++i)
+        asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(bv[i].x), "=f"(bv[i].y), "=f"(bv[i].z), "=f"(bv[i].w) : "l"(src + 4 * i));
+    };
+    // fp32 dump of (accumulator + bias) of one block: segment end (h_io) and the debug tap
+    auto dump_block = [&](uint32_t tcol, const float* bias_vec, int nb, float* dst, int64_t grow) {
+#pragma unroll 1
+      for (int half = 0; half < 2; ++half) {
+        const int n0 = 256 * nb + 128 * hf + 64 * half + 32 * ch;
+        uint32_t v[32];
+        tmem_ld_32x32(tcol + half * 64, v);
+        tmem_wait_ld();
+        if (grow < p.n_rows) {
+          const float4* bp = reinterpret_cast<const float4*>(bias_vec + n0);
+          float4* d = reinterpret_cast<float4*>(dst + grow * 512 + n0);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float4 bv = __ldg(bp + i);
-            x[4 * i + 0] = __uint_as_float(v[4 * i + 0]) + bv.x;
-            x[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + bv.y;
-            x[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + bv.z;
-            x[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + bv.w;
-          }
-          if (dbg && grow < p.n_rows) {
-            float4* d = reinterpret_cast<float4*>(p.debug_h + grow * 512 + n0 + half * 32);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) d[i] = make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
-          }
-          if (mode == 1) {
-            if (grow < p.n_rows) {
-              float4* d = reinterpret_cast<float4*>(p.h_io + grow * 512 + n0 + half * 32);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) d[i] = make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
-            }
-          } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const uint32_t piece = (uint32_t)(half * 4 + i);
-              st_shared_v4(chunk + ((piece ^ sw) << 4), pack_relu_h2(x[8 * i + 0], x[8 * i + 1]),
-                           pack_relu_h2(x[8 * i + 2], x[8 * i + 3]), pack_relu_h2(x[8 * i + 4], x[8 * i + 5]),
-                           pack_relu_h2(x[8 * i + 6], x[8 * i + 7]));
-            }
+            d[i] = make_float4(__uint_as_float(v[4 * i]) + bv.x, __uint_as_float(v[4 * i + 1]) + bv.y,
+                               __uint_as_float(v[4 * i + 2]) + bv.z, __uint_as_float(v[4 * i + 3]) + bv.w);
           }
         }
-        if (mode == 0) fence_proxy_async_smem();
+      }
+    };
+    auto signal_chunk = [&](int c) {
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), 0);
+    };
+    // mode 0: relu -> ACT operand; mode 1: dump fp32 to h_io (segment end)
+    auto epi = [&](int region, const float* bias_vec, int mode, int64_t grow, bool dbg) {
+#pragma unroll 1
+      for (int nb = 0; nb < 2; ++nb) {
+        const int a = region * 2 + nb;
+        const int c0 = nb * 4 + 2 * hf;
+        const uint32_t tcol = tmem_base + lane_addr + (region ? kColT : kColH) + nb * 128 + ch * 32;
+        // the bias loads are in flight while the accumulator is still being produced
+        float4 b0[8], b1[8];
+        ld_bias8(bias_vec + c0 * 64 + 32 * ch, b0);
+        ld_bias8(bias_vec + c0 * 64 + 64 + 32 * ch, b1);
+        wait_bar<false>(bar(BAR_ACC + a), n_acc[a] & 1, p.err, 0x300 + a);
+        ++n_acc[a];
+        tc_fence_after();
+        if (dbg) dump_block(tcol, bias_vec, nb, p.debug_h, grow);
+        if (mode == 1) {
+          dump_block(tcol, bias_vec, nb, p.h_io, grow);
+          tc_fence_before();
+          signal_chunk(c0);
+          signal_chunk(c0 + 1);
+          continue;
+        }
+        uint32_t v0[32], v1[32];
+        tmem_ld_32x32(tcol, v0);
+        tmem_ld_32x32(tcol + 64, v1);
+        tmem_wait_ld();
         tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), 0);
+        const uint32_t dst = smem_base + kOffAct + c0 * kChunkBytes + row_off;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 ba = b0[2 * i], bb = b0[2 * i + 1];
+          st_shared_v4(dst + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
+                       pack_relu_h2(__uint_as_float(v0[8 * i + 0]) + ba.x, __uint_as_float(v0[8 * i + 1]) + ba.y),
+                       pack_relu_h2(__uint_as_float(v0[8 * i + 2]) + ba.z, __uint_as_float(v0[8 * i + 3]) + ba.w),
+                       pack_relu_h2(__uint_as_float(v0[8 * i + 4]) + bb.x, __uint_as_float(v0[8 * i + 5]) + bb.y),
+                       pack_relu_h2(__uint_as_float(v0[8 * i + 6]) + bb.z, __uint_as_float(v0[8 * i + 7]) + bb.w));
+        }
+        fence_proxy_async_smem();
+        signal_chunk(c0);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 ba = b1[2 * i], bb = b1[2 * i + 1];
+          st_shared_v4(dst + kChunkBytes + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
+                       pack_relu_h2(__uint_as_float(v1[8 * i + 0]) + ba.x, __uint_as_float(v1[8 * i + 1]) + ba.y),
+                       pack_relu_h2(__uint_as_float(v1[8 * i + 2]) + ba.z, __uint_as_float(v1[8 * i + 3]) + ba.w),
+                       pack_relu_h2(__uint_as_float(v1[8 * i + 4]) + bb.x, __uint_as_float(v1[8 * i + 5]) + bb.y),
+                       pack_relu_h2(__uint_as_float(v1[8 * i + 6]) + bb.z, __uint_as_float(v1[8 * i + 7]) + bb.w));
+        }
+        fence_proxy_async_smem();
+        signal_chunk(c0 + 1);
       }
     };
     // Segment [3,5] entry: h = mean over views of the fp32 h the first segment wrote.
@@ -408,17 +452,17 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       const float* src = p.h_io + ((obj * p.n_views) * p.ppo + pt) * 512;
       const float inv = (float)p.n_views;
       for (int nb = 0; nb < 2; ++nb) {
-        const int n0 = 256 * nb + 128 * hf + 64 * ch;
-        const int c = n0 >> 6;
-        const uint32_t chunk = smem_base + kOffAct + c * kChunkBytes + row_off;
-#pragma unroll
+#pragma unroll 1
         for (int half = 0; half < 2; ++half) {
+          const int c = nb * 4 + 2 * hf + half;
+          const int n0 = c * 64 + 32 * ch;
+          const uint32_t chunk = smem_base + kOffAct + c * kChunkBytes + row_off;
           float x[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) x[i] = 0.0f;
           if (valid) {
             for (int v = 0; v < p.n_views; ++v) {
-              const float4* s4 = reinterpret_cast<const float4*>(src + (int64_t)v * p.ppo * 512 + n0 + half * 32);
+              const float4* s4 = reinterpret_cast<const float4*>(src + (int64_t)v * p.ppo * 512 + n0);
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
                 const float4 t = s4[i];
@@ -431,20 +475,17 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           uint32_t v[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(x[i]);
-          tmem_st_32x32(tmem_base + lane_addr + kColH + nb * 128 + ch * 64 + half * 32, v);
+          tmem_st_32x32(tmem_base + lane_addr + kColH + nb * 128 + half * 64 + ch * 32, v);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint32_t piece = (uint32_t)(half * 4 + i);
-            st_shared_v4(chunk + ((piece ^ sw) << 4), pack_relu_h2(x[8 * i + 0], x[8 * i + 1]),
+          for (int i = 0; i < 4; ++i)
+            st_shared_v4(chunk + (((uint32_t)(ch * 4 + i) ^ sw) << 4), pack_relu_h2(x[8 * i + 0], x[8 * i + 1]),
                          pack_relu_h2(x[8 * i + 2], x[8 * i + 3]), pack_relu_h2(x[8 * i + 4], x[8 * i + 5]),
                          pack_relu_h2(x[8 * i + 6], x[8 * i + 7]));
-          }
+          tmem_wait_st();
+          fence_proxy_async_smem();
+          tc_fence_before();
+          signal_chunk(c);
         }
-        tmem_wait_st();
-        fence_proxy_async_smem();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), 0);
       }
     };
 
@@ -463,13 +504,16 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         ++n_acc[2];
         tc_fence_after();
         if (hf == 0 && ch == 0) {
-          uint32_t v[4];
-          tmem_ld_32x4(tmem_base + lane_addr + kColT, v);
+          uint32_t v[8];   // columns 0-3: x W_hi, 4-7: x (W - W_hi) * 2^10
+          tmem_ld_32x8(tmem_base + lane_addr + kColT, v);
           tmem_wait_ld();
           if (grow < p.n_rows) {
             const float4 bo = __ldg(reinterpret_cast<const float4*>(p.bias + 11 * 512));
-            const float s0 = __uint_as_float(v[0]) + bo.x, s1 = __uint_as_float(v[1]) + bo.y;
-            const float s2 = __uint_as_float(v[2]) + bo.z, s3 = __uint_as_float(v[3]) + bo.w;
+            const float k = 1.0f / 1024.0f;
+            const float s0 = (__uint_as_float(v[0]) + k * __uint_as_float(v[4])) + bo.x;
+            const float s1 = (__uint_as_float(v[1]) + k * __uint_as_float(v[5])) + bo.y;
+            const float s2 = (__uint_as_float(v[2]) + k * __uint_as_float(v[6])) + bo.z;
+            const float s3 = (__uint_as_float(v[3]) + k * __uint_as_float(v[7])) + bo.w;
             if (p.pre) p.pre[grow] = make_float4(s0, s1, s2, s3);
             p.out[grow] = make_float4(1.0f / (1.0f + expf(-s0)), 1.0f / (1.0f + expf(-s1)),
                                       1.0f / (1.0f + expf(-s2)), fmaxf(s3, 0.0f));
@@ -494,9 +538,18 @@ pack_weights_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
   if (i >= (int64_t)kLayers * 512 * 512) return;
   const int layer = (int)(i / (512 * 512));
   const int n = (int)((i / 512) % 512), k = (int)(i % 512);
+  // fp16 rounding of the weights is the one error that is coherent over all samples of a ray (the same
+  // perturbed network everywhere); lin_in and lin_out carry 60 % of it and are the two
+  // cheap layers, so they are stored as hi + lo: lin_in's lo part in K columns [64, 64+42) (the x chunk is
+  // multiplied by both), lin_out's lo part, scaled by 2^10 into the normal range, in the spare output rows 4-7.
   float v = 0.0f;
   if (layer == L_IN) {
-    if (k < PN_D_CODE) v = w.lin_in_w[n * PN_D_CODE + k];
+    if (k < PN_D_CODE) {
+      v = w.lin_in_w[n * PN_D_CODE + k];
+    } else if (k >= 64 && k < 64 + PN_D_CODE) {
+      const float f = w.lin_in_w[n * PN_D_CODE + k - 64];
+      v = f - __half2float(__float2half_rn(f));
+    }
   } else if (layer < L_FC) {
     v = w.lin_z_w[layer - L_Z0][n * 512 + k];
   } else if (layer < L_OUT) {
@@ -504,6 +557,9 @@ pack_weights_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
     v = ((layer - L_FC) & 1) ? w.fc1_w[b][n * 512 + k] : w.fc0_w[b][n * 512 + k];
   } else if (n < 4) {
     v = w.lin_out_w[n * 512 + k];
+  } else if (n < 8) {
+    const float f = w.lin_out_w[(n - 4) * 512 + k];
+    v = (f - __half2float(__float2half_rn(f))) * 1024.0f;
   }
   dst[i] = __float2half_rn(v);
 }

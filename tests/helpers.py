@@ -39,11 +39,17 @@ def render_case_inputs(fx):
 
 def emulate_tc_chain(w, feat_z, feat_x, ns, ppo):
     """float64 restatement of the tensor-core ResnetFC chain with its operand rounding: weights and
-    GEMM inputs rounded to fp16, exact accumulation, fp32-exact residual stream and biases.
+    GEMM inputs rounded to fp16 (lin_in / lin_out weights as an fp16 hi + lo pair), exact accumulation, fp32-exact residual stream and biases.
     feat_z (N,512), feat_x (N,>=42) are the (already fp16-valued) kernel inputs.
     Returns (list of h at stages 0..5 incl. biases, raw lin_out outputs (N/ns, 4))."""
     def W(k):
-        return w[k + ".weight"].half().double()
+        t = w[k + ".weight"]
+        hi = t.half()
+        if k == "lin_in":      # stored hi + lo (lo in the second K chunk)
+            return hi.double() + (t - hi.float()).half().double()
+        if k == "lin_out":     # lo scaled by 2^10 in the spare output rows
+            return hi.double() + ((t - hi.float()) * 1024.0).half().double() / 1024.0
+        return hi.double()
 
     def B(k):
         return w[k + ".bias"].double()
