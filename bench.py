@@ -286,7 +286,11 @@ def run_gpu(args):
             "clocks": sampler.summary(),
             "roofline": {"bound": "tensor", "kernel": "ResnetFC chain (%s)" % args.precision, "achieved": achieved,
                          "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
-                         "traffic": None, "peak_source": pk["source"] + ", sustained bf16",
+                         "traffic": chain_traffic(flop_step / MLP_FLOP_PER_POINT[ns] / max(1, n_mlp // max(1, args.steps)))
+                         if args.precision == "fp16" else None,
+                         "traffic_source": "profiles/r01h_chain_ncu_summary.json: ncu dram read+write bytes per MLP row of "
+                                           "one captured launch x average rows per launch of this run",
+                         "peak_source": pk["source"] + ", sustained bf16",
                          "launches_per_step": n_mlp // max(1, args.steps), "ms_per_step": mlp_ms},
             "stage_ms_per_step": {k: v / args.steps for k, v in prof.items()},
         }
@@ -299,6 +303,17 @@ def run_gpu(args):
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def chain_traffic(rows_per_launch):
+    """DRAM bytes per chain launch: measured bytes/row of the committed `ncu --set full` capture (a live run
+    cannot read dram counters) times the rows one launch of this run processes; None without the summary."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01h_chain_ncu_summary.json")
+    try:
+        with open(path) as f:
+            return json.load(f)["dram_bytes_per_row"] * rows_per_launch
+    except (OSError, KeyError, ValueError):
+        return None
 
 
 def main():
