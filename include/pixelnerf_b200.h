@@ -104,6 +104,15 @@ PN_API int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc, in
                       int64_t points_per_object, void* feat_z, void* feat_x, int ldx, int out_dtype,
                       pn_stream_t stream);
 
+/* Tensor-core path: the same projection / positional code as pn_point_features, but instead of
+ * blending the latent it records WHERE the blend reads: taps (N,8) 32-bit words per row =
+ * [texel index of the 4 bilinear taps (view*Hl*Wl + y*Wl + x), their 4 fp32 weights]
+ * (grid_sample(align_corners, border), encoder.py:102-108).  feat_x (N,64) fp16 as above.
+ * The chain kernel applies lin_z through per-texel tables (pn_prepare_latent_tables). */
+PN_API int pn_point_taps(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
+                  const float* xyz, const float* viewdirs, int64_t points_per_object,
+                  void* taps, void* feat_x, pn_stream_t stream);
+
 /* Backward of the latent gather (grid_sample backward w.r.t. its input, encoder.py:102-108):
  * g_latent_nhwc (V,Hl,Wl,512) fp32 += scatter of g_feat_z (N,512) with the bilinear weights.
  * Same point addressing as pn_point_features.  The caller zeroes g_latent_nhwc first and hands
@@ -168,6 +177,15 @@ PN_API int pn_mlp_backward_fp32(const pn_mlp_weights_t* w, const pn_mlp_weights_
  * (15 zero-padded [512][512] fp16 layers + fp32 bias tables); `packed` is a caller-owned
  * 256-byte-aligned device buffer of pn_mlp_tc_packed_bytes(). */
 PN_API size_t pn_mlp_tc_packed_bytes(void);
+
+/* lin_z is linear and the latent row of a point is a convex blend of 4 texels, so
+ * lin_z[b](blend) = blend(lin_z[b](texel)) (resnetfc.py:174-180 after encoder.py:102-108):
+ * tables[b][texel][512] fp16 = lin_z[b](latent[texel]) + lin_z[b].bias + c_b, computed in fp32 once per
+ * (encode, parameter version), with c_0 = lin_in.bias, c_b = blocks[b-1].fc_1.bias folded in (bilinear
+ * weights sum to 1).  n_texels = SB*NS*Hl*Wl; latent_nhwc fp32; workspace n_texels*512 floats. */
+PN_API size_t pn_latent_tables_bytes(int64_t n_texels);
+PN_API int pn_prepare_latent_tables(const pn_mlp_weights_t* w, const float* latent_nhwc, int64_t n_texels,
+                             void* tables, void* workspace, size_t workspace_bytes, pn_stream_t stream);
 PN_API int pn_prepare_weights(const pn_mlp_weights_t* w, void* packed, size_t packed_bytes, pn_stream_t stream);
 
 typedef struct pn_mlp_tc_debug {
@@ -177,14 +195,14 @@ typedef struct pn_mlp_tc_debug {
 
 PN_API size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views);
 
-/* ResnetFC.forward + head like pn_mlp_forward_fp32, on the tensor cores.  feat_z (N,512)
- * and feat_x (N,64) are fp16 (pn_point_features with out_dtype PN_DTYPE_F16, ldx 64), rows
+/* ResnetFC.forward + head like pn_mlp_forward_fp32, on the tensor cores.  The latent rows enter as
+ * `taps` (N,8) + `tables` (pn_point_taps, pn_prepare_latent_tables) and feat_x (N,64) fp16, rows
  * ordered (object, view, point).  With n_views > 1 the per-view blocks 0-2 and the merged
  * blocks 3-4 run as two launches with the fp32 view mean in between (workspace).  dbg may
  * be NULL.  The first 4 bytes of workspace receive a nonzero code if a device-side wait
  * timed out (the launch then fails with a CUDA error instead of hanging). */
-PN_API int pn_mlp_forward_tc(const void* packed, const void* feat_z, const void* feat_x,
-                      int n_objects, int n_views, int64_t points_per_object,
+PN_API int pn_mlp_forward_tc(const void* packed, const void* taps, const void* tables, int64_t n_texels,
+                      const void* feat_x, int n_objects, int n_views, int64_t points_per_object,
                       float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                       const pn_mlp_tc_debug_t* dbg, pn_stream_t stream);
 

@@ -99,7 +99,7 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
                       const float* __restrict__ rays, const float* __restrict__ zs, int n_samples,
                       const float* __restrict__ xyz_in, const float* __restrict__ dirs_in,
                       int64_t ppo, OutT* __restrict__ feat_z, OutT* __restrict__ feat_x, int ldx,
-                      int64_t n_rows) {
+                      int64_t n_rows, uint4* __restrict__ taps) {
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5)) * 32;
   if (row0 >= n_rows) return;
@@ -157,10 +157,15 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     w00 = (1.0f - ax) * (1.0f - ay); w01 = ax * (1.0f - ay);
     w10 = (1.0f - ax) * ay; w11 = ax * ay;
     const uint32_t vbase = (uint32_t)view * (uint32_t)(cam.hl * cam.wl);
-    o00 = (vbase + (uint32_t)(y0 * cam.wl + x0)) * PN_D_LATENT;
-    o01 = (vbase + (uint32_t)(y0 * cam.wl + x1)) * PN_D_LATENT;
-    o10 = (vbase + (uint32_t)(y1 * cam.wl + x0)) * PN_D_LATENT;
-    o11 = (vbase + (uint32_t)(y1 * cam.wl + x1)) * PN_D_LATENT;
+    o00 = vbase + (uint32_t)(y0 * cam.wl + x0);
+    o01 = vbase + (uint32_t)(y0 * cam.wl + x1);
+    o10 = vbase + (uint32_t)(y1 * cam.wl + x0);
+    o11 = vbase + (uint32_t)(y1 * cam.wl + x1);
+    if (taps) {  // tensor-core path: the chain kernel blends per-texel lin_z tables with these
+      taps[row * 2] = make_uint4(o00, o01, o10, o11);
+      taps[row * 2 + 1] = make_uint4(__float_as_uint(w00), __float_as_uint(w01), __float_as_uint(w10), __float_as_uint(w11));
+    }
+    o00 *= PN_D_LATENT; o01 *= PN_D_LATENT; o10 *= PN_D_LATENT; o11 *= PN_D_LATENT;
     // code: [x(3), sin(f_j x + phase_j)(36), R d (3)], zero pad to ldx; 4 elements at a time
     OutT* ox = feat_x + (size_t)row * ldx;
     const float comp[3] = {xr, yr, zr};
@@ -197,6 +202,7 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
       else *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ox) + e0) = make_uint2(0u, 0u);
     }
   }
+  if (taps) return;
   // phase 2: the warp blends the taps of each of its rows
   constexpr int N = Vec16<LatT>::N;
   constexpr int kIters = PN_D_LATENT / (32 * N);
@@ -337,12 +343,33 @@ extern "C" int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc
   if (out_dtype == PN_DTYPE_F32)
     pn::point_features_kernel<float, float><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
         *cam, (const float*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
-        (float*)feat_z, (float*)feat_x, ldx, n_rows);
+        (float*)feat_z, (float*)feat_x, ldx, n_rows, nullptr);
   else
     pn::point_features_kernel<__half, __half><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
         *cam, (const __half*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
-        (__half*)feat_z, (__half*)feat_x, ldx, n_rows);
+        (__half*)feat_z, (__half*)feat_x, ldx, n_rows, nullptr);
   PN_LAUNCH_OK("point_features_kernel");
+  pn::count_launch();
+  return PN_OK;
+}
+
+extern "C" int pn_point_taps(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
+                             const float* xyz, const float* viewdirs, int64_t points_per_object,
+                             void* taps, void* feat_x, pn_stream_t stream) {
+  PN_CHECK_ARG(cam && taps && feat_x, "pn_point_taps: null pointer");
+  PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_taps: camera buffers missing (call encode first)");
+  PN_CHECK_ARG((rays && z && n_samples > 0) || xyz, "pn_point_taps: need rays+z or xyz");
+  PN_CHECK_ARG(!rays || points_per_object % n_samples == 0, "pn_point_taps: P must be a multiple of K");
+  PN_CHECK_ARG(cam->hl > 1 && cam->wl > 1 && cam->n_objects > 0 && cam->n_views > 0, "pn_point_taps: bad camera sizes");
+  PN_CHECK_ARG((int64_t)cam->n_objects * cam->n_views * cam->hl * cam->wl < (1ll << 31), "pn_point_taps: too many texels");
+  PN_CHECK_ARG(((uintptr_t)taps & 15) == 0 && ((uintptr_t)feat_x & 15) == 0, "pn_point_taps: misaligned buffer");
+  const int64_t n_rows = (int64_t)cam->n_objects * cam->n_views * points_per_object;
+  if (n_rows == 0) return PN_OK;
+  const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
+  pn::point_features_kernel<__half, __half><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+      *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
+      (uint4*)taps);
+  PN_LAUNCH_OK("point_features_kernel(taps)");
   pn::count_launch();
   return PN_OK;
 }

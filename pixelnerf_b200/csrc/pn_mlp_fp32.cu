@@ -428,6 +428,49 @@ extern "C" int pn_mlp_forward_fp32(const pn_mlp_weights_t* w, const float* feat_
   return PN_OK;
 }
 
+// ---- per-texel lin_z tables for the tensor-core chain (include/pixelnerf_b200.h) --------------
+namespace pn {
+__global__ void __launch_bounds__(256)
+table_finish_kernel(const float4* __restrict__ src, const float* __restrict__ c0, const float* __restrict__ c1,
+                    uint2* __restrict__ dst, int64_t total4) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total4) return;
+  const int n = (int)(i % (PN_D_HIDDEN / 4)) * 4;
+  float4 v = src[i];
+  v.x += c0[n] + c1[n]; v.y += c0[n + 1] + c1[n + 1]; v.z += c0[n + 2] + c1[n + 2]; v.w += c0[n + 3] + c1[n + 3];
+  const __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+  dst[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+}  // namespace pn
+
+extern "C" size_t pn_latent_tables_bytes(int64_t n_texels) {
+  return (size_t)(n_texels > 0 ? n_texels : 0) * PN_COMBINE_LAYER * PN_D_HIDDEN * sizeof(__half);
+}
+
+extern "C" int pn_prepare_latent_tables(const pn_mlp_weights_t* w, const float* latent_nhwc, int64_t n_texels,
+                                        void* tables, void* workspace, size_t workspace_bytes, pn_stream_t stream) {
+  using namespace pn;
+  PN_CHECK_ARG(w && latent_nhwc && tables && workspace, "pn_prepare_latent_tables: null pointer");
+  PN_CHECK_ARG(n_texels > 0, "pn_prepare_latent_tables: no texels");
+  PN_CHECK_ARG(workspace_bytes >= (size_t)n_texels * PN_D_HIDDEN * sizeof(float), "pn_prepare_latent_tables: workspace too small");
+  PN_CHECK_ARG(((uintptr_t)tables & 15) == 0 && ((uintptr_t)workspace & 15) == 0, "pn_prepare_latent_tables: misaligned buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* tmp = (float*)workspace;
+  const int64_t total4 = n_texels * (PN_D_HIDDEN / 4);
+  int rc;
+  for (int b = 0; b < PN_COMBINE_LAYER; ++b) {
+    // fp32 lin_z[b] of every texel (no bias yet), then + lin_z bias + the constant folded into this stage
+    if ((rc = launch_linear<false, false>(latent_nhwc, PN_D_LATENT, w->lin_z_w[b], PN_D_LATENT, nullptr, tmp, n_texels,
+                                          PN_D_LATENT, st))) return rc;
+    const float* folded = b == 0 ? w->lin_in_b : w->fc1_b[b - 1];
+    table_finish_kernel<<<ceil_div(total4, 256), 256, 0, st>>>(
+        (const float4*)tmp, w->lin_z_b[b], folded, (uint2*)tables + (size_t)b * total4, total4);
+    PN_LAUNCH_OK("table_finish_kernel");
+    count_launch();
+  }
+  return PN_OK;
+}
+
 // ---- training: forward that keeps every activation, and the hand-written backward ------------
 // Activation slots (each n_rows x 512 fp32): slot 2b = H_b (input of block b: residual stream after
 // lin_z[b] / the view mean), slot 2b+1 = T_b (fc_0 output, pre-relu), slot 10 = H_5 (input of lin_out).

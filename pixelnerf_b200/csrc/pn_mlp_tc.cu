@@ -1,7 +1,11 @@
 // ResnetFC chain on the 5th-generation tensor cores (reference src/model/resnetfc.py:132-184,
 // block :53-62, head src/model/models.py:257-266): one persistent kernel runs
 //   lin_in, 3 x lin_z, 5 x (fc_0, fc_1), lin_out
-// for a tile of rows with every activation resident on chip.
+// for a tile of rows with every activation resident on chip.  lin_z is not a GEMM here: it is linear
+// and a point's latent row is a convex blend of four texels, so lin_z[b](blend) = blend of per-texel
+// tables lin_z[b](texel) (pn_prepare_latent_tables, once per encode): the epilogue gathers the four
+// table rows of each point and adds their blend to the residual stream (22 % fewer tensor FLOPs,
+// no 1 KB latent row per point in HBM).
 //
 // Work decomposition.  A CTA pair (2-CTA cluster, tcgen05 cta_group::2) owns a tile of 128
 // feature rows, 64 per CTA.  Every GEMM is issued as M=128 x N=256 x K=16 tcgen05.mma
@@ -12,22 +16,22 @@
 // accumulator takes 128 columns: lanes 0-63 hold output features [0,128) of the block, lanes
 // 64-127 features [128,256).  Columns [0,256) hold the fp32 residual stream h (two 256-wide
 // blocks), columns [256,512) hold t = fc_0(relu(h)) (and lin_out's result).  h is never
-// rounded: lin_z and fc_1 accumulate into it in place (tcgen05.mma accumulate), biases are
-// added as a cumulative per-column vector whenever h is read.
+// rounded: fc_1 accumulates into it in place (tcgen05.mma accumulate); before blocks 0-2 the
+// epilogue adds the lin_z table blend (all biases up to there folded into the tables) with a
+// tcgen05.ld / tcgen05.st read-modify-write while h is quiescent, later biases are added as a
+// cumulative per-column vector whenever h is read.
 //
-// Shared memory per CTA (225 KB): ACT (relu'd fp16 operand of the next GEMM, 8 K-chunks of
-// [64 rows x 64 fp16], 128-byte swizzled, 64 KB), a 4-slot ring of operand chunks through
-// which the tile's x and z stream by TMA (8 KB each; z is re-read from L2 for each of the
-// three lin_z, K-outer, so it never needs 64 KB of residency) and a 4-stage ring of weight
+// Shared memory per CTA (209 KB): ACT (relu'd fp16 operand of the next GEMM, 8 K-chunks of
+// [64 rows x 64 fp16], 128-byte swizzled, 64 KB), two 8 KB slots for the tile's positional-code
+// chunk x (TMA) and a 4-stage ring of weight
 // tiles [128 features x 128 K] (32 KB each, two TMA boxes).  128 KB of weights in flight per
 // CTA is what covers the L2 round trip; one stage = 8 tcgen05.mma = 512 tensor-pipe clocks.
 //
 // Overlap.  A GEMM is issued in four quarters (block0,K-lo) (block1,K-lo) (block0,K-hi)
 // (block1,K-hi): block 0's accumulator is complete after the third quarter, so the epilogue
 // warps convert it to the next operand's K-chunks 0-3 while the fourth quarter runs, and
-// the next GEMM's first two quarters only need chunks 0-3.  lin_z of the next block is
-// issued between fc_0 and fc_1.  The tensor pipe therefore never waits for an epilogue in
-// steady state; the next tile's x/z rows are pulled into L2 a tile ahead.
+// the next GEMM's first two quarters only need chunks 0-3.  The table gather of an h epilogue
+// is issued before that epilogue waits for its accumulator, so it is off the critical path.
 #include "pn_common.cuh"
 #include "pn_tc_ptx.cuh"
 
@@ -42,7 +46,7 @@ constexpr int kChunkBytes = kRows * 128;   // [64 rows x 64 fp16]
 constexpr int kWBoxBytes = 128 * 128;      // TMA box [128 features x 64 fp16]
 constexpr int kWStageBytes = 2 * kWBoxBytes;   // one ring stage = K 128 = two boxes
 constexpr int kStages = 4;
-constexpr int kASlots = 4;                 // operand-chunk ring (x and z stream through it)
+constexpr int kASlots = 2;                 // x chunk of the current and the next tile
 constexpr int kOffAct = 0;
 constexpr int kOffA = 8 * kChunkBytes;
 constexpr int kOffW = kOffA + kASlots * kChunkBytes;
@@ -57,7 +61,9 @@ enum {
   BAR_COUNT = BAR_ACC + 4
 };
 constexpr int kOffTmemPtr = kOffBar + BAR_COUNT * 8;
-constexpr int kSmemBytes = kOffTmemPtr + 16;
+constexpr int kOffStage = (kOffTmemPtr + 16 + 127) / 128 * 128;   // per epilogue warp: [32 rows x 32 fp16] table-blend staging
+constexpr int kStageBytes = 32 * 64;
+constexpr int kSmemBytes = kOffStage + 8 * kStageBytes;
 constexpr int kSmemAlloc = kSmemBytes + 1024;  // slack for the manual 1024-byte alignment
 static_assert(kSmemAlloc <= 227 * 1024, "shared memory budget");
 
@@ -74,6 +80,9 @@ constexpr size_t kBiasBytes = ((size_t)kBiasFloats * 4 + 255) / 256 * 256;
 
 struct ChainParams {
   const float* bias;     // table of the segment being run
+  const uint4* taps;     // (rows, 2): 4 texel indices, 4 bilinear weights (pn_point_taps)
+  const __half* tables;  // [3][n_texels][512] per-texel lin_z tables (pn_prepare_latent_tables)
+  int64_t table_stride;  // n_texels * 512
   float4* out;           // (rows, 4) [sigmoid rgb, relu sigma], segments ending in lin_out
   float4* pre;           // optional raw lin_out outputs
   float* h_io;           // segment [0,3): fp32 h written here; segment [3,5]: view-mean of it read
@@ -114,6 +123,11 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 // relu + round-to-nearest fp16 pair in one instruction (a in the low half)
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
   uint32_t d;
   asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
@@ -121,8 +135,8 @@ __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_z,
-                 const __grid_constant__ CUtensorMap map_x, const ChainParams p) {
+mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
+                 const ChainParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -136,7 +150,6 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   cluster_sync_all();
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&map_w);
-    prefetch_tensormap(&map_z);
     prefetch_tensormap(&map_x);
   }
   if (warp == 1 && lane == 0) {
@@ -198,37 +211,17 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) load_w(layer, q & 1, (q >> 1) * 4 + h, (q >> 1) * 4 + h + 2);
     };
-    auto load_lin_z = [&](int layer, int row0) {   // K-outer: z chunk pair, then both blocks' weights
-#pragma unroll 1
-      for (int kp = 0; kp < 4; ++kp) {
-        load_a(&map_z, (2 * kp) * 64, row0);
-        load_a(&map_z, (2 * kp + 1) * 64, row0);
-        load_w(layer, 0, 2 * kp, 2 * kp + 1);
-        load_w(layer, 1, 2 * kp, 2 * kp + 1);
-      }
-    };
-    auto prefetch_l2 = [&](int tile) {   // next tile's x / z rows: DRAM -> L2 ahead of the operand ring
-      if (elect_one()) {
-        const int row0 = tile * kTileRows + (int)rank * kRows;
-        tma_prefetch_2d(&map_x, 0, row0);
-        for (int c = 0; c < 8; ++c) tma_prefetch_2d(&map_z, c * 64, row0);
-      }
-      __syncwarp();
-    };
 #pragma unroll 1
     for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters) {
       const int row0 = tile * kTileRows + (int)rank * kRows;
       if (full_front) {
-        if (tile + n_clusters < p.n_tiles) prefetch_l2(tile + n_clusters);
         load_a(&map_x, 0, row0);
         load_w(L_IN, 0, 0, 1);                 // hi and lo halves of lin_in
         load_w(L_IN, 1, 0, 1);
-        load_lin_z(L_Z0, row0);
       }
 #pragma unroll 1
       for (int b = p.first_block; b < p.last_block; ++b) {
         load_fc(L_FC + 2 * b);
-        if (b < 2) load_lin_z(L_Z0 + b + 1, row0);
         load_fc(L_FC + 2 * b + 1);
       }
       if (has_head) {
@@ -303,19 +296,6 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       ++gen;
     };
-    // h += lin_z(z): z streams through the operand ring, K-outer
-    auto gemm_z = [&](bool completes_h) {
-#pragma unroll 1
-      for (int kp = 0; kp < 4; ++kp) {
-        const uint32_t a0 = take_a(), a1 = take_a();
-        tc_fence_after();
-        item(a0, a1, kColH, false, 0xFFu);
-        item(a0, a1, kColH + 128, false, 0xFFu);
-        release_a(a0);
-        release_a(a1);
-      }
-      if (completes_h) { commit(BAR_ACC + 0); commit(BAR_ACC + 1); }
-    };
 #pragma unroll 1
     for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters) {
       if (full_front) {
@@ -324,12 +304,12 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         item(xa, xa, kColH, true, 0x77u);      // lin_in: x (K = 48 of the zero-padded 64) times W_hi, then W_lo
         item(xa, xa, kColH + 128, true, 0x77u);
         release_a(xa);
-        gemm_z(true);                          // lin_z[0] completes h_0
+        commit(BAR_ACC + 0);                   // the h_0 epilogue adds the lin_z[0] table blend
+        commit(BAR_ACC + 1);
       }
 #pragma unroll 1
       for (int b = p.first_block; b < p.last_block; ++b) {
         gemm_act(kColT, true, 1);              // t = fc_0(relu(h))
-        if (b < 2) gemm_z(false);              // h += lin_z[b+1](z), overlaps the epilogue of t
         gemm_act(kColH, false, 0);             // h += fc_1(relu(t))
       }
       if (has_head) {
@@ -363,11 +343,89 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // of the two 64-feature K-chunks its lane half holds (chunk = nb*4 + 2*hf + half) the 32 features
     // [32*ch, 32*ch+32).  Both warps of a lane quarter work on the same chunk, so chunks 2*hf of a block
     // are complete after half of the epilogue: the issuer consumes K in the order (0,2),(1,3).
-    auto ld_bias8 = [&](const float* src, float4 (&bv)[8]) {
+    auto ld_bias32 = [&](const float* src, float (&bv)[32]) {
 #pragma unroll
       for (int i = 0; i < 8; ++i)
         asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];"
-                     : "=f"(bv[i].x), "=f"(bv[i].y), "=f"(bv[i].z), "=f"(bv[i].w) : "l"(src + 4 * i));
+                     : "=f"(bv[4 * i]), "=f"(bv[4 * i + 1]), "=f"(bv[4 * i + 2]), "=f"(bv[4 * i + 3]) : "l"(src + 4 * i));
+    };
+    // g[0..32) = this lane's row of the lin_z table blend, 32 features starting at `tab`: sum over the row's
+    // four bilinear taps of weight * table row.  Loaded cooperatively -- one 16-byte load instruction covers 8
+    // rows x 64 contiguous bytes (lane = (row in group, 16-byte piece)), each lane blends the four taps of its
+    // piece in fp32 -- then transposed to the tensor-memory layout (lane = row) through a 2 KB per-warp staging
+    // buffer in fp16.  (One row per lane straight from global costs 32 L1 line lookups per instruction for
+    // 16 useful bytes each: 8 % of the L1 data path, measured as 76 % busy epilogue warps, profiles/ r01j.)
+    const uint32_t stage = smem_base + kOffStage + (uint32_t)(warp - kEpiWarp0) * kStageBytes;
+    // Both 32-feature halves of one block for this warp's rows (tab, tab + 64).  All global loads of a half
+    // are issued before any of them is consumed (one L2 round trip per half instead of one per 8 rows); the
+    // staging accesses carry no compiler memory barrier so the second half's loads can move above the first
+    // half's arithmetic -- __syncwarp() orders the staging writes against the reads.
+    auto gather_block = [&](const __half* tab, int64_t wrow0, float (&g0)[32], float (&g1)[32]) {
+      uint4 ti[4], tw[4];
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int64_t row = wrow0 + it * 8 + (lane >> 2);
+        ti[it] = tw[it] = make_uint4(0u, 0u, 0u, 0u);
+        if (row < p.n_rows) {
+          ti[it] = __ldg(p.taps + row * 2);
+          tw[it] = __ldg(p.taps + row * 2 + 1);
+        }
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const uint4* src = reinterpret_cast<const uint4*>(tab + half * 64) + (lane & 3);
+        uint4 t[4][4];
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          t[it][0] = __ldg(src + (size_t)ti[it].x * 64);
+          t[it][1] = __ldg(src + (size_t)ti[it].y * 64);
+          t[it][2] = __ldg(src + (size_t)ti[it].z * 64);
+          t[it][3] = __ldg(src + (size_t)ti[it].w * 64);
+        }
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int rr = it * 8 + (lane >> 2);
+          const float wt[4] = {__uint_as_float(tw[it].x), __uint_as_float(tw[it].y), __uint_as_float(tw[it].z),
+                               __uint_as_float(tw[it].w)};
+          float acc[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t tv[4] = {t[it][k].x, t[it][k].y, t[it][k].z, t[it][k].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&tv[j]));
+              acc[2 * j] = fmaf(wt[k], f.x, acc[2 * j]);
+              acc[2 * j + 1] = fmaf(wt[k], f.y, acc[2 * j + 1]);
+            }
+          }
+          uint32_t pk[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const __half2 h2 = __floats2half2_rn(acc[2 * j], acc[2 * j + 1]);
+            pk[j] = *reinterpret_cast<const uint32_t*>(&h2);
+          }
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                       ::"r"(stage + rr * 64 + ((uint32_t)((lane & 3) ^ ((rr >> 1) & 3)) << 4)),
+                         "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]));
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t tv[4];
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(tv[0]), "=r"(tv[1]), "=r"(tv[2]), "=r"(tv[3])
+                       : "r"(stage + lane * 64 + ((uint32_t)(j ^ ((lane >> 1) & 3)) << 4)));
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&tv[i]));
+            if (half == 0) { g0[8 * j + 2 * i] = f.x; g0[8 * j + 2 * i + 1] = f.y; }
+            else { g1[8 * j + 2 * i] = f.x; g1[8 * j + 2 * i + 1] = f.y; }
+          }
+        }
+        __syncwarp();
+      }
     };
     // fp32 dump of (accumulator + bias) of one block: segment end (h_io) and the debug tap
     auto dump_block = [&](uint32_t tcol, const float* bias_vec, int nb, float* dst, int64_t grow) {
@@ -394,20 +452,28 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), 0);
     };
     // mode 0: relu -> ACT operand; mode 1: dump fp32 to h_io (segment end)
-    auto epi = [&](int region, const float* bias_vec, int mode, int64_t grow, bool dbg) {
+    // gather_b >= 0 (h before blocks 0-2): add the lin_z[gather_b] table blend instead of a bias vector and
+    // write the sum back to tensor memory, so the residual stream carries it from here on.
+    auto epi = [&](int region, const float* bias_vec, int gather_b, int mode, int64_t grow, bool dbg) {
 #pragma unroll 1
       for (int nb = 0; nb < 2; ++nb) {
         const int a = region * 2 + nb;
         const int c0 = nb * 4 + 2 * hf;
         const uint32_t tcol = tmem_base + lane_addr + (region ? kColT : kColH) + nb * 128 + ch * 32;
-        // the bias loads are in flight while the accumulator is still being produced
-        float4 b0[8], b1[8];
-        ld_bias8(bias_vec + c0 * 64 + 32 * ch, b0);
-        ld_bias8(bias_vec + c0 * 64 + 64 + 32 * ch, b1);
+        // the addend (bias, or the gathered table blend) is fetched while the accumulator is still being produced
+        float b0[32], b1[32];
+        if (gather_b >= 0) {
+          const __half* tab = p.tables + (size_t)gather_b * p.table_stride + c0 * 64 + 32 * ch;
+          const int64_t wrow0 = grow - lane;   // first row of this warp's lane quarter
+          gather_block(tab, wrow0, b0, b1);
+        } else {
+          ld_bias32(bias_vec + c0 * 64 + 32 * ch, b0);
+          ld_bias32(bias_vec + c0 * 64 + 64 + 32 * ch, b1);
+        }
         wait_bar<false>(bar(BAR_ACC + a), n_acc[a] & 1, p.err, 0x300 + a);
         ++n_acc[a];
         tc_fence_after();
-        if (dbg) dump_block(tcol, bias_vec, nb, p.debug_h, grow);
+        if (dbg && gather_b < 0) dump_block(tcol, bias_vec, nb, p.debug_h, grow);
         if (mode == 1) {
           dump_block(tcol, bias_vec, nb, p.h_io, grow);
           tc_fence_before();
@@ -419,28 +485,43 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         tmem_ld_32x32(tcol, v0);
         tmem_ld_32x32(tcol + 64, v1);
         tmem_wait_ld();
-        tc_fence_before();
         const uint32_t dst = smem_base + kOffAct + c0 * kChunkBytes + row_off;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float4 ba = b0[2 * i], bb = b0[2 * i + 1];
-          st_shared_v4(dst + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
-                       pack_relu_h2(__uint_as_float(v0[8 * i + 0]) + ba.x, __uint_as_float(v0[8 * i + 1]) + ba.y),
-                       pack_relu_h2(__uint_as_float(v0[8 * i + 2]) + ba.z, __uint_as_float(v0[8 * i + 3]) + ba.w),
-                       pack_relu_h2(__uint_as_float(v0[8 * i + 4]) + bb.x, __uint_as_float(v0[8 * i + 5]) + bb.y),
-                       pack_relu_h2(__uint_as_float(v0[8 * i + 6]) + bb.z, __uint_as_float(v0[8 * i + 7]) + bb.w));
+        for (int i = 0; i < 32; ++i) {
+          b0[i] += __uint_as_float(v0[i]);
+          b1[i] += __uint_as_float(v1[i]);
         }
+        if (gather_b >= 0) {   // h <- h + blend: read-modify-write while no MMA touches h
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            v0[i] = __float_as_uint(b0[i]);
+            v1[i] = __float_as_uint(b1[i]);
+          }
+          tmem_st_32x32(tcol, v0);
+          tmem_st_32x32(tcol + 64, v1);
+          if (dbg && grow < p.n_rows) {
+            float4* d0 = reinterpret_cast<float4*>(p.debug_h + grow * 512 + c0 * 64 + 32 * ch);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              d0[i] = make_float4(b0[4 * i], b0[4 * i + 1], b0[4 * i + 2], b0[4 * i + 3]);
+              d0[16 + i] = make_float4(b1[4 * i], b1[4 * i + 1], b1[4 * i + 2], b1[4 * i + 3]);
+            }
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          st_shared_v4(dst + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
+                       pack_relu_h2(b0[8 * i + 0], b0[8 * i + 1]), pack_relu_h2(b0[8 * i + 2], b0[8 * i + 3]),
+                       pack_relu_h2(b0[8 * i + 4], b0[8 * i + 5]), pack_relu_h2(b0[8 * i + 6], b0[8 * i + 7]));
         fence_proxy_async_smem();
+        if (gather_b >= 0) tmem_wait_st();
+        tc_fence_before();
         signal_chunk(c0);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float4 ba = b1[2 * i], bb = b1[2 * i + 1];
+        for (int i = 0; i < 4; ++i)
           st_shared_v4(dst + kChunkBytes + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
-                       pack_relu_h2(__uint_as_float(v1[8 * i + 0]) + ba.x, __uint_as_float(v1[8 * i + 1]) + ba.y),
-                       pack_relu_h2(__uint_as_float(v1[8 * i + 2]) + ba.z, __uint_as_float(v1[8 * i + 3]) + ba.w),
-                       pack_relu_h2(__uint_as_float(v1[8 * i + 4]) + bb.x, __uint_as_float(v1[8 * i + 5]) + bb.y),
-                       pack_relu_h2(__uint_as_float(v1[8 * i + 6]) + bb.z, __uint_as_float(v1[8 * i + 7]) + bb.w));
-        }
+                       pack_relu_h2(b1[8 * i + 0], b1[8 * i + 1]), pack_relu_h2(b1[8 * i + 2], b1[8 * i + 3]),
+                       pack_relu_h2(b1[8 * i + 4], b1[8 * i + 5]), pack_relu_h2(b1[8 * i + 6], b1[8 * i + 7]));
         fence_proxy_async_smem();
         signal_chunk(c0 + 1);
       }
@@ -494,11 +575,11 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       if (!full_front) epi_load(grow);
       for (int b = p.first_block; b < p.last_block; ++b) {
         if (b > p.first_block || full_front)
-          epi(0, p.bias + b * 512, 0, grow, p.debug_h != nullptr && p.debug_stage == b);
-        epi(1, p.bias + (6 + b) * 512, 0, grow, false);
+          epi(0, p.bias + b * 512, b < 3 ? b : -1, 0, grow, p.debug_h != nullptr && p.debug_stage == b);
+        epi(1, p.bias + (6 + b) * 512, -1, 0, grow, false);
       }
       if (has_head) {
-        epi(0, p.bias + 5 * 512, 0, grow, p.debug_h != nullptr && p.debug_stage == 5);
+        epi(0, p.bias + 5 * 512, -1, 0, grow, p.debug_h != nullptr && p.debug_stage == 5);
         // lin_out result: features 0-3 of block 0 = lanes 0-63, columns kColT..+3
         wait_bar<false>(bar(BAR_ACC + 2), n_acc[2] & 1, p.err, 0x310);
         ++n_acc[2];
@@ -521,7 +602,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
         tc_fence_before();
       } else {
-        epi(0, p.bias + p.last_block * 512, 1, grow, false);
+        epi(0, p.bias + p.last_block * 512, -1, 1, grow, false);
       }
     }
   }
@@ -568,11 +649,12 @@ pack_weights_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
 __global__ void __launch_bounds__(512)
 pack_bias_kernel(pn_mlp_weights_t w, float* __restrict__ ta, float* __restrict__ tb) {
   const int n = threadIdx.x;
-  float cb = w.lin_in_b[n] + w.lin_z_b[0][n];
-  ta[0 * 512 + n] = cb;
-  for (int b = 0; b < 5; ++b) {
+  // rows 0-2 unused: lin_in.bias, lin_z biases and fc_1 biases of blocks 0-1 are folded into the lin_z tables,
+  // whose blend the epilogue writes into h; from block 3 on h is read as h + (fc_1 biases of blocks 2..b-1)
+  ta[0 * 512 + n] = ta[1 * 512 + n] = ta[2 * 512 + n] = 0.0f;
+  float cb = 0.0f;
+  for (int b = 2; b < 5; ++b) {
     cb += w.fc1_b[b][n];
-    if (b + 1 < PN_COMBINE_LAYER) cb += w.lin_z_b[b + 1][n];
     ta[(b + 1) * 512 + n] = cb;
   }
   tb[0 * 512 + n] = tb[1 * 512 + n] = tb[2 * 512 + n] = tb[3 * 512 + n] = 0.0f;
@@ -614,7 +696,7 @@ static int make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t co
   return PN_OK;
 }
 
-static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mz, const CUtensorMap& mx, ChainParams p,
+static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, ChainParams p,
                         cudaStream_t st) {
   static bool attr_set = false;  // idempotent; a benign race at worst repeats the call
   if (!attr_set) {
@@ -626,7 +708,7 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mz, const CUte
   PN_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   p.n_tiles = (int)((p.n_rows + kTileRows - 1) / kTileRows);
   const int clusters = p.n_tiles < sms / 2 ? p.n_tiles : sms / 2;
-  mlp_chain_kernel<<<2 * clusters, kThreads, kSmemAlloc, st>>>(mw, mz, mx, p);
+  mlp_chain_kernel<<<2 * clusters, kThreads, kSmemAlloc, st>>>(mw, mx, p);
   PN_LAUNCH_OK("mlp_chain_kernel");
   count_launch();
   return PN_OK;
@@ -661,25 +743,27 @@ extern "C" size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views) {
   return 256 + (n_views > 1 && n_rows > 0 ? (size_t)n_rows * 512 * sizeof(float) : 0);
 }
 
-extern "C" int pn_mlp_forward_tc(const void* packed, const void* feat_z, const void* feat_x, int n_objects,
+extern "C" int pn_mlp_forward_tc(const void* packed, const void* taps, const void* tables, int64_t n_texels,
+                                 const void* feat_x, int n_objects,
                                  int n_views, int64_t points_per_object, float* out, float* pre_act,
                                  void* workspace, size_t workspace_bytes, const pn_mlp_tc_debug_t* dbg,
                                  pn_stream_t stream) {
   using namespace pn::tc;
-  PN_CHECK_ARG(packed && feat_z && feat_x && out && workspace, "pn_mlp_forward_tc: null pointer");
+  PN_CHECK_ARG(packed && taps && tables && feat_x && out && workspace, "pn_mlp_forward_tc: null pointer");
+  PN_CHECK_ARG(n_texels > 0, "pn_mlp_forward_tc: no texels");
   PN_CHECK_ARG(n_objects > 0 && n_views > 0 && points_per_object >= 0, "pn_mlp_forward_tc: bad sizes");
   const int64_t n_rows = (int64_t)n_objects * n_views * points_per_object;
   const int64_t n_pts = (int64_t)n_objects * points_per_object;
   if (n_rows == 0) return PN_OK;
   PN_CHECK_ARG(n_rows < (1ll << 31) - 256, "pn_mlp_forward_tc: too many rows for one launch");
   PN_CHECK_ARG(workspace_bytes >= pn_mlp_tc_workspace_bytes(n_rows, n_views), "pn_mlp_forward_tc: workspace too small");
-  PN_CHECK_ARG(((uintptr_t)workspace & 255) == 0 && ((uintptr_t)feat_z & 15) == 0 && ((uintptr_t)feat_x & 15) == 0,
+  PN_CHECK_ARG(((uintptr_t)workspace & 255) == 0 && ((uintptr_t)taps & 15) == 0 && ((uintptr_t)tables & 15) == 0 &&
+                   ((uintptr_t)feat_x & 15) == 0,
                "pn_mlp_forward_tc: misaligned buffer");
   cudaStream_t st = (cudaStream_t)stream;
-  CUtensorMap mw, mz, mx;
+  CUtensorMap mw, mx;
   int rc;
   if ((rc = make_map(&mw, packed, (uint64_t)kLayers * 512, 512, 1024, 128))) return rc;
-  if ((rc = make_map(&mz, feat_z, (uint64_t)n_rows, 512, 1024, kRows))) return rc;
   if ((rc = make_map(&mx, feat_x, (uint64_t)n_rows, 64, 128, kRows))) return rc;
   unsigned int* err = (unsigned int*)workspace;
   PN_CUDA_OK(cudaMemsetAsync(err, 0, 4, st));
@@ -687,6 +771,9 @@ extern "C" int pn_mlp_forward_tc(const void* packed, const void* feat_z, const v
   p.out = (float4*)out;
   p.pre = (float4*)pre_act;
   p.err = err;
+  p.taps = (const uint4*)taps;
+  p.tables = (const __half*)tables;
+  p.table_stride = n_texels * 512;
   p.ppo = points_per_object;
   p.n_views = n_views;
   p.debug_h = dbg ? dbg->h : nullptr;
@@ -695,13 +782,13 @@ extern "C" int pn_mlp_forward_tc(const void* packed, const void* feat_z, const v
   const float* tb = (const float*)((const char*)packed + kPackedWeightBytes + kBiasBytes);
   if (n_views == 1) {
     p.bias = ta; p.n_rows = n_rows; p.first_block = 0; p.last_block = 5;
-    return launch_chain(mw, mz, mx, p, st);
+    return launch_chain(mw, mx, p, st);
   }
   // NS > 1: blocks 0-2 per (view, point) row, then the view mean (resnetfc.py:152-172) feeds blocks 3-4
   p.h_io = (float*)((char*)workspace + 256);
   p.bias = ta; p.n_rows = n_rows; p.first_block = 0; p.last_block = 3;
-  if ((rc = launch_chain(mw, mz, mx, p, st))) return rc;
+  if ((rc = launch_chain(mw, mx, p, st))) return rc;
   p.bias = tb; p.n_rows = n_pts; p.first_block = 3; p.last_block = 5;
   p.debug_h = (dbg && dbg->stage >= 4) ? dbg->h : nullptr;
-  return launch_chain(mw, mz, mx, p, st);
+  return launch_chain(mw, mx, p, st);
 }

@@ -58,6 +58,7 @@ class PixelNeRFNet(torch.nn.Module):
         assert self.mlp_precision in _PRECISIONS, self.mlp_precision
         self._cam = None
         self._latent_nhwc = {}
+        self._tables = {}
 
     # ------------------------------------------------------------------ encode
     def encode(self, images, poses, focal, z_bounds=None, c=None):
@@ -117,6 +118,7 @@ class PixelNeRFNet(torch.nn.Module):
                          scale_x=float(scale[0]), scale_y=float(scale[1]),
                          n_objects=n_views_total // ns, n_views=ns)
         self._latent_nhwc = {}
+        self._tables = {}
 
     def latent_nhwc(self, dtype):
         """Channels-last copy of encoder.latent in `dtype`, made once per encode()."""
@@ -126,6 +128,21 @@ class PixelNeRFNet(torch.nn.Module):
             src = lat.detach() if self.stop_encoder_grad or not lat.requires_grad else lat.detach()
             self._latent_nhwc = {"key": key, "t": _lib.prepare_latent(src, dtype)}
         return self._latent_nhwc["t"]
+
+    def latent_tables(self, coarse):
+        """Per-texel lin_z tables of one MLP for the tensor-core chain (lin_z of a bilinear blend = blend of
+        lin_z of the texels, resnetfc.py:174-180 after encoder.py:102-108): rebuilt when the latent or any
+        parameter of that MLP changed."""
+        mlp = self._mlp(coarse)
+        lat = self.latent_nhwc(torch.float32)
+        params = mlp.weight_dict()
+        key = (self._latent_nhwc["key"], tuple((q.data_ptr(), q._version) for q in params.values()))
+        slot = "coarse" if mlp is self.mlp_coarse else "fine"
+        hit = self._tables.get(slot)
+        if hit is None or hit[0] != key:
+            hit = (key, _lib.prepare_latent_tables({k: v.detach() for k, v in params.items()}, lat))
+            self._tables[slot] = hit
+        return hit[1]
 
     # ----------------------------------------------------------------- forward
     def _mlp(self, coarse):
@@ -142,9 +159,10 @@ class PixelNeRFNet(torch.nn.Module):
             fz, fx = _lib.point_features(cam, self.latent_nhwc(torch.float32), ppo, rays=rays, z=z, xyz=xyz,
                                          viewdirs=viewdirs, ldx=44)
             return _lib.mlp_forward_fp32(mlp.packed("fp32"), fz, fx, cam["n_objects"], cam["n_views"], ppo)
-        fz, fx = _lib.point_features(cam, self.latent_nhwc(torch.float16), ppo, rays=rays, z=z, xyz=xyz,
-                                     viewdirs=viewdirs, ldx=64)
-        return _lib.mlp_forward_tc(mlp.packed(prec), fz, fx, cam["n_objects"], cam["n_views"], ppo)
+        tables = self.latent_tables(coarse)
+        _, hl, wl, _ = self.latent_nhwc(torch.float32).shape
+        taps, fx = _lib.point_taps(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
+        return _lib.mlp_forward_tc(mlp.packed(prec), taps, tables, fx, cam["n_objects"], cam["n_views"], ppo)
 
     def forward(self, xyz, coarse=True, viewdirs=None, far=False):
         """(SB,B,3) world points -> (SB,B,4) [sigmoid rgb, relu sigma].  Reference models.py:146-266."""

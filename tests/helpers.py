@@ -37,10 +37,17 @@ def render_case_inputs(fx):
     )
 
 
-def emulate_tc_chain(w, feat_z, feat_x, ns, ppo):
-    """float64 restatement of the tensor-core ResnetFC chain with its operand rounding: weights and
-    GEMM inputs rounded to fp16 (lin_in / lin_out weights as an fp16 hi + lo pair), exact accumulation, fp32-exact residual stream and biases.
-    feat_z (N,512), feat_x (N,>=42) are the (already fp16-valued) kernel inputs.
+def make_taps(idx, wt):
+    """(N,4) texel indices + (N,4) fp32 bilinear weights -> the (N,8) int32 record pn_point_taps writes."""
+    return torch.cat([idx.to(torch.int32), wt.float().contiguous().view(torch.int32)], dim=1).contiguous()
+
+
+def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo):
+    """float64 restatement of the tensor-core ResnetFC chain with its roundings: fc / lin_out weights and
+    GEMM inputs rounded to fp16 (lin_in / lin_out weights as an fp16 hi + lo pair), exact accumulation,
+    fp32-exact residual stream; lin_z through per-texel tables rounded to fp16 (biases folded as in
+    pn_prepare_latent_tables), blended with the row's four taps and rounded to fp16 once more.
+    idx, wt (N,4): texel indices / bilinear weights; latent (T,512) fp32; feat_x (N,>=42) fp16-valued.
     Returns (list of h at stages 0..5 incl. biases, raw lin_out outputs (N/ns, 4))."""
     def W(k):
         t = w[k + ".weight"]
@@ -57,17 +64,26 @@ def emulate_tc_chain(w, feat_z, feat_x, ns, ppo):
     def q(t):
         return torch.relu(t).half().double()
 
-    z, x = feat_z.double(), feat_x[:, :42].double()
-    h = x @ W("lin_in").T + B("lin_in")
+    def table_blend(b):
+        folded = B("lin_in") if b == 0 else B(f"blocks.{b - 1}.fc_1")
+        tab = latent.double() @ w[f"lin_z.{b}.weight"].double().T + B(f"lin_z.{b}") + folded
+        tab = tab.float().half().double()
+        # blended in fp32, handed to the tensor-memory layout through an fp16 staging buffer
+        return (tab[idx.long()] * wt.double().unsqueeze(-1)).sum(1).float().half().double()
+
+    x = feat_x[:, :42].double()
+    h = x @ W("lin_in").T
     stages = []
     for b in range(5):
         if b == 3 and ns > 1:
             h = h.reshape(-1, ns, ppo, 512).sum(1).div(ns).reshape(-1, 512)
         if b < 3:
-            h = h + z @ W(f"lin_z.{b}").T + B(f"lin_z.{b}")
+            h = h + table_blend(b)
         stages.append(h)
         t = q(h) @ W(f"blocks.{b}.fc_0").T + B(f"blocks.{b}.fc_0")
-        h = h + q(t) @ W(f"blocks.{b}.fc_1").T + B(f"blocks.{b}.fc_1")
+        h = h + q(t) @ W(f"blocks.{b}.fc_1").T
+        if b >= 2:             # blocks 0-1: folded into the next table
+            h = h + B(f"blocks.{b}.fc_1")
     stages.append(h)
     pre = q(h) @ W("lin_out").T + B("lin_out")
     return stages, pre

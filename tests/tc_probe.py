@@ -10,7 +10,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
-from helpers import emulate_tc_chain  # noqa: E402
+from helpers import emulate_tc_chain, make_taps  # noqa: E402
 from pixelnerf_b200 import _lib, synthetic as syn  # noqa: E402
 
 
@@ -22,16 +22,23 @@ def main():
     n = ns * ppo
     w = syn.mlp_weights(42)
     g = torch.Generator().manual_seed(0)
-    fz = torch.rand(n, 512, generator=g).half()
+    n_tex = 8 * 24
+    latent = torch.rand(n_tex, 512, generator=g)
+    idx = torch.randint(0, n_tex, (n, 4), generator=g)
+    wt = torch.rand(n, 4, generator=g)
+    wt = wt / wt.sum(1, keepdim=True)
     fx = torch.zeros(n, 64)
     fx[:, :42] = torch.randn(n, 42, generator=g)
     fx = fx.half()
-    ref_stages, ref_pre = emulate_tc_chain(w, fz.float(), fx.float(), ns, ppo)
-    packed = _lib.pack_weights_tc({k: v.cuda() for k, v in w.items()})
+    ref_stages, ref_pre = emulate_tc_chain(w, idx, wt, latent, fx.float(), ns, ppo)
+    wd = {k: v.cuda() for k, v in w.items()}
+    packed = _lib.pack_weights_tc(wd)
+    tables = _lib.prepare_latent_tables(wd, latent.reshape(1, 8, 24, 512).cuda())
+    taps = make_taps(idx, wt).cuda()
     torch.cuda.synchronize()
     print("packed ok", flush=True)
     for st in stages:
-        (out, pre), dbg = _lib.mlp_forward_tc(packed, fz.cuda(), fx.cuda(), 1, ns, ppo, want_pre=True, debug_stage=st)
+        (out, pre), dbg = _lib.mlp_forward_tc(packed, taps, tables, fx.cuda(), 1, ns, ppo, want_pre=True, debug_stage=st)
         torch.cuda.synchronize()
         ref = ref_stages[st]
         d = (dbg.cpu().double() - ref).abs()
