@@ -177,9 +177,9 @@ def run_kernels(args):
     rows = fr.shape[0] * k2
     timeit("point_features_fp16", lambda: _lib.point_features(net._cam, lat, rows, rays=fr, z=zf, ldx=64),
            rows * (512 + 64) * 2 + fr.shape[0] * (32 + 4 * k2) + lat.numel() * 2)
-    # what the tensor-core path runs instead: taps (32 B/row) + positional code (128 B/row), no latent traffic
+    # what the tensor-core path runs instead: positional code + taps record (128 B/row), no latent traffic
     timeit("point_taps", lambda: _lib.point_taps(net._cam, lat.shape[1], lat.shape[2], rows, rays=fr, z=zf),
-           rows * (32 + 128) + fr.shape[0] * (32 + 4 * k2))
+           rows * 128 + fr.shape[0] * (32 + 4 * k2))
     print(json.dumps({"kernels": res, "hbm_peak_GB/s": pk["hbm"], "peak_source": pk["source"], "rays": r}))
 
 

@@ -105,13 +105,14 @@ PN_API int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc, in
                       pn_stream_t stream);
 
 /* Tensor-core path: the same projection / positional code as pn_point_features, but instead of
- * blending the latent it records WHERE the blend reads: taps (N,8) 32-bit words per row =
- * [texel index of the 4 bilinear taps (view*Hl*Wl + y*Wl + x), their 4 fp32 weights]
- * (grid_sample(align_corners, border), encoder.py:102-108).  feat_x (N,64) fp16 as above.
+ * blending the latent it records WHERE the blend reads.  feat_x (N,64) fp16, 128 bytes per row:
+ * columns [0,42) the positional code, [42,48) zero, and in bytes [96,128) the taps record = 8 32-bit
+ * words [texel index of the 4 bilinear taps (view*Hl*Wl + y*Wl + x), their 4 fp32 weights]
+ * (grid_sample(align_corners, border), encoder.py:102-108).
  * The chain kernel applies lin_z through per-texel tables (pn_prepare_latent_tables). */
 PN_API int pn_point_taps(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
                   const float* xyz, const float* viewdirs, int64_t points_per_object,
-                  void* taps, void* feat_x, pn_stream_t stream);
+                  void* feat_x, pn_stream_t stream);
 
 /* Backward of the latent gather (grid_sample backward w.r.t. its input, encoder.py:102-108):
  * g_latent_nhwc (V,Hl,Wl,512) fp32 += scatter of g_feat_z (N,512) with the bilinear weights.
@@ -196,12 +197,12 @@ typedef struct pn_mlp_tc_debug {
 PN_API size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views);
 
 /* ResnetFC.forward + head like pn_mlp_forward_fp32, on the tensor cores.  The latent rows enter as
- * `taps` (N,8) + `tables` (pn_point_taps, pn_prepare_latent_tables) and feat_x (N,64) fp16, rows
+ * `tables` (pn_prepare_latent_tables) + the taps record inside feat_x (N,64) fp16 (pn_point_taps), rows
  * ordered (object, view, point).  With n_views > 1 the per-view blocks 0-2 and the merged
  * blocks 3-4 run as two launches with the fp32 view mean in between (workspace).  dbg may
  * be NULL.  The first 4 bytes of workspace receive a nonzero code if a device-side wait
  * timed out (the launch then fails with a CUDA error instead of hanging). */
-PN_API int pn_mlp_forward_tc(const void* packed, const void* taps, const void* tables, int64_t n_texels,
+PN_API int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t n_texels,
                       const void* feat_x, int n_objects, int n_views, int64_t points_per_object,
                       float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                       const pn_mlp_tc_debug_t* dbg, pn_stream_t stream);

@@ -61,8 +61,8 @@ _SIGNATURES = {
     "pn_mlp_tc_packed_bytes": (_sz, []),
     "pn_prepare_weights": (_int, [C.POINTER(MlpWeights), _vp, _sz, _vp]),
     "pn_mlp_tc_workspace_bytes": (_sz, [_i64, _int]),
-    "pn_mlp_forward_tc": (_int, [_vp, _vp, _vp, _i64, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp, _vp]),
-    "pn_point_taps": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp, _vp]),
+    "pn_mlp_forward_tc": (_int, [_vp, _vp, _i64, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp, _vp]),
+    "pn_point_taps": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp]),
     "pn_latent_tables_bytes": (_sz, [_i64]),
     "pn_prepare_latent_tables": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp, _sz, _vp]),
     "pn_composite_fwd": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
@@ -299,19 +299,19 @@ def point_features_bwd(cam_bufs, g_latent_nhwc, ppo, g_feat_z, *, rays=None, z=N
 
 
 def point_taps(cam_bufs, hl, wl, ppo, *, rays=None, z=None, xyz=None, viewdirs=None):
-    """Tensor-core path: (taps (N,8) int32 = 4 texel indices + 4 fp32 weight bit patterns, feat_x (N,64) fp16)."""
+    """Tensor-core path: feat_x (N,64) fp16 = positional code in columns [0,42) and, in bytes [96,128) of each
+    row, the taps record (4 int32 texel indices + 4 fp32 bilinear weights)."""
     cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
                  cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
     n_rows = cam.n_objects * cam.n_views * ppo
     dev = cam_bufs["poses"].device
-    taps = torch.empty(n_rows, 8, device=dev, dtype=torch.int32)
     feat_x = torch.empty(n_rows, 64, device=dev, dtype=torch.float16)
     rays, z, xyz, viewdirs = _f32c(rays), _f32c(z), _f32c(xyz), _f32c(viewdirs)
     k = 0 if z is None else z.shape[-1]
     with _Timed("features"):
         _check(lib().pn_point_taps(C.byref(cam), _ptr(rays), _ptr(z), k, _ptr(xyz), _ptr(viewdirs), ppo,
-                                   taps.data_ptr(), feat_x.data_ptr(), _stream()), "pn_point_taps")
-    return taps, feat_x
+                                   feat_x.data_ptr(), _stream()), "pn_point_taps")
+    return feat_x
 
 
 def prepare_latent_tables(w, latent_nhwc):
@@ -341,16 +341,14 @@ def pack_weights_tc(w, precision="fp16"):
     return packed
 
 
-def mlp_forward_tc(packed, taps, tables, feat_x, n_objects, n_views, ppo, want_pre=False, debug_stage=None):
-    """taps (N,8) + lin_z tables (3,T,512) fp16 + feat_x (N,64) fp16 -> (SB*ppo, 4) [sigmoid rgb, relu sigma]."""
+def mlp_forward_tc(packed, tables, feat_x, n_objects, n_views, ppo, want_pre=False, debug_stage=None):
+    """lin_z tables (3,T,512) fp16 + feat_x (N,64) fp16 with embedded taps -> (SB*ppo, 4) [sigmoid rgb, relu sigma]."""
     n_rows = n_objects * n_views * ppo
     dev = feat_x.device
-    if taps.shape != (n_rows, 8) or taps.dtype != torch.int32 or not taps.is_contiguous():
-        raise RuntimeError("tensor-core MLP needs contiguous int32 taps of shape (rows, 8)")
+    if feat_x.shape != (n_rows, 64) or feat_x.dtype != torch.float16 or not feat_x.is_contiguous():
+        raise RuntimeError("tensor-core MLP needs contiguous fp16 feat_x of shape (rows, 64)")
     if tables.dtype != torch.float16 or tables.dim() != 3 or tables.shape[0] != COMBINE_LAYER or not tables.is_contiguous():
         raise RuntimeError("tensor-core MLP needs contiguous fp16 lin_z tables of shape (3, texels, 512)")
-    if feat_x.shape[1] != 64:
-        raise RuntimeError("tensor-core MLP needs feat_x with ldx=64")
     out = torch.empty(n_objects * ppo, 4, device=dev, dtype=torch.float32)
     pre = torch.empty_like(out) if want_pre else None
     nbytes = lib().pn_mlp_tc_workspace_bytes(n_rows, n_views)
@@ -360,8 +358,10 @@ def mlp_forward_tc(packed, taps, tables, feat_x, n_objects, n_views, ppo, want_p
         rows = n_rows if debug_stage < COMBINE_LAYER or n_views == 1 else n_objects * ppo
         dbg_h = torch.zeros(rows, D_HIDDEN, device=dev, dtype=torch.float32)
         dbg = C.byref(MlpTcDebug(dbg_h.data_ptr(), int(debug_stage)))
+    if os.environ.get("PN_TC_EXPERIMENT"):   # timing experiments (wrong results), see pn_mlp_tc.cu
+        dbg = C.byref(MlpTcDebug(None, {"no_epilogue": -99, "no_gather": -98}[os.environ["PN_TC_EXPERIMENT"]]))
     with _Timed("mlp"):
-        _check(lib().pn_mlp_forward_tc(packed.data_ptr(), taps.data_ptr(), tables.data_ptr(), tables.shape[1],
+        _check(lib().pn_mlp_forward_tc(packed.data_ptr(), tables.data_ptr(), tables.shape[1],
                                        _ptr(feat_x, torch.float16), n_objects, n_views, ppo, _ptr(out), _ptr(pre), ws.data_ptr(), nbytes, dbg,
                                        _stream()), "pn_mlp_forward_tc")
     ret = (out, pre) if want_pre else out

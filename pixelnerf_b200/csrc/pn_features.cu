@@ -161,9 +161,11 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     o01 = vbase + (uint32_t)(y0 * cam.wl + x1);
     o10 = vbase + (uint32_t)(y1 * cam.wl + x0);
     o11 = vbase + (uint32_t)(y1 * cam.wl + x1);
-    if (taps) {  // tensor-core path: the chain kernel blends per-texel lin_z tables with these
-      taps[row * 2] = make_uint4(o00, o01, o10, o11);
-      taps[row * 2 + 1] = make_uint4(__float_as_uint(w00), __float_as_uint(w01), __float_as_uint(w10), __float_as_uint(w11));
+    if (taps) {  // tensor-core path: the chain kernel blends per-texel lin_z tables with these.  The record
+      // rides in bytes [96,128) of the row's 128-byte positional-code chunk (fp16 columns 48-63, which the
+      // K=48 lin_in MMA never reads), so it reaches shared memory with the TMA load of x.
+      taps[row * 8 + 6] = make_uint4(o00, o01, o10, o11);
+      taps[row * 8 + 7] = make_uint4(__float_as_uint(w00), __float_as_uint(w01), __float_as_uint(w10), __float_as_uint(w11));
     }
     o00 *= PN_D_LATENT; o01 *= PN_D_LATENT; o10 *= PN_D_LATENT; o11 *= PN_D_LATENT;
     // code: [x(3), sin(f_j x + phase_j)(36), R d (3)], zero pad to ldx; 4 elements at a time
@@ -197,7 +199,7 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
             make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
       }
     }
-    for (int e0 = 44; e0 < ldx; e0 += 4) {  // zero padding up to ldx
+    for (int e0 = 44; e0 < (taps ? 48 : ldx); e0 += 4) {  // zero padding up to ldx (up to the taps record)
       if (sizeof(OutT) == 4) *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(0.f, 0.f, 0.f, 0.f);
       else *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ox) + e0) = make_uint2(0u, 0u);
     }
@@ -355,20 +357,20 @@ extern "C" int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc
 
 extern "C" int pn_point_taps(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
                              const float* xyz, const float* viewdirs, int64_t points_per_object,
-                             void* taps, void* feat_x, pn_stream_t stream) {
-  PN_CHECK_ARG(cam && taps && feat_x, "pn_point_taps: null pointer");
+                             void* feat_x, pn_stream_t stream) {
+  PN_CHECK_ARG(cam && feat_x, "pn_point_taps: null pointer");
   PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_taps: camera buffers missing (call encode first)");
   PN_CHECK_ARG((rays && z && n_samples > 0) || xyz, "pn_point_taps: need rays+z or xyz");
   PN_CHECK_ARG(!rays || points_per_object % n_samples == 0, "pn_point_taps: P must be a multiple of K");
   PN_CHECK_ARG(cam->hl > 1 && cam->wl > 1 && cam->n_objects > 0 && cam->n_views > 0, "pn_point_taps: bad camera sizes");
   PN_CHECK_ARG((int64_t)cam->n_objects * cam->n_views * cam->hl * cam->wl < (1ll << 31), "pn_point_taps: too many texels");
-  PN_CHECK_ARG(((uintptr_t)taps & 15) == 0 && ((uintptr_t)feat_x & 15) == 0, "pn_point_taps: misaligned buffer");
+  PN_CHECK_ARG(((uintptr_t)feat_x & 127) == 0, "pn_point_taps: feat_x must be 128-byte aligned");
   const int64_t n_rows = (int64_t)cam->n_objects * cam->n_views * points_per_object;
   if (n_rows == 0) return PN_OK;
   const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
   pn::point_features_kernel<__half, __half><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
       *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
-      (uint4*)taps);
+      (uint4*)feat_x);
   PN_LAUNCH_OK("point_features_kernel(taps)");
   pn::count_launch();
   return PN_OK;

@@ -32,6 +32,8 @@
 // warps convert it to the next operand's K-chunks 0-3 while the fourth quarter runs, and
 // the next GEMM's first two quarters only need chunks 0-3.  The table gather of an h epilogue
 // is issued before that epilogue waits for its accumulator, so it is off the critical path.
+#include <type_traits>
+
 #include "pn_common.cuh"
 #include "pn_tc_ptx.cuh"
 
@@ -80,7 +82,6 @@ constexpr size_t kBiasBytes = ((size_t)kBiasFloats * 4 + 255) / 256 * 256;
 
 struct ChainParams {
   const float* bias;     // table of the segment being run
-  const uint4* taps;     // (rows, 2): 4 texel indices, 4 bilinear weights (pn_point_taps)
   const __half* tables;  // [3][n_texels][512] per-texel lin_z tables (pn_prepare_latent_tables)
   int64_t table_stride;  // n_texels * 512
   float4* out;           // (rows, 4) [sigmoid rgb, relu sigma], segments ending in lin_out
@@ -134,15 +135,23 @@ __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
   return d;
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
                  const ChainParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
-  const int n_clusters = gridDim.x >> 1;
+  // A cluster is two CTA pairs.  Each pair runs its own row tiles; the two pairs walk the same weight
+  // schedule in lockstep and every weight tile is fetched from L2 once per cluster (TMA multicast).
+  const uint32_t rank4 = cluster_ctarank();
+  const uint32_t rank = rank4 & 1;            // rank inside the pair (0 = MMA leader)
+  const uint32_t pair = rank4 >> 1;           // which pair of the cluster
+  const uint16_t pair_mask = (uint16_t)(3u << (2 * pair));
+  const int n_clusters = gridDim.x >> 1;      // historical names: "cluster" below = one CTA pair
   const int cluster_id = blockIdx.x >> 1;
+  // every pair runs the same number of tiles (lockstep ring); tiles past the end are dummies (TMA zero fill,
+  // stores masked by row < n_rows)
+  const int tile_end = (p.n_tiles + n_clusters - 1) / n_clusters * n_clusters;
   auto bar = [&](int i) { return smem_base + kOffBar + i * 8; };
   const bool full_front = p.first_block == 0;      // lin_in / lin_z present (needs X, Z)
   const bool has_head = p.last_block == 5;         // lin_out present
@@ -155,7 +164,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(bar(BAR_W_FULL + s), 1);   // the leader's expect_tx arrive (both CTAs' bytes)
-      mbar_init(bar(BAR_W_EMPTY + s), 1);  // one multicast commit
+      mbar_init(bar(BAR_W_EMPTY + s), 2);  // one multicast commit from each pair of the cluster
     }
     for (int a = 0; a < kASlots; ++a) {
       mbar_init(bar(BAR_A_FULL + a), 1);
@@ -177,24 +186,30 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // The whole warp walks the schedule (warp-uniform control flow keeps addresses and
     // parities in uniform registers); one elected lane issues the copies.  Loads are issued
     // in exactly the order the MMA issuer consumes them, so the two rings cannot deadlock.
-    uint32_t ws = 0, wph = 0;   // weight ring stage / phase
+    // Weight stages are assigned statically (lin_in: 0,1; item i of a 512x512 GEMM: i % 4; lin_out: 0-3) so
+    // that every shared-memory address and barrier is a constant plus one uniform base register; the phase of
+    // each stage is one bit of `wpar`.  The issuer walks the same schedule.
+    uint32_t wpar = 0;          // bit s: phase parity of weight stage s (number of times it was filled, mod 2)
     uint32_t as = 0, aph = 0;   // operand-chunk ring slot / phase
-    // Weight tile for K-chunks kc0 and kc1 (kc1 < 0: kc0 only) of block nb of `layer`: boxes of [128 out x 64 in].
-    auto load_w = [&](int layer, int nb, int kc0, int kc1) {
-      const int nkc = kc1 < 0 ? 1 : 2;
-      wait_bar<false>(bar(BAR_W_EMPTY + ws), wph ^ 1, p.err, 0x100 + ws);
+    // Weight tile for K-chunks kc0 and kc1 of block nb of `layer`: two boxes of [128 out x 64 in].
+    auto load_w = [&](auto stage_c, int layer, int nb, int kc0, int kc1) {
+      constexpr uint32_t ws = decltype(stage_c)::value;
+      wait_bar<false>(bar(BAR_W_EMPTY + ws), ((wpar >> ws) & 1u) ^ 1u, p.err, 0x100 + ws);
+      wpar ^= 1u << ws;
       if (elect_one()) {
         const uint32_t full = bar(BAR_W_FULL + ws);
         // the leader expects both CTAs' bytes; the peer's copies credit the leader's barrier
-        if (rank == 0) mbar_arrive_expect_tx(full, 2 * nkc * kWBoxBytes);
+        if (rank == 0) mbar_arrive_expect_tx(full, 4 * kWBoxBytes);
         const int row = layer * 512 + nb * 256 + (int)rank * 128;
-        tma_load_2d_pair(smem_base + kOffW + ws * kWStageBytes, &map_w, full, kc0 * 64, row);
-        if (kc1 >= 0) tma_load_2d_pair(smem_base + kOffW + ws * kWStageBytes + kWBoxBytes, &map_w, full, kc1 * 64, row);
+        // this CTA and its twin in the other pair (same rank) need the same two boxes: each fetches one and
+        // multicasts it to both
+        const uint16_t twins = (uint16_t)((1u << rank) | (1u << (rank + 2)));
+        tma_load_2d_pair_mc(smem_base + kOffW + ws * kWStageBytes + pair * kWBoxBytes, &map_w, full,
+                            (pair == 0 ? kc0 : kc1) * 64, row, twins);
       }
       __syncwarp();
-      if (++ws == kStages) { ws = 0; wph ^= 1; }
     };
-    // One [64 rows x 64] operand chunk (x, or K-chunk c of z) of this CTA's rows.
+    // One [64 rows x 64] operand chunk (x) of this CTA's rows.
     auto load_a = [&](const CUtensorMap* map, int col, int row0) {
       wait_bar<false>(bar(BAR_A_EMPTY + as), aph ^ 1, p.err, 0x110 + as);
       if (elect_one()) {
@@ -205,19 +220,26 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       __syncwarp();
       if (++as == kASlots) { as = 0; aph ^= 1; }
     };
+    using S0 = std::integral_constant<uint32_t, 0>;
+    using S1 = std::integral_constant<uint32_t, 1>;
+    using S2 = std::integral_constant<uint32_t, 2>;
+    using S3 = std::integral_constant<uint32_t, 3>;
     auto load_fc = [&](int layer) {   // quarter order, two K=128 items per quarter: K-chunks (h, h+2) of the group
 #pragma unroll 1
-      for (int q = 0; q < 4; ++q)
-#pragma unroll 1
-        for (int h = 0; h < 2; ++h) load_w(layer, q & 1, (q >> 1) * 4 + h, (q >> 1) * 4 + h + 2);
+      for (int kg = 0; kg < 2; ++kg) {
+        load_w(S0{}, layer, 0, kg * 4 + 0, kg * 4 + 2);
+        load_w(S1{}, layer, 0, kg * 4 + 1, kg * 4 + 3);
+        load_w(S2{}, layer, 1, kg * 4 + 0, kg * 4 + 2);
+        load_w(S3{}, layer, 1, kg * 4 + 1, kg * 4 + 3);
+      }
     };
 #pragma unroll 1
-    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters) {
+    for (int tile = cluster_id; tile < tile_end; tile += n_clusters) {
       const int row0 = tile * kTileRows + (int)rank * kRows;
       if (full_front) {
         load_a(&map_x, 0, row0);
-        load_w(L_IN, 0, 0, 1);                 // hi and lo halves of lin_in
-        load_w(L_IN, 1, 0, 1);
+        load_w(S0{}, L_IN, 0, 0, 1);           // hi and lo halves of lin_in
+        load_w(S1{}, L_IN, 1, 0, 1);
       }
 #pragma unroll 1
       for (int b = p.first_block; b < p.last_block; ++b) {
@@ -225,20 +247,28 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         load_fc(L_FC + 2 * b + 1);
       }
       if (has_head) {
-#pragma unroll 1
-        for (int kp = 0; kp < 4; ++kp) load_w(L_OUT, 0, 2 * kp, 2 * kp + 1);
+        load_w(S0{}, L_OUT, 0, 0, 1);
+        load_w(S1{}, L_OUT, 0, 2, 3);
+        load_w(S2{}, L_OUT, 0, 4, 5);
+        load_w(S3{}, L_OUT, 0, 6, 7);
       }
     }
   } else if (warp == 1 && rank == 0) {
     // =============================== MMA issuer (leader CTA) ================================
     // Warp-uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit.
-    uint32_t ws = 0, wph = 0, as = 0, aph = 0, gen = 0;
+    using S0 = std::integral_constant<uint32_t, 0>;
+    using S1 = std::integral_constant<uint32_t, 1>;
+    using S2 = std::integral_constant<uint32_t, 2>;
+    using S3 = std::integral_constant<uint32_t, 3>;
+    uint32_t wpar = 0, as = 0, aph = 0, gen = 0;   // wpar bit s: parity to wait for on weight stage s
     const uint32_t w0 = smem_base + kOffW;
     // descriptor = constant high word | (address >> 4): only the low word changes per MMA
     const uint64_t desc_hi = smem_desc_k128(0);
     // One weight stage: nk K=16 steps; A steps [0,4) come from a0, [4,8) from a1 (64-wide chunks).
-    auto item = [&](uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask) {
-      wait_bar<false>(bar(BAR_W_FULL + ws), wph, p.err, 0x200 + ws);
+    auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask) {
+      constexpr uint32_t ws = decltype(stage_c)::value;
+      wait_bar<false>(bar(BAR_W_FULL + ws), (wpar >> ws) & 1u, p.err, 0x200 + ws);
+      wpar ^= 1u << ws;
       tc_fence_after();
       if (elect_one()) {
         const uint32_t b_lo = (w0 + ws * kWStageBytes) >> 4;
@@ -251,13 +281,12 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)a_lo, desc_hi | (uint64_t)bj, kIdesc,
                           (clear && j == 0) ? 0u : 1u);
           }
-        umma_commit_pair(bar(BAR_W_EMPTY + ws), 3);
+        umma_commit_pair(bar(BAR_W_EMPTY + ws), 0xF);   // frees the stage in all four CTAs
       }
       __syncwarp();
-      if (++ws == kStages) { ws = 0; wph ^= 1; }
     };
     auto commit = [&](int b) {
-      if (elect_one()) umma_commit_pair(bar(b), 3);
+      if (elect_one()) umma_commit_pair(bar(b), pair_mask);
       __syncwarp();
     };
     auto wait_chunk = [&](int c) { wait_bar<false>(bar(BAR_ACT + c), gen & 1, p.err, 0x210 + c); };
@@ -278,31 +307,32 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // 512x512 GEMM from the ACT operand, quarter order (see header), D = 2 blocks at d_col.
     auto gemm_act = [&](uint32_t d_col, bool clear, int commit_region) {
 #pragma unroll 1
-      for (int q = 0; q < 4; ++q) {
-        const int nb = q & 1, kg = q >> 1;
-#pragma unroll 1
-        for (int h = 0; h < 2; ++h) {
-          // K-chunks (h, h+2) of the group: the epilogue finishes chunks 0 and 2 of a block first
-          const int c = kg * 4 + h;
-          if (nb == 0) {
-            wait_chunk(c);
-            wait_chunk(c + 2);
-            tc_fence_after();
-          }
-          const uint32_t a = act + c * kChunkBytes;
-          item(a, a + 2 * kChunkBytes, d_col + nb * 128, clear && kg == 0 && h == 0, 0xFFu);
-        }
-        if (kg == 1) commit(BAR_ACC + commit_region * 2 + nb);
+      for (int kg = 0; kg < 2; ++kg) {
+        // K-chunks (h, h+2) of the group: the epilogue finishes chunks 0 and 2 of a block first
+        const uint32_t a = act + kg * 4 * kChunkBytes;
+        const bool clr = clear && kg == 0;
+        wait_chunk(kg * 4 + 0);
+        wait_chunk(kg * 4 + 2);
+        tc_fence_after();
+        item(S0{}, a, a + 2 * kChunkBytes, d_col, clr, 0xFFu);
+        wait_chunk(kg * 4 + 1);
+        wait_chunk(kg * 4 + 3);
+        tc_fence_after();
+        item(S1{}, a + kChunkBytes, a + 3 * kChunkBytes, d_col, false, 0xFFu);
+        if (kg == 1) commit(BAR_ACC + commit_region * 2);
+        item(S2{}, a, a + 2 * kChunkBytes, d_col + 128, clr, 0xFFu);
+        item(S3{}, a + kChunkBytes, a + 3 * kChunkBytes, d_col + 128, false, 0xFFu);
+        if (kg == 1) commit(BAR_ACC + commit_region * 2 + 1);
       }
       ++gen;
     };
 #pragma unroll 1
-    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters) {
+    for (int tile = cluster_id; tile < tile_end; tile += n_clusters) {
       if (full_front) {
         const uint32_t xa = take_a();
         tc_fence_after();
-        item(xa, xa, kColH, true, 0x77u);      // lin_in: x (K = 48 of the zero-padded 64) times W_hi, then W_lo
-        item(xa, xa, kColH + 128, true, 0x77u);
+        item(S0{}, xa, xa, kColH, true, 0x77u);      // lin_in: x (K = 48 of the zero-padded 64) times W_hi, then W_lo
+        item(S1{}, xa, xa, kColH + 128, true, 0x77u);
         release_a(xa);
         commit(BAR_ACC + 0);                   // the h_0 epilogue adds the lin_z[0] table blend
         commit(BAR_ACC + 1);
@@ -314,11 +344,11 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       if (has_head) {
         wait_act(0);
-        item(act, act + kChunkBytes, kColT, true, 0xFFu);
-        item(act + 2 * kChunkBytes, act + 3 * kChunkBytes, kColT, false, 0xFFu);
+        item(S0{}, act, act + kChunkBytes, kColT, true, 0xFFu);
+        item(S1{}, act + 2 * kChunkBytes, act + 3 * kChunkBytes, kColT, false, 0xFFu);
         wait_act(4);
-        item(act + 4 * kChunkBytes, act + 5 * kChunkBytes, kColT, false, 0xFFu);
-        item(act + 6 * kChunkBytes, act + 7 * kChunkBytes, kColT, false, 0xFFu);
+        item(S2{}, act + 4 * kChunkBytes, act + 5 * kChunkBytes, kColT, false, 0xFFu);
+        item(S3{}, act + 6 * kChunkBytes, act + 7 * kChunkBytes, kColT, false, 0xFFu);
         commit(BAR_ACC + 2);
         ++gen;
       } else {
@@ -360,21 +390,20 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // are issued before any of them is consumed (one L2 round trip per half instead of one per 8 rows); the
     // staging accesses carry no compiler memory barrier so the second half's loads can move above the first
     // half's arithmetic -- __syncwarp() orders the staging writes against the reads.
-    auto gather_block = [&](const __half* tab, int64_t wrow0, float (&g0)[32], float (&g1)[32]) {
-      uint4 ti[4], tw[4];
+    // The taps record of a row (4 texel indices, 4 weights) sits in bytes [96,128) of its row of the x chunk
+    // (pn_point_taps), i.e. in 16-byte pieces 6 and 7 of the 128-byte swizzled row in shared memory; rows past
+    // the end of the input are zero-filled by TMA (weight 0, texel 0).
+    auto gather_block = [&](const __half* tab, uint32_t xslot, float (&g0)[32], float (&g1)[32]) {
+      uint4 ti[4];
 #pragma unroll
       for (int it = 0; it < 4; ++it) {
-        const int64_t row = wrow0 + it * 8 + (lane >> 2);
-        ti[it] = tw[it] = make_uint4(0u, 0u, 0u, 0u);
-        if (row < p.n_rows) {
-          ti[it] = __ldg(p.taps + row * 2);
-          tw[it] = __ldg(p.taps + row * 2 + 1);
-        }
+        const uint32_t rc = (uint32_t)((lq & 1) * 32 + it * 8 + (lane >> 2));   // row within the CTA
+        ti[it] = ld_shared_v4(xslot + rc * 128 + ((6u ^ (rc & 7u)) << 4));
       }
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         const uint4* src = reinterpret_cast<const uint4*>(tab + half * 64) + (lane & 3);
-        uint4 t[4][4];
+        uint4 t[4][4];   // every global load of the half is in flight before the first is consumed
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
           t[it][0] = __ldg(src + (size_t)ti[it].x * 64);
@@ -385,8 +414,9 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
           const int rr = it * 8 + (lane >> 2);
-          const float wt[4] = {__uint_as_float(tw[it].x), __uint_as_float(tw[it].y), __uint_as_float(tw[it].z),
-                               __uint_as_float(tw[it].w)};
+          const uint32_t rc = (uint32_t)((lq & 1) * 32 + rr);
+          const uint4 tw = ld_shared_v4(xslot + rc * 128 + ((7u ^ (rc & 7u)) << 4));
+          const float wt[4] = {__uint_as_float(tw.x), __uint_as_float(tw.y), __uint_as_float(tw.z), __uint_as_float(tw.w)};
           float acc[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
@@ -449,28 +479,43 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     };
     auto signal_chunk = [&](int c) {
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), 0);
+      if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), rank4 & 2u);
     };
     // mode 0: relu -> ACT operand; mode 1: dump fp32 to h_io (segment end)
     // gather_b >= 0 (h before blocks 0-2): add the lin_z[gather_b] table blend instead of a bias vector and
     // write the sum back to tensor memory, so the residual stream carries it from here on.
-    auto epi = [&](int region, const float* bias_vec, int gather_b, int mode, int64_t grow, bool dbg) {
+    auto epi = [&](int region, const float* bias_vec, int gather_b, uint32_t xslot, int mode, int64_t grow, bool dbg) {
 #pragma unroll 1
       for (int nb = 0; nb < 2; ++nb) {
         const int a = region * 2 + nb;
         const int c0 = nb * 4 + 2 * hf;
         const uint32_t tcol = tmem_base + lane_addr + (region ? kColT : kColH) + nb * 128 + ch * 32;
         // the addend (bias, or the gathered table blend) is fetched while the accumulator is still being produced
+        if (p.debug_stage == -99 && mode == 0) {
+          // timing experiment only (wrong results): an epilogue of zero length, to measure what the issuer,
+          // the weight ring and the tensor pipe reach on their own
+          wait_bar<false>(bar(BAR_ACC + a), n_acc[a] & 1, p.err, 0x300 + a);
+          ++n_acc[a];
+          tc_fence_after();
+          tc_fence_before();
+          signal_chunk(c0);
+          signal_chunk(c0 + 1);
+          continue;
+        }
         float b0[32], b1[32];
-        if (gather_b >= 0) {
-          const __half* tab = p.tables + (size_t)gather_b * p.table_stride + c0 * 64 + 32 * ch;
-          const int64_t wrow0 = grow - lane;   // first row of this warp's lane quarter
-          gather_block(tab, wrow0, b0, b1);
+        // block 0: the taps arrive with x, which is only known to be in shared memory (of both CTAs) once
+        // lin_in has consumed it, so there the accumulator wait comes first
+        if (gather_b == 0) wait_bar<false>(bar(BAR_ACC + a), n_acc[a] & 1, p.err, 0x300 + a);
+        if (gather_b >= 0 && p.debug_stage == -98) {   // timing experiment only (wrong results): no table gather
+#pragma unroll
+          for (int i = 0; i < 32; ++i) b0[i] = b1[i] = 0.0f;
+        } else if (gather_b >= 0) {
+          gather_block(p.tables + (size_t)gather_b * p.table_stride + c0 * 64 + 32 * ch, xslot, b0, b1);
         } else {
           ld_bias32(bias_vec + c0 * 64 + 32 * ch, b0);
           ld_bias32(bias_vec + c0 * 64 + 64 + 32 * ch, b1);
         }
-        wait_bar<false>(bar(BAR_ACC + a), n_acc[a] & 1, p.err, 0x300 + a);
+        if (gather_b != 0) wait_bar<false>(bar(BAR_ACC + a), n_acc[a] & 1, p.err, 0x300 + a);
         ++n_acc[a];
         tc_fence_after();
         if (dbg && gather_b < 0) dump_block(tcol, bias_vec, nb, p.debug_h, grow);
@@ -570,16 +615,19 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
     };
 
-    for (int tile = cluster_id; tile < p.n_tiles; tile += n_clusters) {
+    uint32_t xs = 0;   // x slot of the current tile (the producer fills the slots round robin)
+    for (int tile = cluster_id; tile < tile_end; tile += n_clusters) {
       const int64_t grow = (int64_t)tile * kTileRows + rank * kRows + r;
+      const uint32_t xslot = smem_base + kOffA + xs * kChunkBytes;
+      if (++xs == kASlots) xs = 0;
       if (!full_front) epi_load(grow);
       for (int b = p.first_block; b < p.last_block; ++b) {
         if (b > p.first_block || full_front)
-          epi(0, p.bias + b * 512, b < 3 ? b : -1, 0, grow, p.debug_h != nullptr && p.debug_stage == b);
-        epi(1, p.bias + (6 + b) * 512, -1, 0, grow, false);
+          epi(0, p.bias + b * 512, b < 3 ? b : -1, xslot, 0, grow, p.debug_h != nullptr && p.debug_stage == b);
+        epi(1, p.bias + (6 + b) * 512, -1, 0u, 0, grow, false);
       }
       if (has_head) {
-        epi(0, p.bias + 5 * 512, -1, 0, grow, p.debug_h != nullptr && p.debug_stage == 5);
+        epi(0, p.bias + 5 * 512, -1, 0u, 0, grow, p.debug_h != nullptr && p.debug_stage == 5);
         // lin_out result: features 0-3 of block 0 = lanes 0-63, columns kColT..+3
         wait_bar<false>(bar(BAR_ACC + 2), n_acc[2] & 1, p.err, 0x310);
         ++n_acc[2];
@@ -602,7 +650,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
         tc_fence_before();
       } else {
-        epi(0, p.bias + p.last_block * 512, -1, 1, grow, false);
+        epi(0, p.bias + p.last_block * 512, -1, 0u, 1, grow, false);
       }
     }
   }
@@ -707,8 +755,20 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, ChainParam
   PN_CUDA_OK(cudaGetDevice(&dev));
   PN_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   p.n_tiles = (int)((p.n_rows + kTileRows - 1) / kTileRows);
-  const int clusters = p.n_tiles < sms / 2 ? p.n_tiles : sms / 2;
-  mlp_chain_kernel<<<2 * clusters, kThreads, kSmemAlloc, st>>>(mw, mx, p);
+  // 4-CTA clusters (two pairs); as many as can be resident at once, but no more than the tiles need
+  static int max_clusters = 0;
+  if (max_clusters == 0) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(sms / 4 * 4);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kSmemAlloc;
+    int n = 0;
+    PN_CUDA_OK(cudaOccupancyMaxActiveClusters(&n, mlp_chain_kernel, &cfg));
+    max_clusters = n > 0 ? (n < sms / 4 ? n : sms / 4) : 1;
+  }
+  const int want = (p.n_tiles + 1) / 2;
+  const int clusters = want < max_clusters ? want : max_clusters;
+  mlp_chain_kernel<<<4 * clusters, kThreads, kSmemAlloc, st>>>(mw, mx, p);
   PN_LAUNCH_OK("mlp_chain_kernel");
   count_launch();
   return PN_OK;
@@ -743,13 +803,13 @@ extern "C" size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views) {
   return 256 + (n_views > 1 && n_rows > 0 ? (size_t)n_rows * 512 * sizeof(float) : 0);
 }
 
-extern "C" int pn_mlp_forward_tc(const void* packed, const void* taps, const void* tables, int64_t n_texels,
+extern "C" int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t n_texels,
                                  const void* feat_x, int n_objects,
                                  int n_views, int64_t points_per_object, float* out, float* pre_act,
                                  void* workspace, size_t workspace_bytes, const pn_mlp_tc_debug_t* dbg,
                                  pn_stream_t stream) {
   using namespace pn::tc;
-  PN_CHECK_ARG(packed && taps && tables && feat_x && out && workspace, "pn_mlp_forward_tc: null pointer");
+  PN_CHECK_ARG(packed && tables && feat_x && out && workspace, "pn_mlp_forward_tc: null pointer");
   PN_CHECK_ARG(n_texels > 0, "pn_mlp_forward_tc: no texels");
   PN_CHECK_ARG(n_objects > 0 && n_views > 0 && points_per_object >= 0, "pn_mlp_forward_tc: bad sizes");
   const int64_t n_rows = (int64_t)n_objects * n_views * points_per_object;
@@ -757,7 +817,7 @@ extern "C" int pn_mlp_forward_tc(const void* packed, const void* taps, const voi
   if (n_rows == 0) return PN_OK;
   PN_CHECK_ARG(n_rows < (1ll << 31) - 256, "pn_mlp_forward_tc: too many rows for one launch");
   PN_CHECK_ARG(workspace_bytes >= pn_mlp_tc_workspace_bytes(n_rows, n_views), "pn_mlp_forward_tc: workspace too small");
-  PN_CHECK_ARG(((uintptr_t)workspace & 255) == 0 && ((uintptr_t)taps & 15) == 0 && ((uintptr_t)tables & 15) == 0 &&
+  PN_CHECK_ARG(((uintptr_t)workspace & 255) == 0 && ((uintptr_t)tables & 15) == 0 &&
                    ((uintptr_t)feat_x & 15) == 0,
                "pn_mlp_forward_tc: misaligned buffer");
   cudaStream_t st = (cudaStream_t)stream;
@@ -771,7 +831,6 @@ extern "C" int pn_mlp_forward_tc(const void* packed, const void* taps, const voi
   p.out = (float4*)out;
   p.pre = (float4*)pre_act;
   p.err = err;
-  p.taps = (const uint4*)taps;
   p.tables = (const __half*)tables;
   p.table_stride = n_texels * 512;
   p.ppo = points_per_object;

@@ -161,8 +161,8 @@ class PixelNeRFNet(torch.nn.Module):
             return _lib.mlp_forward_fp32(mlp.packed("fp32"), fz, fx, cam["n_objects"], cam["n_views"], ppo)
         tables = self.latent_tables(coarse)
         _, hl, wl, _ = self.latent_nhwc(torch.float32).shape
-        taps, fx = _lib.point_taps(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
-        return _lib.mlp_forward_tc(mlp.packed(prec), taps, tables, fx, cam["n_objects"], cam["n_views"], ppo)
+        fx = _lib.point_taps(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
+        return _lib.mlp_forward_tc(mlp.packed(prec), tables, fx, cam["n_objects"], cam["n_views"], ppo)
 
     def forward(self, xyz, coarse=True, viewdirs=None, far=False):
         """(SB,B,3) world points -> (SB,B,4) [sigmoid rgb, relu sigma].  Reference models.py:146-266."""

@@ -37,9 +37,13 @@ def render_case_inputs(fx):
     )
 
 
-def make_taps(idx, wt):
-    """(N,4) texel indices + (N,4) fp32 bilinear weights -> the (N,8) int32 record pn_point_taps writes."""
-    return torch.cat([idx.to(torch.int32), wt.float().contiguous().view(torch.int32)], dim=1).contiguous()
+def make_taps(idx, wt, feat_x):
+    """(N,4) texel indices + (N,4) fp32 bilinear weights, embedded like pn_point_taps does it into bytes
+    [96,128) of the rows of feat_x (N,64) fp16; returns the combined (N,64) fp16 tensor."""
+    rec = torch.cat([idx.to(torch.int32), wt.float().contiguous().view(torch.int32)], dim=1).contiguous()
+    out = feat_x.clone().contiguous()
+    out.view(torch.int32)[:, 24:32] = rec
+    return out
 
 
 def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo):

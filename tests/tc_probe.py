@@ -34,11 +34,11 @@ def main():
     wd = {k: v.cuda() for k, v in w.items()}
     packed = _lib.pack_weights_tc(wd)
     tables = _lib.prepare_latent_tables(wd, latent.reshape(1, 8, 24, 512).cuda())
-    taps = make_taps(idx, wt).cuda()
+    fxt = make_taps(idx, wt, fx).cuda()
     torch.cuda.synchronize()
     print("packed ok", flush=True)
     for st in stages:
-        (out, pre), dbg = _lib.mlp_forward_tc(packed, taps, tables, fx.cuda(), 1, ns, ppo, want_pre=True, debug_stage=st)
+        (out, pre), dbg = _lib.mlp_forward_tc(packed, tables, fxt, 1, ns, ppo, want_pre=True, debug_stage=st)
         torch.cuda.synchronize()
         ref = ref_stages[st]
         d = (dbg.cpu().double() - ref).abs()

@@ -50,7 +50,7 @@ def test_chain_vs_emulation(ns, ppo, sb):
     packed = _lib.pack_weights_tc({k: v.cuda() for k, v in w.items()})
     n = sb * ns * ppo
     idx, wt, latent, fx = _inputs(n)
-    out, pre = _lib.mlp_forward_tc(packed, make_taps(idx, wt).cuda(), _tables(w, latent), fx.cuda(), sb, ns, ppo,
+    out, pre = _lib.mlp_forward_tc(packed, _tables(w, latent), make_taps(idx, wt, fx).cuda(), sb, ns, ppo,
                                    want_pre=True)
     torch.cuda.synchronize()
     # emulate object by object (the view mean is per object)
@@ -74,7 +74,7 @@ def test_residual_stream_stages(stage):
     w = syn.mlp_weights(7)
     packed = _lib.pack_weights_tc({k: v.cuda() for k, v in w.items()})
     idx, wt, latent, fx = _inputs(200, seed=3)
-    _, dbg = _lib.mlp_forward_tc(packed, make_taps(idx, wt).cuda(), _tables(w, latent), fx.cuda(), 1, 1, 200,
+    _, dbg = _lib.mlp_forward_tc(packed, _tables(w, latent), make_taps(idx, wt, fx).cuda(), 1, 1, 200,
                                  debug_stage=stage)
     ref = emulate_tc_chain(w, idx, wt, latent, fx.float(), 1, 200)[0][stage]
     # stage 0 has no rounded activations upstream: what is left are fp16 rounding-boundary flips of single
