@@ -32,6 +32,8 @@
 // warps convert it to the next operand's K-chunks 0-3 while the fourth quarter runs, and
 // the next GEMM's first two quarters only need chunks 0-3.  The table gather of an h epilogue
 // is issued before that epilogue waits for its accumulator, so it is off the critical path.
+#include <cstdio>
+#include <cstdlib>
 #include <type_traits>
 
 #include "pn_common.cuh"
@@ -135,14 +137,17 @@ __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
   return d;
 }
 
-__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 1)
 mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
                  const ChainParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // A cluster is two CTA pairs.  Each pair runs its own row tiles; the two pairs walk the same weight
-  // schedule in lockstep and every weight tile is fetched from L2 once per cluster (TMA multicast).
+  // A cluster is two CTA pairs where the GPU can place four CTAs together (preferred cluster dimension 4),
+  // one pair elsewhere (148 SMs hold 33 clusters of four and 8 of two on B200).  Each pair runs its own row
+  // tiles; the pairs of a 4-cluster walk the same weight schedule in lockstep and every weight tile is
+  // fetched from L2 once per cluster (TMA multicast), which relieves the L2 -> SM path.
+  const bool quad = cluster_nctarank() == 4;
   const uint32_t rank4 = cluster_ctarank();
   const uint32_t rank = rank4 & 1;            // rank inside the pair (0 = MMA leader)
   const uint32_t pair = rank4 >> 1;           // which pair of the cluster
@@ -164,7 +169,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(bar(BAR_W_FULL + s), 1);   // the leader's expect_tx arrive (both CTAs' bytes)
-      mbar_init(bar(BAR_W_EMPTY + s), 2);  // one multicast commit from each pair of the cluster
+      mbar_init(bar(BAR_W_EMPTY + s), quad ? 2 : 1);  // one multicast commit from each pair of the cluster
     }
     for (int a = 0; a < kASlots; ++a) {
       mbar_init(bar(BAR_A_FULL + a), 1);
@@ -203,9 +208,14 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         const int row = layer * 512 + nb * 256 + (int)rank * 128;
         // this CTA and its twin in the other pair (same rank) need the same two boxes: each fetches one and
         // multicasts it to both
-        const uint16_t twins = (uint16_t)((1u << rank) | (1u << (rank + 2)));
-        tma_load_2d_pair_mc(smem_base + kOffW + ws * kWStageBytes + pair * kWBoxBytes, &map_w, full,
-                            (pair == 0 ? kc0 : kc1) * 64, row, twins);
+        if (quad) {
+          const uint16_t twins = (uint16_t)((1u << rank) | (1u << (rank + 2)));
+          tma_load_2d_pair_mc(smem_base + kOffW + ws * kWStageBytes + pair * kWBoxBytes, &map_w, full,
+                              (pair == 0 ? kc0 : kc1) * 64, row, twins);
+        } else {
+          tma_load_2d_pair(smem_base + kOffW + ws * kWStageBytes, &map_w, full, kc0 * 64, row);
+          tma_load_2d_pair(smem_base + kOffW + ws * kWStageBytes + kWBoxBytes, &map_w, full, kc1 * 64, row);
+        }
       }
       __syncwarp();
     };
@@ -281,7 +291,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)a_lo, desc_hi | (uint64_t)bj, kIdesc,
                           (clear && j == 0) ? 0u : 1u);
           }
-        umma_commit_pair(bar(BAR_W_EMPTY + ws), 0xF);   // frees the stage in all four CTAs
+        umma_commit_pair(bar(BAR_W_EMPTY + ws), quad ? 0xF : 0x3);   // frees the stage in every CTA of the cluster
       }
       __syncwarp();
     };
@@ -755,20 +765,24 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, ChainParam
   PN_CUDA_OK(cudaGetDevice(&dev));
   PN_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   p.n_tiles = (int)((p.n_rows + kTileRows - 1) / kTileRows);
-  // 4-CTA clusters (two pairs); as many as can be resident at once, but no more than the tiles need
-  static int max_clusters = 0;
-  if (max_clusters == 0) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(sms / 4 * 4);
-    cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = kSmemAlloc;
-    int n = 0;
-    PN_CUDA_OK(cudaOccupancyMaxActiveClusters(&n, mlp_chain_kernel, &cfg));
-    max_clusters = n > 0 ? (n < sms / 4 ? n : sms / 4) : 1;
-  }
+  // One CTA per SM, in groups of four where the GPU can co-schedule four (preferred cluster dimension) and
+  // pairs elsewhere; no more groups than the tiles need.
+  const int max_groups = sms / 4;
   const int want = (p.n_tiles + 1) / 2;
-  const int clusters = want < max_clusters ? want : max_clusters;
-  mlp_chain_kernel<<<4 * clusters, kThreads, kSmemAlloc, st>>>(mw, mx, p);
+  const int groups = want < max_groups ? want : max_groups;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(4 * groups);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemAlloc;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[2];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = 2; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributePreferredClusterDimension;
+  attrs[1].val.preferredClusterDim.x = 4; attrs[1].val.preferredClusterDim.y = 1; attrs[1].val.preferredClusterDim.z = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 2;
+  PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel, mw, mx, p));
   PN_LAUNCH_OK("mlp_chain_kernel");
   count_launch();
   return PN_OK;

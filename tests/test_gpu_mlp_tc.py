@@ -131,3 +131,25 @@ def test_unimplemented_operand_format_raises():
     from pixelnerf_b200 import _lib, synthetic as syn
     with pytest.raises(NotImplementedError):
         _lib.pack_weights_tc({k: v.cuda() for k, v in syn.mlp_weights(1).items()}, precision="bf16")
+
+
+@pytest.mark.parametrize("ns,ppo", [(1, 1), (1, 77), (1, 128 * 150 + 5), (2, 128 * 40 + 3), (1, 128 * 74 * 3 + 17)])
+def test_chain_is_deterministic(ns, ppo):
+    """The chain has no atomics and a fixed schedule per row tile: repeated launches must agree bit for bit,
+    whatever mix of 4-CTA and 2-CTA clusters the GPU forms (a protocol race would show up here)."""
+    from pixelnerf_b200 import _lib, synthetic as syn
+    w = syn.mlp_weights(5)
+    packed = _lib.pack_weights_tc({k: v.cuda() for k, v in w.items()})
+    n = ns * ppo
+    idx, wt, latent, fx = _inputs(n, seed=11)
+    tables = _tables(w, latent)
+    fxt = make_taps(idx, wt, fx).cuda()
+    first = None
+    for _ in range(12):
+        out, pre = _lib.mlp_forward_tc(packed, tables, fxt, 1, ns, ppo, want_pre=True)
+        torch.cuda.synchronize()
+        if first is None:
+            first = pre.clone()
+            assert torch.isfinite(first).all()
+        else:
+            assert torch.equal(pre, first)
