@@ -55,7 +55,7 @@ __device__ __forceinline__ void load_z(const float* __restrict__ zrow, int k, in
 }
 
 template <int G, int CMAX>
-__global__ void __launch_bounds__(kCompWarps * 32)
+__global__ void __launch_bounds__(kCompWarps * 32, CMAX <= 8 ? 4 : CMAX <= 12 ? 3 : 2)
 composite_fwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ z,
                      const float* __restrict__ rays, float* __restrict__ weights,
                      float* __restrict__ rgb, float* __restrict__ depth, int64_t n_rays, int k,
@@ -130,7 +130,7 @@ composite_fwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ 
 //   g_delta[k] = g_alpha[k] s_k E_k
 //   g_z[k]     = g_delta[k-1] - g_delta[k] + w_k gD        (z_K = far carries no grad)
 template <int G, int CMAX>
-__global__ void __launch_bounds__(kCompWarps * 32)
+__global__ void __launch_bounds__(kCompWarps * 32, 2)
 composite_bwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ z,
                      const float* __restrict__ rays, const float* __restrict__ g_rgb,
                      const float* __restrict__ g_depth, const float* __restrict__ g_weights,
@@ -146,9 +146,27 @@ composite_bwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ 
   const float gr = g_rgb[r * 3 + 0], gg = g_rgb[r * 3 + 1], gb = g_rgb[r * 3 + 2];
   const float gd = g_depth ? g_depth[r] : 0.0f;
   const float gbg = white ? (gr + gg + gb) : 0.0f;
-  float zz[CMAX + 1], al[CMAX], Tk[CMAX], gw[CMAX], E[CMAX];
+  // per sample: E = exp(-delta s) (alpha = 1 - E is recomputed where needed), T_k, g_w
+  float zz[CMAX + 1], Tk[CMAX], gw[CMAX], E[CMAX];
   float4 c[CMAX];
   load_z<G, CMAX>(z + r * k, k, per_lane, k0, gl, far, exact4, zz);
+  // upstream weight gradients of this lane's samples, as float4 when the row splits evenly
+#pragma unroll
+  for (int i = 0; i < CMAX; ++i) gw[i] = 0.0f;
+  if (g_weights) {
+    if (exact4) {
+#pragma unroll
+      for (int i = 0; i < CMAX; i += 4)
+        if (i < per_lane) {
+          const float4 t = *reinterpret_cast<const float4*>(g_weights + r * k + k0 + i);
+          gw[i] = t.x; gw[i + 1] = t.y; gw[i + 2] = t.z; gw[i + 3] = t.w;
+        }
+    } else {
+#pragma unroll
+      for (int i = 0; i < CMAX; ++i)
+        if (i < per_lane && k0 + i < k) gw[i] = g_weights[r * k + k0 + i];
+    }
+  }
   float prod = 1.0f;
 #pragma unroll
   for (int i = 0; i < CMAX; ++i) {
@@ -157,9 +175,8 @@ composite_bwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ 
       if (kk < k) {
         c[i] = rgbs[r * k + kk];
         E[i] = expf(-(zz[i + 1] - zz[i]) * fmaxf(c[i].w, 0.0f));
-        al[i] = 1.0f - E[i];
-        prod *= (1.0f - al[i] + 1e-10f);
-      } else { al[i] = 0.f; E[i] = 1.f; c[i] = make_float4(0.f, 0.f, 0.f, 0.f); }
+        prod *= (1.0f - (1.0f - E[i]) + 1e-10f);
+      } else { E[i] = 1.f; c[i] = make_float4(0.f, 0.f, 0.f, 0.f); }
     }
   }
   float T = group_excl_prod<G>(prod, gl);
@@ -170,12 +187,13 @@ composite_bwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ 
     if (i < per_lane) {
       const int kk = k0 + i;
       Tk[i] = T;
-      gw[i] = 0.0f;
       if (kk < k) {
-        gw[i] = gr * c[i].x + gg * c[i].y + gb * c[i].z + gd * zz[i] - gbg +
-                (g_weights ? g_weights[r * k + kk] : 0.0f);
-        lane_tot += al[i] * T * gw[i];
-        T *= (1.0f - al[i] + 1e-10f);
+        const float al = 1.0f - E[i];
+        gw[i] = gr * c[i].x + gg * c[i].y + gb * c[i].z + gd * zz[i] - gbg + gw[i];
+        lane_tot += al * T * gw[i];
+        T *= (1.0f - al + 1e-10f);
+      } else {
+        gw[i] = 0.0f;
       }
     }
   }
@@ -194,8 +212,9 @@ composite_bwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ 
       const int kk = k0 + i;
       gdel[i] = 0.0f;
       if (kk < k) {
-        const float w = al[i] * Tk[i];
-        const float q = 1.0f - al[i] + 1e-10f;
+        const float al = 1.0f - E[i];
+        const float w = al * Tk[i];
+        const float q = 1.0f - al + 1e-10f;
         const float ga = Tk[i] * gw[i] - suffix / q;
         suffix += w * gw[i];
         const float delta = zz[i + 1] - zz[i];
@@ -218,7 +237,7 @@ composite_bwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ 
     for (int i = 0; i < CMAX; ++i) {
       if (i < per_lane) {
         const int kk = k0 + i;
-        if (live && kk < k) g_z[r * k + kk] = prev - gdel[i] + al[i] * Tk[i] * gd;
+        if (live && kk < k) g_z[r * k + kk] = prev - gdel[i] + (1.0f - E[i]) * Tk[i] * gd;
         prev = gdel[i];
       }
     }
@@ -231,6 +250,7 @@ composite_bwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ 
 #define PN_COMP_DISPATCH(KERNEL, K, ...)                                                        \
   do {                                                                                          \
     if ((K) <= 64) KERNEL<8, 8> __VA_ARGS__;                                                    \
+    else if ((K) <= 96) KERNEL<8, 12> __VA_ARGS__;                                              \
     else if ((K) <= 128) KERNEL<8, 16> __VA_ARGS__;                                             \
     else if ((K) <= 256) KERNEL<16, 16> __VA_ARGS__;                                            \
     else KERNEL<32, 16> __VA_ARGS__;                                                            \
