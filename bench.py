@@ -314,6 +314,60 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+def run_train(args):
+    """--train: BASELINE config 5, one training step = render 4 objects x `--train-rays` rays (want_weights, train
+    mode) -> MSE on coarse+fine rgb vs U(0,1) targets -> backward through composite / ResnetFC / latent gather
+    (hand-written kernels behind torch.autograd.Function) -> Adam step on both MLPs.  Not the headline line."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import build_net, scene_camera, set_encoded
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    sb = 4
+    sc = syn.scene(SCENE)
+    net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), dev, mlp_precision=args.precision)
+    cam = scene_camera(sc)
+    lat = syn.latent_maps(21, sb, sc["hl"], sc["wl"])
+    set_encoded(net, lat, cam["poses"].expand(sb, -1, -1).contiguous(), cam["focal"], cam["c"], cam["image_shape"], 1)
+    net.train()
+    ren.train()
+    for q in net.parameters():
+        q.requires_grad_(True)
+    opt = torch.optim.Adam([q for n, q in net.named_parameters() if n.startswith("mlp_")], lr=1e-4)
+    res = []
+    for n_obj_rays in args.train_rays:
+        g = torch.Generator().manual_seed(n_obj_rays)
+        idx = torch.randint(0, sc["rays"].shape[0], (sb, n_obj_rays), generator=g)
+        rays = sc["rays"][idx].to(dev)                       # (SB, B, 8)
+        target = torch.rand(sb, n_obj_rays, 3, generator=g).to(dev)
+
+        def step():
+            opt.zero_grad(set_to_none=True)
+            out = ren(net, rays, want_weights=True)
+            loss = ((out.coarse.rgb - target) ** 2).mean() + ((out.fine.rgb - target) ** 2).mean()
+            loss.backward()
+            opt.step()
+            return loss
+
+        for _ in range(2):
+            step()
+        torch.cuda.synchronize()
+        steps = max(1, min(args.steps, 5))
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            loss = step()
+        b.record()
+        b.synchronize()
+        ms = a.elapsed_time(b) / steps
+        n = sb * n_obj_rays
+        flop = 3.0 * n * (N_COARSE + N_COARSE + N_FINE) * MLP_FLOP_PER_POINT[1]
+        res.append({"rays_per_step": n, "ms_per_step": ms, "rays/s": n / (ms * 1e-3), "mlp_TFLOP/s_fwd+bwd": flop / (ms * 1e-3) / 1e12,
+                    "loss": float(loss)})
+    print(json.dumps({"metric": "training step rays/sec (config 5)", "unit": "rays/s", "objects": sb,
+                      "forward": "%s chain" % args.precision, "backward": "fp32 CUDA-core kernels, recompute per chunk",
+                      "optimizer": "Adam on both MLPs", "sweep": res}))
+
+
 def chain_traffic(rows_per_launch):
     """DRAM bytes per chain launch: measured bytes/row of the committed `ncu --set full` capture (a live run
     cannot read dram counters) times the rows one launch of this run processes; None without the summary."""
@@ -334,9 +388,13 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp16"), choices=["fp32", "fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernels", action="store_true", help="per-kernel HBM roofline of the memory-bound kernels")
+    ap.add_argument("--train", action="store_true", help="training-step timing (BASELINE config 5), not the headline")
+    ap.add_argument("--train-rays", type=int, nargs="+", default=[128, 4096], help="rays per object for --train")
     args = ap.parse_args()
     if args.kernels:
         run_kernels(args)
+    elif args.train:
+        run_train(args)
     elif args.impl == "reference":
         run_reference(args)
     else:

@@ -73,6 +73,8 @@ static_assert(kSmemAlloc <= 227 * 1024, "shared memory budget");
 
 constexpr uint32_t kColH = 0, kColT = 256;  // TMEM column bases
 constexpr uint32_t kIdesc = idesc_f16(128, 256);
+// lin_out has 8 real output rows (4 hi + 4 lo): N = 16 over the pair, i.e. the first 8 rows of each CTA's box
+constexpr uint32_t kIdescOut = idesc_f16(128, 16);
 
 // Packed weights: 15 layers of [512 features][512 K] fp16 (lin_in and lin_out zero padded).
 constexpr int kLayers = 15;
@@ -275,7 +277,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // descriptor = constant high word | (address >> 4): only the low word changes per MMA
     const uint64_t desc_hi = smem_desc_k128(0);
     // One weight stage: nk K=16 steps; A steps [0,4) come from a0, [4,8) from a1 (64-wide chunks).
-    auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask) {
+    auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask,
+                    uint32_t idesc = kIdesc) {
       constexpr uint32_t ws = decltype(stage_c)::value;
       wait_bar<false>(bar(BAR_W_FULL + ws), (wpar >> ws) & 1u, p.err, 0x200 + ws);
       wpar ^= 1u << ws;
@@ -288,7 +291,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           if ((kmask >> j) & 1u) {
             const uint32_t a_lo = (j < 4 ? a0_lo : a1_lo) + 2 * (j & 3);
             const uint32_t bj = b_lo + (j < 4 ? 0 : (kWBoxBytes >> 4)) + 2 * (j & 3);
-            umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)a_lo, desc_hi | (uint64_t)bj, kIdesc,
+            umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)a_lo, desc_hi | (uint64_t)bj, idesc,
                           (clear && j == 0) ? 0u : 1u);
           }
         umma_commit_pair(bar(BAR_W_EMPTY + ws), quad ? 0xF : 0x3);   // frees the stage in every CTA of the cluster
@@ -354,11 +357,11 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       if (has_head) {
         wait_act(0);
-        item(S0{}, act, act + kChunkBytes, kColT, true, 0xFFu);
-        item(S1{}, act + 2 * kChunkBytes, act + 3 * kChunkBytes, kColT, false, 0xFFu);
+        item(S0{}, act, act + kChunkBytes, kColT, true, 0xFFu, kIdescOut);
+        item(S1{}, act + 2 * kChunkBytes, act + 3 * kChunkBytes, kColT, false, 0xFFu, kIdescOut);
         wait_act(4);
-        item(S2{}, act + 4 * kChunkBytes, act + 5 * kChunkBytes, kColT, false, 0xFFu);
-        item(S3{}, act + 6 * kChunkBytes, act + 7 * kChunkBytes, kColT, false, 0xFFu);
+        item(S2{}, act + 4 * kChunkBytes, act + 5 * kChunkBytes, kColT, false, 0xFFu, kIdescOut);
+        item(S3{}, act + 6 * kChunkBytes, act + 7 * kChunkBytes, kColT, false, 0xFFu, kIdescOut);
         commit(BAR_ACC + 2);
         ++gen;
       } else {
