@@ -207,6 +207,18 @@ PN_API int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t n_t
                       float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                       const pn_mlp_tc_debug_t* dbg, pn_stream_t stream);
 
+/* ---- (5) either side of the render path --------------------------------------- */
+
+/* Camera rays on the device: util.gen_rays (src/util/util.py:238-276) with unproj_map (:113-143) for
+ * n_images camera-to-world poses (row-major, 4 floats per row, pose_stride floats per pose: 16 for 4x4,
+ * 12 for 3x4).  rays (n_images, height, width, 8) = [origin, direction, z_near, z_far].  ndc=False only. */
+PN_API int pn_gen_rays(const float* poses, int pose_stride, int n_images, int width, int height, float fx,
+                float fy, float cx, float cy, float z_near, float z_far, float* rays, pn_stream_t stream);
+
+/* (frames * 255).astype(np.uint8) of eval/gen_video.py:234-236 on the device: truncation, clamped to
+ * [0,255].  n_values floats in, n_values bytes out. */
+PN_API int pn_frame_to_u8(const float* rgb, unsigned char* out, int64_t n_values, pn_stream_t stream);
+
 /* ---- (4) compositing ------------------------------------------------------------------- */
 
 /* NeRFRenderer.composite after the model call, src/render/nerf.py:178-182, 228-249.

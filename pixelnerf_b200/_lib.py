@@ -67,6 +67,8 @@ _SIGNATURES = {
     "pn_prepare_latent_tables": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp, _sz, _vp]),
     "pn_composite_fwd": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "pn_composite_bwd": (_int, [_vp] * 8 + [_i64, _int, _int, _vp]),
+    "pn_gen_rays": (_int, [_vp, _int, _int, _int, _int, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
+    "pn_frame_to_u8": (_int, [_vp, _vp, _i64, _vp]),
 }
 
 _lib = None
@@ -390,3 +392,32 @@ def composite_bwd(rgb_sigma, z, rays, white_bkgd, g_rgb, g_depth=None, g_weights
     _check(lib().pn_composite_bwd(_ptr(rgb_sigma), _ptr(z), _ptr(rays), _ptr(g_rgb), _ptr(g_depth), _ptr(g_weights),
                                   _ptr(g_rs), _ptr(g_z), r, k, int(bool(white_bkgd)), _stream()), "pn_composite_bwd")
     return g_rs, g_z
+
+
+def gen_rays(poses, width, height, focal, z_near, z_far, c=None):
+    """util.gen_rays (src/util/util.py:238-276) on the device: poses (B, 4, 4) or (B, 3, 4) -> (B, H, W, 8)."""
+    poses = _f32c(poses)
+    if poses.dim() != 3 or poses.shape[1] not in (3, 4) or poses.shape[2] != 4:
+        raise ValueError(f"poses must be (B, 3|4, 4), got {tuple(poses.shape)}")
+    f = torch.as_tensor(focal, dtype=torch.float32).reshape(-1)
+    fx, fy = float(f[0]), float(f[-1])
+    if c is None:
+        cx, cy = width * 0.5, height * 0.5
+    else:
+        c = torch.as_tensor(c).reshape(-1)
+        cx, cy = float(c[0]), float(c[1])
+    n = poses.shape[0]
+    rays = torch.empty(n, height, width, 8, device=poses.device, dtype=torch.float32)
+    with _Timed("gen_rays"):
+        _check(lib().pn_gen_rays(_ptr(poses), poses.shape[1] * 4, n, width, height, fx, fy, cx, cy,
+                                 float(z_near), float(z_far), _ptr(rays), _stream()), "pn_gen_rays")
+    return rays
+
+
+def frame_to_u8(rgb):
+    """(frames * 255).astype(np.uint8) of eval/gen_video.py:234-236, on the device; same shape, uint8."""
+    rgb = _f32c(rgb)
+    out = torch.empty(rgb.shape, device=rgb.device, dtype=torch.uint8)
+    with _Timed("frame_to_u8"):
+        _check(lib().pn_frame_to_u8(_ptr(rgb), _ptr(out, torch.uint8), rgb.numel(), _stream()), "pn_frame_to_u8")
+    return out

@@ -51,6 +51,9 @@ def gen_rays(poses, width, height, focal, z_near, z_far, c=None, ndc=False):
     if ndc:
         raise NotImplementedError("ndc rays: the reference calls an undefined ndc_rays here (util.py:260)")
     n, dev = poses.shape[0], poses.device
+    if poses.is_cuda:     # one kernel, no (H, W) host tables (csrc/pn_frame.cu)
+        from .. import _lib
+        return _lib.gen_rays(poses, width, height, focal, z_near, z_far, c=c)
     focal = torch.as_tensor(focal, dtype=torch.float32)
     cam = unproj_map(width, height, focal.squeeze(), c=c, device=dev).unsqueeze(0).repeat(n, 1, 1, 1)
     centers = poses[:, None, None, :3, 3].expand(-1, height, width, -1)
