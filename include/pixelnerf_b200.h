@@ -207,6 +207,23 @@ PN_API int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t n_t
                       float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                       const pn_mlp_tc_debug_t* dbg, pn_stream_t stream);
 
+/* ---- (3c) tensor-core GEMMs of the training path (dgrad / wgrad of the 512-wide linears) -- */
+
+/* D[rows, n] = scale * A[rows, k] x B[k, n]  (both row-major 16-bit of the SAME format, 0 = fp16 or 1 = bf16; k % 64 == 0,
+ * n % 256 == 0), fp32 accumulation on tcgen05.  Epilogue: optional relu-backward mask (mask_f16[rows, n], fp16 or bf16, is
+ * the relu OUTPUT of the layer: D is zeroed where it is zero), optional `+= acc32` (accumulate != 0), then D is
+ * written to acc32 (fp32) and/or out_bf16.  dgrad of a linear y = x W^T: A = dL/dy, B = W as stored ([out, in]).
+ * err_word: optional device word receiving a watchdog code before a trap. */
+PN_API int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
+                    const void* mask_f16, float* acc32, int accumulate, void* out_bf16, float scale,
+                    unsigned int* err_word, pn_stream_t stream);
+
+/* out[512, ldo] (fp32, first n_store columns) += G[rows, 512]^T x X[rows, ldx]  (ldx = 512, or 64 for lin_in's
+ * padded code rows), split over row ranges, partial sums added with red.global.add: wgrad of y = x W^T with
+ * G = dL/dy, X = the layer input.  The caller zeroes `out` first. */
+PN_API int pn_gemm_tc_wgrad(const void* g, int g_fmt, int ldg, const void* x, int x_fmt, int ldx, int64_t n_rows,
+                     int n_store, float* out, int ldo, unsigned int* err_word, pn_stream_t stream);
+
 /* ---- (5) either side of the render path --------------------------------------- */
 
 /* Camera rays on the device: util.gen_rays (src/util/util.py:238-276) with unproj_map (:113-143) for

@@ -67,6 +67,8 @@ _SIGNATURES = {
     "pn_prepare_latent_tables": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp, _sz, _vp]),
     "pn_composite_fwd": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "pn_composite_bwd": (_int, [_vp] * 8 + [_i64, _int, _int, _vp]),
+    "pn_gemm_tc_rows": (_int, [_vp, _int, _vp, _int, _i64, _int, _int, _vp, _vp, _int, _vp, _f32, _vp, _vp]),
+    "pn_gemm_tc_wgrad": (_int, [_vp, _int, _int, _vp, _int, _int, _i64, _int, _vp, _int, _vp, _vp]),
     "pn_gen_rays": (_int, [_vp, _int, _int, _int, _int, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
     "pn_frame_to_u8": (_int, [_vp, _vp, _i64, _vp]),
 }
@@ -420,4 +422,42 @@ def frame_to_u8(rgb):
     out = torch.empty(rgb.shape, device=rgb.device, dtype=torch.uint8)
     with _Timed("frame_to_u8"):
         _check(lib().pn_frame_to_u8(_ptr(rgb), _ptr(out, torch.uint8), rgb.numel(), _stream()), "pn_frame_to_u8")
+    return out
+
+
+_FMT = {torch.float16: 0, torch.bfloat16: 1}
+_ERR_WORD = {}
+
+
+def _err_word(dev):
+    key = str(dev)
+    if key not in _ERR_WORD:
+        _ERR_WORD[key] = torch.zeros(64, device=dev, dtype=torch.int32)
+    return _ERR_WORD[key]
+
+
+def gemm_tc_rows(a, b, mask=None, acc32=None, accumulate=False, want16=True, scale=1.0):
+    """scale * a[rows, k] @ b[k, n] on the tensor cores (16-bit operands, fp32 accumulate), optionally masked by
+    the relu output `mask` and added to `acc32`; returns (acc32 or None, bf16 copy or None)."""
+    rows, k = a.shape
+    n = b.shape[1]
+    assert b.shape[0] == k and a.is_contiguous() and b.is_contiguous()
+    out16 = torch.empty(rows, n, device=a.device, dtype=torch.bfloat16) if want16 else None
+    with _Timed("gemm_rows"):
+        _check(lib().pn_gemm_tc_rows(_ptr(a, a.dtype), _FMT[a.dtype], _ptr(b, b.dtype), _FMT[b.dtype], rows, k, n,
+                                     _ptr(mask, mask.dtype if mask is not None else None), _ptr(acc32), int(bool(accumulate)),
+                                     _ptr(out16, torch.bfloat16), float(scale), _err_word(a.device).data_ptr(),
+                                     _stream()), "pn_gemm_tc_rows")
+    return acc32, out16
+
+
+def gemm_tc_wgrad(g, x, out, n_store=None):
+    """out[512, :n_store] += g[rows, 512]^T @ x[rows, 512 | 64] on the tensor cores."""
+    rows = g.shape[0]
+    n_store = x.shape[1] if n_store is None else n_store
+    assert out.dim() == 2 and out.shape[0] == 512 and out.is_contiguous()
+    with _Timed("gemm_wgrad"):
+        _check(lib().pn_gemm_tc_wgrad(_ptr(g, g.dtype), _FMT[g.dtype], g.shape[1], _ptr(x, x.dtype), _FMT[x.dtype],
+                                      x.shape[1], rows, n_store, _ptr(out), out.shape[1],
+                                      _err_word(g.device).data_ptr(), _stream()), "pn_gemm_tc_wgrad")
     return out

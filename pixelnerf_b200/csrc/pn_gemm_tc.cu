@@ -1,0 +1,474 @@
+// Tensor-core GEMMs of the training path (dgrad + wgrad of the 512-wide linears), tcgen05 +
+// TMEM + TMA, one CTA pair (cta_group::2, M = 256) per tile.
+//
+//   rows GEMM   D[rows, N]  = A[rows, K] * B[K, N]            (dgrad: A = dL/d(out) bf16, B = W[out, in] as stored)
+//   wgrad GEMM  D[M, N]    += A[rows, M]^T * B[rows, N]       (A = dL/d(out) bf16, B = layer input fp16, split over rows)
+//
+// Both read their "transposed" operand straight from its row-major tensor: the shared-memory tile is MN-major
+// (TMA box = 64 contiguous elements of the M/N dimension x 64 K rows, 128-byte swizzle), which the UMMA
+// descriptor supports for 16-bit types (major bits 15/16 of the instruction descriptor), so no transposed copy
+// of any activation, gradient or weight is ever written.  fp32 accumulation in TMEM; A and B are both fp16 or
+// both bf16 (one of each is an illegal instruction on sm_100a, measured).
+//
+// Warp roles per CTA (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (leader CTA only), warps 2-9 =
+// epilogue (lane quarter = warp & 3, column half = (warp - 2) >> 2).
+#include <cuda_bf16.h>
+
+#include "pn_common.cuh"
+#include "pn_tc_ptx.cuh"
+#include "pn_tc_host.cuh"
+
+namespace pn {
+namespace tc {
+
+constexpr int kGThreads = 320;
+constexpr int kGBox = 64 * 64 * 2;                 // one [64 x 64] 16-bit box
+constexpr int kGStageRows = 32 * 1024, kGStagesRows = 6;     // rows GEMM: A [128 x 64] + B 2 boxes
+constexpr int kGStageW = 48 * 1024, kGStagesW = 4;           // wgrad: A 2 boxes + B 2 halves x 2 boxes
+constexpr int kGRing = 192 * 1024;
+constexpr int kGOffBar = kGRing;
+enum { GB_FULL = 0, GB_EMPTY = 8, GB_ACCF = 16, GB_ACCE = 18, GB_COUNT = 20 };
+constexpr int kGOffTmem = kGOffBar + GB_COUNT * 8;
+constexpr int kGSmem = kGOffTmem + 16 + 1024;
+static_assert(kGSmem <= 227 * 1024, "shared memory budget");
+
+// MN-major operand tile, 128-byte swizzle: 64 contiguous M/N elements per 128-byte row, 8 K rows per 1024-byte
+// group (SBO), 64-element M/N blocks `lbo` bytes apart.
+__device__ __forceinline__ uint64_t smem_desc_mn128(uint32_t smem_addr, uint32_t lbo) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
+         ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor with operand formats (0 = fp16, 1 = bf16) and majors (1 = MN-major).
+__host__ __device__ constexpr uint32_t idesc_16(int m, int n, int a_fmt, int b_fmt, int a_mn, int b_mn) {
+  return (1u << 4) | ((uint32_t)a_fmt << 7) | ((uint32_t)b_fmt << 10) | ((uint32_t)a_mn << 15) |
+         ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf2(float a, float b) {   // a in the low half
+  uint32_t d;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  return d;
+}
+
+struct RowsParams {
+  int64_t n_rows;
+  int n_tiles;           // 256-row tiles
+  int k_chunks;          // K / 64
+  int n_halves;          // N / 256
+  int ldn;               // N: row pitch (elements) of mask / acc32 / out16
+  uint32_t idesc;
+  const __half* mask;    // optional [rows, N] fp16 or bf16 relu OUTPUT: D is zeroed where it is +-0 (relu backward)
+  float* acc32;          // optional [rows, N] fp32: written with D (+ its previous content when `accumulate`)
+  int accumulate;
+  __nv_bfloat16* out16;  // optional [rows, N] bf16 copy of what acc32 receives
+  float scale;           // D is multiplied by this first
+  unsigned int* err;
+};
+
+struct WgradParams {
+  int64_t n_rows;
+  int k_split;           // row ranges; grid = 2 (M halves) x k_split pairs
+  int n_halves;          // accumulators of kNB x 128 columns
+  int n_store;           // columns actually stored (<= n_halves * kNB * 128)
+  int ldo;               // pitch of out (floats)
+  uint32_t idesc;
+  float* out;            // [512, ldo] fp32, accumulated with red.global.add
+  unsigned int* err;
+};
+
+// Common prologue: barriers, TMEM.  Returns the TMEM base.
+__device__ __forceinline__ uint32_t gemm_setup(uint32_t smem_base, int warp, int lane, int stages) {
+  auto bar = [&](int i) { return smem_base + kGOffBar + i * 8; };
+  cluster_sync_all();
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(bar(GB_FULL + s), 1);    // the leader's expect_tx arrive (both CTAs' bytes)
+      mbar_init(bar(GB_EMPTY + s), 1);   // one multicast commit
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(bar(GB_ACCF + a), 1);
+      mbar_init(bar(GB_ACCE + a), 16);   // 8 epilogue warps of each CTA of the pair
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc_pair(smem_base + kGOffTmem, 512);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_base + kGOffTmem));
+  return tmem_base;
+}
+
+__device__ __forceinline__ void gemm_teardown(uint32_t tmem_base, int warp) {
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, 512);
+  }
+}
+
+// ---- rows GEMM ----------------------------------------------------------------------------------------
+// Work item = (256-row tile, 256-column half); consecutive items alternate between the two TMEM accumulators so
+// the epilogue of one item overlaps the MMAs of the next.  Stage = A chunk [128 rows x 64 K] (K-major) + this
+// CTA's share of the B chunk [64 K x 128 N] (MN-major, two boxes).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGThreads, 1)
+gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const RowsParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int n_pairs = gridDim.x >> 1, pair_id = blockIdx.x >> 1;
+  auto bar = [&](int i) { return smem_base + kGOffBar + i * 8; };
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_a);
+    prefetch_tensormap(&map_b);
+  }
+  const uint32_t tmem_base = gemm_setup(smem_base, warp, lane, kGStagesRows);
+
+  if (warp == 0) {
+    uint32_t s = 0, ph = 0;
+#pragma unroll 1
+    for (int tile = pair_id; tile < p.n_tiles; tile += n_pairs) {
+#pragma unroll 1
+      for (int half = 0; half < p.n_halves; ++half) {
+        const int n0 = half * 256 + (int)rank * 128;
+#pragma unroll 1
+        for (int kc = 0; kc < p.k_chunks; ++kc) {
+          wait_bar<false>(bar(GB_EMPTY + s), ph ^ 1, p.err, 0x300 + s);
+          if (elect_one()) {
+            const uint32_t full = bar(GB_FULL + s);
+            const uint32_t dst = smem_base + s * kGStageRows;
+            if (rank == 0) mbar_arrive_expect_tx(full, 2 * kGStageRows);
+            tma_load_2d_pair(dst, &map_a, full, kc * 64, tile * 256 + (int)rank * 128);
+            tma_load_2d_pair(dst + 2 * kGBox, &map_b, full, n0, kc * 64);
+            tma_load_2d_pair(dst + 3 * kGBox, &map_b, full, n0 + 64, kc * 64);
+          }
+          __syncwarp();
+          if (++s == kGStagesRows) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1 && rank == 0) {
+    uint32_t s = 0, ph = 0, it = 0;
+    const uint64_t a_hi = smem_desc_k128(0), b_hi = smem_desc_mn128(0, kGBox);
+#pragma unroll 1
+    for (int tile = pair_id; tile < p.n_tiles; tile += n_pairs) {
+#pragma unroll 1
+      for (int half = 0; half < p.n_halves; ++half, ++it) {
+        const uint32_t acc = it & 1, accph = (it >> 1) & 1;
+        wait_bar<true>(bar(GB_ACCE + acc), accph ^ 1, p.err, 0x310 + acc);
+        tc_fence_after();
+#pragma unroll 1
+        for (int kc = 0; kc < p.k_chunks; ++kc) {
+          wait_bar<false>(bar(GB_FULL + s), ph, p.err, 0x320 + s);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t a_lo = (smem_base + s * kGStageRows) >> 4;
+            const uint32_t b_lo = (smem_base + s * kGStageRows + 2 * kGBox) >> 4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              umma_f16_pair(tmem_base + acc * 256, a_hi | (uint64_t)(a_lo + 2 * j), b_hi | (uint64_t)(b_lo + 128 * j),
+                            p.idesc, (kc | j) ? 1u : 0u);
+            umma_commit_pair(bar(GB_EMPTY + s), 0x3);
+          }
+          __syncwarp();
+          if (++s == kGStagesRows) { s = 0; ph ^= 1; }
+        }
+        if (elect_one()) umma_commit_pair(bar(GB_ACCF + acc), 0x3);
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 2) {
+    const int q = warp & 3, ch = (warp - 2) >> 2;
+    uint32_t it = 0;
+#pragma unroll 1
+    for (int tile = pair_id; tile < p.n_tiles; tile += n_pairs) {
+      const int64_t row = (int64_t)tile * 256 + rank * 128 + q * 32 + lane;
+      const bool live = row < p.n_rows;
+#pragma unroll 1
+      for (int half = 0; half < p.n_halves; ++half, ++it) {
+        const uint32_t acc = it & 1, accph = (it >> 1) & 1;
+        wait_bar<false>(bar(GB_ACCF + acc), accph, p.err, 0x330 + acc);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          const int lcol = ch * 128 + c * 32;
+          const size_t off = (size_t)row * p.ldn + half * 256 + lcol;
+          uint4 mk[4];
+          float4 prev[8];
+          if (live && p.mask) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mk[i] = __ldg(reinterpret_cast<const uint4*>(p.mask + off) + i);
+          }
+          if (live && p.accumulate) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) prev[i] = *(reinterpret_cast<const float4*>(p.acc32 + off) + i);
+          }
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * 256 + lcol, v);
+          tmem_wait_ld();
+          if (live) {
+            float f[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.scale;
+            if (p.mask) {
+              const uint32_t* m32 = reinterpret_cast<const uint32_t*>(mk);
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {   // relu outputs are >= 0: "not positive" = all value bits clear
+                if ((m32[i] & 0x7FFFu) == 0) f[2 * i] = 0.0f;
+                if ((m32[i] & 0x7FFF0000u) == 0) f[2 * i + 1] = 0.0f;
+              }
+            }
+            if (p.accumulate) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                f[4 * i] += prev[i].x; f[4 * i + 1] += prev[i].y; f[4 * i + 2] += prev[i].z; f[4 * i + 3] += prev[i].w;
+              }
+            }
+            if (p.acc32) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                *(reinterpret_cast<float4*>(p.acc32 + off) + i) = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+            }
+            if (p.out16) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                *(reinterpret_cast<uint4*>(p.out16 + off) + i) =
+                    make_uint4(pack_bf2(f[8 * i], f[8 * i + 1]), pack_bf2(f[8 * i + 2], f[8 * i + 3]),
+                               pack_bf2(f[8 * i + 4], f[8 * i + 5]), pack_bf2(f[8 * i + 6], f[8 * i + 7]));
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(bar(GB_ACCE + acc), 0);
+      }
+    }
+  }
+  __syncwarp();
+  gemm_teardown(tmem_base, warp);
+}
+
+// ---- wgrad GEMM -----------------------------------------------------------------------------------------
+// Pair (mr, ks): output rows [mr*256, +256) x all N columns, rows [ks-th range) of the K dimension; both operands
+// MN-major.  kNB = 64-column boxes of B per CTA per accumulator (2: N = 256 per accumulator, 1: N = 128).
+// Stage = A 2 boxes + B n_halves * kNB boxes, all [64 x 64].  The partial sums leave through red.global.add.
+template <int kNB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGThreads, 1)
+gemm_wgrad_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                  const WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair_id = blockIdx.x >> 1;
+  const int mr = pair_id & 1, ks = pair_id >> 1;
+  auto bar = [&](int i) { return smem_base + kGOffBar + i * 8; };
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_a);
+    prefetch_tensormap(&map_b);
+  }
+  const uint32_t tmem_base = gemm_setup(smem_base, warp, lane, kGStagesW);
+  const int total_chunks = (int)((p.n_rows + 63) >> 6);
+  const int per = (total_chunks + p.k_split - 1) / p.k_split;
+  const int c_begin = ks * per;
+  const int c_end = (c_begin + per < total_chunks) ? c_begin + per : total_chunks;
+  const int n_acc_cols = kNB * 128;
+  const uint32_t stage_bytes = (uint32_t)(2 + p.n_halves * kNB) * kGBox;
+
+  if (c_begin < c_end) {
+    if (warp == 0) {
+      uint32_t s = 0, ph = 0;
+      const int m0 = mr * 256 + (int)rank * 128;
+#pragma unroll 1
+      for (int c = c_begin; c < c_end; ++c) {
+        wait_bar<false>(bar(GB_EMPTY + s), ph ^ 1, p.err, 0x400 + s);
+        if (elect_one()) {
+          const uint32_t full = bar(GB_FULL + s);
+          const uint32_t dst = smem_base + s * kGStageW;
+          if (rank == 0) mbar_arrive_expect_tx(full, 2 * stage_bytes);
+          tma_load_2d_pair(dst, &map_a, full, m0, c * 64);
+          tma_load_2d_pair(dst + kGBox, &map_a, full, m0 + 64, c * 64);
+          for (int h = 0; h < p.n_halves; ++h)
+#pragma unroll
+            for (int i = 0; i < kNB; ++i)
+              tma_load_2d_pair(dst + (2 + h * kNB + i) * kGBox, &map_b, full,
+                               h * n_acc_cols + (int)rank * (kNB * 64) + i * 64, c * 64);
+        }
+        __syncwarp();
+        if (++s == kGStagesW) { s = 0; ph ^= 1; }
+      }
+    } else if (warp == 1 && rank == 0) {
+      uint32_t s = 0, ph = 0;
+      const uint64_t a_hi = smem_desc_mn128(0, kGBox), b_hi = smem_desc_mn128(0, kGBox);
+#pragma unroll 1
+      for (int c = c_begin; c < c_end; ++c) {
+        wait_bar<false>(bar(GB_FULL + s), ph, p.err, 0x420 + s);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_lo = (smem_base + s * kGStageW) >> 4;
+          for (int h = 0; h < p.n_halves; ++h) {
+            const uint32_t b_lo = (smem_base + s * kGStageW + (2 + h * kNB) * kGBox) >> 4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              umma_f16_pair(tmem_base + h * 256, a_hi | (uint64_t)(a_lo + 128 * j), b_hi | (uint64_t)(b_lo + 128 * j),
+                            p.idesc, (c != c_begin || j) ? 1u : 0u);
+          }
+          umma_commit_pair(bar(GB_EMPTY + s), 0x3);
+        }
+        __syncwarp();
+        if (++s == kGStagesW) { s = 0; ph ^= 1; }
+      }
+      if (elect_one()) umma_commit_pair(bar(GB_ACCF), 0x3);
+      __syncwarp();
+    } else if (warp >= 2) {
+      const int q = warp & 3, ch = (warp - 2) >> 2;
+      wait_bar<false>(bar(GB_ACCF), 0, p.err, 0x430);
+      tc_fence_after();
+      const int m = mr * 256 + (int)rank * 128 + q * 32 + lane;
+      const bool vec = (p.ldo & 3) == 0;
+      for (int h = 0; h < p.n_halves; ++h) {
+#pragma unroll 1
+        for (int c = ch; c < n_acc_cols / 32; c += 2) {
+          const int n = h * n_acc_cols + c * 32;
+          if (n >= p.n_store) continue;     // warp-uniform
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + h * 256 + c * 32, v);
+          tmem_wait_ld();
+          float* o = p.out + (size_t)m * p.ldo + n;
+          if (vec && n + 32 <= p.n_store) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              red_add_v4(o + 4 * i, __uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                         __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (n + i < p.n_store) atomicAdd(o + i, __uint_as_float(v[i]));
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+  __syncwarp();
+  gemm_teardown(tmem_base, warp);
+}
+
+// ---- host side ----------------------------------------------------------------------------------------------
+static int gemm_grid(int* sms_out) {
+  int dev = 0, sms = 0;
+  PN_CUDA_OK(cudaGetDevice(&dev));
+  PN_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  *sms_out = sms;
+  return PN_OK;
+}
+
+template <typename K>
+static int gemm_smem_attr(K kernel) {
+  PN_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmem));
+  return PN_OK;
+}
+
+}  // namespace tc
+}  // namespace pn
+
+extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
+                               const void* mask_f16, float* acc32, int accumulate, void* out_bf16, float scale,
+                               unsigned int* err_word, pn_stream_t stream) {
+  using namespace pn::tc;
+  PN_CHECK_ARG(a && b, "pn_gemm_tc_rows: null pointer");
+  PN_CHECK_ARG((a_fmt | 1) == 1 && a_fmt == b_fmt,
+               "pn_gemm_tc_rows: operands must have the same format, 0 (fp16) or 1 (bf16)");
+  PN_CHECK_ARG(n_rows >= 0 && n_rows < (1ll << 31) - 256, "pn_gemm_tc_rows: bad row count");
+  PN_CHECK_ARG(k > 0 && k % 64 == 0 && n > 0 && n % 256 == 0, "pn_gemm_tc_rows: K must be a multiple of 64, N of 256");
+  PN_CHECK_ARG(acc32 || out_bf16, "pn_gemm_tc_rows: no output");
+  PN_CHECK_ARG(!accumulate || acc32, "pn_gemm_tc_rows: accumulate needs acc32");
+  PN_CHECK_ARG((((uintptr_t)a | (uintptr_t)b | (uintptr_t)mask_f16 | (uintptr_t)acc32 | (uintptr_t)out_bf16) & 15) == 0,
+               "pn_gemm_tc_rows: buffers must be 16-byte aligned");
+  if (n_rows == 0) return PN_OK;
+  static bool attr_set = false;
+  int rc;
+  if (!attr_set) {
+    if ((rc = gemm_smem_attr(gemm_rows_kernel))) return rc;
+    attr_set = true;
+  }
+  CUtensorMap ma, mb;
+  if ((rc = make_map(&ma, a, (uint64_t)n_rows, (uint64_t)k, (uint64_t)k * 2, 128))) return rc;
+  if ((rc = make_map(&mb, b, (uint64_t)k, (uint64_t)n, (uint64_t)n * 2, 64))) return rc;
+  RowsParams p = {};
+  p.n_rows = n_rows;
+  p.n_tiles = (int)((n_rows + 255) / 256);
+  p.k_chunks = k / 64;
+  p.n_halves = n / 256;
+  p.ldn = n;
+  p.idesc = idesc_16(256, 256, a_fmt, b_fmt, 0, 1);
+  p.mask = (const __half*)mask_f16;
+  p.acc32 = acc32;
+  p.accumulate = accumulate;
+  p.out16 = (__nv_bfloat16*)out_bf16;
+  p.scale = scale;
+  p.err = err_word;
+  int sms = 0;
+  if ((rc = gemm_grid(&sms))) return rc;
+  const int pairs = p.n_tiles < sms / 2 ? p.n_tiles : sms / 2;
+  gemm_rows_kernel<<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, p);
+  PN_LAUNCH_OK("gemm_rows_kernel");
+  pn::count_launch();
+  return PN_OK;
+}
+
+extern "C" int pn_gemm_tc_wgrad(const void* g, int g_fmt, int ldg, const void* x, int x_fmt, int ldx, int64_t n_rows,
+                                int n_store, float* out, int ldo, unsigned int* err_word, pn_stream_t stream) {
+  using namespace pn::tc;
+  PN_CHECK_ARG(g && x && out, "pn_gemm_tc_wgrad: null pointer");
+  PN_CHECK_ARG((g_fmt | 1) == 1 && g_fmt == x_fmt,
+               "pn_gemm_tc_wgrad: operands must have the same format, 0 (fp16) or 1 (bf16)");
+  PN_CHECK_ARG(n_rows >= 0 && n_rows < (1ll << 31) - 256, "pn_gemm_tc_wgrad: bad row count");
+  PN_CHECK_ARG(ldg == 512, "pn_gemm_tc_wgrad: the gradient operand must be 512 wide");
+  PN_CHECK_ARG(ldx == 512 || ldx == 64, "pn_gemm_tc_wgrad: the input operand must be 512 or 64 wide");
+  PN_CHECK_ARG(n_store > 0 && n_store <= ldx && ldo >= n_store, "pn_gemm_tc_wgrad: bad output shape");
+  PN_CHECK_ARG((((uintptr_t)g | (uintptr_t)x) & 15) == 0 && ((uintptr_t)out & 3) == 0 &&
+                   ((ldo & 3) != 0 || ((uintptr_t)out & 15) == 0),
+               "pn_gemm_tc_wgrad: misaligned buffer");
+  if (n_rows == 0) return PN_OK;
+  static bool attr_set = false;
+  int rc;
+  if (!attr_set) {
+    if ((rc = gemm_smem_attr(gemm_wgrad_kernel<2>))) return rc;
+    if ((rc = gemm_smem_attr(gemm_wgrad_kernel<1>))) return rc;
+    attr_set = true;
+  }
+  CUtensorMap ma, mb;
+  if ((rc = make_map(&ma, g, (uint64_t)n_rows, (uint64_t)ldg, (uint64_t)ldg * 2, 64))) return rc;
+  if ((rc = make_map(&mb, x, (uint64_t)n_rows, (uint64_t)ldx, (uint64_t)ldx * 2, 64))) return rc;
+  WgradParams p = {};
+  p.n_rows = n_rows;
+  int sms = 0;
+  if ((rc = gemm_grid(&sms))) return rc;
+  const int chunks = (int)((n_rows + 63) / 64);
+  const int max_split = sms / 4;
+  p.k_split = chunks < max_split ? chunks : max_split;
+  p.n_store = n_store;
+  p.ldo = ldo;
+  p.out = out;
+  p.err = err_word;
+  if (ldx == 512) {
+    p.n_halves = 2;
+    p.idesc = idesc_16(256, 256, g_fmt, x_fmt, 1, 1);
+    gemm_wgrad_kernel<2><<<4 * p.k_split, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, p);
+  } else {
+    p.n_halves = 1;   // N = 128 over the pair: rank 1's box lies past column 64 and is zero filled by TMA
+    p.idesc = idesc_16(256, 128, g_fmt, x_fmt, 1, 1);
+    gemm_wgrad_kernel<1><<<4 * p.k_split, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, p);
+  }
+  PN_LAUNCH_OK("gemm_wgrad_kernel");
+  pn::count_launch();
+  return PN_OK;
+}

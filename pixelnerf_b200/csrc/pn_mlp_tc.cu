@@ -38,6 +38,7 @@
 
 #include "pn_common.cuh"
 #include "pn_tc_ptx.cuh"
+#include "pn_tc_host.cuh"
 
 namespace pn {
 namespace tc {
@@ -100,29 +101,6 @@ struct ChainParams {
   int n_views;
   int debug_stage;
 };
-
-__device__ __forceinline__ uint64_t globaltimer_ns() {
-  uint64_t t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-
-// Bounded wait: a protocol bug must become a CUDA error, never a hung GPU.
-template <bool kCluster>
-__device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned int* err, unsigned int code) {
-  uint32_t spins = 0;
-  uint64_t t0 = 0;
-  while (!(kCluster ? mbar_try_wait_cluster(bar, parity) : mbar_try_wait(bar, parity))) {
-    if ((++spins & 0xFFFu) == 0) {
-      const uint64_t t = globaltimer_ns();
-      if (t0 == 0) t0 = t;
-      else if (t - t0 > 4000000000ull) {
-        if (err) atomicExch(err, code);
-        __trap();
-      }
-    }
-  }
-}
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
@@ -726,37 +704,6 @@ pack_bias_kernel(pn_mlp_weights_t w, float* __restrict__ ta, float* __restrict__
 }
 
 // ---- host side ----------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* ptr = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)ptr;
-  }
-  return fn;
-}
-
-// fp16 matrix (rows, cols) with `pitch` bytes per row -> boxes of [box_rows x 64 columns], 128-byte swizzle.
-static int make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch, uint32_t box_rows) {
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) { set_error("cuTensorMapEncodeTiled entry point unavailable"); return PN_ERR_CUDA; }
-  cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {pitch};
-  cuuint32_t box[2] = {64, box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return PN_ERR_CUDA; }
-  return PN_OK;
-}
-
 static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, ChainParams p,
                         cudaStream_t st) {
   static bool attr_set = false;  // idempotent; a benign race at worst repeats the call

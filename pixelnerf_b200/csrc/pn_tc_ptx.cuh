@@ -171,6 +171,30 @@ __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&v
       : "memory");
 }
 
+// ---- bounded barrier wait ---------------------------------------------------------------
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Bounded wait: a protocol bug must become a CUDA error, never a hung GPU.
+template <bool kCluster>
+__device__ __forceinline__ void wait_bar(uint32_t bar, uint32_t parity, unsigned int* err, unsigned int code) {
+  uint32_t spins = 0;
+  uint64_t t0 = 0;
+  while (!(kCluster ? mbar_try_wait_cluster(bar, parity) : mbar_try_wait(bar, parity))) {
+    if ((++spins & 0xFFFu) == 0) {
+      const uint64_t t = globaltimer_ns();
+      if (t0 == 0) t0 = t;
+      else if (t - t0 > 4000000000ull) {
+        if (err) atomicExch(err, code);
+        __trap();
+      }
+    }
+  }
+}
+
 // ---- descriptors ------------------------------------------------------------------------
 // K-major operand tile, 128-byte swizzle: rows of 64 fp16 (128 B), 8-row groups 1024 B apart
 // (SBO), one swizzle atom along K (LBO unused).  Bits: [0,14) addr>>4, [32,46) SBO>>4,
