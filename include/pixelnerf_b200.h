@@ -224,6 +224,31 @@ PN_API int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, i
 PN_API int pn_gemm_tc_wgrad(const void* g, int g_fmt, int ldg, const void* x, int x_fmt, int ldx, int64_t n_rows,
                      int n_store, float* out, int ldo, unsigned int* err_word, pn_stream_t stream);
 
+/* ---- (3d) tensor-core training path of the MLP (forward that keeps activations + backward) ------------- */
+
+/* pn_mlp_forward_tc that also stores the bf16 relu'd operand of every 512-wide GEMM (11 slots of rows x 512:
+ * slot 2b = relu(h_b), 2b+1 = relu(fc_0 out of block b), 10 = relu(h_5); slots 6.. hold n_objects*P rows when
+ * n_views > 1).  `acts` needs pn_mlp_tc_acts_bytes(rows). */
+PN_API size_t pn_mlp_tc_acts_bytes(int64_t n_rows);
+PN_API int pn_mlp_forward_tc_train(const void* packed, const void* tables, int64_t n_texels, const void* feat_x,
+                            int n_objects, int n_views, int64_t points_per_object, float* out, float* pre_act,
+                            void* workspace, size_t workspace_bytes, void* acts, size_t acts_bytes,
+                            pn_stream_t stream);
+
+/* bf16 row-major copies of fc_0[0..4], fc_1[0..4], lin_z[0..2] (the dgrad GEMMs' B operands). */
+PN_API size_t pn_mlp_tc_w16_bytes(void);
+PN_API int pn_prepare_weights_bf16(const pn_mlp_weights_t* w, void* w16, size_t w16_bytes, pn_stream_t stream);
+
+/* Backward of ResnetFC + head (what autograd computes for resnetfc.py:132-184 / models.py:257-266) on the tensor
+ * cores: g_out = dL/d out (n_objects*P, 4); every tensor of `grads` is accumulated into (+=); g_feat_z (optional,
+ * rows x 512 fp32) receives dL/d(latent part of the MLP input) for pn_point_features_bwd.  feat_x is the forward's
+ * (rows, 64) fp16 code rows with the embedded taps record; latent_nhwc the fp32 channels-last latent. */
+PN_API size_t pn_mlp_backward_tc_workspace_bytes(int64_t n_rows, int n_views);
+PN_API int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, const void* feat_x,
+                       const float* latent_nhwc, int n_objects, int n_views, int64_t points_per_object,
+                       const void* acts, const float* out, const float* g_out, const pn_mlp_grads_t* grads,
+                       float* g_feat_z, void* workspace, size_t workspace_bytes, pn_stream_t stream);
+
 /* ---- (5) either side of the render path --------------------------------------- */
 
 /* Camera rays on the device: util.gen_rays (src/util/util.py:238-276) with unproj_map (:113-143) for

@@ -67,6 +67,13 @@ _SIGNATURES = {
     "pn_prepare_latent_tables": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp, _sz, _vp]),
     "pn_composite_fwd": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "pn_composite_bwd": (_int, [_vp] * 8 + [_i64, _int, _int, _vp]),
+    "pn_mlp_tc_acts_bytes": (_sz, [_i64]),
+    "pn_mlp_forward_tc_train": (_int, [_vp, _vp, _i64, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp, _sz, _vp]),
+    "pn_mlp_tc_w16_bytes": (_sz, []),
+    "pn_prepare_weights_bf16": (_int, [C.POINTER(MlpWeights), _vp, _sz, _vp]),
+    "pn_mlp_backward_tc_workspace_bytes": (_sz, [_i64, _int]),
+    "pn_mlp_backward_tc": (_int, [C.POINTER(MlpWeights), _vp, _vp, _vp, _int, _int, _i64, _vp, _vp, _vp,
+                                  C.POINTER(MlpGrads), _vp, _vp, _sz, _vp]),
     "pn_gemm_tc_rows": (_int, [_vp, _int, _vp, _int, _i64, _int, _int, _vp, _vp, _int, _vp, _f32, _vp, _vp]),
     "pn_gemm_tc_wgrad": (_int, [_vp, _int, _int, _vp, _int, _int, _i64, _int, _vp, _int, _vp, _vp]),
     "pn_gen_rays": (_int, [_vp, _int, _int, _int, _int, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
@@ -461,3 +468,49 @@ def gemm_tc_wgrad(g, x, out, n_store=None):
                                       x.shape[1], rows, n_store, _ptr(out), out.shape[1],
                                       _err_word(g.device).data_ptr(), _stream()), "pn_gemm_tc_wgrad")
     return out
+
+
+def mlp_forward_tc_train(packed, tables, feat_x, n_objects, n_views, ppo):
+    """Tensor-core forward that keeps the bf16 operand of every 512-wide GEMM: returns (out (P,4), acts)."""
+    n_rows = n_objects * n_views * ppo
+    dev = feat_x.device
+    if feat_x.shape != (n_rows, 64) or feat_x.dtype != torch.float16 or not feat_x.is_contiguous():
+        raise RuntimeError("tensor-core MLP needs contiguous fp16 feat_x of shape (rows, 64)")
+    out = torch.empty(n_objects * ppo, 4, device=dev, dtype=torch.float32)
+    nbytes = lib().pn_mlp_tc_workspace_bytes(n_rows, n_views)
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    abytes = lib().pn_mlp_tc_acts_bytes(n_rows)
+    acts = torch.empty(abytes, device=dev, dtype=torch.uint8)
+    with _Timed("mlp_train_fwd"):
+        _check(lib().pn_mlp_forward_tc_train(packed.data_ptr(), tables.data_ptr(), tables.shape[1],
+                                             _ptr(feat_x, torch.float16), n_objects, n_views, ppo, _ptr(out), None,
+                                             ws.data_ptr(), nbytes, acts.data_ptr(), abytes, _stream()),
+               "pn_mlp_forward_tc_train")
+    return out, acts
+
+
+def pack_weights_bf16(w):
+    """bf16 copies of the thirteen 512x512 matrices for the tensor-core backward."""
+    s, keep = pack_weights_fp32(w)
+    nbytes = lib().pn_mlp_tc_w16_bytes()
+    w16 = torch.empty(nbytes, device=keep["lin_in.weight"].device, dtype=torch.uint8)
+    _check(lib().pn_prepare_weights_bf16(C.byref(s), w16.data_ptr(), nbytes, _stream()), "pn_prepare_weights_bf16")
+    return w16
+
+
+def mlp_backward_tc(packed32, w16, feat_x, latent_nhwc, n_objects, n_views, ppo, acts, out, g_out, grads,
+                    want_g_feat_z):
+    """grads: dict keyed by weight_names(), accumulated into (+=); returns dL/d feat_z (rows, 512) fp32 or None."""
+    s, _keep = packed32
+    sg = _fill_struct(MlpGrads(), grads)
+    n_rows = n_objects * n_views * ppo
+    dev = feat_x.device
+    g_fz = torch.empty(n_rows, D_LATENT, device=dev, dtype=torch.float32) if want_g_feat_z else None
+    nbytes = lib().pn_mlp_backward_tc_workspace_bytes(n_rows, n_views)
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    with _Timed("mlp_train_bwd"):
+        _check(lib().pn_mlp_backward_tc(C.byref(s), w16.data_ptr(), _ptr(feat_x, torch.float16), _ptr(latent_nhwc),
+                                        n_objects, n_views, ppo, acts.data_ptr(), _ptr(out), _ptr(_f32c(g_out)),
+                                        C.byref(sg), _ptr(g_fz), ws.data_ptr(), nbytes, _stream()),
+               "pn_mlp_backward_tc")
+    return g_fz

@@ -92,6 +92,8 @@ struct ChainParams {
   float4* out;           // (rows, 4) [sigmoid rgb, relu sigma], segments ending in lin_out
   float4* pre;           // optional raw lin_out outputs
   float* h_io;           // segment [0,3): fp32 h written here; segment [3,5]: view-mean of it read
+  uint16_t* save;        // training: 11 slots of (save_stride) bf16, the relu'd operand of every 512-wide GEMM
+  int64_t save_stride;   //   slot 2b = relu(h_b) (fc_0 input), 2b+1 = relu(fc_0 out) (fc_1 input), 10 = lin_out input
   float* debug_h;        // optional (rows, 512) dump of h at stage debug_stage
   unsigned int* err;     // device word set before a watchdog trap
   int64_t n_rows;        // rows this launch processes
@@ -111,12 +113,26 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
   return v;
 }
+__device__ __forceinline__ uint32_t pack_relu_bf2(float a, float b) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  return d;
+}
+// 32 relu'd values of one row -> 64 bytes of bf16
+__device__ __forceinline__ void save_relu32(uint16_t* dst, const float (&x)[32]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    reinterpret_cast<uint4*>(dst)[i] =
+        make_uint4(pack_relu_bf2(x[8 * i + 0], x[8 * i + 1]), pack_relu_bf2(x[8 * i + 2], x[8 * i + 3]),
+                   pack_relu_bf2(x[8 * i + 4], x[8 * i + 5]), pack_relu_bf2(x[8 * i + 6], x[8 * i + 7]));
+}
 __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
   uint32_t d;
   asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
   return d;
 }
 
+template <bool kSave>
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
                  const ChainParams p) {
@@ -475,7 +491,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // mode 0: relu -> ACT operand; mode 1: dump fp32 to h_io (segment end)
     // gather_b >= 0 (h before blocks 0-2): add the lin_z[gather_b] table blend instead of a bias vector and
     // write the sum back to tensor memory, so the residual stream carries it from here on.
-    auto epi = [&](int region, const float* bias_vec, int gather_b, uint32_t xslot, int mode, int64_t grow, bool dbg) {
+    auto epi = [&](int region, const float* bias_vec, int gather_b, uint32_t xslot, int mode, int64_t grow, bool dbg,
+                   int slot) {
 #pragma unroll 1
       for (int nb = 0; nb < 2; ++nb) {
         const int a = region * 2 + nb;
@@ -553,6 +570,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         if (gather_b >= 0) tmem_wait_st();
         tc_fence_before();
         signal_chunk(c0);
+        if (kSave && grow < p.n_rows)
+          save_relu32(p.save + (size_t)slot * p.save_stride + grow * 512 + c0 * 64 + 32 * ch, b0);
 #pragma unroll
         for (int i = 0; i < 4; ++i)
           st_shared_v4(dst + kChunkBytes + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
@@ -560,6 +579,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
                        pack_relu_h2(b1[8 * i + 4], b1[8 * i + 5]), pack_relu_h2(b1[8 * i + 6], b1[8 * i + 7]));
         fence_proxy_async_smem();
         signal_chunk(c0 + 1);
+        if (kSave && grow < p.n_rows)
+          save_relu32(p.save + (size_t)slot * p.save_stride + grow * 512 + c0 * 64 + 64 + 32 * ch, b1);
       }
     };
     // Segment [3,5] entry: h = mean over views of the fp32 h the first segment wrote.
@@ -602,6 +623,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           fence_proxy_async_smem();
           tc_fence_before();
           signal_chunk(c);
+          if (kSave && valid) save_relu32(p.save + (size_t)(2 * p.first_block) * p.save_stride + grow * 512 + n0, x);
         }
       }
     };
@@ -614,11 +636,11 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       if (!full_front) epi_load(grow);
       for (int b = p.first_block; b < p.last_block; ++b) {
         if (b > p.first_block || full_front)
-          epi(0, p.bias + b * 512, b < 3 ? b : -1, xslot, 0, grow, p.debug_h != nullptr && p.debug_stage == b);
-        epi(1, p.bias + (6 + b) * 512, -1, 0u, 0, grow, false);
+          epi(0, p.bias + b * 512, b < 3 ? b : -1, xslot, 0, grow, p.debug_h != nullptr && p.debug_stage == b, 2 * b);
+        epi(1, p.bias + (6 + b) * 512, -1, 0u, 0, grow, false, 2 * b + 1);
       }
       if (has_head) {
-        epi(0, p.bias + 5 * 512, -1, 0u, 0, grow, p.debug_h != nullptr && p.debug_stage == 5);
+        epi(0, p.bias + 5 * 512, -1, 0u, 0, grow, p.debug_h != nullptr && p.debug_stage == 5, 10);
         // lin_out result: features 0-3 of block 0 = lanes 0-63, columns kColT..+3
         wait_bar<false>(bar(BAR_ACC + 2), n_acc[2] & 1, p.err, 0x310);
         ++n_acc[2];
@@ -641,7 +663,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
         tc_fence_before();
       } else {
-        epi(0, p.bias + p.last_block * 512, -1, 0u, 1, grow, false);
+        epi(0, p.bias + p.last_block * 512, -1, 0u, 1, grow, false, -1);
       }
     }
   }
@@ -708,7 +730,8 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, ChainParam
                         cudaStream_t st) {
   static bool attr_set = false;  // idempotent; a benign race at worst repeats the call
   if (!attr_set) {
-    PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
+    PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
+    PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
     attr_set = true;
   }
   int dev = 0, sms = 0;
@@ -732,7 +755,8 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, ChainParam
   attrs[1].val.preferredClusterDim.x = 4; attrs[1].val.preferredClusterDim.y = 1; attrs[1].val.preferredClusterDim.z = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 2;
-  PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel, mw, mx, p));
+  if (p.save) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<true>, mw, mx, p));
+  else PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false>, mw, mx, p));
   PN_LAUNCH_OK("mlp_chain_kernel");
   count_launch();
   return PN_OK;
@@ -767,11 +791,39 @@ extern "C" size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views) {
   return 256 + (n_views > 1 && n_rows > 0 ? (size_t)n_rows * 512 * sizeof(float) : 0);
 }
 
+extern "C" size_t pn_mlp_tc_acts_bytes(int64_t n_rows) {
+  return (size_t)(n_rows > 0 ? n_rows : 0) * 512 * 2 * 11 + 256;
+}
+
+static int mlp_forward_tc_impl(const void* packed, const void* tables, int64_t n_texels, const void* feat_x,
+                               int n_objects, int n_views, int64_t points_per_object, float* out, float* pre_act,
+                               void* workspace, size_t workspace_bytes, const pn_mlp_tc_debug_t* dbg, void* acts,
+                               pn_stream_t stream);
+
 extern "C" int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t n_texels,
                                  const void* feat_x, int n_objects,
                                  int n_views, int64_t points_per_object, float* out, float* pre_act,
                                  void* workspace, size_t workspace_bytes, const pn_mlp_tc_debug_t* dbg,
                                  pn_stream_t stream) {
+  return mlp_forward_tc_impl(packed, tables, n_texels, feat_x, n_objects, n_views, points_per_object, out, pre_act,
+                             workspace, workspace_bytes, dbg, nullptr, stream);
+}
+
+extern "C" int pn_mlp_forward_tc_train(const void* packed, const void* tables, int64_t n_texels,
+                                       const void* feat_x, int n_objects, int n_views, int64_t points_per_object,
+                                       float* out, float* pre_act, void* workspace, size_t workspace_bytes,
+                                       void* acts, size_t acts_bytes, pn_stream_t stream) {
+  PN_CHECK_ARG(acts && ((uintptr_t)acts & 15) == 0, "pn_mlp_forward_tc_train: activation buffer missing or misaligned");
+  PN_CHECK_ARG(acts_bytes >= pn_mlp_tc_acts_bytes((int64_t)n_objects * n_views * points_per_object),
+               "pn_mlp_forward_tc_train: activation buffer too small");
+  return mlp_forward_tc_impl(packed, tables, n_texels, feat_x, n_objects, n_views, points_per_object, out, pre_act,
+                             workspace, workspace_bytes, nullptr, acts, stream);
+}
+
+static int mlp_forward_tc_impl(const void* packed, const void* tables, int64_t n_texels, const void* feat_x,
+                               int n_objects, int n_views, int64_t points_per_object, float* out, float* pre_act,
+                               void* workspace, size_t workspace_bytes, const pn_mlp_tc_debug_t* dbg, void* acts,
+                               pn_stream_t stream) {
   using namespace pn::tc;
   PN_CHECK_ARG(packed && tables && feat_x && out && workspace, "pn_mlp_forward_tc: null pointer");
   PN_CHECK_ARG(n_texels > 0, "pn_mlp_forward_tc: no texels");
@@ -801,6 +853,8 @@ extern "C" int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t
   p.n_views = n_views;
   p.debug_h = dbg ? dbg->h : nullptr;
   p.debug_stage = dbg ? dbg->stage : -1;
+  p.save = (uint16_t*)acts;
+  p.save_stride = n_rows * 512;
   const float* ta = (const float*)((const char*)packed + kPackedWeightBytes);
   const float* tb = (const float*)((const char*)packed + kPackedWeightBytes + kBiasBytes);
   if (n_views == 1) {

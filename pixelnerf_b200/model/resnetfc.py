@@ -66,6 +66,8 @@ class ResnetFC(nn.Module):
         if hit is None or hit[0] != key:
             if precision == "fp32":
                 hit = (key, _lib.pack_weights_fp32(params))
+            elif precision == "bf16_train":   # row-major bf16 copies for the tensor-core backward
+                hit = (key, _lib.pack_weights_bf16(params))
             else:
                 hit = (key, _lib.pack_weights_tc(params, precision))
             self._packed[precision] = hit

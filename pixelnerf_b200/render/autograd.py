@@ -6,7 +6,9 @@ Here the forward is the ordinary kernel path and the backward is hand written:
 
     upstream (g_rgb, g_depth, g_weights) per pass
       -> pn_composite_bwd                    dL/d(rgb, sigma) per sample
-      -> pn_mlp_backward_fp32                head + 15 linears: weight/bias grads, dL/d feat_z
+      -> pn_mlp_backward_fp32 / _tc          head + 15 linears: weight/bias grads, dL/d feat_z
+                                             (mlp_precision fp32: CUDA cores; fp16: tcgen05 dgrad/wgrad GEMMs
+                                             with bf16 gradients, csrc/pn_train_tc.cu)
       -> pn_point_features_bwd               bilinear scatter-add into the latent gradient
       -> returned to torch autograd          the ResNet34 encoder's backward stays in torch
 
@@ -97,10 +99,27 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
             return None
         return t.reshape(sb, b, *t.shape[1:])[:, s:e].reshape(sb * (e - s), *t.shape[1:]).contiguous()
 
+    tensor_core = model.mlp_precision != "fp32"
+    if tensor_core:
+        packed_tc, w16 = mlp.packed(model.mlp_precision), mlp.packed("bf16_train")
+        tables = model.latent_tables(coarse)
+        _, hl, wl, _ = latent.shape
+        chunk = max(1, renderer.max_rows_train_tc // max(1, sb * ns * k))
     for s in range(0, b, chunk):
         e = min(b, s + chunk)
         rr, zz = cut(rays, s, e), cut(z, s, e)
         ppo = (e - s) * k
+        if tensor_core:
+            # forward chain on the tensor cores keeping its bf16 GEMM operands, then dgrad / wgrad GEMMs on them
+            fx = _lib.point_taps(cam, hl, wl, ppo, rays=rr, z=zz)
+            out, acts = _lib.mlp_forward_tc_train(packed_tc, tables, fx, sb, ns, ppo)
+            g_rs, _ = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
+                                         cut(g_depth, s, e), cut(g_w, s, e), want_gz=False)
+            g_fz = _lib.mlp_backward_tc(packed, w16, fx, latent, sb, ns, ppo, acts, out, g_rs.reshape(-1, 4), grads,
+                                        want_g_feat_z=g_lat is not None)
+            if g_lat is not None:
+                _lib.point_features_bwd(cam, g_lat, ppo, g_fz, rays=rr, z=zz)
+            continue
         fz, fx = _lib.point_features(cam, latent, ppo, rays=rr, z=zz, ldx=44)
         out, acts = _lib.mlp_forward_fp32_train(packed, fz, fx, sb, ns, ppo)
         g_rs, _ = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),

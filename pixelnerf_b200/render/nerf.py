@@ -67,6 +67,7 @@ class NeRFRenderer(torch.nn.Module):
         self.injected_z = None  # teacher forcing: dict(z_coarse=..., z_fine=...)
         self.max_rows_per_launch = 1 << 21
         self.max_rows_train = 1 << 16  # rows whose 11 fp32 activation tensors are kept at once (1.4 GB)
+        self.max_rows_train_tc = 1 << 20  # tensor-core training path: ~20 KB per row of activations + workspace
 
     # ---------------------------------------------------------------- sampling
     @staticmethod

@@ -91,3 +91,33 @@ def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo):
     stages.append(h)
     pre = q(h) @ W("lin_out").T + B("lin_out")
     return stages, pre
+
+
+def emulate_tc_backward(w, acts, z, x, out, g_out, sb, ns, ppo):
+    """float64 restatement of pn_mlp_backward_tc given the forward's own saved operands: `acts` is the list of
+    the 11 saved relu outputs (slot 2b = relu(h_b), 2b+1 = relu(fc_0 out), 10 = relu(h_5); rows (obj, view,
+    point) for slots < 6, (obj, point) after the view mean), z (rows, 512) the blended latent, x (rows, 42)
+    the code.  Exact arithmetic (no bf16 rounding of the gradients), relu decisions read off the saved
+    operands exactly as the kernels do.  Returns ({weight name: grad}, dL/dz)."""
+    W = {k: v.double() for k, v in w.items()}
+    o = out.double()
+    gp = torch.cat([o[:, :3] * (1 - o[:, :3]) * g_out[:, :3].double(), (o[:, 3:] > 0) * g_out[:, 3:].double()], -1)
+    g = {"lin_out.weight": gp.t() @ acts[10], "lin_out.bias": gp.sum(0)}
+    gh = (gp @ W["lin_out.weight"]) * (acts[10] > 0)
+    gz = torch.zeros_like(z, dtype=torch.float64)
+    for b in (4, 3, 2, 1, 0):
+        if b == 2 and ns > 1:   # backward of the view mean
+            gh = (gh.reshape(sb, 1, ppo, 512) / ns).expand(sb, ns, ppo, 512).reshape(-1, 512)
+        g[f"blocks.{b}.fc_1.weight"] = gh.t() @ acts[2 * b + 1]
+        g[f"blocks.{b}.fc_1.bias"] = gh.sum(0)
+        g1 = (gh @ W[f"blocks.{b}.fc_1.weight"]) * (acts[2 * b + 1] > 0)
+        g[f"blocks.{b}.fc_0.weight"] = g1.t() @ acts[2 * b]
+        g[f"blocks.{b}.fc_0.bias"] = g1.sum(0)
+        gh = gh + (g1 @ W[f"blocks.{b}.fc_0.weight"]) * (acts[2 * b] > 0)
+        if b < 3:
+            g[f"lin_z.{b}.weight"] = gh.t() @ z.double()
+            g[f"lin_z.{b}.bias"] = gh.sum(0)
+            gz = gz + gh @ W[f"lin_z.{b}.weight"]
+    g["lin_in.weight"] = gh.t() @ x.double()
+    g["lin_in.bias"] = gh.sum(0)
+    return g, gz
