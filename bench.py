@@ -361,10 +361,19 @@ def run_train(args):
         ms = a.elapsed_time(b) / steps
         n = sb * n_obj_rays
         flop = 3.0 * n * (N_COARSE + N_COARSE + N_FINE) * MLP_FLOP_PER_POINT[1]
+        # one more step with CUDA events around every kernel family (not part of the timed region)
+        from pixelnerf_b200 import _lib
+        _lib.PROFILE = {}
+        step()
+        torch.cuda.synchronize()
+        fam = {k: round(sum(e0.elapsed_time(e1) for e0, e1 in v), 3) for k, v in _lib.PROFILE.items()}
+        _lib.PROFILE = None
         res.append({"rays_per_step": n, "ms_per_step": ms, "rays/s": n / (ms * 1e-3), "mlp_TFLOP/s_fwd+bwd": flop / (ms * 1e-3) / 1e12,
-                    "loss": float(loss)})
+                    "loss": float(loss), "kernel_ms": fam})
+    backward = ("tcgen05 dgrad/wgrad GEMMs, bf16 gradients, forward chain re-run per chunk keeping its operands"
+                if args.precision != "fp32" else "fp32 CUDA-core kernels, recompute per chunk")
     print(json.dumps({"metric": "training step rays/sec (config 5)", "unit": "rays/s", "objects": sb,
-                      "forward": "%s chain" % args.precision, "backward": "fp32 CUDA-core kernels, recompute per chunk",
+                      "forward": "%s chain" % args.precision, "backward": backward,
                       "optimizer": "Adam on both MLPs", "sweep": res}))
 
 

@@ -212,11 +212,13 @@ PN_API int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t n_t
 /* D[rows, n] = scale * A[rows, k] x B[k, n]  (both row-major 16-bit of the SAME format, 0 = fp16 or 1 = bf16; k % 64 == 0,
  * n % 256 == 0), fp32 accumulation on tcgen05.  Epilogue: optional relu-backward mask (mask_f16[rows, n], fp16 or bf16, is
  * the relu OUTPUT of the layer: D is zeroed where it is zero), optional `+= acc32` (accumulate != 0), then D is
- * written to acc32 (fp32) and/or out_bf16.  dgrad of a linear y = x W^T: A = dL/dy, B = W as stored ([out, in]).
+ * written to acc32 (fp32) and/or out_bf16.  resid_bf16 (optional, [rows, n] bf16, may alias out_bf16) is added
+ * to D before it is written; colsum0 / colsum1 (optional, [n] fp32, n <= 512) receive += the column sums of
+ * the result (the bias gradient of the layer that produced A's consumer).  dgrad of a linear y = x W^T: A = dL/dy, B = W as stored ([out, in]).
  * err_word: optional device word receiving a watchdog code before a trap. */
 PN_API int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
-                    const void* mask_f16, float* acc32, int accumulate, void* out_bf16, float scale,
-                    unsigned int* err_word, pn_stream_t stream);
+                    const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16, void* out_bf16,
+                    float scale, float* colsum0, float* colsum1, unsigned int* err_word, pn_stream_t stream);
 
 /* out[512, ldo] (fp32, first n_store columns) += G[rows, 512]^T x X[rows, ldx]  (ldx = 512, or 64 for lin_in's
  * padded code rows), split over row ranges, partial sums added with red.global.add: wgrad of y = x W^T with

@@ -74,7 +74,8 @@ _SIGNATURES = {
     "pn_mlp_backward_tc_workspace_bytes": (_sz, [_i64, _int]),
     "pn_mlp_backward_tc": (_int, [C.POINTER(MlpWeights), _vp, _vp, _vp, _int, _int, _i64, _vp, _vp, _vp,
                                   C.POINTER(MlpGrads), _vp, _vp, _sz, _vp]),
-    "pn_gemm_tc_rows": (_int, [_vp, _int, _vp, _int, _i64, _int, _int, _vp, _vp, _int, _vp, _f32, _vp, _vp]),
+    "pn_gemm_tc_rows": (_int, [_vp, _int, _vp, _int, _i64, _int, _int, _vp, _vp, _int, _vp, _vp, _f32, _vp, _vp, _vp,
+                               _vp]),
     "pn_gemm_tc_wgrad": (_int, [_vp, _int, _int, _vp, _int, _int, _i64, _int, _vp, _int, _vp, _vp]),
     "pn_gen_rays": (_int, [_vp, _int, _int, _int, _int, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
     "pn_frame_to_u8": (_int, [_vp, _vp, _i64, _vp]),
@@ -443,17 +444,20 @@ def _err_word(dev):
     return _ERR_WORD[key]
 
 
-def gemm_tc_rows(a, b, mask=None, acc32=None, accumulate=False, want16=True, scale=1.0):
+def gemm_tc_rows(a, b, mask=None, acc32=None, accumulate=False, want16=True, scale=1.0, resid=None, colsum=None,
+                 colsum2=None):
     """scale * a[rows, k] @ b[k, n] on the tensor cores (16-bit operands, fp32 accumulate), optionally masked by
-    the relu output `mask` and added to `acc32`; returns (acc32 or None, bf16 copy or None)."""
+    the relu output `mask`, added to `acc32` (fp32, in place) and/or `resid` (bf16); `colsum` / `colsum2` (n,) fp32
+    receive += the column sums of the result.  Returns (acc32 or None, bf16 copy or None)."""
     rows, k = a.shape
     n = b.shape[1]
     assert b.shape[0] == k and a.is_contiguous() and b.is_contiguous()
     out16 = torch.empty(rows, n, device=a.device, dtype=torch.bfloat16) if want16 else None
     with _Timed("gemm_rows"):
         _check(lib().pn_gemm_tc_rows(_ptr(a, a.dtype), _FMT[a.dtype], _ptr(b, b.dtype), _FMT[b.dtype], rows, k, n,
-                                     _ptr(mask, mask.dtype if mask is not None else None), _ptr(acc32), int(bool(accumulate)),
-                                     _ptr(out16, torch.bfloat16), float(scale), _err_word(a.device).data_ptr(),
+                                     _ptr(mask, mask.dtype if mask is not None else None), _ptr(acc32),
+                                     int(bool(accumulate)), _ptr(resid, torch.bfloat16), _ptr(out16, torch.bfloat16),
+                                     float(scale), _ptr(colsum), _ptr(colsum2), _err_word(a.device).data_ptr(),
                                      _stream()), "pn_gemm_tc_rows")
     return acc32, out16
 

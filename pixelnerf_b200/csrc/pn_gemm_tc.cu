@@ -29,7 +29,8 @@ constexpr int kGRing = 192 * 1024;
 constexpr int kGOffBar = kGRing;
 enum { GB_FULL = 0, GB_EMPTY = 8, GB_ACCF = 16, GB_ACCE = 18, GB_COUNT = 20 };
 constexpr int kGOffTmem = kGOffBar + GB_COUNT * 8;
-constexpr int kGSmem = kGOffTmem + 16 + 1024;
+constexpr int kGOffColsum = kGOffTmem + 16;            // 512 floats: per-CTA column sums (rows GEMM)
+constexpr int kGSmem = kGOffColsum + 512 * 4 + 1024;
 static_assert(kGSmem <= 227 * 1024, "shared memory budget");
 
 // MN-major operand tile, 128-byte swizzle: 64 contiguous M/N elements per 128-byte row, 8 K rows per 1024-byte
@@ -63,7 +64,10 @@ struct RowsParams {
   const __half* mask;    // optional [rows, N] fp16 or bf16 relu OUTPUT: D is zeroed where it is +-0 (relu backward)
   float* acc32;          // optional [rows, N] fp32: written with D (+ its previous content when `accumulate`)
   int accumulate;
-  __nv_bfloat16* out16;  // optional [rows, N] bf16 copy of what acc32 receives
+  const __nv_bfloat16* resid16;  // optional [rows, N] bf16 added to D (may alias out16: same thread reads then writes)
+  __nv_bfloat16* out16;  // optional [rows, N] bf16 copy of the result
+  float* colsum0;        // optional [N] fp32: += column sums of the result (bias gradients), up to two destinations
+  float* colsum1;
   float scale;           // D is multiplied by this first
   unsigned int* err;
 };
@@ -129,7 +133,9 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     prefetch_tensormap(&map_a);
     prefetch_tensormap(&map_b);
   }
-  const uint32_t tmem_base = gemm_setup(smem_base, warp, lane, kGStagesRows);
+  float* cs_smem = reinterpret_cast<float*>(smem_raw + (smem_base - smem_u32(smem_raw)) + kGOffColsum);
+  for (int i = threadIdx.x; i < 512; i += kGThreads) cs_smem[i] = 0.0f;
+  const uint32_t tmem_base = gemm_setup(smem_base, warp, lane, kGStagesRows);   // cluster barrier inside
 
   if (warp == 0) {
     uint32_t s = 0, ph = 0;
@@ -200,49 +206,76 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         for (int c = 0; c < 4; ++c) {
           const int lcol = ch * 128 + c * 32;
           const size_t off = (size_t)row * p.ldn + half * 256 + lcol;
-          uint4 mk[4];
-          float4 prev[8];
+          uint32_t mk[16], prev[32], rs[16];
+          if (live && p.resid16) {
+            ldg_v8(p.resid16 + off, reinterpret_cast<uint32_t(&)[8]>(rs[0]));
+            ldg_v8(p.resid16 + off + 16, reinterpret_cast<uint32_t(&)[8]>(rs[8]));
+          }
           if (live && p.mask) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) mk[i] = __ldg(reinterpret_cast<const uint4*>(p.mask + off) + i);
+            ldg_v8(p.mask + off, reinterpret_cast<uint32_t(&)[8]>(mk[0]));
+            ldg_v8(p.mask + off + 16, reinterpret_cast<uint32_t(&)[8]>(mk[8]));
           }
           if (live && p.accumulate) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) prev[i] = *(reinterpret_cast<const float4*>(p.acc32 + off) + i);
+            for (int i = 0; i < 4; ++i) ldg_v8(p.acc32 + off + 8 * i, reinterpret_cast<uint32_t(&)[8]>(prev[8 * i]));
           }
           uint32_t v[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * 256 + lcol, v);
           tmem_wait_ld();
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = 0.0f;
           if (live) {
-            float f[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.scale;
             if (p.mask) {
-              const uint32_t* m32 = reinterpret_cast<const uint32_t*>(mk);
 #pragma unroll
               for (int i = 0; i < 16; ++i) {   // relu outputs are >= 0: "not positive" = all value bits clear
-                if ((m32[i] & 0x7FFFu) == 0) f[2 * i] = 0.0f;
-                if ((m32[i] & 0x7FFF0000u) == 0) f[2 * i + 1] = 0.0f;
+                if ((mk[i] & 0x7FFFu) == 0) f[2 * i] = 0.0f;
+                if ((mk[i] & 0x7FFF0000u) == 0) f[2 * i + 1] = 0.0f;
               }
             }
             if (p.accumulate) {
 #pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                f[4 * i] += prev[i].x; f[4 * i + 1] += prev[i].y; f[4 * i + 2] += prev[i].z; f[4 * i + 3] += prev[i].w;
+              for (int i = 0; i < 32; ++i) f[i] += __uint_as_float(prev[i]);
+            }
+            if (p.resid16) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                f[2 * i] += __uint_as_float(rs[i] << 16);
+                f[2 * i + 1] += __uint_as_float(rs[i] & 0xFFFF0000u);
               }
             }
             if (p.acc32) {
 #pragma unroll
-              for (int i = 0; i < 8; ++i)
-                *(reinterpret_cast<float4*>(p.acc32 + off) + i) = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+              for (int i = 0; i < 4; ++i)
+                stg_v8(p.acc32 + off + 8 * i, __float_as_uint(f[8 * i]), __float_as_uint(f[8 * i + 1]),
+                       __float_as_uint(f[8 * i + 2]), __float_as_uint(f[8 * i + 3]), __float_as_uint(f[8 * i + 4]),
+                       __float_as_uint(f[8 * i + 5]), __float_as_uint(f[8 * i + 6]), __float_as_uint(f[8 * i + 7]));
             }
             if (p.out16) {
 #pragma unroll
-              for (int i = 0; i < 4; ++i)
-                *(reinterpret_cast<uint4*>(p.out16 + off) + i) =
-                    make_uint4(pack_bf2(f[8 * i], f[8 * i + 1]), pack_bf2(f[8 * i + 2], f[8 * i + 3]),
-                               pack_bf2(f[8 * i + 4], f[8 * i + 5]), pack_bf2(f[8 * i + 6], f[8 * i + 7]));
+              for (int i = 0; i < 2; ++i)
+                stg_v8(p.out16 + off + 16 * i, pack_bf2(f[16 * i], f[16 * i + 1]), pack_bf2(f[16 * i + 2], f[16 * i + 3]),
+                       pack_bf2(f[16 * i + 4], f[16 * i + 5]), pack_bf2(f[16 * i + 6], f[16 * i + 7]),
+                       pack_bf2(f[16 * i + 8], f[16 * i + 9]), pack_bf2(f[16 * i + 10], f[16 * i + 11]),
+                       pack_bf2(f[16 * i + 12], f[16 * i + 13]), pack_bf2(f[16 * i + 14], f[16 * i + 15]));
             }
+          }
+          if (p.colsum0) {
+            // column sums over the warp's 32 rows by a transposing butterfly (31 shuffles): lane l ends up
+            // with column lcol + l; dead rows hold zeros
+#pragma unroll
+            for (int sft = 16; sft >= 1; sft >>= 1) {
+              const bool up = (lane & sft) != 0;
+#pragma unroll
+              for (int i = 0; i < sft; ++i) {
+                const float send = up ? f[i] : f[i + sft];
+                const float recv = __shfl_xor_sync(0xffffffffu, send, sft);
+                f[i] = (up ? f[i + sft] : f[i]) + recv;
+              }
+            }
+            atomicAdd(cs_smem + half * 256 + lcol + lane, f[0]);
           }
         }
         tc_fence_before();
@@ -252,7 +285,15 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
   }
   __syncwarp();
-  gemm_teardown(tmem_base, warp);
+  gemm_teardown(tmem_base, warp);   // cluster barrier: every epilogue warp's shared-memory atomics are done
+  if (p.colsum0) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < p.n_halves * 256; i += kGThreads) {
+      const float v = cs_smem[i];
+      atomicAdd(p.colsum0 + i, v);
+      if (p.colsum1) atomicAdd(p.colsum1 + i, v);
+    }
+  }
 }
 
 // ---- wgrad GEMM -----------------------------------------------------------------------------------------
@@ -380,7 +421,8 @@ static int gemm_smem_attr(K kernel) {
 }  // namespace pn
 
 extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
-                               const void* mask_f16, float* acc32, int accumulate, void* out_bf16, float scale,
+                               const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16,
+                               void* out_bf16, float scale, float* colsum0, float* colsum1,
                                unsigned int* err_word, pn_stream_t stream) {
   using namespace pn::tc;
   PN_CHECK_ARG(a && b, "pn_gemm_tc_rows: null pointer");
@@ -390,8 +432,11 @@ extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fm
   PN_CHECK_ARG(k > 0 && k % 64 == 0 && n > 0 && n % 256 == 0, "pn_gemm_tc_rows: K must be a multiple of 64, N of 256");
   PN_CHECK_ARG(acc32 || out_bf16, "pn_gemm_tc_rows: no output");
   PN_CHECK_ARG(!accumulate || acc32, "pn_gemm_tc_rows: accumulate needs acc32");
-  PN_CHECK_ARG((((uintptr_t)a | (uintptr_t)b | (uintptr_t)mask_f16 | (uintptr_t)acc32 | (uintptr_t)out_bf16) & 15) == 0,
-               "pn_gemm_tc_rows: buffers must be 16-byte aligned");
+  PN_CHECK_ARG(colsum0 || !colsum1, "pn_gemm_tc_rows: colsum1 without colsum0");
+  PN_CHECK_ARG(n <= 512 || !colsum0, "pn_gemm_tc_rows: column sums need n <= 512");
+  PN_CHECK_ARG((((uintptr_t)a | (uintptr_t)b) & 15) == 0 &&
+                   (((uintptr_t)mask_f16 | (uintptr_t)acc32 | (uintptr_t)out_bf16 | (uintptr_t)resid_bf16) & 31) == 0,
+               "pn_gemm_tc_rows: operands must be 16-byte, mask / outputs 32-byte aligned");
   if (n_rows == 0) return PN_OK;
   static bool attr_set = false;
   int rc;
@@ -413,6 +458,9 @@ extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fm
   p.acc32 = acc32;
   p.accumulate = accumulate;
   p.out16 = (__nv_bfloat16*)out_bf16;
+  p.resid16 = (const __nv_bfloat16*)resid_bf16;
+  p.colsum0 = colsum0;
+  p.colsum1 = colsum1;
   p.scale = scale;
   p.err = err_word;
   int sms = 0;

@@ -121,10 +121,11 @@ __device__ __forceinline__ uint32_t pack_relu_bf2(float a, float b) {
 // 32 relu'd values of one row -> 64 bytes of bf16
 __device__ __forceinline__ void save_relu32(uint16_t* dst, const float (&x)[32]) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
-    reinterpret_cast<uint4*>(dst)[i] =
-        make_uint4(pack_relu_bf2(x[8 * i + 0], x[8 * i + 1]), pack_relu_bf2(x[8 * i + 2], x[8 * i + 3]),
-                   pack_relu_bf2(x[8 * i + 4], x[8 * i + 5]), pack_relu_bf2(x[8 * i + 6], x[8 * i + 7]));
+  for (int i = 0; i < 2; ++i)
+    stg_v8(dst + 16 * i, pack_relu_bf2(x[16 * i + 0], x[16 * i + 1]), pack_relu_bf2(x[16 * i + 2], x[16 * i + 3]),
+           pack_relu_bf2(x[16 * i + 4], x[16 * i + 5]), pack_relu_bf2(x[16 * i + 6], x[16 * i + 7]),
+           pack_relu_bf2(x[16 * i + 8], x[16 * i + 9]), pack_relu_bf2(x[16 * i + 10], x[16 * i + 11]),
+           pack_relu_bf2(x[16 * i + 12], x[16 * i + 13]), pack_relu_bf2(x[16 * i + 14], x[16 * i + 15]));
 }
 __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
   uint32_t d;
@@ -813,7 +814,7 @@ extern "C" int pn_mlp_forward_tc_train(const void* packed, const void* tables, i
                                        const void* feat_x, int n_objects, int n_views, int64_t points_per_object,
                                        float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                                        void* acts, size_t acts_bytes, pn_stream_t stream) {
-  PN_CHECK_ARG(acts && ((uintptr_t)acts & 15) == 0, "pn_mlp_forward_tc_train: activation buffer missing or misaligned");
+  PN_CHECK_ARG(acts && ((uintptr_t)acts & 31) == 0, "pn_mlp_forward_tc_train: activation buffer missing or misaligned");
   PN_CHECK_ARG(acts_bytes >= pn_mlp_tc_acts_bytes((int64_t)n_objects * n_views * points_per_object),
                "pn_mlp_forward_tc_train: activation buffer too small");
   return mlp_forward_tc_impl(packed, tables, n_texels, feat_x, n_objects, n_views, points_per_object, out, pre_act,

@@ -2,15 +2,19 @@
 // loss.backward() (train/train.py:271-281) over resnetfc.py:132-184, restated as 13 dgrad and 14 wgrad GEMMs on
 // tcgen05 (csrc/pn_gemm_tc.cu) around the activations the forward chain kernel saved (pn_mlp_forward_tc_train).
 //
-// Precision: gradients travel between layers as bf16 (fp32 range, 8-bit mantissa), the residual-stream gradient
-// dL/dh keeps an fp32 master copy that every block adds to, all sums are fp32.  The saved activations are the bf16
-// relu outputs that fed each forward GEMM; the relu derivative is read off them (zero / non-zero).
+// Precision: gradients travel between layers as bf16 (fp32 range, 8-bit mantissa), including the residual-stream
+// gradient dL/dh (each block's contribution is added in fp32 registers and the sum rounded once); every GEMM and
+// every bias/weight-gradient sum accumulates in fp32.  The saved activations are the bf16 relu outputs that fed
+// each forward GEMM; the relu derivative is read off them (zero / non-zero).  An fp32 master copy of dL/dh was
+// measured: it costs 4 KB of HBM traffic per row and block (the dgrad GEMMs are HBM-bound) for a gradient that
+// is rounded to bf16 for the next GEMM anyway.
 #include <cuda_bf16.h>
 
 #include "pn_common.cuh"
 
 extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
-                               const void* mask_f16, float* acc32, int accumulate, void* out_bf16, float scale,
+                               const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16,
+                               void* out_bf16, float scale, float* colsum0, float* colsum1,
                                unsigned int* err_word, pn_stream_t stream);
 extern "C" int pn_gemm_tc_wgrad(const void* g, int g_fmt, int ldg, const void* x, int x_fmt, int ldx, int64_t n_rows,
                                 int n_store, float* out, int ldo, unsigned int* err_word, pn_stream_t stream);
@@ -83,11 +87,11 @@ blend_taps_kernel(const uint4* __restrict__ feat_x, const float* __restrict__ la
 }
 
 // Head + lin_out backward (models.py:257-266, resnetfc.py:182): g_pre = [c(1-c) g_c, [sigma > 0] g_sigma];
-// dL/dh5 = [x10 > 0] (g_pre . W_out) as fp32 and bf16; dW_out += g_pre^T x10, db_out += sum g_pre, where
+// dL/dh5 = [x10 > 0] (g_pre . W_out) as bf16; dW_out += g_pre^T x10, db_out += sum g_pre, where
 // x10 = relu(h5) is the saved bf16 operand.  One warp per row, block-level reduction of the weight gradient.
 __global__ void __launch_bounds__(256)
 head_bwd16_kernel(const uint2* __restrict__ x10, const float4* __restrict__ out, const float4* __restrict__ g_out,
-                  const float* __restrict__ w_out, float* __restrict__ g_h, uint2* __restrict__ g_h16,
+                  const float* __restrict__ w_out, uint2* __restrict__ g_h16,
                   float* __restrict__ dw_out, float* __restrict__ db_out, int64_t rows, int rows_per_block) {
   __shared__ float sdw[4][512];
   __shared__ float sdb[4];
@@ -127,7 +131,6 @@ head_bwd16_kernel(const uint2* __restrict__ x10, const float4* __restrict__ out,
 #pragma unroll
         for (int k = 0; k < 4; ++k) dwl[k][i * 4 + e] += gp[k] * hh[e];
       }
-      *reinterpret_cast<float4*>(g_h + r * 512 + c) = make_float4(gh[0], gh[1], gh[2], gh[3]);
       g_h16[(r * 512 + c) / 4] = make_uint2(bf2(gh[0], gh[1]), bf2(gh[2], gh[3]));
     }
   }
@@ -145,16 +148,13 @@ head_bwd16_kernel(const uint2* __restrict__ x10, const float4* __restrict__ out,
 
 // backward of combine_interleaved(average) (util.py:461-466): g (SB,P,512) -> (SB,NS,P,512), each view gets g / NS
 __global__ void __launch_bounds__(256)
-view_mean_bwd16_kernel(const float4* __restrict__ g, float4* __restrict__ out, uint2* __restrict__ out16, int ns,
-                       int64_t ppo4, int64_t total4) {
+view_mean_bwd16_kernel(const uint2* __restrict__ g16, uint2* __restrict__ out16, int ns, int64_t ppo4, int64_t total4) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total4) return;
   const int64_t ov = i / ppo4, rem = i - ov * ppo4;
-  const float4 v = g[(ov / ns) * ppo4 + rem];
+  const uint2 v = __ldg(g16 + (ov / ns) * ppo4 + rem);
   const float d = (float)ns;
-  const float4 r = make_float4(v.x / d, v.y / d, v.z / d, v.w / d);
-  out[i] = r;
-  out16[i] = make_uint2(bf2(r.x, r.y), bf2(r.z, r.w));
+  out16[i] = make_uint2(bf2(bf_lo(v.x) / d, bf_hi(v.x) / d), bf2(bf_lo(v.y) / d, bf_hi(v.y) / d));
 }
 
 // db[512] += column sums of the bf16 matrix G[M, 512]; thread t owns columns 2t, 2t+1
@@ -189,10 +189,10 @@ extern "C" int pn_prepare_weights_bf16(const pn_mlp_weights_t* w, void* w16, siz
   return PN_OK;
 }
 
-// Workspace: [256 B error word] GH fp32 | GH16 | G1 (bf16) | Z16 | x16 | (NS > 1: second fp32 GH)
+// Workspace: [256 B error word] GH16 | G1 | Z16 (bf16 rows x 512) | x16 (rows x 64) | (NS > 1: second GH16)
 extern "C" size_t pn_mlp_backward_tc_workspace_bytes(int64_t n_rows, int n_views) {
   const size_t r = (size_t)(n_rows > 0 ? n_rows : 0);
-  return 256 + r * 512 * 4 + 3 * r * 512 * 2 + r * 64 * 2 + (n_views > 1 ? r * 512 * 4 : 0);
+  return 256 + 3 * r * 512 * 2 + r * 64 * 2 + (n_views > 1 ? r * 512 * 2 : 0);
 }
 
 extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, const void* feat_x,
@@ -209,18 +209,17 @@ extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, co
   const int64_t n_pts = (int64_t)n_objects * points_per_object;
   if (n_rows == 0) return PN_OK;
   PN_CHECK_ARG(workspace_bytes >= pn_mlp_backward_tc_workspace_bytes(n_rows, n_views), "pn_mlp_backward_tc: workspace too small");
-  PN_CHECK_ARG((((uintptr_t)workspace | (uintptr_t)acts | (uintptr_t)feat_x | (uintptr_t)w16 | (uintptr_t)g_feat_z) & 15) == 0,
+  PN_CHECK_ARG((((uintptr_t)workspace | (uintptr_t)acts | (uintptr_t)feat_x | (uintptr_t)w16 | (uintptr_t)g_feat_z) & 31) == 0,
                "pn_mlp_backward_tc: misaligned buffer");
   cudaStream_t st = (cudaStream_t)stream;
   const size_t R = (size_t)n_rows;
   char* ws = (char*)workspace;
   unsigned int* err = (unsigned int*)ws;
-  float* GH = (float*)(ws + 256);
-  uint16_t* GH16 = (uint16_t*)(GH + R * 512);
+  uint16_t* GH16 = (uint16_t*)(ws + 256);
   uint16_t* G1 = GH16 + R * 512;
   uint16_t* Z16 = G1 + R * 512;
   uint16_t* X16 = Z16 + R * 512;
-  float* GH2 = (float*)(X16 + R * 64);
+  uint16_t* GH16b = X16 + R * 64;
   const uint16_t* W16 = (const uint16_t*)w16;
   auto X = [&](int slot) { return (const uint16_t*)acts + (size_t)slot * R * 512; };
   auto Wm = [&](int mat) { return W16 + (size_t)mat * kW16Elems; };
@@ -237,42 +236,46 @@ extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, co
   {
     blend_taps_kernel<<<2048, 256, 0, st>>>((const uint4*)feat_x, latent_nhwc, (uint2*)Z16, (uint4*)X16, n_rows);
     PN_LAUNCH_OK("blend_taps_kernel");
-    const int rpb = 64;
+    const int rpb = 1024;
     head_bwd16_kernel<<<ceil_div(n_pts, rpb), 256, 0, st>>>((const uint2*)X(10), (const float4*)out, (const float4*)g_out,
-                                                            w->lin_out_w, GH, (uint2*)GH16, grads->lin_out_w,
+                                                            w->lin_out_w, (uint2*)GH16, grads->lin_out_w,
                                                             grads->lin_out_b, n_pts, rpb);
     PN_LAUNCH_OK("head_bwd16_kernel");
     count_launch(2);
   }
   int64_t m = n_pts;
+  // Bias gradients are column sums of the gradient tensors: of dL/dh_5 by its own kernel, of everything a dgrad
+  // GEMM produces by that GEMM's epilogue (dL/dh_b feeds fc_1.bias of block b-1, lin_z[b].bias and, for b = 0,
+  // lin_in.bias; summed over the per-point rows before the view-mean backward, which is the same number).
+  colsum(GH16, grads->fc1_b[PN_N_BLOCKS - 1], m);
   for (int b = PN_N_BLOCKS - 1; b >= 0; --b) {
     if (b == PN_COMBINE_LAYER - 1 && n_views > 1) {   // backward of the view mean (resnetfc.py:152-172)
       const int64_t ppo4 = points_per_object * 128, total4 = n_rows * 128;
-      view_mean_bwd16_kernel<<<ceil_div(total4, 256), 256, 0, st>>>((const float4*)GH, (float4*)GH2, (uint2*)GH16,
-                                                                    n_views, ppo4, total4);
+      view_mean_bwd16_kernel<<<ceil_div(total4, 256), 256, 0, st>>>((const uint2*)GH16, (uint2*)GH16b, n_views, ppo4, total4);
       PN_LAUNCH_OK("view_mean_bwd16_kernel");
       count_launch();
-      float* t = GH; GH = GH2; GH2 = t;
+      uint16_t* t = GH16; GH16 = GH16b; GH16b = t;
       m = n_rows;
     }
     // h_{b+1} = h_b + fc_1(x_{2b+1}) + b1,  x_{2b+1} = relu(fc_0(x_{2b}) + b0),  x_{2b} = relu(h_b)
     if ((rc = wgrad(GH16, X(2 * b + 1), 512, 512, grads->fc1_w[b], m))) return rc;
-    colsum(GH16, grads->fc1_b[b], m);
-    if ((rc = pn_gemm_tc_rows(GH16, 1, Wm(5 + b), 1, m, 512, 512, X(2 * b + 1), nullptr, 0, G1, 1.0f, err, stream))) return rc;
+    if ((rc = pn_gemm_tc_rows(GH16, 1, Wm(5 + b), 1, m, 512, 512, X(2 * b + 1), nullptr, 0, nullptr, G1, 1.0f,
+                              grads->fc0_b[b], nullptr, err, stream)))
+      return rc;
     if ((rc = wgrad(G1, X(2 * b), 512, 512, grads->fc0_w[b], m))) return rc;
-    colsum(G1, grads->fc0_b[b], m);
-    if ((rc = pn_gemm_tc_rows(G1, 1, Wm(b), 1, m, 512, 512, X(2 * b), GH, 1, GH16, 1.0f, err, stream))) return rc;
+    float* cs0 = b > 0 ? grads->fc1_b[b - 1] : grads->lin_in_b;
+    float* cs1 = b < PN_COMBINE_LAYER ? grads->lin_z_b[b] : nullptr;
+    if ((rc = pn_gemm_tc_rows(G1, 1, Wm(b), 1, m, 512, 512, X(2 * b), nullptr, 0, GH16, GH16, 1.0f, cs0, cs1, err, stream)))
+      return rc;
     if (b < PN_COMBINE_LAYER) {   // h_b = ... + lin_z[b](z)  (resnetfc.py:174-180)
       if ((rc = wgrad(GH16, Z16, 512, 512, grads->lin_z_w[b], m))) return rc;
-      colsum(GH16, grads->lin_z_b[b], m);
       if (g_feat_z &&
           (rc = pn_gemm_tc_rows(GH16, 1, Wm(10 + b), 1, m, 512, 512, nullptr, g_feat_z, b != PN_COMBINE_LAYER - 1, nullptr,
-                                1.0f, err, stream)))
+                                nullptr, 1.0f, nullptr, nullptr, err, stream)))
         return rc;
     }
   }
   if ((rc = wgrad(GH16, X16, 64, PN_D_CODE, grads->lin_in_w, m))) return rc;
-  colsum(GH16, grads->lin_in_b, m);
   PN_LAUNCH_OK("pn_mlp_backward_tc");
   return PN_OK;
 }

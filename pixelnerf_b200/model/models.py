@@ -162,6 +162,14 @@ class PixelNeRFNet(torch.nn.Module):
         tables = self.latent_tables(coarse)
         _, hl, wl, _ = self.latent_nhwc(torch.float32).shape
         fx = _lib.point_taps(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
+        stash = getattr(self, "_train_stash", None)
+        if stash is not None and rays is not None:
+            # training forward (render/autograd.py): keep what the tensor-core backward needs, so that it does
+            # not have to re-run the chain
+            out, acts = _lib.mlp_forward_tc_train(mlp.packed(prec), tables, fx, cam["n_objects"], cam["n_views"], ppo)
+            stash.append(dict(coarse=coarse, ppo=ppo, rays=rays, z=z, fx=fx, out=out, acts=acts,
+                              range=getattr(self, "_stash_range", None)))
+            return out
         return _lib.mlp_forward_tc(mlp.packed(prec), tables, fx, cam["n_objects"], cam["n_views"], ppo)
 
     def forward(self, xyz, coarse=True, viewdirs=None, far=False):

@@ -41,8 +41,16 @@ def _flat_params(model):
 class RenderFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, renderer, model, rays, sb, draws, forced, seed, latent, *params):
-        with torch.no_grad():
-            coarse, fine = renderer._render_all(model, rays, sb, draws, forced, seed)
+        ns = getattr(model, "num_views_per_obj", 1)
+        k_all = renderer.n_coarse + ((renderer.n_coarse + renderer.n_fine) if renderer.using_fine else 0)
+        stash_bytes = rays.shape[0] * ns * k_all * (11 * 1024 + 160)
+        keep = model.mlp_precision != "fp32" and stash_bytes <= renderer.train_stash_bytes
+        model._train_stash = [] if keep else None
+        try:
+            with torch.no_grad():
+                coarse, fine = renderer._render_all(model, rays, sb, draws, forced, seed)
+        finally:
+            ctx.stash, model._train_stash = model._train_stash, None
         ctx.renderer, ctx.model, ctx.sb = renderer, model, sb
         ctx.n_params = len(params)
         ctx.has_fine = fine is not None
@@ -71,15 +79,16 @@ class RenderFunction(torch.autograd.Function):
 
         grads_c = zero_grads(coarse_p)
         grads_f = zero_grads(fine_p) if fine_p else grads_c
-        _backward_pass(renderer, model, True, rays, z_c, sb, g[0], g[1], g[2], grads_c, g_lat)
+        stash, ctx.stash = ctx.stash, None
+        _backward_pass(renderer, model, True, rays, z_c, sb, g[0], g[1], g[2], grads_c, g_lat, stash)
         if ctx.has_fine:
-            _backward_pass(renderer, model, False, rays, z_f, sb, g[4], g[5], g[6], grads_f, g_lat)
+            _backward_pass(renderer, model, False, rays, z_f, sb, g[4], g[5], g[6], grads_f, g_lat, stash)
         flat = [grads_c[k] for k in names] + ([grads_f[k] for k in names] if fine_p else [])
         g_latent = g_lat.permute(0, 3, 1, 2) if want_latent else None
         return (None, None, None, None, None, None, None, g_latent, *flat)
 
 
-def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, grads, g_lat):
+def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, grads, g_lat, stash=None):
     r_total, k = z.shape
     if g_w is None and g_rgb is None and g_depth is None:
         return
@@ -100,6 +109,22 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
         return t.reshape(sb, b, *t.shape[1:])[:, s:e].reshape(sb * (e - s), *t.shape[1:]).contiguous()
 
     tensor_core = model.mlp_precision != "fp32"
+    if stash is not None:
+        # the forward kept its operands: one backward per forward chunk, nothing is recomputed
+        w16 = mlp.packed("bf16_train")
+        for ent in stash:
+            if ent.get("coarse") is None or ent["coarse"] != coarse:   # other pass, or already consumed
+                continue
+            s, e = ent["range"]
+            out, ppo = ent["out"], ent["ppo"]
+            g_rs, _ = _lib.composite_bwd(out.reshape(-1, k, 4), ent["z"], ent["rays"], renderer.white_bkgd,
+                                         cut(g_rgb, s, e), cut(g_depth, s, e), cut(g_w, s, e), want_gz=False)
+            g_fz = _lib.mlp_backward_tc(packed, w16, ent["fx"], latent, sb, ns, ppo, ent["acts"], out,
+                                        g_rs.reshape(-1, 4), grads, want_g_feat_z=g_lat is not None)
+            if g_lat is not None:
+                _lib.point_features_bwd(cam, g_lat, ppo, g_fz, rays=ent["rays"], z=ent["z"])
+            ent.clear()     # release this chunk's activations
+        return
     if tensor_core:
         packed_tc, w16 = mlp.packed(model.mlp_precision), mlp.packed("bf16_train")
         tables = model.latent_tables(coarse)

@@ -68,6 +68,9 @@ class NeRFRenderer(torch.nn.Module):
         self.max_rows_per_launch = 1 << 21
         self.max_rows_train = 1 << 16  # rows whose 11 fp32 activation tensors are kept at once (1.4 GB)
         self.max_rows_train_tc = 1 << 20  # tensor-core training path: ~20 KB per row of activations + workspace
+        # tensor-core training path: the forward keeps its GEMM operands (11.3 KB per MLP row) for the backward
+        # when they fit in this many bytes; above it the backward re-runs the forward chunk by chunk
+        self.train_stash_bytes = 64 << 30
 
     # ---------------------------------------------------------------- sampling
     @staticmethod
@@ -134,6 +137,7 @@ class NeRFRenderer(torch.nn.Module):
         # chunk along the per-object ray axis so every launch keeps (object, view, point) row order
         chunk = max(1, self.max_rows_per_launch // max(1, sb * ns * k_max))
         if chunk >= b:
+            model._stash_range = (0, b)
             return self._render_chunk(model, rays, sb, draws, forced, False, seed)
 
         def cut(t, s, e):  # (SB*B, ...) -> (SB*(e-s), ...), keeping object-major order
@@ -144,6 +148,7 @@ class NeRFRenderer(torch.nn.Module):
             e = min(b, s + chunk)
             dr = {k: cut(v, s, e) for k, v in draws.items()} if draws else None
             fz = {k: cut(v, s, e) for k, v in forced.items()}
+            model._stash_range = (s, e)
             parts.append(self._render_chunk(model, cut(rays, s, e), sb, dr, fz, False, seed + s))
 
         def join(which):

@@ -55,7 +55,7 @@ def test_mlp_backward_vs_autograd(ns, ppo, sb):
     _close(g_fz, zr.grad, "g_feat_z")
 
 
-def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False):
+def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, stash=True):
     """loss = <coarse rgb, Gc> + <fine rgb, Gf> + <coarse weights, Gw>: gradients w.r.t. both MLPs' parameters
     and the encoder latent, through the public NeRFRenderer API.  Returns (loss, reference loss, {tensor name:
     max abs gradient error / largest reference gradient entry})."""
@@ -64,6 +64,11 @@ def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False):
     wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
     net, ren = build_net(sc, wc, wf, dev, mlp_precision=mlp_precision)
     ren.max_rows_train = ren.max_rows_train_tc = 96 * 40 * sc["ns"]      # force several backward chunks
+    if mlp_precision != "fp32":
+        if stash:   # the forward keeps its operands: several forward chunks, one backward per chunk
+            ren.max_rows_per_launch = 160 * 40 * sc["ns"]
+        else:       # the backward re-runs the forward chunk by chunk
+            ren.train_stash_bytes = 0
     rays = sc["rays"][torch.linspace(0, sc["rays"].shape[0] - 1, n_rays).long()]
     draws = syn.draws(9, n_rays, 64, 16, 16)
     g = torch.Generator().manual_seed(3)

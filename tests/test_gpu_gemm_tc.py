@@ -75,3 +75,25 @@ def test_mixed_operand_formats_raise():
         _lib.gemm_tc_rows(a, b)
     with pytest.raises(RuntimeError, match="same format"):
         _lib.gemm_tc_wgrad(a, _rand((8, 512), torch.float16, 3), torch.zeros(512, 512, device=DEV))
+
+
+@pytest.mark.parametrize("rows", [77, 256 * 149 + 3])
+def test_rows_gemm_residual_and_column_sums(rows):
+    """dgrad of fc_0 as the backward uses it: masked product added to the bf16 residual-stream gradient in place,
+    column sums of the result (bias gradients) added to two destinations."""
+    a, b = _rand((rows, 512), torch.bfloat16, 11), _rand((512, 512), torch.bfloat16, 12, 0.05)
+    mask = torch.relu(_rand((rows, 512), torch.bfloat16, 13))
+    resid = _rand((rows, 512), torch.bfloat16, 14)
+    ref = (a.double() @ b.double()) * (mask > 0) + resid.double()
+    cs0, cs1 = torch.full((512,), 2.0, device=DEV), torch.zeros(512, device=DEV)
+    out = resid.clone()
+    lib = _lib.lib()
+    _lib._check(lib.pn_gemm_tc_rows(a.data_ptr(), 1, b.data_ptr(), 1, rows, 512, 512, mask.data_ptr(), None, 0,
+                                    out.data_ptr(), out.data_ptr(), 1.0, cs0.data_ptr(), cs1.data_ptr(), None,
+                                    torch.cuda.current_stream().cuda_stream), "pn_gemm_tc_rows")
+    scale = ref.abs().max().item()
+    assert (out.double() - ref).abs().max().item() < 2.0 ** -8 * scale
+    col = ref.sum(0)
+    tol = 2.0 ** -9 * ref.abs().sum(0).max().item() / rows ** 0.5 * 4 + 1e-3   # bf16-exact values are not summed: fp32 sums of the unrounded result
+    assert (cs1.double() - col).abs().max().item() < max(tol, 1e-4 * col.abs().max().item())
+    assert torch.allclose(cs0 - 2.0, cs1, rtol=1e-4, atol=1e-3 * float(col.abs().max()))
