@@ -76,3 +76,28 @@ def test_full_frame_fp16_vs_fp32_coarse_pass():
     assert float((outs["fp16"].rgb - outs["fp32"].rgb).abs().max()) < 2e-3
     assert float((outs["fp16"].weights - outs["fp32"].weights).abs().max()) < 2e-3
     assert float((outs["fp16"].depth - outs["fp32"].depth).abs().max()) < 2e-3 * max(1.0, span)
+
+
+def test_dense_point_query_chunks():
+    """the reference's sigma-volume extraction calls ``net.forward`` on 65 536-point chunks of
+    a regular grid (src/util/recon.py:12-78, train/train.py:412-425) -- same gather + MLP kernels, no sampling,
+    no compositing.  A 64^3 grid: chunked = unchunked bit for bit, tensor-core path within north_star's
+    reduced-precision tolerance of the fp32 path, densities non-negative and colours in [0, 1]."""
+    sc = syn.scene("srn_car")
+    wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
+    t = torch.linspace(-0.6, 0.6, 64)
+    xyz = torch.stack(torch.meshgrid(t, t, t, indexing="ij"), -1).reshape(1, -1, 3).to(DEV)
+    dirs = torch.nn.functional.normalize(torch.randn(xyz.shape, generator=torch.Generator().manual_seed(2)), dim=-1).to(DEV)
+    outs = {}
+    for prec in ("fp16", "fp32"):
+        net, _ = build_net(sc, wc, wf, torch.device(DEV), mlp_precision=prec)
+        with torch.no_grad():
+            whole = net(xyz, coarse=True, viewdirs=dirs)
+            parts = torch.cat([net(xyz[:, s:s + 65536], coarse=True, viewdirs=dirs[:, s:s + 65536])
+                               for s in range(0, xyz.shape[1], 65536)], dim=1)
+        assert whole.shape == (1, 64 ** 3, 4) and torch.equal(whole, parts)
+        assert float(whole[..., 3].min()) >= 0.0 and 0.0 <= float(whole[..., :3].min()) and float(whole[..., :3].max()) <= 1.0
+        outs[prec] = whole
+    assert float((outs["fp16"][..., :3] - outs["fp32"][..., :3]).abs().max()) < 2e-3
+    sig = outs["fp32"][..., 3]
+    assert float((outs["fp16"][..., 3] - sig).abs().max()) < 2e-3 * max(1.0, float(sig.max()))
