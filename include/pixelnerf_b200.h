@@ -122,6 +122,18 @@ PN_API int pn_point_features_bwd(const pn_camera_t* cam, const float* rays, cons
                           const float* xyz, int64_t points_per_object, const float* g_feat_z,
                           float* g_latent_nhwc, pn_stream_t stream);
 
+/* Backward of the depth-guided sample positions (autograd of nerf.py:150-161 + :290-295; the only sample
+ * positions the reference does not detach): g_depth (R) += sum over each ray's depth samples z_depth (R,Kd) that
+ * lie strictly inside (near, far) of dL/dz at the sample's place in the sorted row z_sorted (R,K).  dL/dz =
+ * g_z (R,K) from pn_composite_bwd (or NULL) + the path through the MLP inputs: code rows (g_h0 = dL/d lin_in
+ * output, rows x 512, PN_DTYPE_F32 or PN_DTYPE_BF16, times lin_in_w (512,42), code.py:30-42) and latent rows
+ * (g_feat_z rows x 512 fp32 times grid_sample's grid gradient, encoder.py:102-108, through models.py:162-212).
+ * latent_nhwc is the fp32 channels-last latent; rows are ordered (object, view, ray, sample). */
+PN_API int pn_depth_sample_bwd(const pn_camera_t* cam, const float* latent_nhwc, const float* rays,
+                        const float* z_sorted, int n_samples, const float* z_depth, int n_depth,
+                        const float* g_z, const void* g_h0, int g_h0_dtype, const float* g_feat_z,
+                        const float* lin_in_w, int64_t rays_per_object, float* g_depth, pn_stream_t stream);
+
 /* ---- (3) ResnetFC ---------------------------------------------------------------------- */
 
 typedef struct pn_mlp_weights {
@@ -167,6 +179,8 @@ PN_API size_t pn_mlp_backward_workspace_bytes(int64_t n_rows);
  * ACCUMULATED (+=) into `grads` (same shapes as the weights); wt holds the transposed fc_0 / fc_1 /
  * lin_z matrices ([in][out] row-major) for the data-gradient GEMMs.  If g_feat_z (N,512) is not NULL
  * it receives dL/d feat_z (the latent rows), for pn_point_features_bwd. */
+/* byte offset in `workspace` where the call leaves dL/dh_0 (rows x 512 fp32), for pn_depth_sample_bwd */
+PN_API size_t pn_mlp_backward_gh0_offset(int64_t n_rows, int n_views);
 PN_API int pn_mlp_backward_fp32(const pn_mlp_weights_t* w, const pn_mlp_weights_t* wt, const float* feat_z,
                          const float* feat_x, int ldx, int n_objects, int n_views, int64_t points_per_object,
                          const void* acts, const float* out, const float* g_out, const pn_mlp_grads_t* grads,
@@ -246,6 +260,8 @@ PN_API int pn_prepare_weights_bf16(const pn_mlp_weights_t* w, void* w16, size_t 
  * rows x 512 fp32) receives dL/d(latent part of the MLP input) for pn_point_features_bwd.  feat_x is the forward's
  * (rows, 64) fp16 code rows with the embedded taps record; latent_nhwc the fp32 channels-last latent. */
 PN_API size_t pn_mlp_backward_tc_workspace_bytes(int64_t n_rows, int n_views);
+/* byte offset in `workspace` where the call leaves dL/dh_0 (rows x 512 bf16), for pn_depth_sample_bwd */
+PN_API size_t pn_mlp_backward_tc_gh0_offset(int64_t n_rows, int n_views);
 PN_API int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, const void* feat_x,
                        const float* latent_nhwc, int n_objects, int n_views, int64_t points_per_object,
                        const void* acts, const float* out, const float* g_out, const pn_mlp_grads_t* grads,

@@ -102,8 +102,9 @@ def render_rays(net_fn, rays, sb, n_coarse, n_fine, n_fine_depth, draws, *,
     rays (SB*B,8) flattened; ``sb`` the number of objects.
     draws = dict(u_coarse (R,Kc), u_bin (R,Kf), u_in (R,Kf), noise (R,Kd)).
     force = optional dict for teacher forcing (SURVEY section 7 hard part 12):
-      'z_coarse', 'w_coarse', 'depth_coarse', 'z_fine' replace the values the
-      oracle would compute itself at that stage.
+      'z_coarse', 'w_coarse', 'depth_coarse', 'z_imp', 'z_fine' replace the values the
+      oracle would compute itself at that stage ('z_imp' keeps the depth samples a
+      differentiable function of the coarse depth, as in nerf.py:290-293).
     Returns a dict of every intermediate the parity tests compare.
     """
     force = force or {}
@@ -129,6 +130,7 @@ def render_rays(net_fn, rays, sb, n_coarse, n_fine, n_fine_depth, draws, *,
         d_in = force.get("depth_coarse", d_c)
         if n_fine - n_fine_depth > 0:
             z_i, inds = sample_fine(rays, w_in, n_coarse, draws["u_bin"], draws["u_in"], lindisp)
+            z_i = force.get("z_imp", z_i)
             parts.append(z_i)
             out.update(z_imp=z_i, inds=inds)
         if n_fine_depth > 0:

@@ -52,6 +52,10 @@ _SIGNATURES = {
     "pn_mlp_forward_fp32": (_int, [C.POINTER(MlpWeights), _vp, _vp, _int, _int, _int, _i64, _vp, _vp, _vp,
                                    _sz, _vp]),
     "pn_point_features_bwd": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _i64, _vp, _vp, _vp]),
+    "pn_depth_sample_bwd": (_int, [C.POINTER(Camera), _vp, _vp, _vp, _int, _vp, _int, _vp, _vp, _int, _vp, _vp, _i64,
+                                   _vp, _vp]),
+    "pn_mlp_backward_gh0_offset": (_sz, [_i64, _int]),
+    "pn_mlp_backward_tc_gh0_offset": (_sz, [_i64, _int]),
     "pn_mlp_train_acts_bytes": (_sz, [_i64]),
     "pn_mlp_forward_fp32_train": (_int, [C.POINTER(MlpWeights), _vp, _vp, _int, _int, _int, _i64, _vp, _vp, _vp,
                                          _sz, _vp]),
@@ -282,8 +286,9 @@ def mlp_forward_fp32_train(packed, feat_z, feat_x, n_objects, n_views, ppo):
 
 
 def mlp_backward_fp32(packed, weights, feat_z, feat_x, n_objects, n_views, ppo, acts, out, g_out, grads,
-                      want_g_feat_z):
-    """weights / grads: dicts keyed by weight_names(); grads are accumulated into (+=)."""
+                      want_g_feat_z, want_g_h0=False):
+    """weights / grads: dicts keyed by weight_names(); grads are accumulated into (+=).  Returns dL/d feat_z
+    (or None); with want_g_h0 also dL/dh_0 (rows, 512) fp32, a view into the call's workspace."""
     s, _keep = packed
     wt = {k: (v.detach().t().contiguous() if v.dim() == 2 and v.shape[0] == v.shape[1] else v.detach().contiguous())
           for k, v in weights.items()}
@@ -297,6 +302,9 @@ def mlp_backward_fp32(packed, weights, feat_z, feat_x, n_objects, n_views, ppo, 
     _check(lib().pn_mlp_backward_fp32(C.byref(s), C.byref(st), _ptr(feat_z), _ptr(feat_x), feat_x.shape[1], n_objects,
                                       n_views, ppo, acts.data_ptr(), _ptr(out), _ptr(_f32c(g_out)), C.byref(sg),
                                       _ptr(g_fz), ws.data_ptr(), nbytes, _stream()), "pn_mlp_backward_fp32")
+    if want_g_h0:
+        off = lib().pn_mlp_backward_gh0_offset(n_rows, n_views)
+        return g_fz, ws[off:off + n_rows * D_HIDDEN * 4].view(torch.float32).view(n_rows, D_HIDDEN)
     return g_fz
 
 
@@ -308,6 +316,24 @@ def point_features_bwd(cam_bufs, g_latent_nhwc, ppo, g_feat_z, *, rays=None, z=N
     k = 0 if z is None else z.shape[-1]
     _check(lib().pn_point_features_bwd(C.byref(cam), _ptr(rays), _ptr(z), k, _ptr(xyz), ppo, _ptr(g_feat_z),
                                        _ptr(g_latent_nhwc), _stream()), "pn_point_features_bwd")
+
+
+def depth_sample_bwd(cam_bufs, latent_nhwc, rays, z_sorted, z_depth, g_z, g_h0, g_feat_z, lin_in_w, g_depth):
+    """g_depth (R) += dL/d(coarse depth) through the depth-guided samples of the fine pass (nerf.py:150-161)."""
+    v, hl, wl, _ = latent_nhwc.shape
+    cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
+                 cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
+    rays, z_sorted, z_depth, g_z = _f32c(rays), _f32c(z_sorted), _f32c(z_depth), _f32c(g_z)
+    r, k = z_sorted.shape
+    if g_h0.dtype not in (torch.float32, torch.bfloat16) or not g_h0.is_contiguous():
+        raise RuntimeError("depth_sample_bwd: g_h0 must be contiguous fp32 or bf16")
+    if g_depth.dtype != torch.float32 or g_depth.shape != (r,) or not g_depth.is_contiguous():
+        raise RuntimeError("depth_sample_bwd: g_depth must be a contiguous fp32 (R,) tensor")
+    fmt = 0 if g_h0.dtype == torch.float32 else 2
+    _check(lib().pn_depth_sample_bwd(C.byref(cam), _ptr(latent_nhwc), _ptr(rays), _ptr(z_sorted), k, _ptr(z_depth),
+                                     z_depth.shape[1], _ptr(g_z), g_h0.data_ptr(), fmt, _ptr(g_feat_z),
+                                     _ptr(_f32c(lin_in_w)), r // cam_bufs["n_objects"], _ptr(g_depth), _stream()),
+           "pn_depth_sample_bwd")
 
 
 def point_taps(cam_bufs, hl, wl, ppo, *, rays=None, z=None, xyz=None, viewdirs=None):
@@ -503,8 +529,9 @@ def pack_weights_bf16(w):
 
 
 def mlp_backward_tc(packed32, w16, feat_x, latent_nhwc, n_objects, n_views, ppo, acts, out, g_out, grads,
-                    want_g_feat_z):
-    """grads: dict keyed by weight_names(), accumulated into (+=); returns dL/d feat_z (rows, 512) fp32 or None."""
+                    want_g_feat_z, want_g_h0=False):
+    """grads: dict keyed by weight_names(), accumulated into (+=); returns dL/d feat_z (rows, 512) fp32 or None;
+    with want_g_h0 also dL/dh_0 (rows, 512) bf16, a view into the call's workspace."""
     s, _keep = packed32
     sg = _fill_struct(MlpGrads(), grads)
     n_rows = n_objects * n_views * ppo
@@ -517,4 +544,7 @@ def mlp_backward_tc(packed32, w16, feat_x, latent_nhwc, n_objects, n_views, ppo,
                                         n_objects, n_views, ppo, acts.data_ptr(), _ptr(out), _ptr(_f32c(g_out)),
                                         C.byref(sg), _ptr(g_fz), ws.data_ptr(), nbytes, _stream()),
                "pn_mlp_backward_tc")
+    if want_g_h0:
+        off = lib().pn_mlp_backward_tc_gh0_offset(n_rows, n_views)
+        return g_fz, ws[off:off + n_rows * D_HIDDEN * 2].view(torch.bfloat16).view(n_rows, D_HIDDEN)
     return g_fz

@@ -6,6 +6,8 @@
 // one contiguous C-vector; one warp produces one feature row, lanes stride the
 // channel axis in 16-byte vectors (512 B per warp load instruction, fully coalesced).
 // Rows are ordered (object, view, point) like the reference's repeat_interleave.
+#include <algorithm>
+
 #include "pn_common.cuh"
 
 namespace pn {
@@ -292,6 +294,147 @@ point_features_bwd_kernel(pn_camera_t cam, const float* __restrict__ rays, const
   }
 }
 
+// Gradient of the fine pass w.r.t. the coarse depth through the depth-guided sample positions
+// (src/render/nerf.py:150-161 and :290-295): z_d = clamp(depth + noise * std, near, far) is the only sample set whose
+// positions are not detached, so dL/d depth[ray] = sum over the ray's depth samples strictly inside (near, far) of
+// dL/dz at that sample's place in the sorted row.  dL/dz has three parts:
+//   compositing   g_z[k] from pn_composite_bwd (deltas and the depth output)
+//   code rows     x = [R p, sin(f R p + phase), R d] (models.py:162-171, code.py:30-42):
+//                 dL/dh0 . W_in . dx/dz with d(R p)/dz = R d and d sin(..)/dz = f cos(..) (R d)
+//   latent rows   grid_sample's grid gradient (encoder.py:102-108; zero where the border clamp is active) through
+//                 uv = -xy/z * focal + c (models.py:206-212)
+// One warp per (ray, depth sample); lanes split the 512 hidden / latent channels; lin_in.weight sits transposed
+// in shared memory ([code entry][hidden], conflict-free 16-byte reads).
+constexpr int kDsWarps = 8;
+constexpr int kDsCode = 39;   // code entries that depend on the position (the 3 view-direction entries do not)
+
+template <bool kBf16>
+__global__ void __launch_bounds__(kDsWarps * 32)
+depth_sample_bwd_kernel(pn_camera_t cam, const float* __restrict__ latent, const float* __restrict__ rays,
+                        const float* __restrict__ zs, int k, const float* __restrict__ z_dep, int kd,
+                        const float* __restrict__ g_zd, const void* __restrict__ g_h0v,
+                        const float* __restrict__ g_fz, const float* __restrict__ w_in, int64_t rays_per_object,
+                        int64_t n_rays, float* __restrict__ g_depth) {
+  extern __shared__ __align__(16) float ds_smem[];
+  float* Ws = ds_smem;                                              // [39][512]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* dxs = ds_smem + kDsCode * 512 + warp * 40;                 // this warp's dx/dz vector
+  for (int idx = threadIdx.x; idx < 512 * PN_D_CODE; idx += kDsWarps * 32) {
+    const int o = idx / PN_D_CODE, i = idx - o * PN_D_CODE;
+    if (i < kDsCode) Ws[i * 512 + o] = __ldg(w_in + idx);
+  }
+  __syncthreads();
+  const int64_t n_items = n_rays * kd;
+  for (int64_t item = (int64_t)blockIdx.x * kDsWarps + warp; item < n_items; item += (int64_t)gridDim.x * kDsWarps) {
+    const int64_t ray = item / kd;
+    const float* rr = rays + ray * 8;
+    const float zd = __ldg(z_dep + item);
+    if (!(zd > rr[6] && zd < rr[7])) continue;      // max(min(z, far), near): no gradient once a bound is active
+    const float* zrow = zs + ray * k;
+    int lo = 0, hi = k;
+    while (lo < hi) {                               // the sample's place after the sort (nerf.py:295)
+      const int mid = (lo + hi) >> 1;
+      if (__ldg(zrow + mid) < zd) lo = mid + 1; else hi = mid;
+    }
+    if (lo >= k || __ldg(zrow + lo) != zd) continue;
+    const int64_t obj = ray / rays_per_object, rio = ray - obj * rays_per_object;
+    const float dwx = rr[3], dwy = rr[4], dwz = rr[5];
+    const float x = __fadd_rn(rr[0], __fmul_rn(zd, dwx));
+    const float y = __fadd_rn(rr[1], __fmul_rn(zd, dwy));
+    const float z = __fadd_rn(rr[2], __fmul_rn(zd, dwz));
+    float total = g_zd ? __ldg(g_zd + ray * k + lo) : 0.0f;
+    for (int v = 0; v < cam.n_views; ++v) {
+      const int view = (int)obj * cam.n_views + v;
+      const int64_t row = ((int64_t)view * rays_per_object + rio) * k + lo;
+      const float* P = cam.poses + (size_t)view * 12;
+      const float comp[3] = {P[0] * x + P[1] * y + P[2] * z, P[4] * x + P[5] * y + P[6] * z, P[8] * x + P[9] * y + P[10] * z};
+      const float rd[3] = {P[0] * dwx + P[1] * dwy + P[2] * dwz, P[4] * dwx + P[5] * dwy + P[6] * dwz,
+                           P[8] * dwx + P[9] * dwy + P[10] * dwz};
+      const float xc = comp[0] + P[3], yc = comp[1] + P[7], zc = comp[2] + P[11];
+      // d(code entry)/dz
+      for (int e = lane; e < kDsCode; e += 32) {
+        float val;
+        if (e < 3) {
+          val = rd[e];
+        } else {
+          const int j = (e - 3) / 3, d = (e - 3) - j * 3;
+          const float freq = 1.5f * (float)(1 << (j >> 1));
+          const float phase = (j & 1) ? 1.57079637050628662109375f : 0.0f;
+          val = freq * cosf(__fadd_rn(phase, __fmul_rn(comp[d], freq))) * rd[d];
+        }
+        dxs[e] = val;
+      }
+      __syncwarp();
+      float s = 0.0f;
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int o = it * 128 + lane * 4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 13
+        for (int i = 0; i < kDsCode; ++i) {
+          const float4 w = *reinterpret_cast<const float4*>(Ws + i * 512 + o);
+          const float d = dxs[i];
+          acc.x += w.x * d; acc.y += w.y * d; acc.z += w.z * d; acc.w += w.w * d;
+        }
+        float4 gh;
+        if (kBf16) {
+          const uint2 u = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const uint16_t*>(g_h0v) + row * 512 + o));
+          gh = make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xFFFF0000u),
+                           __uint_as_float(u.y << 16), __uint_as_float(u.y & 0xFFFF0000u));
+        } else {
+          gh = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(g_h0v) + row * 512 + o));
+        }
+        s += acc.x * gh.x + acc.y * gh.y + acc.z * gh.z + acc.w * gh.w;
+      }
+      // grid gradient of the bilinear gather
+      const float f0 = cam.focal[view * 2 + 0], f1 = cam.focal[view * 2 + 1];
+      const float u = (-xc / zc) * f0 + cam.c[view * 2 + 0];
+      const float vv = (-yc / zc) * f1 + cam.c[view * 2 + 1];
+      const float gx = u * cam.scale_x - 1.0f, gy = vv * cam.scale_y - 1.0f;
+      const float ixu = ((gx + 1.0f) * 0.5f) * (float)(cam.wl - 1);
+      const float iyu = ((gy + 1.0f) * 0.5f) * (float)(cam.hl - 1);
+      const bool in_x = ixu > 0.0f && ixu < (float)(cam.wl - 1), in_y = iyu > 0.0f && iyu < (float)(cam.hl - 1);
+      const float ix = fminf(fmaxf(ixu, 0.0f), (float)(cam.wl - 1)), iy = fminf(fmaxf(iyu, 0.0f), (float)(cam.hl - 1));
+      const float fx0 = floorf(ix), fy0 = floorf(iy);
+      const int x0 = (int)fx0, y0 = (int)fy0;
+      const int x1 = min(x0 + 1, cam.wl - 1), y1 = min(y0 + 1, cam.hl - 1);
+      const float ax = ix - fx0, ay = iy - fy0;
+      float gix = 0.0f, giy = 0.0f;
+      if (in_x || in_y) {
+        const float* base = latent + (size_t)view * cam.hl * cam.wl * PN_D_LATENT;
+        const float* p00 = base + ((size_t)y0 * cam.wl + x0) * PN_D_LATENT;
+        const float* p01 = base + ((size_t)y0 * cam.wl + x1) * PN_D_LATENT;
+        const float* p10 = base + ((size_t)y1 * cam.wl + x0) * PN_D_LATENT;
+        const float* p11 = base + ((size_t)y1 * cam.wl + x1) * PN_D_LATENT;
+        const float* g = g_fz + (size_t)row * PN_D_LATENT;
+#pragma unroll
+        for (int it = 0; it < PN_D_LATENT / 128; ++it) {
+          const int ch = it * 128 + lane * 4;
+          const float4 gv = __ldg(reinterpret_cast<const float4*>(g + ch));
+          const float4 a = load_vec4(p00 + ch), b = load_vec4(p01 + ch), c = load_vec4(p10 + ch), d = load_vec4(p11 + ch);
+          gix += gv.x * ((1.0f - ay) * (b.x - a.x) + ay * (d.x - c.x)) + gv.y * ((1.0f - ay) * (b.y - a.y) + ay * (d.y - c.y)) +
+                 gv.z * ((1.0f - ay) * (b.z - a.z) + ay * (d.z - c.z)) + gv.w * ((1.0f - ay) * (b.w - a.w) + ay * (d.w - c.w));
+          giy += gv.x * ((1.0f - ax) * (c.x - a.x) + ax * (d.x - b.x)) + gv.y * ((1.0f - ax) * (c.y - a.y) + ax * (d.y - b.y)) +
+                 gv.z * ((1.0f - ax) * (c.z - a.z) + ax * (d.z - b.z)) + gv.w * ((1.0f - ax) * (c.w - a.w) + ax * (d.w - b.w));
+        }
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, off);
+        gix += __shfl_xor_sync(0xffffffffu, gix, off);
+        giy += __shfl_xor_sync(0xffffffffu, giy, off);
+      }
+      const float gu = in_x ? gix * (0.5f * (float)(cam.wl - 1)) * cam.scale_x : 0.0f;
+      const float gv2 = in_y ? giy * (0.5f * (float)(cam.hl - 1)) * cam.scale_y : 0.0f;
+      // u = -xc/zc f0 + c0, v = -yc/zc f1 + c1; d(xc, yc, zc)/dz = R d
+      const float gxc = -gu * f0 / zc, gyc = -gv2 * f1 / zc, gzc = (gu * f0 * xc + gv2 * f1 * yc) / (zc * zc);
+      total += s + gxc * rd[0] + gyc * rd[1] + gzc * rd[2];
+      __syncwarp();
+    }
+    if (lane == 0) atomicAdd(g_depth + ray, total);
+  }
+}
+
 }  // namespace pn
 
 extern "C" int pn_point_features_bwd(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
@@ -306,6 +449,35 @@ extern "C" int pn_point_features_bwd(const pn_camera_t* cam, const float* rays, 
   pn::point_features_bwd_kernel<<<pn::ceil_div(n_rows, pn::kFeatWarps), pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
       *cam, rays, z, n_samples, xyz, points_per_object, g_feat_z, g_latent_nhwc, n_rows);
   PN_LAUNCH_OK("point_features_bwd_kernel");
+  pn::count_launch();
+  return PN_OK;
+}
+
+extern "C" int pn_depth_sample_bwd(const pn_camera_t* cam, const float* latent_nhwc, const float* rays,
+                                   const float* z_sorted, int n_samples, const float* z_depth, int n_depth,
+                                   const float* g_z, const void* g_h0, int g_h0_dtype, const float* g_feat_z,
+                                   const float* lin_in_w, int64_t rays_per_object, float* g_depth,
+                                   pn_stream_t stream) {
+  PN_CHECK_ARG(cam && latent_nhwc && rays && z_sorted && z_depth && g_h0 && g_feat_z && lin_in_w && g_depth,
+               "pn_depth_sample_bwd: null pointer");
+  PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_depth_sample_bwd: camera buffers missing");
+  PN_CHECK_ARG(n_samples > 0 && n_depth >= 0 && rays_per_object >= 0, "pn_depth_sample_bwd: bad sizes");
+  PN_CHECK_ARG(g_h0_dtype == PN_DTYPE_F32 || g_h0_dtype == PN_DTYPE_BF16, "pn_depth_sample_bwd: g_h0 must be f32 or bf16");
+  PN_CHECK_ARG((((uintptr_t)g_h0 | (uintptr_t)g_feat_z | (uintptr_t)latent_nhwc) & 15) == 0, "pn_depth_sample_bwd: misaligned buffer");
+  const int64_t n_rays = (int64_t)cam->n_objects * rays_per_object;
+  const int64_t n_items = n_rays * n_depth;
+  if (n_items == 0) return PN_OK;
+  const size_t smem = (size_t)(pn::kDsCode * 512 + pn::kDsWarps * 40) * sizeof(float);
+  const int blocks = (int)std::min<int64_t>(pn::ceil_div(n_items, pn::kDsWarps), 148 * 2);
+  auto launch = [&](auto kern) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<blocks, pn::kDsWarps * 32, smem, (cudaStream_t)stream>>>(*cam, latent_nhwc, rays, z_sorted, n_samples, z_depth,
+                                                                    n_depth, g_z, g_h0, g_feat_z, lin_in_w,
+                                                                    rays_per_object, n_rays, g_depth);
+  };
+  if (g_h0_dtype == PN_DTYPE_BF16) launch(pn::depth_sample_bwd_kernel<true>);
+  else launch(pn::depth_sample_bwd_kernel<false>);
+  PN_LAUNCH_OK("depth_sample_bwd_kernel");
   pn::count_launch();
   return PN_OK;
 }

@@ -526,6 +526,11 @@ extern "C" size_t pn_mlp_backward_workspace_bytes(int64_t n_rows) {
   return (size_t)(n_rows > 0 ? n_rows : 0) * PN_D_HIDDEN * sizeof(float) * 2 + 256;
 }
 
+// dL/dh_0 (rows x 512 fp32, the gradient at lin_in's output) is left in the workspace at this byte offset
+extern "C" size_t pn_mlp_backward_gh0_offset(int64_t n_rows, int n_views) {
+  return n_views > 1 ? (size_t)(n_rows > 0 ? n_rows : 0) * PN_D_HIDDEN * sizeof(float) : 0;
+}
+
 extern "C" int pn_mlp_backward_fp32(const pn_mlp_weights_t* w, const pn_mlp_weights_t* wt, const float* feat_z,
                                     const float* feat_x, int ldx, int n_objects, int n_views,
                                     int64_t points_per_object, const void* acts, const float* out,

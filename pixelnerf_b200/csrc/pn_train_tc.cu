@@ -195,6 +195,12 @@ extern "C" size_t pn_mlp_backward_tc_workspace_bytes(int64_t n_rows, int n_views
   return 256 + 3 * r * 512 * 2 + r * 64 * 2 + (n_views > 1 ? r * 512 * 2 : 0);
 }
 
+// dL/dh_0 (rows x 512 bf16, the gradient at lin_in's output) is left in the workspace at this byte offset
+extern "C" size_t pn_mlp_backward_tc_gh0_offset(int64_t n_rows, int n_views) {
+  const size_t r = (size_t)(n_rows > 0 ? n_rows : 0);
+  return n_views > 1 ? 256 + 3 * r * 512 * 2 + r * 64 * 2 : 256;
+}
+
 extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, const void* feat_x,
                                   const float* latent_nhwc, int n_objects, int n_views, int64_t points_per_object,
                                   const void* acts, const float* out, const float* g_out,

@@ -16,10 +16,12 @@ Activations are not kept from the forward: the backward re-runs the fp32 forward
 (pn_mlp_forward_fp32_train keeps the 11 activation tensors of one chunk), so memory is bounded for
 any ray count (config 5's sweep goes to 2^22 rays).
 
-Deviation from the reference, on purpose and documented in DESIGN.md: sample positions are treated
-as constants.  In the reference the 16 depth samples of the fine pass depend differentiably on the
-coarse depth (src/render/nerf.py:150-161, 290-293), a second-order path from the fine loss into the
-coarse MLP; every other sample position is detached there too (``weights.detach()``, :130, :288).
+Sample positions: the reference detaches all of them (``weights.detach()``, src/render/nerf.py:130, :288)
+except the depth-guided samples of the fine pass, z_d = clamp(depth_coarse + noise * std, near, far)
+(:150-161, 290-293), through which the fine loss reaches the coarse MLP.  That path is kept: the fine pass's
+backward runs first and pn_depth_sample_bwd turns dL/dz at those samples (compositing + code rows + latent
+rows) into an extra dL/d depth_coarse that joins the coarse pass's upstream gradient
+(``renderer.depth_sample_grad = False`` drops it).
 """
 import torch
 
@@ -46,25 +48,28 @@ class RenderFunction(torch.autograd.Function):
         stash_bytes = rays.shape[0] * ns * k_all * (11 * 1024 + 160)
         keep = model.mlp_precision != "fp32" and stash_bytes <= renderer.train_stash_bytes
         model._train_stash = [] if keep else None
+        renderer._keep_parts = bool(renderer.depth_sample_grad and renderer.n_fine_depth > 0)
         try:
             with torch.no_grad():
                 coarse, fine = renderer._render_all(model, rays, sb, draws, forced, seed)
         finally:
             ctx.stash, model._train_stash = model._train_stash, None
+            renderer._keep_parts = False
         ctx.renderer, ctx.model, ctx.sb = renderer, model, sb
         ctx.n_params = len(params)
         ctx.has_fine = fine is not None
         ctx.latent_shape = latent.shape
         z_f = fine[3] if fine is not None else coarse[3].new_zeros(0)
-        ctx.save_for_backward(rays, coarse[3], z_f)
+        z_dep = fine[4] if fine is not None else coarse[3].new_zeros(0)
+        ctx.save_for_backward(rays, coarse[3], z_f, z_dep)
         outs = tuple(coarse) + (tuple(fine) if fine is not None else ())
-        ctx.mark_non_differentiable(coarse[3], *((fine[3],) if fine is not None else ()))
+        ctx.mark_non_differentiable(coarse[3], *((fine[3], fine[4]) if fine is not None else ()))
         return outs
 
     @staticmethod
     def backward(ctx, *g):
         renderer, model, sb = ctx.renderer, ctx.model, ctx.sb
-        rays, z_c, z_f = ctx.saved_tensors
+        rays, z_c, z_f, z_dep = ctx.saved_tensors
         names = _lib.weight_names()
         coarse_p, fine_p = _flat_params(model)
         dev = rays.device
@@ -80,15 +85,25 @@ class RenderFunction(torch.autograd.Function):
         grads_c = zero_grads(coarse_p)
         grads_f = zero_grads(fine_p) if fine_p else grads_c
         stash, ctx.stash = ctx.stash, None
-        _backward_pass(renderer, model, True, rays, z_c, sb, g[0], g[1], g[2], grads_c, g_lat, stash)
-        if ctx.has_fine:
-            _backward_pass(renderer, model, False, rays, z_f, sb, g[4], g[5], g[6], grads_f, g_lat, stash)
+        g_depth_c = g[2]
+        if ctx.has_fine:    # fine pass first: its depth samples hand a gradient to the coarse depth
+            g_dep = None
+            if renderer.depth_sample_grad and z_dep.numel() > 0 and not all(x is None for x in (g[4], g[5], g[6])):
+                g_dep = torch.zeros(rays.shape[0], device=dev, dtype=torch.float32)
+            _backward_pass(renderer, model, False, rays, z_f, sb, g[4], g[5], g[6], grads_f, g_lat, stash,
+                           z_dep=z_dep, g_dep=g_dep)
+            if g_dep is not None:
+                g_depth_c = g_dep if g_depth_c is None else g_depth_c + g_dep
+        _backward_pass(renderer, model, True, rays, z_c, sb, g[0], g[1], g_depth_c, grads_c, g_lat, stash)
         flat = [grads_c[k] for k in names] + ([grads_f[k] for k in names] if fine_p else [])
         g_latent = g_lat.permute(0, 3, 1, 2) if want_latent else None
         return (None, None, None, None, None, None, None, g_latent, *flat)
 
 
-def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, grads, g_lat, stash=None):
+def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, grads, g_lat, stash=None,
+                   z_dep=None, g_dep=None):
+    """One pass's backward, chunk by chunk.  g_dep (R) / z_dep (R,Kd): fine pass only -- receives the gradient
+    the depth-guided sample positions carry to the coarse depth."""
     r_total, k = z.shape
     if g_w is None and g_rgb is None and g_depth is None:
         return
@@ -108,6 +123,16 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
             return None
         return t.reshape(sb, b, *t.shape[1:])[:, s:e].reshape(sb * (e - s), *t.shape[1:]).contiguous()
 
+    want_pos = g_dep is not None
+    want_fz = g_lat is not None or want_pos
+    w_in = weights["lin_in.weight"]
+
+    def positions(rr, zz, s, e, g_z, g_h0, g_fz):
+        """dL/dz of this chunk's depth samples -> g_dep[object, s:e]"""
+        part = torch.zeros(rr.shape[0], device=rr.device, dtype=torch.float32)
+        _lib.depth_sample_bwd(cam, latent, rr, zz, cut(z_dep, s, e), g_z, g_h0, g_fz, w_in, part)
+        g_dep.view(sb, b)[:, s:e] += part.view(sb, e - s)
+
     tensor_core = model.mlp_precision != "fp32"
     if stash is not None:
         # the forward kept its operands: one backward per forward chunk, nothing is recomputed
@@ -117,10 +142,12 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
                 continue
             s, e = ent["range"]
             out, ppo = ent["out"], ent["ppo"]
-            g_rs, _ = _lib.composite_bwd(out.reshape(-1, k, 4), ent["z"], ent["rays"], renderer.white_bkgd,
-                                         cut(g_rgb, s, e), cut(g_depth, s, e), cut(g_w, s, e), want_gz=False)
-            g_fz = _lib.mlp_backward_tc(packed, w16, ent["fx"], latent, sb, ns, ppo, ent["acts"], out,
-                                        g_rs.reshape(-1, 4), grads, want_g_feat_z=g_lat is not None)
+            g_rs, g_z = _lib.composite_bwd(out.reshape(-1, k, 4), ent["z"], ent["rays"], renderer.white_bkgd,
+                                           cut(g_rgb, s, e), cut(g_depth, s, e), cut(g_w, s, e), want_gz=want_pos)
+            g_fz, g_h0 = _lib.mlp_backward_tc(packed, w16, ent["fx"], latent, sb, ns, ppo, ent["acts"], out,
+                                              g_rs.reshape(-1, 4), grads, want_g_feat_z=want_fz, want_g_h0=True)
+            if want_pos:
+                positions(ent["rays"], ent["z"], s, e, g_z, g_h0, g_fz)
             if g_lat is not None:
                 _lib.point_features_bwd(cam, g_lat, ppo, g_fz, rays=ent["rays"], z=ent["z"])
             ent.clear()     # release this chunk's activations
@@ -138,18 +165,22 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
             # forward chain on the tensor cores keeping its bf16 GEMM operands, then dgrad / wgrad GEMMs on them
             fx = _lib.point_taps(cam, hl, wl, ppo, rays=rr, z=zz)
             out, acts = _lib.mlp_forward_tc_train(packed_tc, tables, fx, sb, ns, ppo)
-            g_rs, _ = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
-                                         cut(g_depth, s, e), cut(g_w, s, e), want_gz=False)
-            g_fz = _lib.mlp_backward_tc(packed, w16, fx, latent, sb, ns, ppo, acts, out, g_rs.reshape(-1, 4), grads,
-                                        want_g_feat_z=g_lat is not None)
+            g_rs, g_z = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
+                                           cut(g_depth, s, e), cut(g_w, s, e), want_gz=want_pos)
+            g_fz, g_h0 = _lib.mlp_backward_tc(packed, w16, fx, latent, sb, ns, ppo, acts, out, g_rs.reshape(-1, 4),
+                                              grads, want_g_feat_z=want_fz, want_g_h0=True)
+            if want_pos:
+                positions(rr, zz, s, e, g_z, g_h0, g_fz)
             if g_lat is not None:
                 _lib.point_features_bwd(cam, g_lat, ppo, g_fz, rays=rr, z=zz)
             continue
         fz, fx = _lib.point_features(cam, latent, ppo, rays=rr, z=zz, ldx=44)
         out, acts = _lib.mlp_forward_fp32_train(packed, fz, fx, sb, ns, ppo)
-        g_rs, _ = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
-                                     cut(g_depth, s, e), cut(g_w, s, e), want_gz=False)
-        g_fz = _lib.mlp_backward_fp32(packed, weights, fz, fx, sb, ns, ppo, acts, out, g_rs.reshape(-1, 4), grads,
-                                      want_g_feat_z=g_lat is not None)
+        g_rs, g_z = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
+                                       cut(g_depth, s, e), cut(g_w, s, e), want_gz=want_pos)
+        g_fz, g_h0 = _lib.mlp_backward_fp32(packed, weights, fz, fx, sb, ns, ppo, acts, out, g_rs.reshape(-1, 4),
+                                            grads, want_g_feat_z=want_fz, want_g_h0=True)
+        if want_pos:
+            positions(rr, zz, s, e, g_z, g_h0, g_fz)
         if g_lat is not None:
             _lib.point_features_bwd(cam, g_lat, ppo, g_fz, rays=rr, z=zz)

@@ -71,6 +71,10 @@ class NeRFRenderer(torch.nn.Module):
         # tensor-core training path: the forward keeps its GEMM operands (11.3 KB per MLP row) for the backward
         # when they fit in this many bytes; above it the backward re-runs the forward chunk by chunk
         self.train_stash_bytes = 64 << 30
+        # training: the depth-guided samples are differentiable w.r.t. the coarse depth like in the reference
+        # (nerf.py:150-161, 290-293); False treats every sample position as a constant
+        self.depth_sample_grad = True
+        self._keep_parts = False   # set by render/autograd.py: sample_fine also returns the unsorted depth samples
 
     # ---------------------------------------------------------------- sampling
     @staticmethod
@@ -120,13 +124,17 @@ class NeRFRenderer(torch.nn.Module):
         if self.using_fine:
             n_dep = self.n_fine_depth
             n_imp = self.n_fine - n_dep
-            z_f = forced.get("z_fine")
+            z_f, z_dep = forced.get("z_fine"), forced.get("z_depth")
             if z_f is None:
                 z_f = _lib.sample_fine(rays, z_c, forced.get("w_coarse", coarse[0]),
                                        forced.get("depth_coarse", coarse[2]), n_imp, n_dep, self.depth_std,
                                        self.lindisp, u_bin=d.get("u_bin"), u_in=d.get("u_in"), noise=d.get("noise"),
-                                       seed=seed)
-            fine = self.composite(model, rays, z_f, coarse=False, sb=sb) + (z_f,)
+                                       seed=seed, want_parts=self._keep_parts)
+                if self._keep_parts:
+                    z_f, _, z_dep = z_f
+            if z_dep is None:   # teacher-forced z_fine without its depth samples: nothing to differentiate
+                z_dep = z_f.new_zeros(z_f.shape[0], 0)
+            fine = self.composite(model, rays, z_f, coarse=False, sb=sb) + (z_f, z_dep)
         return coarse + (z_c,), fine
 
     def _render_all(self, model, rays, sb, draws, forced, seed):
@@ -154,8 +162,9 @@ class NeRFRenderer(torch.nn.Module):
         def join(which):
             if parts[0][which] is None:
                 return None
-            return tuple(torch.cat([p[which][i].reshape(sb, -1, *p[which][i].shape[1:]) for p in parts], dim=1)
-                         .reshape(sb * b, *parts[0][which][i].shape[1:]) for i in range(4))
+            return tuple(torch.cat([p[which][i].reshape(sb, p[which][i].shape[0] // sb, *p[which][i].shape[1:])
+                                    for p in parts], dim=1)
+                         .reshape(sb * b, *parts[0][which][i].shape[1:]) for i in range(len(parts[0][which])))
         return join(0), join(1)
 
     def forward(self, model, rays, want_weights=False):
@@ -181,7 +190,7 @@ class NeRFRenderer(torch.nn.Module):
             from .autograd import RenderFunction, _flat_params
             coarse_p, fine_p = _flat_params(model)
             res = RenderFunction.apply(self, model, rays, sb, draws, forced, seed, latent, *coarse_p, *fine_p)
-            coarse, fine = res[:4], (res[4:8] if self.using_fine else None)
+            coarse, fine = res[:4], (res[4:9] if self.using_fine else None)
         else:
             coarse, fine = self._render_all(model, rays, sb, draws, forced, seed)
 
@@ -196,6 +205,7 @@ class NeRFRenderer(torch.nn.Module):
             outputs.fine = fmt(fine)
         # sample positions of the last call, for the stage-wise parity tests
         self.last_z = (coarse[3].reshape(sb, b, -1), fine[3].reshape(sb, b, -1) if self.using_fine else None)
+        self.last_z_depth = fine[4].reshape(sb, b, fine[4].shape[-1]) if self.using_fine else None
         return outputs
 
     def sched_step(self, steps=1):

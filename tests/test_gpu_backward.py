@@ -55,7 +55,8 @@ def test_mlp_backward_vs_autograd(ns, ppo, sb):
     _close(g_fz, zr.grad, "g_feat_z")
 
 
-def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, stash=True):
+def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, stash=True, depth_grad=True,
+                        fine_only=False):
     """loss = <coarse rgb, Gc> + <fine rgb, Gf> + <coarse weights, Gw>: gradients w.r.t. both MLPs' parameters
     and the encoder latent, through the public NeRFRenderer API.  Returns (loss, reference loss, {tensor name:
     max abs gradient error / largest reference gradient entry})."""
@@ -64,6 +65,7 @@ def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, sta
     wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
     net, ren = build_net(sc, wc, wf, dev, mlp_precision=mlp_precision)
     ren.max_rows_train = ren.max_rows_train_tc = 96 * 40 * sc["ns"]      # force several backward chunks
+    ren.depth_sample_grad = depth_grad
     if mlp_precision != "fp32":
         if stash:   # the forward keeps its operands: several forward chunks, one backward per chunk
             ren.max_rows_per_launch = 160 * 40 * sc["ns"]
@@ -84,10 +86,20 @@ def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, sta
         p.requires_grad_(True)
     ren.injected_draws = {k: v.to(dev) for k, v in draws.items()}
     out = ren(net, rays[None].to(dev), want_weights=True)
+    if fine_only:   # the coarse MLP then gets its whole gradient through the depth-guided sample positions
+        gc, gw = gc * 0, gw * 0
     loss = (out.coarse.rgb[0] * gc.to(dev)).sum() + (out.fine.rgb[0] * gf.to(dev)).sum() \
         + (out.coarse.weights[0] * gw.to(dev)).sum()
     loss.backward()
     z_c, z_f = ren.last_z
+    # sample positions are constants on both sides, except (depth_grad) the depth-guided samples, which the oracle
+    # recomputes from its own coarse depth like the reference (nerf.py:290-293): force only z_coarse and z_imp
+    force = dict(z_coarse=z_c[0].cpu().double(), z_fine=z_f[0].cpu().double())
+    if depth_grad:
+        with torch.no_grad():
+            z_imp = ren.sample_fine(rays.to(dev), out.coarse.weights[0].detach(), u_bin=draws["u_bin"].to(dev),
+                                    u_in=draws["u_in"].to(dev))
+        force = dict(z_coarse=force["z_coarse"], z_imp=z_imp.cpu().double())
     # oracle: same sample positions as constants, autograd for everything else.  Evaluated in float64:
     # the fp32 torch-CPU oracle is itself up to 5e-3 (of a tensor's largest entry) away from its own
     # float64 evaluation on these scenes (a few dominant samples per ray, relu decisions of near-zero
@@ -104,8 +116,7 @@ def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, sta
     torch.set_default_dtype(torch.float64)
     try:
         ref = oracle.render_rays(net_fn, rays.double(), 1, 64, 32, 16, {k: v.double() for k, v in draws.items()},
-                                 white_bkgd=sc["white"],
-                                 force=dict(z_coarse=z_c[0].cpu().double(), z_fine=z_f[0].cpu().double()))
+                                 white_bkgd=sc["white"], force=force)
         loss_ref = (ref["rgb_coarse"] * gc).sum() + (ref["rgb_fine"] * gf).sum() + (ref["w_coarse"] * gw).sum()
         loss_ref.backward()
     finally:
@@ -132,6 +143,26 @@ def test_render_backward_vs_oracle(scene, n_rays):
     vals = sorted(worst.values())
     assert vals[-1] < 1e-2, worst
     assert vals[len(vals) // 2] < REL, worst
+
+
+@pytest.mark.parametrize("scene,n_rays", [("sn64", 96), ("srn_chair", 64)])
+def test_depth_sample_gradient_reaches_coarse_mlp(scene, n_rays):
+    """Loss on the fine rgb only: the coarse MLP's whole gradient arrives through the depth-guided sample positions
+    (nerf.py:150-161, 290-293 -> pn_depth_sample_bwd: compositing, positional code and grid_sample grid gradient)."""
+    loss, loss_ref, worst = run_render_backward(scene, n_rays, fine_only=True)
+    assert abs(loss - loss_ref) < 1e-3 * max(1.0, abs(loss_ref))
+    coarse = {k: v for k, v in worst.items() if k.startswith("mlp_coarse.")}
+    assert len(coarse) == len(_lib.weight_names())
+    vals = sorted(coarse.values())
+    assert vals[-1] < 2e-2, coarse
+    assert vals[len(vals) // 2] < 5e-3, coarse
+
+
+def test_detached_sample_positions_option():
+    """renderer.depth_sample_grad = False: every sample position is a constant (oracle with z_fine forced)."""
+    loss, loss_ref, worst = run_render_backward("sn64", 96, depth_grad=False)
+    vals = sorted(worst.values())
+    assert vals[-1] < 1e-2 and vals[len(vals) // 2] < REL, worst
 
 
 def test_stop_encoder_grad_and_eval_need_no_graph():
