@@ -101,7 +101,7 @@ def run_reference(args):
     from pixelnerf_b200 import synthetic as syn
     sc = syn.scene(SCENE)
     wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
-    sample = 512
+    sample = 2048
     for _ in range(args.warmup):
         cpu_oracle_rays_per_s(sc, wc, wf, sample)
     t0 = time.perf_counter()
@@ -304,7 +304,7 @@ def run_gpu(args):
             "stage_ms_per_step": {k: v / args.steps for k, v in prof.items()},
         }
         if world == 1 and not args.no_cpu_baseline:
-            sample = 1024
+            sample = 8192
             v, secs = cpu_oracle_rays_per_s(sc, wc, wf, sample)
             line["cpu_baseline"] = {"value": v, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": f"{sample} evenly spaced rays of the same frame, {secs:.1f} s, torch "

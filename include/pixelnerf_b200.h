@@ -295,6 +295,65 @@ PN_API int pn_composite_bwd(const float* rgb_sigma, const float* z, const float*
                      float* g_rgb_sigma, float* g_z,
                      int64_t n_rays, int n_samples, int white_bkgd, pn_stream_t stream);
 
+/* ---- (6) the whole render in one call ---------------------------------------------------- */
+
+/* NeRFRenderer.forward without gradients, src/render/nerf.py:251-303, on the tensor-core path:
+ * pn_sample_coarse -> pn_point_taps -> pn_mlp_forward_tc -> pn_composite_fwd -> pn_sample_fine ->
+ * pn_point_taps -> pn_mlp_forward_tc -> pn_composite_fwd, enqueued back to back on `stream` with every
+ * intermediate in `workspace` (pn_render_rays_workspace_bytes; 256-byte aligned).  n_imp = n_fine -
+ * n_fine_depth importance samples and n_depth depth-guided ones; both 0 = coarse pass only. */
+typedef struct pn_render_config {
+  int n_coarse, n_imp, n_depth;
+  float depth_std;   /* conf renderer.depth_std */
+  int lindisp;       /* nerf.py:113-118 */
+  int white_bkgd;    /* nerf.py:239-244 */
+  uint64_t seed;     /* in-kernel draws when the matching pn_render_draws pointer is NULL */
+} pn_render_config_t;
+
+/* Injected draws in the order the reference consumes them (nerf.py:111,135,141,158); any may be NULL. */
+typedef struct pn_render_draws {
+  const float* u_coarse; /* (R,Kc) */
+  const float* u_bin;    /* (R,n_imp) */
+  const float* u_in;     /* (R,n_imp) */
+  const float* noise;    /* (R,n_depth) */
+} pn_render_draws_t;
+
+/* One MLP as the chain kernel wants it: pn_prepare_weights + pn_prepare_latent_tables outputs. */
+typedef struct pn_render_mlp {
+  const void* packed;
+  const void* tables;
+} pn_render_mlp_t;
+
+/* Outputs of one pass (nerf.py:305-316): rgb (R,3) and depth (R) are required; weights (R,K) and the
+ * sample positions z (R,K) are optional (NULL = kept in the workspace only). */
+typedef struct pn_render_out {
+  float* rgb;
+  float* depth;
+  float* weights;
+  float* z;
+} pn_render_out_t;
+
+/* Optional cudaEvent_t handles recorded on `stream` around the stages of pass 0 (coarse) and 1 (fine):
+ * [pass][0] before, [pass][1] after.  NULL entries are skipped.  bench.py's per-kernel roofline times. */
+typedef struct pn_render_events {
+  void* taps[2][2];
+  void* mlp[2][2];
+  void* composite[2][2];
+  void* sample[2][2];
+} pn_render_events_t;
+
+PN_API size_t pn_render_rays_workspace_bytes(int64_t n_rays, int n_views, const pn_render_config_t* cfg);
+
+/* rays (R,8) ordered (object, ray) with R = cam->n_objects * rays-per-object; lin = device table
+ * torch.linspace(0, 1-1/Kc, Kc) like pn_sample_coarse; mlp_fine may be NULL (the fine pass then runs
+ * through mlp_coarse like models.py:242 when mlp_fine is None); out_fine is required iff n_imp+n_depth > 0.
+ * The first 4 bytes of the workspace receive the chain kernel's watchdog code (see pn_mlp_forward_tc). */
+PN_API int pn_render_rays(const pn_camera_t* cam, const pn_render_mlp_t* mlp_coarse, const pn_render_mlp_t* mlp_fine,
+                   int64_t n_texels, const float* rays, int64_t n_rays, const float* lin,
+                   const pn_render_config_t* cfg, const pn_render_draws_t* draws,
+                   const pn_render_out_t* out_coarse, const pn_render_out_t* out_fine,
+                   void* workspace, size_t workspace_bytes, const pn_render_events_t* events, pn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

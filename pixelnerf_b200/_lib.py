@@ -39,6 +39,28 @@ class MlpGrads(C.Structure):
     _fields_ = MlpWeights._fields_
 
 
+class RenderConfig(C.Structure):
+    _fields_ = [("n_coarse", _int), ("n_imp", _int), ("n_depth", _int), ("depth_std", _f32), ("lindisp", _int),
+                ("white_bkgd", _int), ("seed", _u64)]
+
+
+class RenderDraws(C.Structure):
+    _fields_ = [("u_coarse", _vp), ("u_bin", _vp), ("u_in", _vp), ("noise", _vp)]
+
+
+class RenderMlp(C.Structure):
+    _fields_ = [("packed", _vp), ("tables", _vp)]
+
+
+class RenderOut(C.Structure):
+    _fields_ = [("rgb", _vp), ("depth", _vp), ("weights", _vp), ("z", _vp)]
+
+
+class RenderEvents(C.Structure):
+    _fields_ = [("taps", (_vp * 2) * 2), ("mlp", (_vp * 2) * 2), ("composite", (_vp * 2) * 2),
+                ("sample", (_vp * 2) * 2)]
+
+
 _SIGNATURES = {
     "pn_version": (_int, []),
     "pn_last_error": (C.c_char_p, []),
@@ -83,6 +105,10 @@ _SIGNATURES = {
     "pn_gemm_tc_wgrad": (_int, [_vp, _int, _int, _vp, _int, _int, _i64, _int, _vp, _int, _vp, _vp]),
     "pn_gen_rays": (_int, [_vp, _int, _int, _int, _int, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
     "pn_frame_to_u8": (_int, [_vp, _vp, _i64, _vp]),
+    "pn_render_rays_workspace_bytes": (_sz, [_i64, _int, C.POINTER(RenderConfig)]),
+    "pn_render_rays": (_int, [C.POINTER(Camera), C.POINTER(RenderMlp), C.POINTER(RenderMlp), _i64, _vp, _i64, _vp,
+                              C.POINTER(RenderConfig), C.POINTER(RenderDraws), C.POINTER(RenderOut),
+                              C.POINTER(RenderOut), _vp, _sz, C.POINTER(RenderEvents), _vp]),
 }
 
 _lib = None
@@ -428,6 +454,58 @@ def composite_bwd(rgb_sigma, z, rays, white_bkgd, g_rgb, g_depth=None, g_weights
     _check(lib().pn_composite_bwd(_ptr(rgb_sigma), _ptr(z), _ptr(rays), _ptr(g_rgb), _ptr(g_depth), _ptr(g_weights),
                                   _ptr(g_rs), _ptr(g_z), r, k, int(bool(white_bkgd)), _stream()), "pn_composite_bwd")
     return g_rs, g_z
+
+
+def _new_event():
+    """A timing event whose raw cudaEvent_t exists (torch creates it lazily on the first record)."""
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    return e
+
+
+def render_rays(cam_bufs, hl, wl, mlp_coarse, mlp_fine, rays, n_coarse, n_imp, n_depth, depth_std, lindisp,
+                white_bkgd, seed=0, draws=None):
+    """The whole no-grad render in one C call (pn_render_rays): mlp_* = (packed, tables) pairs of the tensor-core
+    chain, mlp_fine None = the fine pass uses mlp_coarse.  rays (R,8) ordered (object, ray).  Returns
+    (weights, rgb, depth, z) for the coarse pass and the same tuple (or None) for the fine pass."""
+    rays = _f32c(rays)
+    r = rays.shape[0]
+    dev = rays.device
+    cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
+                 cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
+    cfg = RenderConfig(n_coarse, n_imp, n_depth, float(depth_std), int(bool(lindisp)), int(bool(white_bkgd)), seed)
+    d = {k: _f32c(v) for k, v in (draws or {}).items()}
+    dr = RenderDraws(_ptr(d.get("u_coarse")), _ptr(d.get("u_bin")), _ptr(d.get("u_in")), _ptr(d.get("noise")))
+    n_tex = mlp_coarse[1].shape[1]
+    for pk, tb in (mlp_coarse,) + ((mlp_fine,) if mlp_fine is not None else ()):
+        if tb.dtype != torch.float16 or tb.dim() != 3 or tb.shape[1] != n_tex or not tb.is_contiguous():
+            raise RuntimeError("render_rays needs contiguous fp16 lin_z tables of shape (3, texels, 512)")
+    mc = RenderMlp(mlp_coarse[0].data_ptr(), mlp_coarse[1].data_ptr())
+    mf = RenderMlp(mlp_fine[0].data_ptr(), mlp_fine[1].data_ptr()) if mlp_fine is not None else None
+
+    def outs(k):
+        t = (torch.empty(r, k, device=dev), torch.empty(r, 3, device=dev), torch.empty(r, device=dev),
+             torch.empty(r, k, device=dev))
+        return t, RenderOut(_ptr(t[1]), _ptr(t[2]), _ptr(t[0]), _ptr(t[3]))
+
+    k_f = n_imp + n_depth
+    coarse, oc = outs(n_coarse)
+    fine, of = outs(n_coarse + k_f) if k_f > 0 else (None, None)
+    nbytes = lib().pn_render_rays_workspace_bytes(r, cam.n_views, C.byref(cfg))
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    ev, keep = None, None
+    if PROFILE is not None:
+        ev, keep = RenderEvents(), {}
+        for name, key in (("taps", "features"), ("mlp", "mlp"), ("composite", "composite"), ("sample", "sampling")):
+            for p in range(2 if k_f > 0 else 1):
+                pair = (_new_event(), _new_event())
+                getattr(ev, name)[p][0], getattr(ev, name)[p][1] = pair[0].cuda_event, pair[1].cuda_event
+                PROFILE.setdefault(key, []).append(pair)
+    _check(lib().pn_render_rays(C.byref(cam), C.byref(mc), C.byref(mf) if mf is not None else None, n_tex, _ptr(rays),
+                                r, _ptr(_linspace(n_coarse, dev)), C.byref(cfg), C.byref(dr), C.byref(oc),
+                                C.byref(of) if of is not None else None, ws.data_ptr(), nbytes,
+                                C.byref(ev) if ev is not None else None, _stream()), "pn_render_rays")
+    return coarse, fine
 
 
 def gen_rays(poses, width, height, focal, z_near, z_far, c=None):

@@ -5,8 +5,11 @@ read at call time, persistent buffers ``iter_idx`` / ``last_sched``, ``sched_ste
 ``bind_parallel`` and output structure.  Per ray chunk the forward is
     pn_sample_coarse -> pn_point_features -> MLP -> pn_composite_fwd
     -> pn_sample_fine (importance + depth + merge sort) -> features -> MLP -> composite
-with no host synchronisation in between.
+with no host synchronisation in between; on the tensor-core path without gradients the whole
+chunk is one C call (pn_render_rays).
 """
+import os
+
 import torch
 
 from .. import _lib
@@ -114,7 +117,33 @@ class NeRFRenderer(torch.nn.Module):
         return _lib.composite_fwd(rgbs.reshape(b, k, 4), z_samp, rays, self.white_bkgd)
 
     # ----------------------------------------------------------------- forward
+    def _fused_ok(self, model, forced):
+        """The whole chunk can go through pn_render_rays: tensor-core MLP, nothing teacher-forced, and no
+        training forward that has to keep intermediates for the backward."""
+        return (model.mlp_precision != "fp32" and not forced and not self._keep_parts
+                and getattr(model, "_train_stash", None) is None and os.environ.get("PIXELNERF_B200_STAGED") != "1")
+
+    def _render_fused(self, model, rays, draws, seed):
+        if self.training and self.noise_std > 0.0:
+            raise NotImplementedError("sigma noise (noise_std > 0) is unused by every shipped conf")
+        if model._cam is None:
+            raise RuntimeError("call encode() before forward()")
+        prec = model.mlp_precision
+        _, hl, wl, _ = model.latent_nhwc(torch.float32).shape
+        mc = (model.mlp_coarse.packed(prec), model.latent_tables(True))
+        fine_mlp = model._mlp(False)
+        mf = None if fine_mlp is model.mlp_coarse else (fine_mlp.packed(prec), model.latent_tables(False))
+        n_dep = self.n_fine_depth if self.using_fine else 0
+        n_imp = self.n_fine - n_dep if self.using_fine else 0
+        coarse, fine = _lib.render_rays(model._cam, hl, wl, mc, mf, rays, self.n_coarse, n_imp, n_dep, self.depth_std,
+                                        self.lindisp, self.white_bkgd, seed=seed, draws=draws)
+        if fine is not None:
+            fine = fine + (fine[3].new_zeros(rays.shape[0], 0),)
+        return coarse, fine
+
     def _render_chunk(self, model, rays, sb, draws, forced, want_weights, seed):
+        if self._fused_ok(model, forced):
+            return self._render_fused(model, rays, draws, seed)
         d = draws or {}
         z_c = forced.get("z_coarse")
         if z_c is None:
