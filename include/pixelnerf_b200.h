@@ -279,6 +279,16 @@ PN_API int pn_gen_rays(const float* poses, int pose_stride, int n_images, int wi
  * [0,255].  n_values floats in, n_values bytes out. */
 PN_API int pn_frame_to_u8(const float* rgb, unsigned char* out, int64_t n_values, pn_stream_t stream);
 
+/* SpatialEncoder.forward's tail, src/model/encoder.py:150-163: every ResNet level map (n_maps, channels[l],
+ * h[l], w[l]) fp32 NCHW is resized to level 0's size with F.interpolate(bilinear, align_corners=True), the
+ * levels are concatenated over channels and the result is written channels-last (n_maps, h[0], w[0],
+ * sum channels) in fp32 or fp16 -- the layout pn_prepare_latent would produce from the NCHW concat.
+ * level_maps / level_channels / level_h / level_w are HOST arrays of n_levels (<= 4) entries; channel counts
+ * must be multiples of 32 (ResNet34: 64, 64, 128, 256). */
+PN_API int pn_encoder_latent(const float* const* level_maps, const int* level_channels, const int* level_h,
+                      const int* level_w, int n_levels, int n_maps, void* latent_nhwc, int dtype,
+                      pn_stream_t stream);
+
 /* ---- (4) compositing ------------------------------------------------------------------- */
 
 /* NeRFRenderer.composite after the model call, src/render/nerf.py:178-182, 228-249.

@@ -105,6 +105,7 @@ _SIGNATURES = {
     "pn_gemm_tc_wgrad": (_int, [_vp, _int, _int, _vp, _int, _int, _i64, _int, _vp, _int, _vp, _vp]),
     "pn_gen_rays": (_int, [_vp, _int, _int, _int, _int, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
     "pn_frame_to_u8": (_int, [_vp, _vp, _i64, _vp]),
+    "pn_encoder_latent": (_int, [_vp, _vp, _vp, _vp, _int, _int, _vp, _int, _vp]),
     "pn_render_rays_workspace_bytes": (_sz, [_i64, _int, C.POINTER(RenderConfig)]),
     "pn_render_rays": (_int, [C.POINTER(Camera), C.POINTER(RenderMlp), C.POINTER(RenderMlp), _i64, _vp, _i64, _vp,
                               C.POINTER(RenderConfig), C.POINTER(RenderDraws), C.POINTER(RenderOut),
@@ -526,6 +527,27 @@ def gen_rays(poses, width, height, focal, z_near, z_far, c=None):
         _check(lib().pn_gen_rays(_ptr(poses), poses.shape[1] * 4, n, width, height, fx, fy, cx, cy,
                                  float(z_near), float(z_far), _ptr(rays), _stream()), "pn_gen_rays")
     return rays
+
+
+def encoder_latent(levels, dtype=torch.float32):
+    """SpatialEncoder.forward's tail (encoder.py:150-163) in one kernel: list of NCHW fp32 level maps ->
+    channels-last (V, H0, W0, sum C) latent = cat([interpolate(l, (H0, W0), bilinear, align_corners=True)])."""
+    levels = [_f32c(l) for l in levels]
+    n = len(levels)
+    v = levels[0].shape[0]
+    dev = levels[0].device
+    if any(l.dim() != 4 or l.shape[0] != v or not l.is_cuda for l in levels):
+        raise RuntimeError("encoder_latent needs CUDA level maps of shape (V, C_l, H_l, W_l)")
+    ctot = sum(l.shape[1] for l in levels)
+    out = torch.empty(v, levels[0].shape[2], levels[0].shape[3], ctot, device=dev, dtype=dtype)
+    maps = (_vp * n)(*[l.data_ptr() for l in levels])
+    ch = (_int * n)(*[l.shape[1] for l in levels])
+    hh = (_int * n)(*[l.shape[2] for l in levels])
+    ww = (_int * n)(*[l.shape[3] for l in levels])
+    code = DTYPE_F32 if dtype == torch.float32 else DTYPE_F16
+    with _Timed("encoder_latent"):
+        _check(lib().pn_encoder_latent(maps, ch, hh, ww, n, v, out.data_ptr(), code, _stream()), "pn_encoder_latent")
+    return out
 
 
 def frame_to_u8(rgb):

@@ -95,18 +95,26 @@ template <> struct Vec16<__half> {
 // (its own 36 sinf) -- per-row scalar work is done once, not 32 times.  Phase 2: for each of the
 // 32 rows the tap offsets / weights are broadcast by shuffle and the whole warp blends the four
 // contiguous channels-last taps with 16-byte loads and stores (512 B per warp request).
-template <typename LatT, typename OutT>
+// kTaps (tensor-core path, fp16): no blend; each row's 128 bytes = [code 88 B, zero 8 B, taps record 32 B] are
+// staged in shared memory (row pitch 144 B: 8-byte stores of a half-warp land 2-way, 16-byte reads of a
+// quarter-warp conflict free) and leave as fully coalesced 16-byte stores, 512 B per warp instruction --
+// one lane storing its own row directly touches 32 lines for 8 bytes each per instruction.
+constexpr int kTapsPitch = 144;
+
+template <typename LatT, typename OutT, bool kTaps>
 __global__ void __launch_bounds__(kFeatWarps * 32)
 point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
                       const float* __restrict__ rays, const float* __restrict__ zs, int n_samples,
                       const float* __restrict__ xyz_in, const float* __restrict__ dirs_in,
                       int64_t ppo, OutT* __restrict__ feat_z, OutT* __restrict__ feat_x, int ldx,
                       int64_t n_rows, uint4* __restrict__ taps) {
+  __shared__ __align__(16) unsigned char stage_all[kTaps ? kFeatWarps * 32 * kTapsPitch : 16];
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5)) * 32;
   if (row0 >= n_rows) return;
   const int64_t row = row0 + lane;
   const bool valid = row < n_rows;
+  unsigned char* stage = stage_all + (kTaps ? (threadIdx.x >> 5) * 32 * kTapsPitch : 0);
   uint32_t o00 = 0, o01 = 0, o10 = 0, o11 = 0;
   float w00 = 0.f, w01 = 0.f, w10 = 0.f, w11 = 0.f;
   if (valid) {
@@ -163,15 +171,16 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     o01 = vbase + (uint32_t)(y0 * cam.wl + x1);
     o10 = vbase + (uint32_t)(y1 * cam.wl + x0);
     o11 = vbase + (uint32_t)(y1 * cam.wl + x1);
-    if (taps) {  // tensor-core path: the chain kernel blends per-texel lin_z tables with these.  The record
+    if (kTaps) {  // tensor-core path: the chain kernel blends per-texel lin_z tables with these.  The record
       // rides in bytes [96,128) of the row's 128-byte positional-code chunk (fp16 columns 48-63, which the
       // K=48 lin_in MMA never reads), so it reaches shared memory with the TMA load of x.
-      taps[row * 8 + 6] = make_uint4(o00, o01, o10, o11);
-      taps[row * 8 + 7] = make_uint4(__float_as_uint(w00), __float_as_uint(w01), __float_as_uint(w10), __float_as_uint(w11));
+      uint4* rec = reinterpret_cast<uint4*>(stage + lane * kTapsPitch + 96);
+      rec[0] = make_uint4(o00, o01, o10, o11);
+      rec[1] = make_uint4(__float_as_uint(w00), __float_as_uint(w01), __float_as_uint(w10), __float_as_uint(w11));
     }
     o00 *= PN_D_LATENT; o01 *= PN_D_LATENT; o10 *= PN_D_LATENT; o11 *= PN_D_LATENT;
     // code: [x(3), sin(f_j x + phase_j)(36), R d (3)], zero pad to ldx; 4 elements at a time
-    OutT* ox = feat_x + (size_t)row * ldx;
+    OutT* ox = kTaps ? reinterpret_cast<OutT*>(stage + lane * kTapsPitch) : feat_x + (size_t)row * ldx;
     const float comp[3] = {xr, yr, zr};
     const float rd[3] = {r0 * dx + r1 * dy + r2 * dz, r3 * dx + r4 * dy + r5 * dz, r6 * dx + r7 * dy + r8 * dz};
 #pragma unroll
@@ -201,12 +210,21 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
             make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
       }
     }
-    for (int e0 = 44; e0 < (taps ? 48 : ldx); e0 += 4) {  // zero padding up to ldx (up to the taps record)
+    for (int e0 = 44; e0 < (kTaps ? 48 : ldx); e0 += 4) {  // zero padding up to ldx (up to the taps record)
       if (sizeof(OutT) == 4) *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(0.f, 0.f, 0.f, 0.f);
       else *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ox) + e0) = make_uint2(0u, 0u);
     }
   }
-  if (taps) return;
+  if (kTaps) {
+    __syncwarp();
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int j = it * 32 + lane, rr = j >> 3, piece = j & 7;
+      if (row0 + rr < n_rows)
+        taps[(row0 + rr) * 8 + piece] = *reinterpret_cast<const uint4*>(stage + rr * kTapsPitch + piece * 16);
+    }
+    return;
+  }
   // phase 2: the warp blends the taps of each of its rows
   constexpr int N = Vec16<LatT>::N;
   constexpr int kIters = PN_D_LATENT / (32 * N);
@@ -515,11 +533,11 @@ extern "C" int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc
   if (n_rows == 0) return PN_OK;
   const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
   if (out_dtype == PN_DTYPE_F32)
-    pn::point_features_kernel<float, float><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+    pn::point_features_kernel<float, float, false><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
         *cam, (const float*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
         (float*)feat_z, (float*)feat_x, ldx, n_rows, nullptr);
   else
-    pn::point_features_kernel<__half, __half><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+    pn::point_features_kernel<__half, __half, false><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
         *cam, (const __half*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
         (__half*)feat_z, (__half*)feat_x, ldx, n_rows, nullptr);
   PN_LAUNCH_OK("point_features_kernel");
@@ -540,7 +558,7 @@ extern "C" int pn_point_taps(const pn_camera_t* cam, const float* rays, const fl
   const int64_t n_rows = (int64_t)cam->n_objects * cam->n_views * points_per_object;
   if (n_rows == 0) return PN_OK;
   const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
-  pn::point_features_kernel<__half, __half><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+  pn::point_features_kernel<__half, __half, true><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
       *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
       (uint4*)feat_x);
   PN_LAUNCH_OK("point_features_kernel(taps)");

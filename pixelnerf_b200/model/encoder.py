@@ -59,9 +59,18 @@ class SpatialEncoder(nn.Module):
                 x = layer(x)
                 latents.append(x)
         self.latents = latents
-        size = latents[0].shape[-2:]
-        latents = [F.interpolate(l, size, mode=self.upsample_interp, align_corners=True) for l in latents]
-        self.latent = torch.cat(latents, dim=1)
+        fused = (x.is_cuda and self.upsample_interp == "bilinear" and all(l.shape[1] % 32 == 0 for l in latents)
+                 and not (torch.is_grad_enabled() and any(l.requires_grad for l in latents)))
+        if fused:
+            # inference hand-off: resize + concat + channels-last conversion in one kernel
+            # (pn_encoder_latent); ``latent`` stays an NCHW-shaped tensor, as a view of channels-last memory,
+            # which PixelNeRFNet.latent_nhwc recognises and uses without a transpose
+            from .. import _lib
+            self.latent = _lib.encoder_latent(latents, torch.float32).permute(0, 3, 1, 2)
+        else:
+            size = latents[0].shape[-2:]
+            latents = [F.interpolate(l, size, mode=self.upsample_interp, align_corners=True) for l in latents]
+            self.latent = torch.cat(latents, dim=1)
         ls = torch.tensor([self.latent.shape[-1], self.latent.shape[-2]], dtype=torch.float32,
                           device=self.latent.device)
         self.latent_scaling = ls / (ls - 1) * 2.0

@@ -125,8 +125,15 @@ class PixelNeRFNet(torch.nn.Module):
         lat = self.encoder.latent
         key = (dtype, lat.data_ptr(), lat._version)
         if self._latent_nhwc.get("key") != key:
-            src = lat.detach() if self.stop_encoder_grad or not lat.requires_grad else lat.detach()
-            self._latent_nhwc = {"key": key, "t": _lib.prepare_latent(src, dtype)}
+            src = lat.detach()
+            nhwc = src.permute(0, 2, 3, 1)
+            if lat.dim() == 4 and lat.dtype == torch.float32 and lat.is_cuda and nhwc.is_contiguous() \
+                    and not src.is_contiguous():
+                # the encoder already wrote channels-last memory (pn_encoder_latent): no transpose
+                t = nhwc if dtype == torch.float32 else nhwc.to(dtype)
+            else:
+                t = _lib.prepare_latent(src, dtype)
+            self._latent_nhwc = {"key": key, "t": t}
         return self._latent_nhwc["t"]
 
     def latent_tables(self, coarse):

@@ -6,7 +6,8 @@ scatters the rays along dim 1 and gathers the outputs on gpus[0].  Rays are inde
 encoded scene, so here each rank keeps its weights resident, the encoder rank broadcasts the encoded
 scene once per ``encode`` (``broadcast_encoded``) and every call only moves results: a contiguous
 ray range per rank in, one all-gather of the rendered values out (16 B/ray for rgb+depth).
-There is no collective inside the data path.
+There is no collective inside the data path.  Training uses the same sharding: the gather is differentiable
+(each rank back-propagates its own ray range) and ``allreduce_gradients`` sums the weight gradients.
 
 The wrapper is backend agnostic (NCCL on the GPUs; the CPU tests drive the same code over gloo with
 a stand-in render function).
@@ -41,6 +42,60 @@ def _gather_dim1(t, counts, group):
     out = [torch.empty_like(pad) for _ in range(world)]
     dist.all_gather(out, pad.contiguous(), group=group)
     return torch.cat([o[:, :c] for o, c in zip(out, counts)], dim=1)
+
+
+class _GatherDim1Grad(torch.autograd.Function):
+    """_gather_dim1 with a backward: every rank evaluates the same loss on the same gathered tensor, so the
+    gradient of this rank's slice is the matching slice of the upstream gradient.  The parameter gradients
+    each rank then holds are its rays' share of the single-process gradient; ``allreduce_gradients`` sums them."""
+
+    @staticmethod
+    def forward(ctx, t, counts, rank, group):
+        ctx.start, ctx.count = sum(counts[:rank]), counts[rank]
+        return _gather_dim1(t, counts, group)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g[:, ctx.start:ctx.start + ctx.count].contiguous(), None, None, None
+
+
+def allreduce_gradients(modules, group=None, latent=None, latent_src=0):
+    """Training, SURVEY 8e: after ``loss.backward()`` on every rank (each over its own ray range of the same
+    batch), sum the parameter gradients over the ranks -- one flat bucket per dtype (the two ResnetFC weight sets
+    are 27.5 MB of fp32; the replicated encoder's gradients ride along when it is trained) and one all-reduce each.
+    Parameters without a gradient on some rank (an empty ray range) contribute zeros.  If ``latent`` is a
+    non-parameter tensor with a gradient (an encoder that lives on rank ``latent_src`` only), its gradient is
+    reduced to that rank.  Returns the number of bytes all-reduced."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return 0
+    if isinstance(modules, torch.nn.Module):
+        modules = [modules]
+    params = [q for m in modules for q in m.parameters() if q.requires_grad]
+    nbytes = 0
+    by_type = {}
+    for q in params:
+        by_type.setdefault((q.dtype, q.device), []).append(q)
+    for (dtype, dev), qs in by_type.items():
+        flat = torch.zeros(sum(q.numel() for q in qs), dtype=dtype, device=dev)
+        off = 0
+        for q in qs:
+            if q.grad is not None:
+                flat[off:off + q.numel()].copy_(q.grad.reshape(-1))
+            off += q.numel()
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        nbytes += flat.numel() * flat.element_size()
+        off = 0
+        for q in qs:
+            g = flat[off:off + q.numel()].view_as(q)
+            if q.grad is None:
+                q.grad = g.clone()
+            else:
+                q.grad.copy_(g)
+            off += q.numel()
+    if latent is not None and latent.grad is not None:
+        dist.reduce(latent.grad, dst=latent_src, op=dist.ReduceOp.SUM, group=group)
+        nbytes += latent.grad.numel() * latent.grad.element_size()
+    return nbytes
 
 
 def _map_tensors(obj, fn):
@@ -78,7 +133,12 @@ class RaySharded(torch.nn.Module):
         if renderer is not None and getattr(renderer, "injected_draws", None) is not None:
             renderer.injected_draws = shard_draws(renderer.injected_draws, n, rays.shape[0], world, rank)
         local = self.wrapped(rays[:, s:e].contiguous(), want_weights)
-        return _map_tensors(local, lambda t: _gather_dim1(t, counts, self.group))
+
+        def gather(t):
+            if t.requires_grad:   # training: keep the autograd graph through the gather
+                return _GatherDim1Grad.apply(t, counts, rank, self.group)
+            return _gather_dim1(t, counts, self.group)
+        return _map_tensors(local, gather)
 
 
 def broadcast_encoded(net, src=0, group=None):
