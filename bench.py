@@ -27,6 +27,8 @@ import torch  # noqa: E402
 
 SCENE = "srn_car"
 N_COARSE, N_FINE, N_DEPTH = 64, 32, 16
+WORKLOADS = {"srn_car": "SRN car 128x128 NS=1", "srn_chair": "SRN chair 128x128 NS=2 (BASELINE config 3, one frame)",
+             "dtu": "DTU 300x400 NS=3 (BASELINE config 4)", "sn64": "NMR 64x64 NS=1 (BASELINE config 1)"}
 MLP_FLOP_PER_POINT = {1: 2 * (1 * 2380800 + 1050624), 2: 2 * (2 * 2380800 + 1050624), 3: 2 * (3 * 2380800 + 1050624)}
 
 
@@ -122,6 +124,60 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def run_torch_cuda(args):
+    """--impl torch-cuda: the reference's torch op sequence (the oracle port) run as torch-CUDA eager on the same
+    B200 -- the "existing Blackwell path" (cuBLAS/ATen library kernels) the new kernels replace.  Whole
+    frame per step; fp32 (TF32 off), TF32 allowed, and bf16 autocast.  A baseline measurement, not a product path."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import scene_camera
+    import oracle
+    from oracle import model as omodel
+    dev = torch.device("cuda", 0)
+    sc = syn.scene(args.scene)
+    wc = {k: v.to(dev) for k, v in syn.mlp_weights(1).items()}
+    wf = {k: v.to(dev) for k, v in syn.mlp_weights(2).items()}
+    cam = {k: v.to(dev) for k, v in scene_camera(sc).items()}
+    lat = sc["latent"].to(dev)
+    rays = sc["rays"].to(dev)
+    n = rays.shape[0]
+    draws = {k: v.to(dev) for k, v in syn.draws(7, n, N_COARSE, N_FINE - N_DEPTH, N_DEPTH).items()}
+    chunk = 4096   # rays per call: 0.4 M points x NS views, like the reference's eval_batch_size chunks
+
+    def net_fn(xyz, dirs, coarse):
+        return omodel.net_forward(wc if coarse else wf, lat, cam, sc["ns"], xyz, dirs)
+
+    def frame():
+        with torch.no_grad():
+            for s0 in range(0, n, chunk):
+                d = {k: v[s0:s0 + chunk] for k, v in draws.items()}
+                oracle.render_rays(net_fn, rays[s0:s0 + chunk], 1, N_COARSE, N_FINE, N_DEPTH, d, depth_std=0.01,
+                                   white_bkgd=sc["white"])
+
+    res = {}
+    for mode in ("fp32", "tf32", "bf16_autocast"):
+        torch.backends.cuda.matmul.allow_tf32 = mode == "tf32"
+        torch.backends.cudnn.allow_tf32 = mode == "tf32"
+        ctx = torch.autocast("cuda", dtype=torch.bfloat16) if mode == "bf16_autocast" else torch.autocast("cuda", enabled=False)
+        with ctx:
+            for _ in range(max(args.warmup, 2)):
+                frame()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            steps = max(1, min(args.steps, 5))
+            a.record()
+            for _ in range(steps):
+                frame()
+            b.record()
+            b.synchronize()
+        ms = a.elapsed_time(b) / steps
+        res[mode] = {"ms_per_frame": ms, "rays/s": n / (ms * 1e-3)}
+    print(json.dumps({"impl": "torch-cuda-eager", "metric": "rays/sec coarse+fine", "unit": "rays/s",
+                      "config": {"workload": f"{WORKLOADS[args.scene]} full frame, {n} rays, {chunk}-ray chunks",
+                                 "code": "oracle port of the reference's torch op sequence on cuda:0, torch "
+                                         + torch.__version__},
+                      "modes": res}))
+
+
 def run_kernels(args):
     """--kernels: every HBM-bound kernel of the path alone at a size that exceeds L2, as achieved GB/s of
     its ALGORITHMIC bytes against the measured copy bandwidth."""
@@ -196,7 +252,7 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    sc = syn.scene(SCENE, target_az=10.0 * rank)  # every rank: its own target frame, same scene
+    sc = syn.scene(args.scene, target_az=10.0 * rank)  # every rank: its own target frame, same scene
     wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
     net, ren = build_net(sc, wc, wf, dev, mlp_precision=args.precision)
     if world > 1:  # encoder features come from rank 0 once per encode
@@ -274,12 +330,17 @@ def run_gpu(args):
         flop_step = n_rays * (N_COARSE + N_COARSE + N_FINE) * MLP_FLOP_PER_POINT[ns]
         mlp_ms = prof.get("mlp", 0.0) / max(1, args.steps)
         achieved = flop_step / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else 0.0
+        # share of the algorithmic FLOPs the fp16 chain executes as MMAs (lin_z goes through tables): MMA counts
+        # per 128 rows at NS=1 (padding included), MAC counts for NS > 1
+        exe = 1.0
+        if args.precision == "fp16":
+            exe = 686.0 / 878.0 if ns == 1 else (ns * (6 * 262144 + 21504) + 1050624) / (ns * 2380800 + 1050624)
         line = {
             "metric": "rays/sec coarse+fine", "value": rays_total / (ms * 1e-3), "unit": "rays/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": {"fp32": "f32", "fp16": "f16", "bf16": "bf16"}[args.precision], "data": "synthetic",
-            "config": {"workload": f"SRN car 128x128 NS=1 full frame: {n_rays} rays/GPU/step, {N_COARSE} coarse + "
+            "config": {"workload": f"{WORKLOADS[args.scene]} full frame: {n_rays} rays/GPU/step, {N_COARSE} coarse + "
                                    f"{N_FINE} fine ({N_DEPTH} depth) samples, ResnetFC 5x512 x2",
                        "mlp_precision": args.precision, "parallelism": f"ray-sharded x{world}",
                        "cache": "256 MiB L2 flush between steps",
@@ -292,8 +353,8 @@ def run_gpu(args):
             # chain applies lin_z through per-texel tables and executes 686 of those 878 MMAs per
             # 128 rows, so `achieved` can exceed the hardware peak: `executed` is what the tensor pipe really did
             "roofline": {"bound": "tensor", "kernel": "ResnetFC chain (%s)" % args.precision, "achieved": achieved,
-                         "executed": achieved * (686.0 / 878.0 if args.precision == "fp16" else 1.0),
-                         "executed_frac": achieved * (686.0 / 878.0 if args.precision == "fp16" else 1.0) / pk["tf_sustained"],
+                         "executed": achieved * exe,
+                         "executed_frac": achieved * exe / pk["tf_sustained"],
                          "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
                          "traffic": chain_traffic(flop_step / MLP_FLOP_PER_POINT[ns] / max(1, n_mlp // max(1, args.steps)))
                          if args.precision == "fp16" else None,
@@ -393,9 +454,11 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "torch-cuda"])
     ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp16"), choices=["fp32", "fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scene", default=SCENE, choices=sorted(WORKLOADS),
+                    help="srn_car = the headline workload (BASELINE configs[1]); the others are extra measurements")
     ap.add_argument("--kernels", action="store_true", help="per-kernel HBM roofline of the memory-bound kernels")
     ap.add_argument("--train", action="store_true", help="training-step timing (BASELINE config 5), not the headline")
     ap.add_argument("--train-rays", type=int, nargs="+", default=[128, 4096], help="rays per object for --train")
@@ -406,6 +469,8 @@ def main():
         run_train(args)
     elif args.impl == "reference":
         run_reference(args)
+    elif args.impl == "torch-cuda":
+        run_torch_cuda(args)
     else:
         run_gpu(args)
 

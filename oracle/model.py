@@ -24,7 +24,7 @@ def camera_state(poses, focal, c, width, height):
     rot = poses[:, :3, :3].transpose(1, 2)
     trans = -torch.bmm(rot, poses[:, :3, 3:])
     w2c = torch.cat((rot, trans), dim=-1)
-    image_shape = torch.tensor([float(width), float(height)])
+    image_shape = torch.tensor([float(width), float(height)]).to(poses.device)
     if focal.dim() == 0:
         focal = focal[None, None].repeat((1, 2))
     elif focal.dim() == 1:
@@ -49,11 +49,11 @@ def _repeat_interleave(x, n):
 
 def positional_encoding(x, num_freqs=6, freq_factor=1.5):
     """[x, sin(f_k x), sin(f_k x + pi/2)] interleaved.  src/model/code.py:12-42."""
-    freqs = freq_factor * 2.0 ** torch.arange(0, num_freqs)
+    freqs = (freq_factor * 2.0 ** torch.arange(0, num_freqs)).to(x.device)
     f = torch.repeat_interleave(freqs, 2).view(1, -1, 1)
     ph = torch.zeros(2 * num_freqs)
     ph[1::2] = math.pi * 0.5
-    ph = ph.view(1, -1, 1)
+    ph = ph.view(1, -1, 1).to(x.device)
     emb = x.unsqueeze(1).repeat(1, num_freqs * 2, 1)
     emb = torch.sin(torch.addcmul(ph, emb, f)).view(x.shape[0], -1)
     return torch.cat((x, emb), dim=-1)
@@ -84,7 +84,7 @@ def point_features(latent, cam, xyz, viewdirs, ns, num_freqs=6, freq_factor=1.5)
     # encoder.index: src/model/encoder.py:94-109
     hl, wl = latent.shape[-2:]
     ls = torch.tensor([float(wl), float(hl)])
-    ls = ls / (ls - 1) * 2.0
+    ls = (ls / (ls - 1) * 2.0).to(latent.device)
     scale = ls / cam["image_shape"]
     uvn = (uv * scale - 1.0).unsqueeze(2)
     samples = F.grid_sample(latent, uvn, align_corners=True, mode="bilinear",

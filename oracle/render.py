@@ -27,7 +27,7 @@ def sample_coarse(rays, n_coarse, u, lindisp=False):
     """
     near, far = rays[:, -2:-1], rays[:, -1:]
     step = 1.0 / n_coarse
-    zs = torch.linspace(0, 1 - step, n_coarse).unsqueeze(0).repeat(rays.shape[0], 1)
+    zs = torch.linspace(0, 1 - step, n_coarse).to(rays.device).unsqueeze(0).repeat(rays.shape[0], 1)
     zs = zs + u * step
     return _lerp_depth(near, far, zs, lindisp)
 

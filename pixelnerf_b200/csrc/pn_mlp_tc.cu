@@ -91,7 +91,7 @@ struct ChainParams {
   int64_t table_stride;  // n_texels * 512
   float4* out;           // (rows, 4) [sigmoid rgb, relu sigma], segments ending in lin_out
   float4* pre;           // optional raw lin_out outputs
-  float* h_io;           // segment [0,3): fp32 h written here; segment [3,5]: view-mean of it read
+  __half* h_io;          // segment [0,3): h written here as fp16; segment [3,5]: view-mean of it read
   uint16_t* save;        // training: 11 slots of (save_stride) bf16, the relu'd operand of every 512-wide GEMM
   int64_t save_stride;   //   slot 2b = relu(h_b) (fc_0 input), 2b+1 = relu(fc_0 out) (fc_1 input), 10 = lin_out input
   float* debug_h;        // optional (rows, 512) dump of h at stage debug_stage
@@ -243,6 +243,18 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll 1
     for (int tile = cluster_id; tile < tile_end; tile += n_clusters) {
       const int row0 = tile * kTileRows + (int)rank * kRows;
+      if (!full_front && elect_one()) {
+        // merged segment: pull the NEXT tile's h rows (one contiguous 64 KB run per view) into L2 while this
+        // tile computes; the epilogue warps' view-mean load then streams from L2 instead of HBM
+        const int64_t nrow = (int64_t)(tile + n_clusters) * kTileRows + (int64_t)rank * kRows;
+        if (tile + n_clusters < tile_end && nrow + kRows <= p.n_rows) {
+          const int64_t obj = nrow / p.ppo, pt = nrow - obj * p.ppo;
+          if (pt + kRows <= p.ppo)
+            for (int v = 0; v < p.n_views; ++v)
+              bulk_prefetch_l2(p.h_io + ((obj * p.n_views + v) * p.ppo + pt) * 512, kRows * 512 * 2);
+        }
+      }
+      __syncwarp();
       if (full_front) {
         load_a(&map_x, 0, row0);
         load_w(S0{}, L_IN, 0, 0, 1);           // hi and lo halves of lin_in
@@ -485,6 +497,32 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
       }
     };
+    // fp16 dump of (accumulator + bias): the hand-off of h from the per-view segment to the merged one.  One
+    // rounding of the residual stream to fp16 (the same rounding every GEMM operand of the chain gets) halves the
+    // hand-off traffic: 1 KB written per (view, point) row and NS KB read per point.
+    auto dump_block16 = [&](uint32_t tcol, const float* bias_vec, int nb, __half* dst, int64_t grow) {
+#pragma unroll 1
+      for (int half = 0; half < 2; ++half) {
+        const int n0 = 256 * nb + 128 * hf + 64 * half + 32 * ch;
+        uint32_t v[32];
+        tmem_ld_32x32(tcol + half * 64, v);
+        tmem_wait_ld();
+        if (grow < p.n_rows) {
+          const float4* bp = reinterpret_cast<const float4*>(bias_vec + n0);
+          uint4* d = reinterpret_cast<uint4*>(dst + grow * 512 + n0);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 b0 = __ldg(bp + 2 * i), b1 = __ldg(bp + 2 * i + 1);
+            const __half2 h0 = __floats2half2_rn(__uint_as_float(v[8 * i]) + b0.x, __uint_as_float(v[8 * i + 1]) + b0.y);
+            const __half2 h1 = __floats2half2_rn(__uint_as_float(v[8 * i + 2]) + b0.z, __uint_as_float(v[8 * i + 3]) + b0.w);
+            const __half2 h2 = __floats2half2_rn(__uint_as_float(v[8 * i + 4]) + b1.x, __uint_as_float(v[8 * i + 5]) + b1.y);
+            const __half2 h3 = __floats2half2_rn(__uint_as_float(v[8 * i + 6]) + b1.z, __uint_as_float(v[8 * i + 7]) + b1.w);
+            d[i] = make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
+                              *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+          }
+        }
+      }
+    };
     auto signal_chunk = [&](int c) {
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(bar(BAR_ACT + c), rank4 & 2u);
@@ -529,7 +567,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         tc_fence_after();
         if (dbg && gather_b < 0) dump_block(tcol, bias_vec, nb, p.debug_h, grow);
         if (mode == 1) {
-          dump_block(tcol, bias_vec, nb, p.h_io, grow);
+          dump_block16(tcol, bias_vec, nb, p.h_io, grow);
           tc_fence_before();
           signal_chunk(c0);
           signal_chunk(c0 + 1);
@@ -588,7 +626,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     auto epi_load = [&](int64_t grow) {
       const bool valid = grow < p.n_rows;
       const int64_t obj = valid ? grow / p.ppo : 0, pt = valid ? grow - obj * p.ppo : 0;
-      const float* src = p.h_io + ((obj * p.n_views) * p.ppo + pt) * 512;
+      const __half* src = p.h_io + ((obj * p.n_views) * p.ppo + pt) * 512;
       const float inv = (float)p.n_views;
       for (int nb = 0; nb < 2; ++nb) {
 #pragma unroll 1
@@ -601,11 +639,16 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           for (int i = 0; i < 32; ++i) x[i] = 0.0f;
           if (valid) {
             for (int v = 0; v < p.n_views; ++v) {
-              const float4* s4 = reinterpret_cast<const float4*>(src + (int64_t)v * p.ppo * 512 + n0);
+              const uint4* s4 = reinterpret_cast<const uint4*>(src + (int64_t)v * p.ppo * 512 + n0);
 #pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float4 t = s4[i];
-                x[4 * i] += t.x; x[4 * i + 1] += t.y; x[4 * i + 2] += t.z; x[4 * i + 3] += t.w;
+              for (int i = 0; i < 4; ++i) {
+                const uint4 t = s4[i];
+                const uint32_t tw[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&tw[j]));
+                  x[8 * i + 2 * j] += f.x; x[8 * i + 2 * j + 1] += f.y;
+                }
               }
             }
 #pragma unroll
@@ -788,8 +831,8 @@ extern "C" int pn_prepare_weights(const pn_mlp_weights_t* w, void* packed, size_
 }
 
 extern "C" size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views) {
-  // fp32 h of every (view, point) row handed from the per-view segment to the merged one, + error word
-  return 256 + (n_views > 1 && n_rows > 0 ? (size_t)n_rows * 512 * sizeof(float) : 0);
+  // fp16 h of every (view, point) row handed from the per-view segment to the merged one, + error word
+  return 256 + (n_views > 1 && n_rows > 0 ? (size_t)n_rows * 512 * sizeof(__half) : 0);
 }
 
 extern "C" size_t pn_mlp_tc_acts_bytes(int64_t n_rows) {
@@ -863,7 +906,7 @@ static int mlp_forward_tc_impl(const void* packed, const void* tables, int64_t n
     return launch_chain(mw, mx, p, st);
   }
   // NS > 1: blocks 0-2 per (view, point) row, then the view mean (resnetfc.py:152-172) feeds blocks 3-4
-  p.h_io = (float*)((char*)workspace + 256);
+  p.h_io = (__half*)((char*)workspace + 256);
   p.bias = ta; p.n_rows = n_rows; p.first_block = 0; p.last_block = 3;
   if ((rc = launch_chain(mw, mx, p, st))) return rc;
   p.bias = tb; p.n_rows = n_pts; p.first_block = 3; p.last_block = 5;

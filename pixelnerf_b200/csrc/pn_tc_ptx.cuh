@@ -104,6 +104,10 @@ __device__ __forceinline__ void tma_load_2d_pair_mc(uint32_t dst, const CUtensor
 }
 
 // Pull a tile into L2 only (no shared-memory destination, no barrier).
+// L2 prefetch of a contiguous global range (16-byte aligned, size a multiple of 16)
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* map, int c0, int c1) {
   asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
 }

@@ -80,7 +80,8 @@ def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo):
     stages = []
     for b in range(5):
         if b == 3 and ns > 1:
-            h = h.reshape(-1, ns, ppo, 512).sum(1).div(ns).reshape(-1, 512)
+            # the per-view h crosses the two launches as fp16, the mean is taken in fp32 (sum in view order, divide)
+            h = h.float().half().double().reshape(-1, ns, ppo, 512).sum(1).div(ns).reshape(-1, 512)
         if b < 3:
             h = h + table_blend(b)
         stages.append(h)
