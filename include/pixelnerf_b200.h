@@ -244,7 +244,8 @@ PN_API int pn_gemm_tc_wgrad(const void* g, int g_fmt, int ldg, const void* x, in
 
 /* pn_mlp_forward_tc that also stores the bf16 relu'd operand of every 512-wide GEMM (11 slots of rows x 512:
  * slot 2b = relu(h_b), 2b+1 = relu(fc_0 out of block b), 10 = relu(h_5); slots 6.. hold n_objects*P rows when
- * n_views > 1).  `acts` needs pn_mlp_tc_acts_bytes(rows). */
+ * n_views > 1; the slot pitch is `rows` rounded up to a multiple of 128).  `acts` needs
+ * pn_mlp_tc_acts_bytes(rows) and 128-byte alignment. */
 PN_API size_t pn_mlp_tc_acts_bytes(int64_t n_rows);
 PN_API int pn_mlp_forward_tc_train(const void* packed, const void* tables, int64_t n_texels, const void* feat_x,
                             int n_objects, int n_views, int64_t points_per_object, float* out, float* pre_act,

@@ -619,6 +619,13 @@ def mlp_forward_tc_train(packed, tables, feat_x, n_objects, n_views, ppo):
     return out, acts
 
 
+def tc_acts_view(acts, n_rows):
+    """The saved-operand buffer of mlp_forward_tc_train as a (11, n_rows, 512) bf16 view (slot pitch = n_rows
+    rounded up to whole 128-row tiles)."""
+    pitch = (n_rows + 127) // 128 * 128
+    return acts[: 11 * pitch * 1024].view(torch.bfloat16).reshape(11, pitch, 512)[:, :n_rows]
+
+
 def pack_weights_bf16(w):
     """bf16 copies of the thirteen 512x512 matrices for the tensor-core backward."""
     s, keep = pack_weights_fp32(w)

@@ -66,7 +66,7 @@ enum {
   BAR_COUNT = BAR_ACC + 4
 };
 constexpr int kOffTmemPtr = kOffBar + BAR_COUNT * 8;
-constexpr int kOffStage = (kOffTmemPtr + 16 + 127) / 128 * 128;   // per epilogue warp: [32 rows x 32 fp16] table-blend staging
+constexpr int kOffStage = (kOffTmemPtr + 16 + 511) / 512 * 512;   // per epilogue warp: [32 rows x 32 x 16 bit], 64-byte swizzle: table-blend staging and TMA-store source
 constexpr int kStageBytes = 32 * 64;
 constexpr int kSmemBytes = kOffStage + 8 * kStageBytes;
 constexpr int kSmemAlloc = kSmemBytes + 1024;  // slack for the manual 1024-byte alignment
@@ -92,8 +92,9 @@ struct ChainParams {
   float4* out;           // (rows, 4) [sigmoid rgb, relu sigma], segments ending in lin_out
   float4* pre;           // optional raw lin_out outputs
   __half* h_io;          // segment [0,3): h written here as fp16; segment [3,5]: view-mean of it read
-  uint16_t* save;        // training: 11 slots of (save_stride) bf16, the relu'd operand of every 512-wide GEMM
-  int64_t save_stride;   //   slot 2b = relu(h_b) (fc_0 input), 2b+1 = relu(fc_0 out) (fc_1 input), 10 = lin_out input
+  uint16_t* save;        // training: 11 slots of save_rows x 512 bf16, the relu'd operand of every 512-wide GEMM
+  int64_t save_rows;     //   slot 2b = relu(h_b) (fc_0 input), 2b+1 = relu(fc_0 out) (fc_1 input), 10 = lin_out input;
+                         //   rows per slot, padded to whole tiles (stores of a ragged last tile land in the padding)
   float* debug_h;        // optional (rows, 512) dump of h at stage debug_stage
   unsigned int* err;     // device word set before a watchdog trap
   int64_t n_rows;        // rows this launch processes
@@ -118,14 +119,26 @@ __device__ __forceinline__ uint32_t pack_relu_bf2(float a, float b) {
   asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
   return d;
 }
-// 32 relu'd values of one row -> 64 bytes of bf16
-__device__ __forceinline__ void save_relu32(uint16_t* dst, const float (&x)[32]) {
+// Training: 32 relu'd values of each of the warp's 32 rows -> one [32 x 32] bf16 box in global memory.  A lane
+// storing its own row's 64 bytes straight to global touches 32 lines per instruction on the L1/shared-memory data
+// path that bounds this kernel (the forward with such stores ran 48 % slower per row); instead the box is written to
+// the warp's staging buffer (64-byte rows, 64-byte swizzle, the same 4 st.shared.v4 an ACT chunk costs) and leaves
+// through one TMA store issued by lane 0, asynchronously.  `stage` must be free (bulk_wait_read0 + __syncwarp).
+__device__ __forceinline__ void save_relu32(const CUtensorMap* map, uint32_t stage, int lane, int col, int64_t row0,
+                                            bool store, const float (&x)[32]) {
+  if (lane == 0) bulk_wait_read0();   // the previous box has left the staging buffer
+  __syncwarp();
 #pragma unroll
-  for (int i = 0; i < 2; ++i)
-    stg_v8(dst + 16 * i, pack_relu_bf2(x[16 * i + 0], x[16 * i + 1]), pack_relu_bf2(x[16 * i + 2], x[16 * i + 3]),
-           pack_relu_bf2(x[16 * i + 4], x[16 * i + 5]), pack_relu_bf2(x[16 * i + 6], x[16 * i + 7]),
-           pack_relu_bf2(x[16 * i + 8], x[16 * i + 9]), pack_relu_bf2(x[16 * i + 10], x[16 * i + 11]),
-           pack_relu_bf2(x[16 * i + 12], x[16 * i + 13]), pack_relu_bf2(x[16 * i + 14], x[16 * i + 15]));
+  for (int j = 0; j < 4; ++j)
+    st_shared_v4(stage + lane * 64 + ((uint32_t)(j ^ ((lane >> 1) & 3)) << 4),
+                 pack_relu_bf2(x[8 * j + 0], x[8 * j + 1]), pack_relu_bf2(x[8 * j + 2], x[8 * j + 3]),
+                 pack_relu_bf2(x[8 * j + 4], x[8 * j + 5]), pack_relu_bf2(x[8 * j + 6], x[8 * j + 7]));
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0 && store) {
+    tma_store_2d(map, stage, col, (int)row0);
+    bulk_commit_group();
+  }
 }
 __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
   uint32_t d;
@@ -136,7 +149,7 @@ __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
 template <bool kSave>
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
-                 const ChainParams p) {
+                 const __grid_constant__ CUtensorMap map_s, const ChainParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -162,6 +175,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&map_w);
     prefetch_tensormap(&map_x);
+    if (kSave) prefetch_tensormap(&map_s);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -557,6 +571,10 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll
           for (int i = 0; i < 32; ++i) b0[i] = b1[i] = 0.0f;
         } else if (gather_b >= 0) {
+          if (kSave) {   // the staging buffer may still be the source of the previous TMA store
+            if (lane == 0) bulk_wait_read0();
+            __syncwarp();
+          }
           gather_block(p.tables + (size_t)gather_b * p.table_stride + c0 * 64 + 32 * ch, xslot, b0, b1);
         } else {
           ld_bias32(bias_vec + c0 * 64 + 32 * ch, b0);
@@ -609,8 +627,9 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         if (gather_b >= 0) tmem_wait_st();
         tc_fence_before();
         signal_chunk(c0);
-        if (kSave && grow < p.n_rows)
-          save_relu32(p.save + (size_t)slot * p.save_stride + grow * 512 + c0 * 64 + 32 * ch, b0);
+        if (kSave)
+          save_relu32(&map_s, stage, lane, c0 * 64 + 32 * ch, (int64_t)slot * p.save_rows + (grow - lane),
+                      grow - lane < p.n_rows, b0);
 #pragma unroll
         for (int i = 0; i < 4; ++i)
           st_shared_v4(dst + kChunkBytes + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
@@ -618,8 +637,9 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
                        pack_relu_h2(b1[8 * i + 4], b1[8 * i + 5]), pack_relu_h2(b1[8 * i + 6], b1[8 * i + 7]));
         fence_proxy_async_smem();
         signal_chunk(c0 + 1);
-        if (kSave && grow < p.n_rows)
-          save_relu32(p.save + (size_t)slot * p.save_stride + grow * 512 + c0 * 64 + 64 + 32 * ch, b1);
+        if (kSave)
+          save_relu32(&map_s, stage, lane, c0 * 64 + 64 + 32 * ch, (int64_t)slot * p.save_rows + (grow - lane),
+                      grow - lane < p.n_rows, b1);
       }
     };
     // Segment [3,5] entry: h = mean over views of the fp32 h the first segment wrote.
@@ -667,7 +687,9 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           fence_proxy_async_smem();
           tc_fence_before();
           signal_chunk(c);
-          if (kSave && valid) save_relu32(p.save + (size_t)(2 * p.first_block) * p.save_stride + grow * 512 + n0, x);
+          if (kSave)
+            save_relu32(&map_s, stage, lane, n0, (int64_t)(2 * p.first_block) * p.save_rows + (grow - lane),
+                        grow - lane < p.n_rows, x);
         }
       }
     };
@@ -712,6 +734,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     }
   }
   __syncwarp();
+  if (kSave) bulk_wait0();   // this thread's TMA stores (lane 0 of the epilogue warps) are complete
   tc_fence_before();
   cluster_sync_all();
   if (warp == 2) tmem_dealloc_pair(tmem_base, 512);
@@ -770,7 +793,7 @@ pack_bias_kernel(pn_mlp_weights_t w, float* __restrict__ ta, float* __restrict__
 }
 
 // ---- host side ----------------------------------------------------------------------------
-static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, ChainParams p,
+static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap& ms, ChainParams p,
                         cudaStream_t st) {
   static bool attr_set = false;  // idempotent; a benign race at worst repeats the call
   if (!attr_set) {
@@ -799,8 +822,8 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, ChainParam
   attrs[1].val.preferredClusterDim.x = 4; attrs[1].val.preferredClusterDim.y = 1; attrs[1].val.preferredClusterDim.z = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 2;
-  if (p.save) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<true>, mw, mx, p));
-  else PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false>, mw, mx, p));
+  if (p.save) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<true>, mw, mx, ms, p));
+  else PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false>, mw, mx, ms, p));
   PN_LAUNCH_OK("mlp_chain_kernel");
   count_launch();
   return PN_OK;
@@ -835,8 +858,12 @@ extern "C" size_t pn_mlp_tc_workspace_bytes(int64_t n_rows, int n_views) {
   return 256 + (n_views > 1 && n_rows > 0 ? (size_t)n_rows * 512 * sizeof(__half) : 0);
 }
 
+// rows per slot of the saved-operand buffer: whole 128-row tiles (the TMA stores of a ragged last tile end in the
+// padding instead of the next slot)
+static inline int64_t acts_rows(int64_t n_rows) { return (n_rows > 0 ? n_rows + 127 : 0) / 128 * 128; }
+
 extern "C" size_t pn_mlp_tc_acts_bytes(int64_t n_rows) {
-  return (size_t)(n_rows > 0 ? n_rows : 0) * 512 * 2 * 11 + 256;
+  return (size_t)acts_rows(n_rows) * 512 * 2 * 11 + 256;
 }
 
 static int mlp_forward_tc_impl(const void* packed, const void* tables, int64_t n_texels, const void* feat_x,
@@ -898,18 +925,20 @@ static int mlp_forward_tc_impl(const void* packed, const void* tables, int64_t n
   p.debug_h = dbg ? dbg->h : nullptr;
   p.debug_stage = dbg ? dbg->stage : -1;
   p.save = (uint16_t*)acts;
-  p.save_stride = n_rows * 512;
+  p.save_rows = acts_rows(n_rows);
+  CUtensorMap ms = mw;   // placeholder when nothing is saved (the kernel variant without stores never reads it)
+  if (acts && (rc = make_store_map(&ms, acts, (uint64_t)(11 * p.save_rows)))) return rc;
   const float* ta = (const float*)((const char*)packed + kPackedWeightBytes);
   const float* tb = (const float*)((const char*)packed + kPackedWeightBytes + kBiasBytes);
   if (n_views == 1) {
     p.bias = ta; p.n_rows = n_rows; p.first_block = 0; p.last_block = 5;
-    return launch_chain(mw, mx, p, st);
+    return launch_chain(mw, mx, ms, p, st);
   }
   // NS > 1: blocks 0-2 per (view, point) row, then the view mean (resnetfc.py:152-172) feeds blocks 3-4
   p.h_io = (__half*)((char*)workspace + 256);
   p.bias = ta; p.n_rows = n_rows; p.first_block = 0; p.last_block = 3;
-  if ((rc = launch_chain(mw, mx, p, st))) return rc;
+  if ((rc = launch_chain(mw, mx, ms, p, st))) return rc;
   p.bias = tb; p.n_rows = n_pts; p.first_block = 3; p.last_block = 5;
   p.debug_h = (dbg && dbg->stage >= 4) ? dbg->h : nullptr;
-  return launch_chain(mw, mx, p, st);
+  return launch_chain(mw, mx, ms, p, st);
 }

@@ -40,5 +40,21 @@ static inline int make_map(CUtensorMap* m, const void* base, uint64_t rows, uint
   return PN_OK;
 }
 
+// bf16 matrix (rows, 512) -> store boxes of [32 rows x 32 columns] = 64-byte rows, 64-byte swizzle (the layout of
+// the chain kernel's per-warp staging buffer).
+static inline int make_store_map(CUtensorMap* m, const void* base, uint64_t rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled entry point unavailable"); return PN_ERR_CUDA; }
+  cuuint64_t dims[2] = {512, rows};
+  cuuint64_t strides[1] = {1024};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (store map) failed (%d)", (int)r); return PN_ERR_CUDA; }
+  return PN_OK;
+}
+
 }  // namespace tc
 }  // namespace pn

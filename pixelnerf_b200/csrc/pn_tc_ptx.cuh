@@ -103,6 +103,17 @@ __device__ __forceinline__ void tma_load_2d_pair_mc(uint32_t dst, const CUtensor
       ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1), "h"(mask) : "memory");
 }
 
+// TMA store of one box from shared memory (bulk async-group completion)
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all of this thread's bulk groups have finished READING their shared-memory source
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// ... have completed
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // Pull a tile into L2 only (no shared-memory destination, no barrier).
 // L2 prefetch of a contiguous global range (16-byte aligned, size a multiple of 16)
 __device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {

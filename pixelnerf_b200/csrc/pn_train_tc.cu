@@ -227,7 +227,8 @@ extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, co
   uint16_t* X16 = Z16 + R * 512;
   uint16_t* GH16b = X16 + R * 64;
   const uint16_t* W16 = (const uint16_t*)w16;
-  auto X = [&](int slot) { return (const uint16_t*)acts + (size_t)slot * R * 512; };
+  const size_t R_slot = (R + 127) / 128 * 128;   // slot pitch of the forward's saved operands (pn_mlp_tc_acts_bytes)
+  auto X = [&](int slot) { return (const uint16_t*)acts + (size_t)slot * R_slot * 512; };
   auto Wm = [&](int mat) { return W16 + (size_t)mat * kW16Elems; };
   int rc;
   PN_CUDA_OK(cudaMemsetAsync(err, 0, 4, st));

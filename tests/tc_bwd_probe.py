@@ -43,7 +43,7 @@ def rel(a, b): return (a.cpu().double() - b).abs().max().item() / max(b.abs().ma
 if MODE == "emu":
     from helpers import emulate_tc_backward
     m = sb * ppo
-    a = acts[: 11 * n * 512 * 2].view(torch.bfloat16).reshape(11, n, 512)
+    a = _lib.tc_acts_view(acts, n)
     al = [a[i].cpu().double() if i < 6 or ns == 1 else a[i, :m].cpu().double() for i in range(11)]
     z64 = (wt.double()[:, :, None] * latent.double()[idx]).sum(1)
     ge, gz = emulate_tc_backward(w, al, z64, fx[:, :42].double(), out.cpu(), g_out, sb, ns, ppo)
@@ -58,5 +58,5 @@ for k in order:
           f"   |gW|max {wr[k + '.weight'].grad.abs().max().item():.2e}")
 print("g_feat_z", rel(g_fz, zr.grad))
 # saved activations vs the float64 forward: slot 10 = relu(h5)
-a = acts[: 11 * n * 512 * 2].view(torch.bfloat16).reshape(11, n, 512)
+a = _lib.tc_acts_view(acts, n)
 print("acts finite", torch.isfinite(a.float()).all().item(), "slot means", [round(a[i].float().mean().item(), 4) for i in range(11)])

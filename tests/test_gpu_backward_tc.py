@@ -57,7 +57,7 @@ def test_mlp_backward_tc_vs_emulation(ns, ppo, sb):
     largest entry."""
     c = _case(ns, ppo, sb, positive=False)
     n, m = c["n"], sb * ppo
-    a = c["acts"][: 11 * n * 512 * 2].view(torch.bfloat16).reshape(11, n, 512)
+    a = _lib.tc_acts_view(c["acts"], n)
     al = [a[i].cpu().double() if i < 6 or ns == 1 else a[i, :m].cpu().double() for i in range(11)]
     ref, gz = emulate_tc_backward(c["w"], al, c["z64"], c["fx"][:, :42].double(), c["out"], c["g_out"], sb, ns, ppo)
     worst = {k: _rel(c["grads"][k], ref[k]) for k in _lib.weight_names()}
