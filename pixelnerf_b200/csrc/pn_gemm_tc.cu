@@ -30,7 +30,9 @@ constexpr int kGOffBar = kGRing;
 enum { GB_FULL = 0, GB_EMPTY = 8, GB_ACCF = 16, GB_ACCE = 18, GB_COUNT = 20 };
 constexpr int kGOffTmem = kGOffBar + GB_COUNT * 8;
 constexpr int kGOffColsum = kGOffTmem + 16;            // 512 floats: per-CTA column sums (rows GEMM)
-constexpr int kGSmem = kGOffColsum + 512 * 4 + 1024;
+constexpr int kGOffOut = (kGOffColsum + 512 * 4 + 511) / 512 * 512;   // rows GEMM: per epilogue warp, one [32 x 32] bf16
+constexpr int kGOutBytes = 32 * 64;                                   //   box (64-byte rows, 64-byte swizzle) = TMA-store source
+constexpr int kGSmem = kGOffOut + 8 * kGOutBytes + 1024;
 static_assert(kGSmem <= 227 * 1024, "shared memory budget");
 
 // MN-major operand tile, 128-byte swizzle: 64 contiguous M/N elements per 128-byte row, 8 K rows per 1024-byte
@@ -126,7 +128,7 @@ __device__ __forceinline__ void gemm_teardown(uint32_t tmem_base, int warp) {
 template <bool kAcc>   // kAcc: the fp32 accumulate / output path (acc32) is compiled in
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGThreads, 1)
 gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 const RowsParams p) {
+                 const __grid_constant__ CUtensorMap map_o, const RowsParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -136,6 +138,7 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&map_a);
     prefetch_tensormap(&map_b);
+    if (p.out16) prefetch_tensormap(&map_o);
   }
   float* cs_smem = reinterpret_cast<float*>(smem_raw + (smem_base - smem_u32(smem_raw)) + kGOffColsum);
   for (int i = threadIdx.x; i < 512; i += kGThreads) cs_smem[i] = 0.0f;
@@ -196,6 +199,7 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
   } else if (warp >= 2) {
     const int q = warp & 3, ch = (warp - 2) >> 2;
+    const uint32_t ostage = smem_base + kGOffOut + (uint32_t)(warp - 2) * kGOutBytes;
     uint32_t it = 0;
 #pragma unroll 1
     for (int tile = pair_id; tile < p.n_tiles; tile += n_pairs) {
@@ -284,13 +288,28 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                        __float_as_uint(f[8 * i + 2]), __float_as_uint(f[8 * i + 3]), __float_as_uint(f[8 * i + 4]),
                        __float_as_uint(f[8 * i + 5]), __float_as_uint(f[8 * i + 6]), __float_as_uint(f[8 * i + 7]));
             }
-            if (p.out16) {
+          }
+          if (p.out16) {
+            // The bf16 result leaves as one [32 rows x 32 columns] box per warp and chunk: staged in shared memory
+            // (64-byte rows, 64-byte swizzle) and written by one TMA store, asynchronously -- a lane storing its own
+            // row's 64 bytes touches 32 lines per instruction, and L1 wavefronts are what bounds this epilogue
+            // (ncu r01v: l1tex 62-69 %).  Rows past the end are clipped by the tensor map; in-place use (out16 ==
+            // resid16) is safe: the box is exactly what this warp has already read.
+            if (lane == 0) bulk_wait_read0();   // the previous box has left the staging buffer
+            __syncwarp();
 #pragma unroll
-              for (int i = 0; i < 2; ++i)
-                stg_v8(p.out16 + off + 16 * i, pack_bf2(f[16 * i], f[16 * i + 1]), pack_bf2(f[16 * i + 2], f[16 * i + 3]),
-                       pack_bf2(f[16 * i + 4], f[16 * i + 5]), pack_bf2(f[16 * i + 6], f[16 * i + 7]),
-                       pack_bf2(f[16 * i + 8], f[16 * i + 9]), pack_bf2(f[16 * i + 10], f[16 * i + 11]),
-                       pack_bf2(f[16 * i + 12], f[16 * i + 13]), pack_bf2(f[16 * i + 14], f[16 * i + 15]));
+            for (int j = 0; j < 4; ++j)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                           ::"r"(ostage + lane * 64 + ((uint32_t)(j ^ ((lane >> 1) & 3)) << 4)),
+                             "r"(pack_bf2(f[8 * j], f[8 * j + 1])), "r"(pack_bf2(f[8 * j + 2], f[8 * j + 3])),
+                             "r"(pack_bf2(f[8 * j + 4], f[8 * j + 5])), "r"(pack_bf2(f[8 * j + 6], f[8 * j + 7]))
+                           : "memory");
+            fence_proxy_async_smem();
+            __syncwarp();
+            const int64_t row0 = row - lane;
+            if (lane == 0 && row0 < p.n_rows) {
+              tma_store_2d(&map_o, ostage, half * 256 + lcol, (int)row0);
+              bulk_commit_group();
             }
           }
           if (p.colsum0) {
@@ -338,6 +357,7 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
   }
   __syncwarp();
+  bulk_wait0();                     // this thread's TMA stores are complete
   gemm_teardown(tmem_base, warp);   // cluster barrier: every epilogue warp's shared-memory atomics are done
   if (p.colsum0) {
     __syncthreads();
@@ -520,8 +540,10 @@ extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fm
   int sms = 0;
   if ((rc = gemm_grid(&sms))) return rc;
   const int pairs = p.n_tiles < sms / 2 ? p.n_tiles : sms / 2;
-  if (acc32) gemm_rows_kernel<true><<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, p);
-  else gemm_rows_kernel<false><<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, p);
+  CUtensorMap mo = ma;   // placeholder when there is no bf16 output (never read then)
+  if (out_bf16 && (rc = make_store_map(&mo, out_bf16, (uint64_t)n_rows, (uint64_t)n))) return rc;
+  if (acc32) gemm_rows_kernel<true><<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, mo, p);
+  else gemm_rows_kernel<false><<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, mo, p);
   PN_LAUNCH_OK("gemm_rows_kernel");
   pn::count_launch();
   return PN_OK;

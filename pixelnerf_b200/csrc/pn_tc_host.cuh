@@ -40,13 +40,13 @@ static inline int make_map(CUtensorMap* m, const void* base, uint64_t rows, uint
   return PN_OK;
 }
 
-// bf16 matrix (rows, 512) -> store boxes of [32 rows x 32 columns] = 64-byte rows, 64-byte swizzle (the layout of
-// the chain kernel's per-warp staging buffer).
-static inline int make_store_map(CUtensorMap* m, const void* base, uint64_t rows) {
+// bf16 matrix (rows, cols) -> store boxes of [32 rows x 32 columns] = 64-byte rows, 64-byte swizzle (the layout of
+// the per-warp staging buffers of the chain and rows-GEMM epilogues).
+static inline int make_store_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols = 512) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) { set_error("cuTensorMapEncodeTiled entry point unavailable"); return PN_ERR_CUDA; }
-  cuuint64_t dims[2] = {512, rows};
-  cuuint64_t strides[1] = {1024};
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
   cuuint32_t box[2] = {32, 32};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
