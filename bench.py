@@ -358,7 +358,7 @@ def run_gpu(args):
                          "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
                          "traffic": chain_traffic(flop_step / MLP_FLOP_PER_POINT[ns] / max(1, n_mlp // max(1, args.steps)))
                          if args.precision == "fp16" else None,
-                         "traffic_source": "profiles/r01t_chain_ncu_summary.json: ncu dram read+write bytes per MLP row of "
+                         "traffic_source": "profiles/r01z_chain_ncu_summary.json: ncu dram read+write bytes per MLP row of "
                                            "one captured launch x average rows per launch of this run",
                          "peak_source": pk["source"] + ", sustained bf16",
                          "launches_per_step": n_mlp // max(1, args.steps), "ms_per_step": mlp_ms},
@@ -441,7 +441,7 @@ def run_train(args):
 def chain_traffic(rows_per_launch):
     """DRAM bytes per chain launch: measured bytes/row of the committed `ncu --set full` capture (a live run
     cannot read dram counters) times the rows one launch of this run processes; None without the summary."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01t_chain_ncu_summary.json")
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01z_chain_ncu_summary.json")
     try:
         with open(path) as f:
             return json.load(f)["dram_bytes_per_row"] * rows_per_launch

@@ -111,27 +111,46 @@ head_bwd16_kernel(const uint2* __restrict__ x10, const float4* __restrict__ out,
 #pragma unroll
     for (int j = 0; j < 16; ++j) dwl[k][j] = 0.0f;
   float dbl[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int64_t r = r0 + warp; r < r0 + rows_per_block && r < rows; r += 8) {
-    const float4 o = out[r], go = g_out[r];
-    const float gp[4] = {o.x * (1.0f - o.x) * go.x, o.y * (1.0f - o.y) * go.y, o.z * (1.0f - o.z) * go.z,
-                         o.w > 0.0f ? go.w : 0.0f};
+  // kU rows per warp iteration with every load issued before the first use: one row at a time left 1 KB per warp
+  // in flight (8 KB per SM at this register count) and the kernel at a third of the HBM rate
+  constexpr int kU = 4;
+  const int64_t r_end = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+  for (int64_t rb = r0 + warp; rb < r_end; rb += 8 * kU) {
+    float4 o[kU], go[kU];
+    uint2 xv[kU][4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) dbl[k] += gp[k];
+    for (int u = 0; u < kU; ++u) {
+      const int64_t r = rb + 8 * u;
+      if (r < r_end) {
+        o[u] = out[r];
+        go[u] = g_out[r];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int c = i * 128 + lane * 4;
-      const uint2 xv = __ldg(x10 + (r * 512 + c) / 4);
-      const float hh[4] = {bf_lo(xv.x), bf_hi(xv.x), bf_lo(xv.y), bf_hi(xv.y)};
-      float gh[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float w0 = (&wv[0][i].x)[e], w1 = (&wv[1][i].x)[e], w2 = (&wv[2][i].x)[e], w3 = (&wv[3][i].x)[e];
-        const float g = gp[0] * w0 + gp[1] * w1 + gp[2] * w2 + gp[3] * w3;
-        gh[e] = hh[e] > 0.0f ? g : 0.0f;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) dwl[k][i * 4 + e] += gp[k] * hh[e];
+        for (int i = 0; i < 4; ++i) xv[u][i] = __ldg(x10 + (r * 512 + i * 128 + lane * 4) / 4);
       }
-      g_h16[(r * 512 + c) / 4] = make_uint2(bf2(gh[0], gh[1]), bf2(gh[2], gh[3]));
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t r = rb + 8 * u;
+      if (r >= r_end) break;
+      const float gp[4] = {o[u].x * (1.0f - o[u].x) * go[u].x, o[u].y * (1.0f - o[u].y) * go[u].y,
+                           o[u].z * (1.0f - o[u].z) * go[u].z, o[u].w > 0.0f ? go[u].w : 0.0f};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) dbl[k] += gp[k];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int c = i * 128 + lane * 4;
+        const float hh[4] = {bf_lo(xv[u][i].x), bf_hi(xv[u][i].x), bf_lo(xv[u][i].y), bf_hi(xv[u][i].y)};
+        float gh[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float w0 = (&wv[0][i].x)[e], w1 = (&wv[1][i].x)[e], w2 = (&wv[2][i].x)[e], w3 = (&wv[3][i].x)[e];
+          const float g = gp[0] * w0 + gp[1] * w1 + gp[2] * w2 + gp[3] * w3;
+          gh[e] = hh[e] > 0.0f ? g : 0.0f;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) dwl[k][i * 4 + e] += gp[k] * hh[e];
+        }
+        g_h16[(r * 512 + c) / 4] = make_uint2(bf2(gh[0], gh[1]), bf2(gh[2], gh[3]));
+      }
     }
   }
 #pragma unroll
