@@ -65,10 +65,12 @@ def merge_sorted(z_parts):
     return torch.sort(torch.cat(z_parts, dim=-1), dim=-1)[0]
 
 
-def composite(rgb_sigma, z, rays, white_bkgd):
+def composite(rgb_sigma, z, rays, white_bkgd, sigma_noise=None, noise_std=0.0):
     """Alpha compositing.  src/render/nerf.py:178-182, 221-249.
 
     rgb_sigma (R,K,4) is the model output already reshaped per ray; z (R,K).
+    sigma_noise (R,K): standard normal draws replacing ``torch.randn_like`` at :226 (training
+    with noise_std > 0 only; None = the branch at :225 is not taken).
     Returns (weights (R,K), rgb (R,3), depth (R,)).
     """
     deltas = z[:, 1:] - z[:, :-1]
@@ -76,6 +78,8 @@ def composite(rgb_sigma, z, rays, white_bkgd):
     deltas = torch.cat([deltas, delta_inf], -1)
     rgbs = rgb_sigma[..., :3]
     sigmas = rgb_sigma[..., 3]
+    if sigma_noise is not None and noise_std > 0.0:
+        sigmas = sigmas + sigma_noise * noise_std
     alphas = 1 - torch.exp(-deltas * torch.relu(sigmas))
     shifted = torch.cat([torch.ones_like(alphas[:, :1]), 1 - alphas + 1e-10], -1)
     T = torch.cumprod(shifted, -1)
@@ -95,7 +99,7 @@ def points_and_dirs(rays, z):
 
 
 def render_rays(net_fn, rays, sb, n_coarse, n_fine, n_fine_depth, draws, *,
-                depth_std=0.01, white_bkgd=False, lindisp=False, force=None):
+                depth_std=0.01, white_bkgd=False, lindisp=False, force=None, noise_std=0.0):
     """Whole renderer forward.  src/render/nerf.py:251-303.
 
     net_fn(xyz (SB,P,3), viewdirs (SB,P,3), coarse: bool) -> (SB,P,4)
@@ -116,7 +120,9 @@ def render_rays(net_fn, rays, sb, n_coarse, n_fine, n_fine_depth, draws, *,
         pts, dirs = points_and_dirs(rays, z)
         rs = net_fn(pts.reshape(sb, -1, 3), dirs.reshape(sb, -1, 3), coarse)
         rs = rs.reshape(R, K, 4)
-        return rs, composite(rs, z, rays, white_bkgd)
+        # training with noise_std > 0 (nerf.py:225-226): draws["sigma_noise_coarse" | "sigma_noise_fine"]
+        sn = draws.get("sigma_noise_coarse" if coarse else "sigma_noise_fine") if noise_std > 0.0 else None
+        return rs, composite(rs, z, rays, white_bkgd, sn, noise_std)
 
     z_c = force.get("z_coarse")
     if z_c is None:

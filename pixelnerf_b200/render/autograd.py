@@ -56,6 +56,8 @@ class RenderFunction(torch.autograd.Function):
             ctx.stash, model._train_stash = model._train_stash, None
             renderer._keep_parts = False
         ctx.renderer, ctx.model, ctx.sb = renderer, model, sb
+        noisy = renderer.training and renderer.noise_std > 0.0 and draws is not None
+        ctx.sigma_noise = (draws.get("sigma_noise_coarse"), draws.get("sigma_noise_fine")) if noisy else (None, None)
         ctx.n_params = len(params)
         ctx.has_fine = fine is not None
         ctx.latent_shape = latent.shape
@@ -91,17 +93,18 @@ class RenderFunction(torch.autograd.Function):
             if renderer.depth_sample_grad and z_dep.numel() > 0 and not all(x is None for x in (g[4], g[5], g[6])):
                 g_dep = torch.zeros(rays.shape[0], device=dev, dtype=torch.float32)
             _backward_pass(renderer, model, False, rays, z_f, sb, g[4], g[5], g[6], grads_f, g_lat, stash,
-                           z_dep=z_dep, g_dep=g_dep)
+                           z_dep=z_dep, g_dep=g_dep, sigma_noise=ctx.sigma_noise[1])
             if g_dep is not None:
                 g_depth_c = g_dep if g_depth_c is None else g_depth_c + g_dep
-        _backward_pass(renderer, model, True, rays, z_c, sb, g[0], g[1], g_depth_c, grads_c, g_lat, stash)
+        _backward_pass(renderer, model, True, rays, z_c, sb, g[0], g[1], g_depth_c, grads_c, g_lat, stash,
+                       sigma_noise=ctx.sigma_noise[0])
         flat = [grads_c[k] for k in names] + ([grads_f[k] for k in names] if fine_p else [])
         g_latent = g_lat.permute(0, 3, 1, 2) if want_latent else None
         return (None, None, None, None, None, None, None, g_latent, *flat)
 
 
 def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, grads, g_lat, stash=None,
-                   z_dep=None, g_dep=None):
+                   z_dep=None, g_dep=None, sigma_noise=None):
     """One pass's backward, chunk by chunk.  g_dep (R) / z_dep (R,Kd): fine pass only -- receives the gradient
     the depth-guided sample positions carry to the coarse depth."""
     r_total, k = z.shape
@@ -123,6 +126,11 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
             return None
         return t.reshape(sb, b, *t.shape[1:])[:, s:e].reshape(sb * (e - s), *t.shape[1:]).contiguous()
 
+    def composited(out, s, e):
+        """What the forward composited: the model output, with the forward's sigma noise (nerf.py:225-226)."""
+        rs = out.reshape(-1, k, 4)
+        return rs if sigma_noise is None else renderer.noisy_sigma(rs, cut(sigma_noise, s, e))
+
     want_pos = g_dep is not None
     want_fz = g_lat is not None or want_pos
     w_in = weights["lin_in.weight"]
@@ -142,7 +150,7 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
                 continue
             s, e = ent["range"]
             out, ppo = ent["out"], ent["ppo"]
-            g_rs, g_z = _lib.composite_bwd(out.reshape(-1, k, 4), ent["z"], ent["rays"], renderer.white_bkgd,
+            g_rs, g_z = _lib.composite_bwd(composited(out, s, e), ent["z"], ent["rays"], renderer.white_bkgd,
                                            cut(g_rgb, s, e), cut(g_depth, s, e), cut(g_w, s, e), want_gz=want_pos)
             g_fz, g_h0 = _lib.mlp_backward_tc(packed, w16, ent["fx"], latent, sb, ns, ppo, ent["acts"], out,
                                               g_rs.reshape(-1, 4), grads, want_g_feat_z=want_fz, want_g_h0=True)
@@ -165,7 +173,7 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
             # forward chain on the tensor cores keeping its bf16 GEMM operands, then dgrad / wgrad GEMMs on them
             fx = _lib.point_taps(cam, hl, wl, ppo, rays=rr, z=zz)
             out, acts = _lib.mlp_forward_tc_train(packed_tc, tables, fx, sb, ns, ppo)
-            g_rs, g_z = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
+            g_rs, g_z = _lib.composite_bwd(composited(out, s, e), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
                                            cut(g_depth, s, e), cut(g_w, s, e), want_gz=want_pos)
             g_fz, g_h0 = _lib.mlp_backward_tc(packed, w16, fx, latent, sb, ns, ppo, acts, out, g_rs.reshape(-1, 4),
                                               grads, want_g_feat_z=want_fz, want_g_h0=True)
@@ -176,7 +184,7 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
             continue
         fz, fx = _lib.point_features(cam, latent, ppo, rays=rr, z=zz, ldx=44)
         out, acts = _lib.mlp_forward_fp32_train(packed, fz, fx, sb, ns, ppo)
-        g_rs, g_z = _lib.composite_bwd(out.reshape(-1, k, 4), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
+        g_rs, g_z = _lib.composite_bwd(composited(out, s, e), zz, rr, renderer.white_bkgd, cut(g_rgb, s, e),
                                        cut(g_depth, s, e), cut(g_w, s, e), want_gz=want_pos)
         g_fz, g_h0 = _lib.mlp_backward_fp32(packed, weights, fz, fx, sb, ns, ppo, acts, out, g_rs.reshape(-1, 4),
                                             grads, want_g_feat_z=want_fz, want_g_h0=True)

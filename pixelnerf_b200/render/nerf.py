@@ -106,26 +106,32 @@ class NeRFRenderer(torch.nn.Module):
         return z_dep
 
     # --------------------------------------------------------------- composite
-    def composite(self, model, rays, z_samp, coarse=True, sb=0):
+    def noisy_sigma(self, rgbs, sigma_noise):
+        """sigmas + randn * noise_std in training mode (reference nerf.py:225-226); rgbs (B,K,4), draws (B,K)."""
+        rgbs = rgbs.clone()
+        rgbs[..., 3].add_(sigma_noise, alpha=float(self.noise_std))
+        return rgbs
+
+    def composite(self, model, rays, z_samp, coarse=True, sb=0, sigma_noise=None):
         """Model evaluation + alpha compositing.  Reference nerf.py:163-249.
-        rays (B,8), z_samp (B,K) -> weights (B,K), rgb (B,3), depth (B)."""
-        if self.training and self.noise_std > 0.0:
-            raise NotImplementedError("sigma noise (noise_std > 0) is unused by every shipped conf")
+        rays (B,8), z_samp (B,K) -> weights (B,K), rgb (B,3), depth (B).  sigma_noise (B,K): the standard normal
+        draws of nerf.py:226 when training with noise_std > 0 (drawn here if not given)."""
         b, k = z_samp.shape
         n_obj = max(sb, 1)
-        rgbs = model.run_points(coarse, (b // n_obj) * k, rays=rays, z=z_samp)
-        return _lib.composite_fwd(rgbs.reshape(b, k, 4), z_samp, rays, self.white_bkgd)
+        rgbs = model.run_points(coarse, (b // n_obj) * k, rays=rays, z=z_samp).reshape(b, k, 4)
+        if self.training and self.noise_std > 0.0:
+            rgbs = self.noisy_sigma(rgbs, torch.randn_like(z_samp) if sigma_noise is None else sigma_noise)
+        return _lib.composite_fwd(rgbs, z_samp, rays, self.white_bkgd)
 
     # ----------------------------------------------------------------- forward
     def _fused_ok(self, model, forced):
         """The whole chunk can go through pn_render_rays: tensor-core MLP, nothing teacher-forced, and no
         training forward that has to keep intermediates for the backward."""
         return (model.mlp_precision != "fp32" and not forced and not self._keep_parts
+                and not (self.training and self.noise_std > 0.0)
                 and getattr(model, "_train_stash", None) is None and os.environ.get("PIXELNERF_B200_STAGED") != "1")
 
     def _render_fused(self, model, rays, draws, seed):
-        if self.training and self.noise_std > 0.0:
-            raise NotImplementedError("sigma noise (noise_std > 0) is unused by every shipped conf")
         if model._cam is None:
             raise RuntimeError("call encode() before forward()")
         prec = model.mlp_precision
@@ -148,7 +154,7 @@ class NeRFRenderer(torch.nn.Module):
         z_c = forced.get("z_coarse")
         if z_c is None:
             z_c = _lib.sample_coarse(rays, self.n_coarse, self.lindisp, u=d.get("u_coarse"), seed=seed)
-        coarse = self.composite(model, rays, z_c, coarse=True, sb=sb)
+        coarse = self.composite(model, rays, z_c, coarse=True, sb=sb, sigma_noise=d.get("sigma_noise_coarse"))
         fine = None
         if self.using_fine:
             n_dep = self.n_fine_depth
@@ -163,7 +169,8 @@ class NeRFRenderer(torch.nn.Module):
                     z_f, _, z_dep = z_f
             if z_dep is None:   # teacher-forced z_fine without its depth samples: nothing to differentiate
                 z_dep = z_f.new_zeros(z_f.shape[0], 0)
-            fine = self.composite(model, rays, z_f, coarse=False, sb=sb) + (z_f, z_dep)
+            fine = self.composite(model, rays, z_f, coarse=False, sb=sb,
+                                  sigma_noise=d.get("sigma_noise_fine")) + (z_f, z_dep)
         return coarse + (z_c,), fine
 
     def _render_all(self, model, rays, sb, draws, forced, seed):
@@ -208,7 +215,14 @@ class NeRFRenderer(torch.nn.Module):
         rays = rays.reshape(-1, 8).float().contiguous()
         draws, forced = self.injected_draws, self.injected_z or {}
         self.injected_draws, self.injected_z = None, None
-        seed = 0 if draws else self._seed()
+        seed = 0 if (draws and "u_coarse" in draws) else self._seed()
+        if self.training and self.noise_std > 0.0:
+            # sigma noise (nerf.py:225-226): drawn once per call so that the backward sees the forward's draws
+            draws = dict(draws or {})
+            if "sigma_noise_coarse" not in draws:
+                draws["sigma_noise_coarse"] = torch.randn(rays.shape[0], self.n_coarse, device=rays.device)
+            if self.using_fine and "sigma_noise_fine" not in draws:
+                draws["sigma_noise_fine"] = torch.randn(rays.shape[0], self.n_coarse + self.n_fine, device=rays.device)
         latent = model.encoder.latent
         if model.stop_encoder_grad:
             latent = latent.detach()

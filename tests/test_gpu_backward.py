@@ -56,7 +56,7 @@ def test_mlp_backward_vs_autograd(ns, ppo, sb):
 
 
 def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, stash=True, depth_grad=True,
-                        fine_only=False):
+                        fine_only=False, noise_std=0.0):
     """loss = <coarse rgb, Gc> + <fine rgb, Gf> + <coarse weights, Gw>: gradients w.r.t. both MLPs' parameters
     and the encoder latent, through the public NeRFRenderer API.  Returns (loss, reference loss, {tensor name:
     max abs gradient error / largest reference gradient entry})."""
@@ -74,6 +74,11 @@ def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, sta
     rays = sc["rays"][torch.linspace(0, sc["rays"].shape[0] - 1, n_rays).long()]
     draws = syn.draws(9, n_rays, 64, 16, 16)
     g = torch.Generator().manual_seed(3)
+    if noise_std > 0.0:   # training-mode sigma noise (nerf.py:225-226) with injected draws
+        ren.train()
+        ren.noise_std = noise_std
+        draws["sigma_noise_coarse"] = torch.randn(n_rays, 64, generator=g)
+        draws["sigma_noise_fine"] = torch.randn(n_rays, 96, generator=g)
     gc, gf = torch.randn(n_rays, 3, generator=g), torch.randn(n_rays, 3, generator=g)
     gw = torch.randn(n_rays, 64, generator=g) * 0.1
     if positive:    # upstream gradients of one sign: the parameter gradients are then non-cancelling sums
@@ -116,7 +121,7 @@ def run_render_backward(scene, n_rays, mlp_precision="fp32", positive=False, sta
     torch.set_default_dtype(torch.float64)
     try:
         ref = oracle.render_rays(net_fn, rays.double(), 1, 64, 32, 16, {k: v.double() for k, v in draws.items()},
-                                 white_bkgd=sc["white"], force=force)
+                                 white_bkgd=sc["white"], force=force, noise_std=noise_std)
         loss_ref = (ref["rgb_coarse"] * gc).sum() + (ref["rgb_fine"] * gf).sum() + (ref["w_coarse"] * gw).sum()
         loss_ref.backward()
     finally:
@@ -156,6 +161,45 @@ def test_depth_sample_gradient_reaches_coarse_mlp(scene, n_rays):
     vals = sorted(coarse.values())
     assert vals[-1] < 2e-2, coarse
     assert vals[len(vals) // 2] < 5e-3, coarse
+
+
+@pytest.mark.parametrize("precision,stash", [("fp32", True), ("fp16", True), ("fp16", False)])
+def test_sigma_noise_training_mode(precision, stash):
+    """noise_std > 0 in training mode (nerf.py:225-226): the forward composites sigma + noise * std and the backward
+    differentiates exactly that (same injected draws on both sides), on every backward variant."""
+    tc = precision != "fp32"   # tensor-core path: same regime as test_gpu_backward_tc (one-signed upstream, no depth term)
+    loss0, _, _ = run_render_backward("sn64", 96, mlp_precision=precision, stash=stash, positive=tc, depth_grad=not tc)
+    loss, loss_ref, worst = run_render_backward("sn64", 96, mlp_precision=precision, stash=stash, noise_std=1.0,
+                                                positive=tc, depth_grad=not tc)
+    assert abs(loss - loss_ref) < (2e-3 if tc else 1e-3) * max(1.0, abs(loss_ref))
+    assert abs(loss - loss0) > 1e-2   # the noise really changed the render
+    vals = sorted(worst.values())
+    if tc:
+        assert vals[-1] < 2e-2 and vals[len(vals) // 2] < 1e-2, worst
+    else:
+        assert vals[-1] < 1e-2 and vals[len(vals) // 2] < REL, worst
+
+
+def test_sigma_noise_only_in_training_mode_and_eval_is_fused():
+    dev = torch.device("cuda")
+    sc = syn.scene("sn64")
+    net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), dev, mlp_precision="fp16")
+    ren.noise_std = 1.0
+    rays = sc["rays"][:64].to(dev)[None]
+    d = {k: v.to(dev) for k, v in syn.draws(4, 64, 64, 16, 16).items()}
+    with torch.no_grad():
+        ren.injected_draws = dict(d)
+        a = ren(net, rays)
+        ren.noise_std = 0.0
+        ren.injected_draws = dict(d)
+        b = ren(net, rays)
+        assert torch.equal(a.fine.rgb, b.fine.rgb)          # eval mode: the branch at nerf.py:225 is not taken
+        ren.train()
+        ren.noise_std = 1.0
+        ren.injected_draws = dict(d)
+        c = ren(net, rays)
+        assert not torch.equal(c.coarse.rgb, a.coarse.rgb)  # training mode without gradients: noisy too
+    ren.eval()
 
 
 def test_detached_sample_positions_option():
