@@ -107,3 +107,36 @@ def test_fused_wrapper_empty_and_c_abi_errors():
             _lib.render_rays(net._cam, sc["hl"], sc["wl"], mc, None, sc["rays"][:64].cuda(), 64, 16, 16, 0.01, False, True)
         finally:
             _lib._lib.pn_render_rays_workspace_bytes = real
+
+
+@pytest.mark.parametrize("prec,tol", [("fp32", 1e-4), ("fp16", 2e-3)])
+def test_eval_override_64_coarse_128_fine(prec, tol, monkeypatch):
+    """The sampling resolution the reference's eval scripts switch to after construction (eval/eval_approx.py:79-82,
+    eval/gen_video.py:192-195): n_coarse = 64, n_fine = 128 (112 importance + 16 depth samples, K2 = 192: the 256-wide
+    sort and the 32-lane composite).  Stage-wise against the oracle: fine sampling fed the oracle's coarse weights and
+    depth must reproduce its 192 sorted positions bit for bit, both passes within the path's tolerance."""
+    from pixelnerf_b200.testing import oracle_render
+    sc = syn.scene("sn64")
+    wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
+    n = 300
+    rays = sc["rays"][torch.linspace(0, 4095, n).long()]
+    draws = syn.draws(8, n, 64, 112, 16)
+    ref = oracle_render(sc, wc, wf, rays, draws, 64, 128, 16)
+    net, ren = build_net(sc, wc, wf, torch.device("cuda"), mlp_precision=prec)
+    ren.n_fine, ren.using_fine = 128, True
+    d = {k: v.cuda() for k, v in draws.items()}
+    ren.injected_draws = dict(d)
+    ren.injected_z = dict(w_coarse=ref["w_coarse"].cuda(), depth_coarse=ref["depth_coarse"].cuda())
+    with torch.no_grad():
+        out = ren(net, rays[None].cuda(), want_weights=True)
+    z_c, z_f = ren.last_z
+    assert torch.equal(z_c[0].cpu(), ref["z_coarse"]) and torch.equal(z_f[0].cpu(), ref["z_fine"])
+    assert out.fine.weights.shape == (1, n, 192)
+    span = float((rays[:, 7] - rays[:, 6]).max())
+    for part, key in (("coarse", "coarse"), ("fine", "fine")):
+        assert (out[part].rgb[0].cpu() - ref[f"rgb_{key}"]).abs().max().item() < tol
+        assert (out[part].weights[0].cpu() - ref[f"w_{key}"]).abs().max().item() < tol
+        assert (out[part].depth[0].cpu() - ref[f"depth_{key}"]).abs().max().item() < (4e-4 if prec == "fp32" else tol * max(1.0, span))
+    if prec == "fp16":   # and the one-call path equals the staged one at this resolution too
+        a, b = _both(ren, net, rays[None].cuda(), d, monkeypatch)
+        _same(a, b)
