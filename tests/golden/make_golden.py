@@ -142,9 +142,22 @@ def build_reference_net(ConfigTree, make_model, conf, wc, wf):
     return net.eval()
 
 
+GRAD_SUB = 16   # stride of the subsample kept of every 512 x 512 gradient (32 x 32 entries)
+
+
+def sub_grad(name, g):
+    """What a grad_*.npz fixture keeps of one gradient tensor: small tensors whole, 512 x 512 matrices strided."""
+    g = g.detach()
+    if g.dim() == 2 and g.shape[0] == 512 and g.shape[1] == 512:
+        return g[::GRAD_SUB, ::GRAD_SUB].contiguous().numpy()
+    return g.numpy()
+
+
 def case_render(name, ConfigTree, make_model, NeRFRenderer, *, h, w, ns, sb, n_rays, seed, focal, c,
-                near_far, white, lindisp, hl=None, wl=None, per_ray_bounds=False):
-    """One full coarse+fine reference render on a synthetic scene; returns the fixture dict."""
+                near_far, white, lindisp, hl=None, wl=None, per_ray_bounds=False, with_grad=False):
+    """One full coarse+fine reference render on a synthetic scene; returns the fixture dict.  with_grad: also the
+    reference's own autograd gradients of the training loss (train/train.py:264-281: MSE of the coarse and of the
+    fine rgb against a target) w.r.t. both MLPs' parameters and the encoder latent."""
     from pixelnerf_b200 import synthetic as syn
     conf = reference_conf(ConfigTree, use_first_pool=not (h == 64 and w == 64), white_bkgd=white)
     wc, wf = syn.mlp_weights(seed + 1), syn.mlp_weights(seed + 2)
@@ -201,6 +214,28 @@ def case_render(name, ConfigTree, make_model, NeRFRenderer, *, h, w, ns, sb, n_r
         fx["probe_xyz"], fx["probe_dirs"] = pts.numpy(), dirs.numpy()
         fx["probe_coarse"] = net(pts, coarse=True, viewdirs=dirs).numpy()
         fx["probe_fine"] = net(pts, coarse=False, viewdirs=dirs).numpy()
+    if with_grad:
+        tgt = torch.from_numpy(g.random((sb, n_rays, 3), dtype=np.float32))
+        lat_leaf = lat.clone().requires_grad_(True)
+        net.encoder.latent = lat_leaf
+        for q in net.parameters():
+            q.requires_grad_(True)
+            q.grad = None
+        renderer.train()
+        with DrawInjector([d["u_coarse"], d["u_bin"], d["u_in"], d["noise"]]):
+            o2 = renderer.bind_parallel(net, [0], simple_output=False)(rays, want_weights=True)
+        crit = torch.nn.MSELoss()
+        loss = crit(o2["coarse"]["rgb"], tgt) + crit(o2["fine"]["rgb"], tgt)   # lambda_coarse = lambda_fine = 1
+        loss.backward()
+        fx["target_rgb"] = tgt.numpy()
+        fx["loss"] = np.float64(loss.item())
+        for prefix, mlp in (("mlp_coarse", net.mlp_coarse), ("mlp_fine", net.mlp_fine)):
+            for k, q in mlp.named_parameters():
+                fx[f"g.{prefix}.{k}"] = sub_grad(k, q.grad)
+                fx[f"gmax.{prefix}.{k}"] = np.float64(q.grad.abs().max().item())
+        fx["g.latent"] = lat_leaf.grad[:, ::16, ::4, ::4].contiguous().numpy()
+        fx["gmax.latent"] = np.float64(lat_leaf.grad.abs().max().item())
+        renderer.eval()
     sw = float(out["fine"]["weights"].sum(-1).mean())
     print(f"{name}: R={R} mean sum(w_fine)={sw:.3f} rgb_fine mean={float(out['fine']['rgb'].mean()):.3f} "
           f"sum(w) range [{float(out['fine']['weights'].sum(-1).min()):.3f}, {float(out['fine']['weights'].sum(-1).max()):.3f}]")
@@ -238,6 +273,10 @@ def case_sampling(NeRFRenderer, n_coarse, lindisp, seed, n_rays=1024):
 def main():
     torch.manual_seed(0)
     ConfigTree, make_model, NeRFRenderer = load_reference()
+    args = (ConfigTree, make_model, NeRFRenderer)
+    if "--grad-only" in sys.argv:   # the grad_*.npz fixtures alone (the render/sampling ones are left untouched)
+        grad_cases(args)
+        return
     for kc, lindisp in ((64, False), (64, True), (128, False), (48, False), (96, True)):
         fx = case_sampling(NeRFRenderer, kc, lindisp, seed=100 + kc + int(lindisp))
         np.savez_compressed(os.path.join(HERE, f"sampling_k{kc}_{'disp' if lindisp else 'lin'}.npz"), **fx)
@@ -254,6 +293,21 @@ def main():
     ]
     for fx in cases:
         np.savez_compressed(os.path.join(HERE, f"render_{fx['name']}.npz"), **fx)
+    grad_cases(args)
+
+
+def grad_cases(args):
+    """Forward fixture + the reference's autograd gradients: NS=2 (view-mean backward) and the
+    two-object NS=3 lindisp case with per-ray bounds."""
+    cases = [
+        case_render("srn128_ns2", *args, h=128, w=128, ns=2, sb=1, n_rays=64, seed=2000, focal=131.25, c=None,
+                    near_far=(1.25, 2.75), white=True, lindisp=False, with_grad=True),
+        case_render("dtu_ns3_sb2", *args, h=60, w=80, ns=3, sb=2, n_rays=40, seed=3000,
+                    focal=[[140.0, 150.0], [150.0, 140.0]], c=[[41.0, 29.0], [39.5, 30.5]],
+                    near_far=(1.0, 3.2), white=False, lindisp=True, per_ray_bounds=True, with_grad=True),
+    ]
+    for fx in cases:
+        np.savez_compressed(os.path.join(HERE, f"grad_{fx['name']}.npz"), **fx)
 
 
 if __name__ == "__main__":

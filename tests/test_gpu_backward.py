@@ -3,6 +3,7 @@ over the CPU oracle, i.e. against what the reference's ``loss.backward()`` compu
 (train/train.py:271-281) on identical inputs.  Sample positions are teacher-forced constants on both
 sides (render/autograd.py explains the one deliberate deviation).  Tolerance: 1e-3 of the largest
 gradient entry of each tensor (fp32 sums of up to ~10^5 terms in a different order, atomics)."""
+import numpy as np
 import pytest
 import torch
 
@@ -10,6 +11,7 @@ import oracle
 from oracle import model as omodel
 from pixelnerf_b200 import _lib, synthetic as syn
 from pixelnerf_b200.testing import build_net, scene_camera
+from helpers import golden_files, load, render_case_inputs
 
 pytestmark = pytest.mark.gpu
 REL = 1e-3
@@ -226,3 +228,47 @@ def test_stop_encoder_grad_and_eval_need_no_graph():
     with torch.no_grad():
         out = ren(net, rays)
     assert not out.fine.rgb.requires_grad
+
+
+@pytest.mark.parametrize("precision", ["fp32", "fp16"])
+@pytest.mark.parametrize("path", golden_files("grad_"))
+def test_render_backward_vs_reference_golden(path, precision):
+    """The hand-written backward against the LIVE reference's own loss.backward() (tests/golden/grad_*.npz, made by
+    make_golden.py from /root/reference): training loss of train/train.py:264-281 through NeRFRenderer in train
+    mode, NS = 2 and the two-object NS = 3 lindisp case with per-ray bounds.  The fine sampler is fed the reference's
+    coarse weights and depth (teacher forcing, SURVEY section 7 hard part 12) so both sides differentiate the same
+    sample positions; the depth-guided samples still hand their gradient to the coarse pass."""
+    from test_gpu_model import _net_for
+    from test_oracle_golden import grad_subsample
+    fx = load(path)
+    inp = render_case_inputs(fx)
+    net, ren = _net_for(fx, inp, precision=precision)
+    dev = torch.device("cuda")
+    lat = inp["latent"].to(dev).clone().requires_grad_(True)
+    net.encoder.latent = lat
+    net._refresh_camera()
+    for p in net.parameters():
+        p.requires_grad_(True)
+    ren.train()
+    ren.injected_draws = {k: v.to(dev) for k, v in inp["draws"].items()}
+    ren.injected_z = dict(w_coarse=torch.from_numpy(fx["w_coarse"]).reshape(-1, 64).to(dev),
+                          depth_coarse=torch.from_numpy(fx["depth_coarse"]).reshape(-1).to(dev))
+    out = ren(net, inp["rays"].to(dev), want_weights=True)
+    tgt = torch.from_numpy(fx["target_rgb"]).to(dev)
+    loss = ((out.coarse.rgb - tgt) ** 2).mean() + ((out.fine.rgb - tgt) ** 2).mean()
+    loss.backward()
+    tc = precision != "fp32"
+    assert abs(loss.item() - float(fx["loss"])) < (2e-3 if tc else 1e-5) * max(1.0, float(fx["loss"]))
+    sd = dict(net.named_parameters())
+    worst = {}
+    for prefix in ("mlp_coarse", "mlp_fine"):
+        for k in _lib.weight_names():
+            got = grad_subsample(sd[f"{prefix}.{k}"].grad).cpu().numpy()
+            worst[f"{prefix}.{k}"] = np.abs(got - fx[f"g.{prefix}.{k}"]).max() / max(float(fx[f"gmax.{prefix}.{k}"]), 1e-12)
+    worst["latent"] = np.abs(lat.grad[:, ::16, ::4, ::4].cpu().numpy() - fx["g.latent"]).max() / float(fx["gmax.latent"])
+    vals = sorted(worst.values())
+    print({k: f"{v:.1e}" for k, v in sorted(worst.items(), key=lambda kv: -kv[1])[:6]})
+    if tc:   # bf16 gradients, fp16-operand forward (DESIGN 4b); measured worst tensor 1.3e-2
+        assert vals[-1] < 3e-2 and vals[len(vals) // 2] < 1.5e-2, worst
+    else:    # measured worst tensor 2.8e-4 of its largest entry
+        assert vals[-1] < 1e-3 and vals[len(vals) // 2] < 3e-4, worst

@@ -63,3 +63,53 @@ def test_render_matches_reference(path):
     np.testing.assert_allclose(out["rgb_fine"].reshape(*shp, 3).numpy(), fx["rgb_fine"], rtol=0, atol=1e-5)
     np.testing.assert_allclose(out["w_fine"].reshape(*shp, -1).numpy(), fx["w_fine"], rtol=0, atol=1e-5)
     np.testing.assert_allclose(out["depth_fine"].reshape(shp).numpy(), fx["depth_fine"], rtol=0, atol=1e-5)
+
+
+def grad_subsample(g):
+    """The part of a gradient tensor the grad_*.npz fixtures keep (tests/golden/make_golden.py: sub_grad)."""
+    if g.dim() == 2 and g.shape[0] == 512 and g.shape[1] == 512:
+        return g[::16, ::16]
+    return g
+
+
+def grad_case_loss(fx, inp, out):
+    """train/train.py:264-281 with lambda_coarse = lambda_fine = 1: MSE of both passes' rgb against the target."""
+    tgt = torch.from_numpy(fx["target_rgb"]).reshape(-1, 3).to(out["rgb_coarse"].dtype)
+    return ((out["rgb_coarse"] - tgt) ** 2).mean() + ((out["rgb_fine"] - tgt) ** 2).mean()
+
+
+@pytest.mark.parametrize("path", golden_files("grad_"))
+def test_gradients_match_reference_autograd(path):
+    """autograd over the oracle reproduces the LIVE reference's own loss.backward() -- parameters of
+    both MLPs and the encoder latent, through compositing, the view mean, the bilinear gather and the depth-guided
+    sample positions.  Stratified and importance positions are the reference's (recomputed bit-exactly from its
+    coarse weights, which the pinned sampler reproduces); the depth samples stay a function of the coarse depth."""
+    fx = load(path)
+    inp = render_case_inputs(fx)
+    sb, ns = inp["sb"], inp["ns"]
+    rays = inp["rays"].reshape(-1, 8)
+    wc = {k: v.clone().requires_grad_(True) for k, v in inp["wc"].items()}
+    wf = {k: v.clone().requires_grad_(True) for k, v in inp["wf"].items()}
+    lat = inp["latent"].clone().requires_grad_(True)
+
+    def net_fn(xyz, dirs, coarse):
+        return omodel.net_forward(wc if coarse else wf, lat, inp["cam"], ns, xyz, dirs)
+
+    d = inp["draws"]
+    z_c = oracle.sample_coarse(rays, 64, d["u_coarse"], inp["lindisp"])
+    z_i, _ = oracle.sample_fine(rays, torch.from_numpy(fx["w_coarse"]).reshape(-1, 64), 64, d["u_bin"], d["u_in"],
+                                inp["lindisp"])
+    out = oracle.render_rays(net_fn, rays, sb, 64, 32, 16, d, depth_std=0.01, white_bkgd=inp["white"],
+                             lindisp=inp["lindisp"], force=dict(z_coarse=z_c, z_imp=z_i))
+    loss = grad_case_loss(fx, inp, out)
+    assert abs(loss.item() - float(fx["loss"])) < 1e-5 * max(1.0, float(fx["loss"]))
+    loss.backward()
+    worst = {}
+    for prefix, w in (("mlp_coarse", wc), ("mlp_fine", wf)):
+        for k, q in w.items():
+            ref = fx[f"g.{prefix}.{k}"]
+            got = grad_subsample(q.grad).numpy()
+            worst[f"{prefix}.{k}"] = np.abs(got - ref).max() / max(float(fx[f"gmax.{prefix}.{k}"]), 1e-12)
+    worst["latent"] = np.abs(lat.grad[:, ::16, ::4, ::4].numpy() - fx["g.latent"]).max() / float(fx["gmax.latent"])
+    bad = {k: v for k, v in worst.items() if v > 2e-4}
+    assert not bad, bad
