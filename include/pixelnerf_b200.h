@@ -201,6 +201,12 @@ PN_API size_t pn_mlp_tc_packed_bytes(void);
 PN_API size_t pn_latent_tables_bytes(int64_t n_texels);
 PN_API int pn_prepare_latent_tables(const pn_mlp_weights_t* w, const float* latent_nhwc, int64_t n_texels,
                              void* tables, void* workspace, size_t workspace_bytes, pn_stream_t stream);
+/* The same tables computed on the tensor cores, for training mode where they are rebuilt every step: latent_nhwc_f16
+ * is the fp16 channels-last latent, lin_z weights enter as fp16 hi + lo pairs (two GEMMs per layer, fp32 sums).
+ * workspace: pn_latent_tables_tc_workspace_bytes(n_texels), 256-byte aligned. */
+PN_API size_t pn_latent_tables_tc_workspace_bytes(int64_t n_texels);
+PN_API int pn_prepare_latent_tables_tc(const pn_mlp_weights_t* w, const void* latent_nhwc_f16, int64_t n_texels,
+                                void* tables, void* workspace, size_t workspace_bytes, pn_stream_t stream);
 PN_API int pn_prepare_weights(const pn_mlp_weights_t* w, void* packed, size_t packed_bytes, pn_stream_t stream);
 
 typedef struct pn_mlp_tc_debug {

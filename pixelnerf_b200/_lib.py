@@ -91,6 +91,8 @@ _SIGNATURES = {
     "pn_point_taps": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp]),
     "pn_latent_tables_bytes": (_sz, [_i64]),
     "pn_prepare_latent_tables": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp, _sz, _vp]),
+    "pn_latent_tables_tc_workspace_bytes": (_sz, [_i64]),
+    "pn_prepare_latent_tables_tc": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp, _sz, _vp]),
     "pn_composite_fwd": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "pn_composite_bwd": (_int, [_vp] * 8 + [_i64, _int, _int, _vp]),
     "pn_mlp_tc_acts_bytes": (_sz, [_i64]),
@@ -380,14 +382,24 @@ def point_taps(cam_bufs, hl, wl, ppo, *, rays=None, z=None, xyz=None, viewdirs=N
 
 
 def prepare_latent_tables(w, latent_nhwc):
-    """Per-texel lin_z tables (3, V*Hl*Wl, 512) fp16 of one MLP for the tensor-core chain; fp32 NHWC latent."""
-    if latent_nhwc.dtype != torch.float32:
-        raise RuntimeError("prepare_latent_tables needs the fp32 channels-last latent")
+    """Per-texel lin_z tables (3, V*Hl*Wl, 512) fp16 of one MLP for the tensor-core chain.  fp32 NHWC latent: the
+    fp32 CUDA-core product (once per encode: inference); fp16 NHWC latent: the tensor-core product with hi + lo
+    weights (training mode, where the tables are rebuilt every step)."""
     s, keep = pack_weights_fp32(w)
     v, hl, wl, ch = latent_nhwc.shape
     n_tex = v * hl * wl
     dev = latent_nhwc.device
     tables = torch.empty(COMBINE_LAYER, n_tex, D_HIDDEN, device=dev, dtype=torch.float16)
+    if latent_nhwc.dtype == torch.float16:
+        nbytes = lib().pn_latent_tables_tc_workspace_bytes(n_tex)
+        ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+        with _Timed("tables"):
+            _check(lib().pn_prepare_latent_tables_tc(C.byref(s), _ptr(latent_nhwc, torch.float16), n_tex,
+                                                     tables.data_ptr(), ws.data_ptr(), nbytes, _stream()),
+                   "pn_prepare_latent_tables_tc")
+        return tables
+    if latent_nhwc.dtype != torch.float32:
+        raise RuntimeError("prepare_latent_tables needs the fp32 or fp16 channels-last latent")
     ws = torch.empty(n_tex * D_HIDDEN, device=dev, dtype=torch.float32)
     _check(lib().pn_prepare_latent_tables(C.byref(s), latent_nhwc.data_ptr(), n_tex, tables.data_ptr(), ws.data_ptr(),
                                           ws.numel() * 4, _stream()), "pn_prepare_latent_tables")

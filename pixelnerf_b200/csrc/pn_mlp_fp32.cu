@@ -471,6 +471,70 @@ extern "C" int pn_prepare_latent_tables(const pn_mlp_weights_t* w, const float* 
   return PN_OK;
 }
 
+// Training mode rebuilds the tables every step (the lin_z weights change): the same product on the tensor cores.
+// latent16 = the fp16 channels-last latent; lin_z[b].weight enters as an fp16 pair hi + lo * 2^-10 (two GEMMs into
+// the fp32 workspace), so the one coherent error source of DESIGN 3.1 -- weight rounding -- stays out of the tables;
+// the latent's own fp16 rounding is independent per texel.
+extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
+                               const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16,
+                               void* out_bf16, float scale, float* colsum0, float* colsum1,
+                               unsigned int* err_word, pn_stream_t stream);
+namespace pn {
+// dst[(2 b + part)][in][out] = fp16 hi (part 0) / (W - hi) * 2^10 (part 1) of lin_z[b].weight[out][in]
+__global__ void __launch_bounds__(256)
+wz_transpose16_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const float* src = w.lin_z_w[b];
+  const int o0 = blockIdx.y * 32, i0 = blockIdx.x * 32;
+  for (int r = threadIdx.y; r < 32; r += 8) tile[r][threadIdx.x] = src[(size_t)(o0 + r) * 512 + i0 + threadIdx.x];
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const float v = tile[threadIdx.x][r];           // W[o0 + tx][i0 + r]
+    const __half hi = __float2half_rn(v);
+    const size_t at = (size_t)(i0 + r) * 512 + o0 + threadIdx.x;
+    dst[(size_t)(2 * b) * 512 * 512 + at] = hi;
+    dst[(size_t)(2 * b + 1) * 512 * 512 + at] = __float2half_rn((v - __half2float(hi)) * 1024.0f);
+  }
+}
+}  // namespace pn
+
+extern "C" size_t pn_latent_tables_tc_workspace_bytes(int64_t n_texels) {
+  return (size_t)(n_texels > 0 ? n_texels : 0) * PN_D_HIDDEN * sizeof(float) + (size_t)6 * 512 * 512 * sizeof(__half) + 256;
+}
+
+extern "C" int pn_prepare_latent_tables_tc(const pn_mlp_weights_t* w, const void* latent_nhwc_f16, int64_t n_texels,
+                                           void* tables, void* workspace, size_t workspace_bytes,
+                                           pn_stream_t stream) {
+  using namespace pn;
+  PN_CHECK_ARG(w && latent_nhwc_f16 && tables && workspace, "pn_prepare_latent_tables_tc: null pointer");
+  PN_CHECK_ARG(n_texels > 0, "pn_prepare_latent_tables_tc: no texels");
+  PN_CHECK_ARG(workspace_bytes >= pn_latent_tables_tc_workspace_bytes(n_texels), "pn_prepare_latent_tables_tc: workspace too small");
+  PN_CHECK_ARG(((uintptr_t)tables & 15) == 0 && ((uintptr_t)workspace & 255) == 0 && ((uintptr_t)latent_nhwc_f16 & 15) == 0,
+               "pn_prepare_latent_tables_tc: misaligned buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  __half* wt = (__half*)workspace;
+  float* tmp = (float*)((char*)workspace + (size_t)6 * 512 * 512 * sizeof(__half));
+  wz_transpose16_kernel<<<dim3(16, 16, PN_COMBINE_LAYER), dim3(32, 8), 0, st>>>(*w, wt);
+  PN_LAUNCH_OK("wz_transpose16_kernel");
+  count_launch();
+  const int64_t total4 = n_texels * (PN_D_HIDDEN / 4);
+  int rc;
+  for (int b = 0; b < PN_COMBINE_LAYER; ++b) {
+    const __half* hi = wt + (size_t)(2 * b) * 512 * 512;
+    if ((rc = pn_gemm_tc_rows(latent_nhwc_f16, 0, hi, 0, n_texels, 512, 512, nullptr, tmp, 0, nullptr, nullptr, 1.0f,
+                              nullptr, nullptr, nullptr, stream))) return rc;
+    if ((rc = pn_gemm_tc_rows(latent_nhwc_f16, 0, hi + 512 * 512, 0, n_texels, 512, 512, nullptr, tmp, 1, nullptr, nullptr,
+                              1.0f / 1024.0f, nullptr, nullptr, nullptr, stream))) return rc;
+    const float* folded = b == 0 ? w->lin_in_b : w->fc1_b[b - 1];
+    table_finish_kernel<<<ceil_div(total4, 256), 256, 0, st>>>(
+        (const float4*)tmp, w->lin_z_b[b], folded, (uint2*)tables + (size_t)b * total4, total4);
+    PN_LAUNCH_OK("table_finish_kernel");
+    count_launch();
+  }
+  return PN_OK;
+}
+
 // ---- training: forward that keeps every activation, and the hand-written backward ------------
 // Activation slots (each n_rows x 512 fp32): slot 2b = H_b (input of block b: residual stream after
 // lin_z[b] / the view mean), slot 2b+1 = T_b (fc_0 output, pre-relu), slot 10 = H_5 (input of lin_out).

@@ -123,8 +123,9 @@ class PixelNeRFNet(torch.nn.Module):
     def latent_nhwc(self, dtype):
         """Channels-last copy of encoder.latent in `dtype`, made once per encode()."""
         lat = self.encoder.latent
-        key = (dtype, lat.data_ptr(), lat._version)
-        if self._latent_nhwc.get("key") != key:
+        key = (lat.data_ptr(), lat._version, tuple(lat.shape))
+        hit = self._latent_nhwc.get(dtype)
+        if hit is None or hit[0] != key:
             src = lat.detach()
             nhwc = src.permute(0, 2, 3, 1)
             if lat.dim() == 4 and lat.dtype == torch.float32 and lat.is_cuda and nhwc.is_contiguous() \
@@ -133,17 +134,19 @@ class PixelNeRFNet(torch.nn.Module):
                 t = nhwc if dtype == torch.float32 else nhwc.to(dtype)
             else:
                 t = _lib.prepare_latent(src, dtype)
-            self._latent_nhwc = {"key": key, "t": t}
-        return self._latent_nhwc["t"]
+            self._latent_nhwc[dtype] = hit = (key, t)
+        return hit[1]
 
     def latent_tables(self, coarse):
         """Per-texel lin_z tables of one MLP for the tensor-core chain (lin_z of a bilinear blend = blend of
         lin_z of the texels, resnetfc.py:174-180 after encoder.py:102-108): rebuilt when the latent or any
         parameter of that MLP changed."""
         mlp = self._mlp(coarse)
-        lat = self.latent_nhwc(torch.float32)
+        # training mode rebuilds the tables every optimiser step: tensor-core product from the fp16 latent
+        # (hi + lo weights); eval mode builds them once per encode in fp32
+        lat = self.latent_nhwc(torch.float16 if self.training else torch.float32)
         params = mlp.weight_dict()
-        key = (self._latent_nhwc["key"], tuple((q.data_ptr(), q._version) for q in params.values()))
+        key = (self._latent_nhwc[lat.dtype][0], lat.dtype, tuple((q.data_ptr(), q._version) for q in params.values()))
         slot = "coarse" if mlp is self.mlp_coarse else "fine"
         hit = self._tables.get(slot)
         if hit is None or hit[0] != key:

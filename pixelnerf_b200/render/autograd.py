@@ -82,7 +82,13 @@ class RenderFunction(torch.autograd.Function):
             g_lat = torch.zeros(v, hl, wl, ch, device=dev, dtype=torch.float32)
 
         def zero_grads(ps):
-            return {k: torch.zeros_like(p, dtype=torch.float32) for k, p in zip(names, ps)}
+            # one zero-filled buffer per MLP, the 30 gradient tensors are views of it (one fill instead of 30)
+            flat = torch.zeros(sum(p.numel() for p in ps), device=dev, dtype=torch.float32)
+            out, off = {}, 0
+            for k, p in zip(names, ps):
+                out[k] = flat[off:off + p.numel()].view(p.shape)
+                off += p.numel()
+            return out
 
         grads_c = zero_grads(coarse_p)
         grads_f = zero_grads(fine_p) if fine_p else grads_c

@@ -153,3 +153,47 @@ def test_chain_is_deterministic(ns, ppo):
             assert torch.isfinite(first).all()
         else:
             assert torch.equal(pre, first)
+
+
+@pytest.mark.parametrize("texels", [(1, 8, 24), (4, 64, 64), (3, 15, 20)])
+def test_tensor_core_tables_match_fp32_tables(texels):
+    """Training mode rebuilds the per-texel lin_z tables every step on the tensor cores (fp16 latent, fp16 hi + lo
+    weights, fp32 sums): against the fp32 CUDA-core tables of eval mode and against a float64 product of the same
+    fp16-rounded latent.  Texel counts that are and are not multiples of the 256-row GEMM tile."""
+    from pixelnerf_b200 import _lib, synthetic as syn
+    w = {k: v.cuda() for k, v in syn.mlp_weights(42).items()}
+    v, hl, wl = texels
+    lat = syn.latent_maps(3, v, hl, wl).permute(0, 2, 3, 1).contiguous().cuda()     # channels-last fp32
+    t32 = _lib.prepare_latent_tables(w, lat).float()
+    t16 = _lib.prepare_latent_tables(w, lat.half()).float()
+    assert t16.shape == t32.shape == (3, v * hl * wl, 512)
+    scale = t32.abs().max().item()
+    # vs the fp32 tables: the latent's fp16 rounding (5e-4 relative per element, summed over 512 terms) + fp16 output
+    assert (t16 - t32).abs().max().item() < 2e-3 * scale
+    # vs float64 on the SAME fp16 latent: only the weight split's residue (2^-22) and the fp16 output rounding remain
+    l16 = lat.half().double().reshape(-1, 512)
+    for b in range(3):
+        folded = w["lin_in.bias"] if b == 0 else w[f"blocks.{b - 1}.fc_1.bias"]
+        ref = l16 @ w[f"lin_z.{b}.weight"].double().T + w[f"lin_z.{b}.bias"].double() + folded.double()
+        assert (t16[b].double() - ref).abs().max().item() < 6e-4 * scale   # half an fp16 ulp at the largest entry + slack
+
+
+def test_training_mode_uses_tensor_core_tables_and_stays_in_tolerance():
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import build_net, oracle_render
+    sc = syn.scene("srn_chair")
+    wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
+    net, ren = build_net(sc, wc, wf, torch.device("cuda"), mlp_precision="fp16")
+    rays = sc["rays"][torch.linspace(0, sc["rays"].shape[0] - 1, 200).long()]
+    draws = syn.draws(3, 200, 64, 16, 16)
+    ref = oracle_render(sc, wc, wf, rays, draws)
+    outs = {}
+    for mode in ("eval", "train"):
+        getattr(net, mode)()
+        ren.injected_draws = {k: v.cuda() for k, v in draws.items()}
+        with torch.no_grad():
+            outs[mode] = ren(net, rays[None].cuda(), want_weights=True)
+        assert (outs[mode].coarse.rgb[0].cpu() - ref["rgb_coarse"]).abs().max().item() < 2e-3
+        assert (outs[mode].coarse.weights[0].cpu() - ref["w_coarse"]).abs().max().item() < 2e-3
+    assert not torch.equal(outs["eval"].coarse.weights, outs["train"].coarse.weights)   # different table builds
+    net.eval()
