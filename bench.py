@@ -153,6 +153,51 @@ def run_torch_cuda(args):
                 oracle.render_rays(net_fn, rays[s0:s0 + chunk], 1, N_COARSE, N_FINE, N_DEPTH, d, depth_std=0.01,
                                    white_bkgd=sc["white"])
 
+    if args.train:   # config 5 on the same comparator: 4 objects x --train-rays rays, fwd + autograd bwd + Adam
+        sb = 4
+        params = [v.requires_grad_(True) for v in list(wc.values()) + list(wf.values())]
+        opt = torch.optim.Adam(params, lr=1e-4)
+        lat4 = syn.latent_maps(21, sb, sc["hl"], sc["wl"]).to(dev)
+        cam4 = dict(cam, poses=cam["poses"].expand(sb, -1, -1).contiguous())
+        res = {}
+        for n_obj in args.train_rays:
+            g = torch.Generator().manual_seed(n_obj)
+            idx = torch.randint(0, n, (sb, n_obj), generator=g)
+            rr = sc["rays"][idx].reshape(-1, 8).to(dev)
+            tgt = torch.rand(sb * n_obj, 3, generator=g).to(dev)
+            dd = {k: v.to(dev) for k, v in syn.draws(7, sb * n_obj, N_COARSE, N_FINE - N_DEPTH, N_DEPTH).items()}
+
+            def net4(xyz, dirs, coarse):
+                return omodel.net_forward(wc if coarse else wf, lat4, cam4, sc["ns"], xyz, dirs)
+
+            def tstep():
+                opt.zero_grad(set_to_none=True)
+                o = oracle.render_rays(net4, rr, sb, N_COARSE, N_FINE, N_DEPTH, dd, depth_std=0.01, white_bkgd=sc["white"])
+                loss = ((o["rgb_coarse"] - tgt) ** 2).mean() + ((o["rgb_fine"] - tgt) ** 2).mean()
+                loss.backward()
+                opt.step()
+
+            for mode in ("fp32", "tf32", "bf16_autocast"):
+                torch.backends.cuda.matmul.allow_tf32 = mode == "tf32"
+                ctx = torch.autocast("cuda", dtype=torch.bfloat16, enabled=mode == "bf16_autocast")
+                with ctx:
+                    for _ in range(3):
+                        tstep()
+                    torch.cuda.synchronize()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    steps = max(1, min(args.steps, 10))
+                    a.record()
+                    for _ in range(steps):
+                        tstep()
+                    b.record()
+                    b.synchronize()
+                ms = a.elapsed_time(b) / steps
+                res[f"{sb * n_obj}_rays_{mode}"] = {"ms_per_step": ms, "rays/s": sb * n_obj / (ms * 1e-3)}
+        print(json.dumps({"impl": "torch-cuda-eager", "metric": "training step rays/sec (config 5)", "unit": "rays/s",
+                          "config": {"workload": "4 objects, fwd + autograd bwd + Adam on both MLPs; oracle port of the "
+                                                 "reference's torch op sequence on cuda:0, torch " + torch.__version__},
+                          "modes": res}))
+        return
     res = {}
     for mode in ("fp32", "tf32", "bf16_autocast"):
         torch.backends.cuda.matmul.allow_tf32 = mode == "tf32"
@@ -465,6 +510,8 @@ def main():
     args = ap.parse_args()
     if args.kernels:
         run_kernels(args)
+    elif args.train and args.impl == "torch-cuda":
+        run_torch_cuda(args)
     elif args.train:
         run_train(args)
     elif args.impl == "reference":
