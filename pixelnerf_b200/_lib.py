@@ -176,7 +176,12 @@ def _ptr(t, dtype=torch.float32):
 
 
 def _f32c(t):
-    return None if t is None else t.detach().to(torch.float32).contiguous()
+    """Contiguous fp32 view of `t` without autograd history (no copy, no dispatcher call, when it already is one)."""
+    if t is None:
+        return None
+    if t.dtype == torch.float32 and t.is_contiguous() and not t.requires_grad:
+        return t
+    return t.detach().to(torch.float32).contiguous()
 
 
 def _stream():
