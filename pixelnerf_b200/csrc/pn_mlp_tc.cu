@@ -126,7 +126,9 @@ __device__ __forceinline__ uint32_t pack_relu_bf2(float a, float b) {
 // through one TMA store issued by lane 0, asynchronously.  `stage` must be free (bulk_wait_read0 + __syncwarp).
 __device__ __forceinline__ void save_relu32(const CUtensorMap* map, uint32_t stage, int lane, int col, int64_t row0,
                                             bool store, const float (&x)[32]) {
+#ifndef PN_EXPERIMENT_SAVE_NOWAIT   // timing experiment only (races on the staging buffer)
   if (lane == 0) bulk_wait_read0();   // the previous box has left the staging buffer
+#endif
   __syncwarp();
 #pragma unroll
   for (int j = 0; j < 4; ++j)
