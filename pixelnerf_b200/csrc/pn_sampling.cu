@@ -188,8 +188,15 @@ sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_c
       __syncwarp();
       for (int q = lane; q < kf; q += 32) {
         const int64_t di = r * kf + q;
-        const float ub = u_bin ? u_bin[di] : rand_uniform(seed, PN_STREAM_BIN, (uint64_t)di);
-        const float ui = u_in ? u_in[di] : rand_uniform(seed, PN_STREAM_IN, (uint64_t)di);
+        float ub, ui;
+        if (u_bin && u_in) {
+          ub = u_bin[di];
+          ui = u_in[di];
+        } else {   // both draws of a sample from one Philox block (x: bin, y: position inside the bin)
+          const uint4 rnd = Philox(seed)((uint64_t)di, (uint64_t)PN_STREAM_BIN + 16);
+          ub = u_bin ? u_bin[di] : u01(rnd.x);
+          ui = u_in ? u_in[di] : u01(rnd.y);
+        }
         int lo = 0, hi = kc + 1;  // upper bound: first index with cdf > ub
         while (lo < hi) {
           int mid = (lo + hi) >> 1;
@@ -212,6 +219,76 @@ sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_c
         srt[kc + kf + q] = zz;
         if (z_depth) z_depth[di] = zz;
       }
+    }
+    __syncwarp();
+    // The stratified samples arrive sorted (nerf.py:98-118 is monotone in k) and at most 32 samples are new: sort
+    // the new ones across the lanes (15 compare-exchange steps) and merge by rank -- each element's place is its
+    // own index plus the number of elements of the other list in front of it (ties: stratified first) -- instead
+    // of a full 128-wide bitonic sort (28 steps over 4 elements per lane).  Same multiset, so the same sorted row
+    // bit for bit.  Anything else (unsorted z_coarse, more than 32 new samples, Kc outside [32,128]) takes the
+    // general bitonic path below.
+    const int n_new = kf + kd;
+    bool merge_ok = n_new <= 32 && kc >= 32 && kc <= 128;
+    if (merge_ok) {
+      bool sorted = true;
+      for (int k = lane; k + 1 < kc; k += 32) sorted = sorted && (srt[k] <= srt[k + 1]);
+      merge_ok = __all_sync(0xffffffffu, sorted);
+    }
+    if (merge_ok) {
+      float v = lane < n_new ? srt[kc + lane] : __int_as_float(0x7f800000);
+#pragma unroll
+      for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+          const float p = __shfl_xor_sync(0xffffffffu, v, stride);
+          const bool keep_min = ((lane & stride) == 0) == ((lane & size) == 0 || size == 32);
+          v = keep_min ? fminf(v, p) : fmaxf(v, p);
+        }
+      }
+      w[lane] = v;            // the pdf buffer is free by now (Kc >= 32 floats)
+      __syncwarp();
+      int rank_new = 0;
+      if (lane < n_new) {     // stratified samples <= v
+        int lo = 0, hi = kc;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (srt[mid] <= v) lo = mid + 1; else hi = mid;
+        }
+        rank_new = lane + lo;
+      }
+      float cval[4];
+      int crank[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = lane + 32 * j;
+        cval[j] = 0.0f;
+        crank[j] = -1;
+        if (k < kc) {
+          const float c = srt[k];
+          int lo = 0, hi = n_new;   // new samples < c
+          while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (w[mid] < c) lo = mid + 1; else hi = mid;
+          }
+          cval[j] = c;
+          crank[j] = k + lo;
+        }
+      }
+      __syncwarp();
+      if (lane < n_new) srt[rank_new] = v;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (crank[j] >= 0) srt[crank[j]] = cval[j];
+      __syncwarp();
+      float* dst = z_sorted + r * k2;
+      if ((k2 & 3) == 0 && ((uintptr_t)dst & 15) == 0) {
+        for (int e = lane * 4; e < k2; e += 128)
+          *reinterpret_cast<float4*>(dst + e) = make_float4(srt[e], srt[e + 1], srt[e + 2], srt[e + 3]);
+      } else {
+        for (int e = lane; e < k2; e += 32) dst[e] = srt[e];
+      }
+      __syncwarp();
+      continue;
     }
     for (int k = k2 + lane; k < sort_n; k += 32) srt[k] = __int_as_float(0x7f800000);  // +inf padding
     __syncwarp();
