@@ -54,12 +54,18 @@ __device__ __forceinline__ float4 load_vec4(const __half* p) {
 __device__ __forceinline__ void store_one(float* p, float v) { *p = v; }
 __device__ __forceinline__ void store_one(__half* p, float v) { *p = __float2half_rn(v); }
 
-constexpr int kFeatWarps = 8;
+#ifndef PN_FEAT_WARPS
+#define PN_FEAT_WARPS 8
+#endif
+constexpr int kFeatWarps = PN_FEAT_WARPS;
 
 // 16-byte vector of latent / feature elements as floats
 template <typename T> struct Vec16;
 template <> struct Vec16<float> {
   static constexpr int N = 4;
+  typedef float4 Raw;
+  static __device__ __forceinline__ Raw load_raw(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+  static __device__ __forceinline__ void unpack(const Raw& t, float (&v)[4]) { v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
   static __device__ __forceinline__ void load(const float* p, float (&v)[4]) {
     const float4 t = __ldg(reinterpret_cast<const float4*>(p));
     v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
@@ -70,6 +76,16 @@ template <> struct Vec16<float> {
 };
 template <> struct Vec16<__half> {
   static constexpr int N = 8;
+  typedef uint4 Raw;
+  static __device__ __forceinline__ Raw load_raw(const __half* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+  static __device__ __forceinline__ void unpack(const Raw& t, float (&v)[8]) {
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+      v[2 * i] = f.x; v[2 * i + 1] = f.y;
+    }
+  }
   static __device__ __forceinline__ void load(const __half* p, float (&v)[8]) {
     const uint4 t = __ldg(reinterpret_cast<const uint4*>(p));
     const uint32_t w[4] = {t.x, t.y, t.z, t.w};
@@ -232,11 +248,11 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
   // Consecutive rows of a warp are consecutive samples of one ray, and several of them fall into the same texel
   // cell: the four tap vectors stay in registers and are only re-read when a row names different texels (the
   // condition is warp uniform).  The kernel is bound by the L1 data path (4 KB of taps read per 1 KB written), so
-  // every skipped reload is time: 58 % -> 67 % of the HBM peak on the bench frame.  (A second buffer that requests
+  // every skipped reload is time: 58 % -> 69 % of the HBM peak on the bench frame (taps held packed).  (A second buffer that requests
   // the next row's taps before the current row is blended was measured slower, 58 %: 125 registers and the
   // buffer moves cost more than the overlap gains.)
   uint32_t p00 = 0xffffffffu, p01 = 0xffffffffu, p10 = 0xffffffffu, p11 = 0xffffffffu;
-  float ta[kIters][N], tb[kIters][N], tc[kIters][N], td[kIters][N];
+  typename Vec16<LatT>::Raw ta[kIters], tb[kIters], tc[kIters], td[kIters];   // kept packed: half the registers for fp16
 #pragma unroll 1
   for (int r = 0; r < n_here; ++r) {
     const uint32_t a00 = __shfl_sync(0xffffffffu, o00, r), a01 = __shfl_sync(0xffffffffu, o01, r);
@@ -248,19 +264,23 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
 #pragma unroll
       for (int it = 0; it < kIters; ++it) {
         const int ch = (it * 32 + lane) * N;
-        Vec16<LatT>::load(latent + a00 + ch, ta[it]);
-        Vec16<LatT>::load(latent + a01 + ch, tb[it]);
-        Vec16<LatT>::load(latent + a10 + ch, tc[it]);
-        Vec16<LatT>::load(latent + a11 + ch, td[it]);
+        ta[it] = Vec16<LatT>::load_raw(latent + a00 + ch);
+        tb[it] = Vec16<LatT>::load_raw(latent + a01 + ch);
+        tc[it] = Vec16<LatT>::load_raw(latent + a10 + ch);
+        td[it] = Vec16<LatT>::load_raw(latent + a11 + ch);
       }
       p00 = a00; p01 = a01; p10 = a10; p11 = a11;
     }
 #pragma unroll
     for (int it = 0; it < kIters; ++it) {
       const int ch = (it * 32 + lane) * N;
-      float o[N];
+      float va[N], vb[N], vc[N], vd[N], o[N];
+      Vec16<LatT>::unpack(ta[it], va);
+      Vec16<LatT>::unpack(tb[it], vb);
+      Vec16<LatT>::unpack(tc[it], vc);
+      Vec16<LatT>::unpack(td[it], vd);
 #pragma unroll
-      for (int i = 0; i < N; ++i) o[i] = ta[it][i] * b00 + tb[it][i] * b01 + tc[it][i] * b10 + td[it][i] * b11;
+      for (int i = 0; i < N; ++i) o[i] = va[i] * b00 + vb[i] * b01 + vc[i] * b10 + vd[i] * b11;
       Vec16<OutT>::store(oz + ch, o);
     }
   }
