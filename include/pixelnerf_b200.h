@@ -240,6 +240,13 @@ PN_API int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, i
                     const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16, void* out_bf16,
                     float scale, float* colsum0, float* colsum1, unsigned int* err_word, pn_stream_t stream);
 
+/* acc32[rows, n] (+)= scale * sum_s A_s[rows, 512] x B[s*512 .. s*512+512, n]: the same GEMM with its K = k dimension
+ * spread over k/512 operands A_s stored one after the other, slab_rows rows apart (slab_rows % 256 == 0, >= n_rows;
+ * rows past n_rows of a slab are never stored).  dL/dz = sum_b dL/dh_b W_z[b] of the MLP backward in one launch. */
+PN_API int pn_gemm_tc_rows_slabs(const void* a_slabs, int64_t slab_rows, int fmt, const void* b, int64_t n_rows, int k,
+                          int n, float* acc32, int accumulate, float scale, unsigned int* err_word,
+                          pn_stream_t stream);
+
 /* out[512, ldo] (fp32, first n_store columns) += G[rows, 512]^T x X[rows, ldx]  (ldx = 512, or 64 for lin_in's
  * padded code rows), split over row ranges, partial sums added with red.global.add: wgrad of y = x W^T with
  * G = dL/dy, X = the layer input.  The caller zeroes `out` first. */

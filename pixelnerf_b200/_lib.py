@@ -104,6 +104,7 @@ _SIGNATURES = {
                                   C.POINTER(MlpGrads), _vp, _vp, _sz, _vp]),
     "pn_gemm_tc_rows": (_int, [_vp, _int, _vp, _int, _i64, _int, _int, _vp, _vp, _int, _vp, _vp, _f32, _vp, _vp, _vp,
                                _vp]),
+    "pn_gemm_tc_rows_slabs": (_int, [_vp, _i64, _int, _vp, _i64, _int, _int, _vp, _int, _f32, _vp, _vp]),
     "pn_gemm_tc_wgrad": (_int, [_vp, _int, _int, _vp, _int, _int, _i64, _int, _vp, _int, _vp, _vp]),
     "pn_gen_rays": (_int, [_vp, _int, _int, _int, _int, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
     "pn_frame_to_u8": (_int, [_vp, _vp, _i64, _vp]),
@@ -603,6 +604,22 @@ def gemm_tc_rows(a, b, mask=None, acc32=None, accumulate=False, want16=True, sca
                                      float(scale), _ptr(colsum), _ptr(colsum2), _err_word(a.device).data_ptr(),
                                      _stream()), "pn_gemm_tc_rows")
     return acc32, out16
+
+
+def gemm_tc_rows_slabs(a_slabs, b, n_rows, acc32=None, accumulate=False, scale=1.0):
+    """sum_s a_slabs[s, :n_rows] @ b[s*512:(s+1)*512] in one launch: a_slabs (S, slab_rows, 512) 16-bit with
+    slab_rows % 256 == 0, b (S*512, n) of the same format; fp32 result (n_rows, n)."""
+    s_, slab_rows, _ = a_slabs.shape
+    n = b.shape[1]
+    assert b.shape[0] == s_ * 512 and a_slabs.is_contiguous() and b.is_contiguous() and a_slabs.dtype == b.dtype
+    if acc32 is None:
+        acc32 = torch.empty(n_rows, n, device=a_slabs.device, dtype=torch.float32)
+    with _Timed("gemm_rows"):
+        _check(lib().pn_gemm_tc_rows_slabs(_ptr(a_slabs, a_slabs.dtype), slab_rows, _FMT[a_slabs.dtype],
+                                           _ptr(b, b.dtype), n_rows, s_ * 512, n, _ptr(acc32), int(bool(accumulate)),
+                                           float(scale), _err_word(a_slabs.device).data_ptr(), _stream()),
+               "pn_gemm_tc_rows_slabs")
+    return acc32
 
 
 def gemm_tc_wgrad(g, x, out, n_store=None):

@@ -74,6 +74,8 @@ struct RowsParams {
   float* colsum0;        // optional [N] fp32: += column sums of the result (bias gradients), up to two destinations
   float* colsum1;
   float scale;           // D is multiplied by this first
+  int a_slab_rows;       // 0: A is [rows, K].  > 0: A is K/512 slabs of [a_slab_rows, 512] stacked along the rows
+                         // (K chunk kc lives in slab kc / 8): sum over several 512-wide operands in one launch
   unsigned int* err;
 };
 
@@ -158,7 +160,9 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const uint32_t full = bar(GB_FULL + s);
             const uint32_t dst = smem_base + s * kGStageRows;
             if (rank == 0) mbar_arrive_expect_tx(full, 2 * kGStageRows);
-            tma_load_2d_pair(dst, &map_a, full, kc * 64, tile * 256 + (int)rank * 128);
+            const int a_col = p.a_slab_rows ? (kc & 7) * 64 : kc * 64;
+            const int a_row = tile * 256 + (int)rank * 128 + (p.a_slab_rows ? (kc >> 3) * p.a_slab_rows : 0);
+            tma_load_2d_pair(dst, &map_a, full, a_col, a_row);
             tma_load_2d_pair(dst + 2 * kGBox, &map_b, full, n0, kc * 64);
             tma_load_2d_pair(dst + 3 * kGBox, &map_b, full, n0 + 64, kc * 64);
           }
@@ -493,10 +497,34 @@ static int gemm_smem_attr(K kernel) {
 }  // namespace tc
 }  // namespace pn
 
+static int gemm_tc_rows_impl(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
+                             const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16,
+                             void* out_bf16, float scale, float* colsum0, float* colsum1,
+                             unsigned int* err_word, pn_stream_t stream, int64_t a_slab_rows);
+
 extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
                                const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16,
                                void* out_bf16, float scale, float* colsum0, float* colsum1,
                                unsigned int* err_word, pn_stream_t stream) {
+  return gemm_tc_rows_impl(a, a_fmt, b, b_fmt, n_rows, k, n, mask_f16, acc32, accumulate, resid_bf16, out_bf16, scale,
+                           colsum0, colsum1, err_word, stream, 0);
+}
+
+extern "C" int pn_gemm_tc_rows_slabs(const void* a_slabs, int64_t slab_rows, int fmt, const void* b, int64_t n_rows,
+                                     int k, int n, float* acc32, int accumulate, float scale, unsigned int* err_word,
+                                     pn_stream_t stream) {
+  PN_CHECK_ARG(k > 0 && k % 512 == 0, "pn_gemm_tc_rows_slabs: K must be a multiple of 512 (one slab per 512)");
+  PN_CHECK_ARG(slab_rows >= n_rows && slab_rows % 256 == 0 && slab_rows * (k / 512) < (1ll << 31),
+               "pn_gemm_tc_rows_slabs: slab pitch must be a multiple of 256 rows, >= n_rows");
+  PN_CHECK_ARG(acc32, "pn_gemm_tc_rows_slabs: fp32 output required");
+  return gemm_tc_rows_impl(a_slabs, fmt, b, fmt, n_rows, k, n, nullptr, acc32, accumulate, nullptr, nullptr, scale,
+                           nullptr, nullptr, err_word, stream, slab_rows);
+}
+
+static int gemm_tc_rows_impl(const void* a, int a_fmt, const void* b, int b_fmt, int64_t n_rows, int k, int n,
+                             const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16,
+                             void* out_bf16, float scale, float* colsum0, float* colsum1,
+                             unsigned int* err_word, pn_stream_t stream, int64_t a_slab_rows) {
   using namespace pn::tc;
   PN_CHECK_ARG(a && b, "pn_gemm_tc_rows: null pointer");
   PN_CHECK_ARG((a_fmt | 1) == 1 && a_fmt == b_fmt,
@@ -519,7 +547,9 @@ extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fm
     attr_set = true;
   }
   CUtensorMap ma, mb;
-  if ((rc = make_map(&ma, a, (uint64_t)n_rows, (uint64_t)k, (uint64_t)k * 2, 128))) return rc;
+  if (a_slab_rows > 0) {
+    if ((rc = make_map(&ma, a, (uint64_t)a_slab_rows * (k / 512), 512, 1024, 128))) return rc;
+  } else if ((rc = make_map(&ma, a, (uint64_t)n_rows, (uint64_t)k, (uint64_t)k * 2, 128))) return rc;
   if ((rc = make_map(&mb, b, (uint64_t)k, (uint64_t)n, (uint64_t)n * 2, 64))) return rc;
   RowsParams p = {};
   p.n_rows = n_rows;
@@ -536,6 +566,7 @@ extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fm
   p.colsum0 = colsum0;
   p.colsum1 = colsum1;
   p.scale = scale;
+  p.a_slab_rows = (int)a_slab_rows;
   p.err = err_word;
   int sms = 0;
   if ((rc = gemm_grid(&sms))) return rc;

@@ -16,6 +16,9 @@ extern "C" int pn_gemm_tc_rows(const void* a, int a_fmt, const void* b, int b_fm
                                const void* mask_f16, float* acc32, int accumulate, const void* resid_bf16,
                                void* out_bf16, float scale, float* colsum0, float* colsum1,
                                unsigned int* err_word, pn_stream_t stream);
+extern "C" int pn_gemm_tc_rows_slabs(const void* a_slabs, int64_t slab_rows, int fmt, const void* b, int64_t n_rows,
+                                     int k, int n, float* acc32, int accumulate, float scale, unsigned int* err_word,
+                                     pn_stream_t stream);
 extern "C" int pn_gemm_tc_wgrad(const void* g, int g_fmt, int ldg, const void* x, int x_fmt, int ldx, int64_t n_rows,
                                 int n_store, float* out, int ldo, unsigned int* err_word, pn_stream_t stream);
 
@@ -208,16 +211,22 @@ extern "C" int pn_prepare_weights_bf16(const pn_mlp_weights_t* w, void* w16, siz
   return PN_OK;
 }
 
-// Workspace: [256 B error word] GH16 | G1 | Z16 (bf16 rows x 512) | x16 (rows x 64) | (NS > 1: second GH16)
+// Workspace: [256 B error word] slab 0 | slab 1 | slab 2 (dL/dh_b, bf16, pitch rows rounded up to 256) | G1 | Z16
+// (bf16 rows x 512) | x16 (rows x 64).  The three residual-stream gradients that feed lin_z stay side by side so
+// that dL/dz = sum_b dL/dh_b W_z[b] is ONE K = 1536 GEMM over the slabs instead of three accumulating launches
+// (each of which re-read and re-wrote the rows x 512 fp32 result).
+static inline size_t slab_rows_of(int64_t n_rows) { return (size_t)((n_rows > 0 ? n_rows : 0) + 255) / 256 * 256; }
+
 extern "C" size_t pn_mlp_backward_tc_workspace_bytes(int64_t n_rows, int n_views) {
   const size_t r = (size_t)(n_rows > 0 ? n_rows : 0);
-  return 256 + 3 * r * 512 * 2 + r * 64 * 2 + (n_views > 1 ? r * 512 * 2 : 0);
+  (void)n_views;
+  return 256 + 3 * slab_rows_of(n_rows) * 512 * 2 + 2 * r * 512 * 2 + r * 64 * 2;
 }
 
-// dL/dh_0 (rows x 512 bf16, the gradient at lin_in's output) is left in the workspace at this byte offset
+// dL/dh_0 (rows x 512 bf16, the gradient at lin_in's output) is left in the workspace at this byte offset (slab 0)
 extern "C" size_t pn_mlp_backward_tc_gh0_offset(int64_t n_rows, int n_views) {
-  const size_t r = (size_t)(n_rows > 0 ? n_rows : 0);
-  return n_views > 1 ? 256 + 3 * r * 512 * 2 + r * 64 * 2 : 256;
+  (void)n_rows; (void)n_views;
+  return 256;
 }
 
 extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, const void* feat_x,
@@ -240,11 +249,15 @@ extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, co
   const size_t R = (size_t)n_rows;
   char* ws = (char*)workspace;
   unsigned int* err = (unsigned int*)ws;
-  uint16_t* GH16 = (uint16_t*)(ws + 256);
-  uint16_t* G1 = GH16 + R * 512;
+  const size_t Rp = slab_rows_of(n_rows);
+  uint16_t* slab[3] = {(uint16_t*)(ws + 256), (uint16_t*)(ws + 256) + Rp * 512, (uint16_t*)(ws + 256) + 2 * Rp * 512};
+  uint16_t* G1 = slab[2] + Rp * 512;
   uint16_t* Z16 = G1 + R * 512;
   uint16_t* X16 = Z16 + R * 512;
-  uint16_t* GH16b = X16 + R * 64;
+  // dL/dh_5 .. dL/dh_3 (one row per point) are updated in place: in slab 2 when NS = 1 (block 2 then continues in
+  // place and leaves dL/dh_2 there), in slab 1 (free until block 1) when the view-mean backward expands them into
+  // slab 2 first
+  uint16_t* GH16 = n_views > 1 ? slab[1] : slab[2];
   const uint16_t* W16 = (const uint16_t*)w16;
   const size_t R_slot = (R + 127) / 128 * 128;   // slot pitch of the forward's saved operands (pn_mlp_tc_acts_bytes)
   auto X = [&](int slot) { return (const uint16_t*)acts + (size_t)slot * R_slot * 512; };
@@ -277,10 +290,10 @@ extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, co
   for (int b = PN_N_BLOCKS - 1; b >= 0; --b) {
     if (b == PN_COMBINE_LAYER - 1 && n_views > 1) {   // backward of the view mean (resnetfc.py:152-172)
       const int64_t ppo4 = points_per_object * 128, total4 = n_rows * 128;
-      view_mean_bwd16_kernel<<<ceil_div(total4, 256), 256, 0, st>>>((const uint2*)GH16, (uint2*)GH16b, n_views, ppo4, total4);
+      view_mean_bwd16_kernel<<<ceil_div(total4, 256), 256, 0, st>>>((const uint2*)GH16, (uint2*)slab[2], n_views, ppo4, total4);
       PN_LAUNCH_OK("view_mean_bwd16_kernel");
       count_launch();
-      uint16_t* t = GH16; GH16 = GH16b; GH16b = t;
+      GH16 = slab[2];
       m = n_rows;
     }
     // h_{b+1} = h_b + fc_1(x_{2b+1}) + b1,  x_{2b+1} = relu(fc_0(x_{2b}) + b0),  x_{2b} = relu(h_b)
@@ -291,16 +304,19 @@ extern "C" int pn_mlp_backward_tc(const pn_mlp_weights_t* w, const void* w16, co
     if ((rc = wgrad(G1, X(2 * b), 512, 512, grads->fc0_w[b], m))) return rc;
     float* cs0 = b > 0 ? grads->fc1_b[b - 1] : grads->lin_in_b;
     float* cs1 = b < PN_COMBINE_LAYER ? grads->lin_z_b[b] : nullptr;
-    if ((rc = pn_gemm_tc_rows(G1, 1, Wm(b), 1, m, 512, 512, X(2 * b), nullptr, 0, GH16, GH16, 1.0f, cs0, cs1, err, stream)))
+    // dL/dh_b = dL/dh_{b+1} + ...: in place, except that blocks 1 and 0 leave their result in their own slab
+    uint16_t* gh_out = b < PN_COMBINE_LAYER - 1 ? slab[b] : GH16;
+    if ((rc = pn_gemm_tc_rows(G1, 1, Wm(b), 1, m, 512, 512, X(2 * b), nullptr, 0, GH16, gh_out, 1.0f, cs0, cs1, err, stream)))
       return rc;
+    GH16 = gh_out;
     if (b < PN_COMBINE_LAYER) {   // h_b = ... + lin_z[b](z)  (resnetfc.py:174-180)
       if ((rc = wgrad(GH16, Z16, 512, 512, grads->lin_z_w[b], m))) return rc;
-      if (g_feat_z &&
-          (rc = pn_gemm_tc_rows(GH16, 1, Wm(10 + b), 1, m, 512, 512, nullptr, g_feat_z, b != PN_COMBINE_LAYER - 1, nullptr,
-                                nullptr, 1.0f, nullptr, nullptr, err, stream)))
-        return rc;
     }
   }
+  // dL/dz = [dL/dh_0 | dL/dh_1 | dL/dh_2] x [W_z0; W_z1; W_z2] (the three lin_z matrices are consecutive in w16)
+  if (g_feat_z && (rc = pn_gemm_tc_rows_slabs(slab[0], (int64_t)Rp, 1, Wm(10), m, 3 * 512, 512, g_feat_z, 0, 1.0f, err,
+                                             stream)))
+    return rc;
   if ((rc = wgrad(GH16, X16, 64, PN_D_CODE, grads->lin_in_w, m))) return rc;
   PN_LAUNCH_OK("pn_mlp_backward_tc");
   return PN_OK;

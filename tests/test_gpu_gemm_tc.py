@@ -97,3 +97,22 @@ def test_rows_gemm_residual_and_column_sums(rows):
     tol = 2.0 ** -9 * ref.abs().sum(0).max().item() / rows ** 0.5 * 4 + 1e-3   # bf16-exact values are not summed: fp32 sums of the unrounded result
     assert (cs1.double() - col).abs().max().item() < max(tol, 1e-4 * col.abs().max().item())
     assert torch.allclose(cs0 - 2.0, cs1, rtol=1e-4, atol=1e-3 * float(col.abs().max()))
+
+
+@pytest.mark.parametrize("rows,slabs", [(1000, 3), (256, 1), (70000, 3), (1, 2)])
+def test_rows_gemm_over_slabs(rows, slabs):
+    """pn_gemm_tc_rows_slabs: K spread over several 512-wide operands stored slab_rows apart (dL/dz = sum_b dL/dh_b
+    W_z[b] in one launch).  The padding rows of every slab hold NaN: they must never reach a stored row."""
+    from pixelnerf_b200 import _lib
+    g = torch.Generator().manual_seed(rows)
+    pitch = (rows + 255) // 256 * 256
+    a = torch.full((slabs, pitch, 512), float("nan"))
+    a[:, :rows] = torch.randn(slabs, rows, 512, generator=g)
+    a = a.bfloat16().cuda()
+    b = (torch.randn(slabs * 512, 512, generator=g) * 0.05).bfloat16().cuda()
+    out = _lib.gemm_tc_rows_slabs(a, b, rows)
+    ref = sum(a[s, :rows].double() @ b[s * 512:(s + 1) * 512].double() for s in range(slabs))
+    assert torch.isfinite(out).all()
+    assert (out.double() - ref).abs().max().item() < 2e-5 * max(1.0, ref.abs().max().item())
+    out2 = _lib.gemm_tc_rows_slabs(a, b, rows, acc32=out.clone(), accumulate=True, scale=0.5)
+    assert (out2.double() - 1.5 * ref).abs().max().item() < 4e-5 * max(1.0, ref.abs().max().item())
