@@ -23,11 +23,11 @@ namespace tc {
 
 constexpr int kGThreads = 320;
 constexpr int kGBox = 64 * 64 * 2;                 // one [64 x 64] 16-bit box
-constexpr int kGStageRows = 32 * 1024, kGStagesRows = 6;     // rows GEMM: A [128 x 64] + B 2 boxes
+constexpr int kGStageRows = 32 * 1024;                       // rows GEMM: A [128 x 64] + B 2 boxes; 4-6 stages (see kernel)
 constexpr int kGStageW = 48 * 1024, kGStagesW = 4;           // wgrad: A 2 boxes + B 2 halves x 2 boxes
 constexpr int kGRing = 192 * 1024;
 constexpr int kGOffBar = kGRing;
-enum { GB_FULL = 0, GB_EMPTY = 8, GB_ACCF = 16, GB_ACCE = 18, GB_COUNT = 20 };
+enum { GB_FULL = 0, GB_EMPTY = 8, GB_ACCF = 16, GB_ACCE = 18, GB_IN = 20, GB_COUNT = 36 };   // GB_IN: 2 per epilogue warp
 constexpr int kGOffTmem = kGOffBar + GB_COUNT * 8;
 constexpr int kGOffColsum = kGOffTmem + 16;            // 512 floats: per-CTA column sums (rows GEMM)
 constexpr int kGOffOut = (kGOffColsum + 512 * 4 + 511) / 512 * 512;   // rows GEMM: per epilogue warp, one [32 x 32] bf16
@@ -130,7 +130,8 @@ __device__ __forceinline__ void gemm_teardown(uint32_t tmem_base, int warp) {
 template <bool kAcc>   // kAcc: the fp32 accumulate / output path (acc32) is compiled in
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGThreads, 1)
 gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 const __grid_constant__ CUtensorMap map_o, const RowsParams p) {
+                 const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_m,
+                 const __grid_constant__ CUtensorMap map_r, const RowsParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -141,10 +142,17 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     prefetch_tensormap(&map_a);
     prefetch_tensormap(&map_b);
     if (p.out16) prefetch_tensormap(&map_o);
+    if (!kAcc && p.mask) prefetch_tensormap(&map_m);
+    if (!kAcc && p.resid16) prefetch_tensormap(&map_r);
   }
+  if (warp == 1 && lane == 0)   // published by the fence + cluster barrier inside gemm_setup
+    for (int i = 0; i < 16; ++i) mbar_init(bar(GB_IN + i), 1);
   float* cs_smem = reinterpret_cast<float*>(smem_raw + (smem_base - smem_u32(smem_raw)) + kGOffColsum);
   for (int i = threadIdx.x; i < 512; i += kGThreads) cs_smem[i] = 0.0f;
-  const uint32_t tmem_base = gemm_setup(smem_base, warp, lane, kGStagesRows);   // cluster barrier inside
+  // Operand ring depth: 6 stages when the epilogue takes its inputs with plain loads (fp32 accumulate path); the
+  // dgrad forms give 64 KB (mask + residual boxes) or 32 KB (mask only) of the ring to the epilogue's TMA inputs.
+  const int n_stages = kAcc ? 6 : (p.resid16 ? 4 : 5);
+  const uint32_t tmem_base = gemm_setup(smem_base, warp, lane, n_stages);   // cluster barrier inside
 
   if (warp == 0) {
     uint32_t s = 0, ph = 0;
@@ -167,7 +175,7 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             tma_load_2d_pair(dst + 3 * kGBox, &map_b, full, n0 + 64, kc * 64);
           }
           __syncwarp();
-          if (++s == kGStagesRows) { s = 0; ph ^= 1; }
+          if (++s == (uint32_t)n_stages) { s = 0; ph ^= 1; }
         }
       }
     }
@@ -195,7 +203,7 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             umma_commit_pair(bar(GB_EMPTY + s), 0x3);
           }
           __syncwarp();
-          if (++s == kGStagesRows) { s = 0; ph ^= 1; }
+          if (++s == (uint32_t)n_stages) { s = 0; ph ^= 1; }
         }
         if (elect_one()) umma_commit_pair(bar(GB_ACCF + acc), 0x3);
         __syncwarp();
@@ -204,6 +212,54 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   } else if (warp >= 2) {
     const int q = warp & 3, ch = (warp - 2) >> 2;
     const uint32_t ostage = smem_base + kGOffOut + (uint32_t)(warp - 2) * kGOutBytes;
+    // !kAcc (the dgrad forms): the [32 rows x 32 columns] mask / residual boxes of a chunk arrive by TMA in one of
+    // the warp's two buffers (64-byte rows, 64-byte swizzle, their own mbarrier), requested two chunks ahead --
+    // across item boundaries too -- so neither the lookahead nor the 32-lines-per-instruction global loads of the
+    // earlier version cost registers or L1 wavefronts.  (in_t, in_h, in_c) is the next chunk to request; a
+    // chunk's buffer is c & 1.  (Four mask-only buffers, four chunks ahead, measured no faster.)
+    const uint32_t in_stride = p.resid16 ? 4096u : 2048u;
+    const uint32_t in_base = smem_base + (uint32_t)n_stages * kGStageRows + (uint32_t)(warp - 2) * 2 * in_stride;
+    const uint32_t in_bar0 = bar(GB_IN + 2 * (warp - 2));
+    const uint32_t in_mask = 1u;
+    uint32_t in_ph = 0;
+    int in_t = pair_id, in_h = 0, in_c = 0;
+    auto in_issue = [&]() {   // warp uniform; buffer = parity of the chunk (4 chunks per item)
+      if (in_t < p.n_tiles) {
+        if (lane == 0) {
+          const uint32_t buf = (uint32_t)in_c & in_mask, ib = in_bar0 + 8 * buf;
+          const int col = in_h * 256 + ch * 128 + in_c * 32;
+          const int row0 = in_t * 256 + (int)rank * 128 + q * 32;
+          mbar_arrive_expect_tx(ib, (p.mask ? 2048u : 0u) + (p.resid16 ? 2048u : 0u));
+          if (p.mask) tma_load_2d_cta(in_base + buf * in_stride, &map_m, ib, col, row0);
+          if (p.resid16) tma_load_2d_cta(in_base + buf * in_stride + 2048, &map_r, ib, col, row0);
+        }
+        if (++in_c == 4) {
+          in_c = 0;
+          if (++in_h == p.n_halves) { in_h = 0; in_t += n_pairs; }
+        }
+      }
+    };
+    auto in_take = [&](int c, uint32_t (&mk)[16], uint32_t (&rs)[16]) {
+      const uint32_t buf = (uint32_t)c & in_mask;
+      wait_bar<false>(in_bar0 + 8 * buf, (in_ph >> buf) & 1u, p.err, 0x340 + buf);
+      in_ph ^= 1u << buf;
+      const uint32_t src = in_base + buf * in_stride + lane * 64;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t o = (uint32_t)(j ^ ((lane >> 1) & 3)) << 4;
+        if (p.mask)
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(mk[4 * j]), "=r"(mk[4 * j + 1]), "=r"(mk[4 * j + 2]), "=r"(mk[4 * j + 3]) : "r"(src + o) : "memory");
+        if (p.resid16)
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(rs[4 * j]), "=r"(rs[4 * j + 1]), "=r"(rs[4 * j + 2]), "=r"(rs[4 * j + 3]) : "r"(src + 2048 + o) : "memory");
+      }
+      __syncwarp();   // every lane holds its copy: the buffer may be refilled
+    };
+    if (!kAcc) {
+      in_issue();
+      in_issue();
+    }
     uint32_t it = 0;
 #pragma unroll 1
     for (int tile = pair_id; tile < p.n_tiles; tile += n_pairs) {
@@ -219,7 +275,7 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           const int half2 = half + 1 < p.n_halves ? half + 1 : 0;
           const int tile2 = half + 1 < p.n_halves ? tile : tile + n_pairs;
           const int64_t row2 = (int64_t)tile2 * 256 + rank * 128 + q * 32 + lane;
-          if (tile2 < p.n_tiles && row2 < p.n_rows) {
+          if (kAcc && tile2 < p.n_tiles && row2 < p.n_rows) {
             const size_t off2 = (size_t)row2 * p.ldn + half2 * 256 + ch * 128;
             if (p.mask) {
               prefetch_l2(p.mask + off2);
@@ -342,17 +398,15 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             process(c, mk, rs);
           }
         } else {
-          uint32_t mkA[16], rsA[16], mkB[16], rsB[16];
-          issue(0, mkA, rsA);
           wait_bar<false>(bar(GB_ACCF + acc), accph, p.err, 0x330 + acc);
           tc_fence_after();
-          issue(1, mkB, rsB);
-          process(0, mkA, rsA);
-          issue(2, mkA, rsA);
-          process(1, mkB, rsB);
-          issue(3, mkB, rsB);
-          process(2, mkA, rsA);
-          process(3, mkB, rsB);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t mk[16], rs[16];
+            in_take(c, mk, rs);
+            in_issue();          // chunk c + 2 (this item's or the next one's) into the buffer just read
+            process(c, mk, rs);
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -573,8 +627,11 @@ static int gemm_tc_rows_impl(const void* a, int a_fmt, const void* b, int b_fmt,
   const int pairs = p.n_tiles < sms / 2 ? p.n_tiles : sms / 2;
   CUtensorMap mo = ma;   // placeholder when there is no bf16 output (never read then)
   if (out_bf16 && (rc = make_store_map(&mo, out_bf16, (uint64_t)n_rows, (uint64_t)n))) return rc;
-  if (acc32) gemm_rows_kernel<true><<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, mo, p);
-  else gemm_rows_kernel<false><<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, mo, p);
+  CUtensorMap mm = ma, mr = ma;   // placeholders (never read without the matching pointer)
+  if (!acc32 && mask_f16 && (rc = make_store_map(&mm, mask_f16, (uint64_t)n_rows, (uint64_t)n))) return rc;
+  if (!acc32 && resid_bf16 && (rc = make_store_map(&mr, resid_bf16, (uint64_t)n_rows, (uint64_t)n))) return rc;
+  if (acc32) gemm_rows_kernel<true><<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, mo, mm, mr, p);
+  else gemm_rows_kernel<false><<<2 * pairs, kGThreads, kGSmem, (cudaStream_t)stream>>>(ma, mb, mo, mm, mr, p);
   PN_LAUNCH_OK("gemm_rows_kernel");
   pn::count_launch();
   return PN_OK;

@@ -92,6 +92,13 @@ __device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap
       ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
 }
 
+// 2-D tile load into this CTA's shared memory, completion on this CTA's own barrier (no pairing).
+__device__ __forceinline__ void tma_load_2d_cta(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+
 // The same load delivered to the same shared-memory offset of every CTA in `mask` (cluster ranks); each
 // destination's completion bytes go to the barrier at that offset in the leader of ITS pair.
 __device__ __forceinline__ void tma_load_2d_pair_mc(uint32_t dst, const CUtensorMap* map, uint32_t bar,
