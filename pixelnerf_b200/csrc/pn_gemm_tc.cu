@@ -254,6 +254,10 @@ gemm_rows_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
                        : "=r"(rs[4 * j]), "=r"(rs[4 * j + 1]), "=r"(rs[4 * j + 2]), "=r"(rs[4 * j + 3]) : "r"(src + 2048 + o) : "memory");
       }
+      // The refill is an async-proxy write: order this lane's generic-proxy reads in front of it.  (Without this
+      // fence a 25-run determinism test saw, about once in ten launches, a few 16-byte pieces of a mask box
+      // replaced by the next chunk's -- tests/test_gpu_guards.py.)
+      fence_proxy_async_smem();
       __syncwarp();   // every lane holds its copy: the buffer may be refilled
     };
     if (!kAcc) {

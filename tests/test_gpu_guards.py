@@ -169,3 +169,31 @@ def test_training_forward_saved_operands_stay_inside(ns, ppo):
     assert torch.equal(ref, out.t)
     a = _lib.tc_acts_view(acts.t.view(torch.uint8), n)
     assert torch.isfinite(a[:6].float()).all() and float(a[0].float().abs().max()) > 0
+
+
+def test_dgrad_epilogue_pipeline_is_deterministic():
+    """The TMA-input pipeline of the rows GEMM (two buffers per warp, requests two chunks ahead across items, stores
+    through one staging buffer): 25 runs over 300 tiles (four items per CTA pair and more) give bit-identical results,
+    in place and out of place -- a phase or buffer-reuse error would show as a run-to-run difference."""
+    lib = _lib.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    rows = 76800 + 37
+    g = torch.Generator().manual_seed(1)
+    a = torch.randn(rows, 512, generator=g).bfloat16().cuda()
+    w = (torch.randn(512, 512, generator=g) * 0.05).bfloat16().cuda()
+    mask = torch.relu(torch.randn(rows, 512, generator=g)).bfloat16().cuda()
+    r0 = torch.randn(rows, 512, generator=g).bfloat16().cuda()
+    cs = torch.zeros(512, device="cuda")
+    first = None
+    for rep in range(25):
+        out = torch.empty(rows, 512, device="cuda", dtype=torch.bfloat16)
+        res = r0.clone()
+        _lib._check(lib.pn_gemm_tc_rows(a.data_ptr(), 1, w.data_ptr(), 1, rows, 512, 512, mask.data_ptr(), None, 0, None,
+                                        out.data_ptr(), 1.0, cs.data_ptr(), None, None, st), "fc_1 form")
+        _lib._check(lib.pn_gemm_tc_rows(out.data_ptr(), 1, w.data_ptr(), 1, rows, 512, 512, mask.data_ptr(), None, 0,
+                                        res.data_ptr(), res.data_ptr(), 1.0, cs.data_ptr(), cs.data_ptr(), None, st),
+                    "fc_0 form")
+        if first is None:
+            first = (out.clone(), res.clone())
+        else:
+            assert torch.equal(out, first[0]) and torch.equal(res, first[1]), rep
