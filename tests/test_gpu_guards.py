@@ -197,3 +197,29 @@ def test_dgrad_epilogue_pipeline_is_deterministic():
             first = (out.clone(), res.clone())
         else:
             assert torch.equal(out, first[0]) and torch.equal(res, first[1]), rep
+
+
+@pytest.mark.parametrize("ns,ppo", [(1, 128 * 160 + 5), (2, 128 * 90 + 3)])
+def test_training_forward_is_deterministic(ns, ppo):
+    """The chain kernel that saves its operands (staging buffer shared between the table gather and the TMA stores)
+    and the two-launch NS > 1 chain (fp16 hand-off, L2 prefetch): 12 runs over more tiles than CTA pairs give
+    bit-identical outputs and saved operands."""
+    from helpers import make_taps
+    from test_gpu_mlp_tc import _inputs, _tables
+    w = syn.mlp_weights(42)
+    packed = _lib.pack_weights_tc({k: v.cuda() for k, v in w.items()})
+    n = ns * ppo
+    idx, wt, latent, fx = _inputs(n)
+    tables = _tables(w, latent)
+    fx_t = make_taps(idx, wt, fx).cuda()
+    first = None
+    for rep in range(12):
+        out, acts = _lib.mlp_forward_tc_train(packed, tables, fx_t, 1, ns, ppo)
+        a = _lib.tc_acts_view(acts, n)
+        got = (out.clone(), a[:6].clone(), a[6:, :ppo].clone())
+        if first is None:
+            first = got
+        else:
+            for x, y in zip(got, first):
+                assert torch.equal(x, y), rep
+    assert torch.equal(first[0], _lib.mlp_forward_tc(packed, tables, fx_t, 1, ns, ppo))
