@@ -5,6 +5,7 @@ not on a CUDA device the call raises.  torch is used only to own device memory a
 to supply the current stream.
 """
 import ctypes as C
+import functools
 import os
 
 import torch
@@ -186,7 +187,44 @@ def _f32c(t):
 
 
 def _stream():
+    # the current stream of the CURRENT device: every launching entry point below runs under _on_device, which
+    # makes the tensors' device current first
     return torch.cuda.current_stream().cuda_stream
+
+
+def _tensor_device(objs):
+    """The one CUDA device every tensor among `objs` (nested dicts / lists / tuples included) lives on; raises if
+    they disagree (a kernel launched on one GPU's stream with another GPU's pointers faults or, with peer access
+    enabled, silently reads across NVLink)."""
+    dev = None
+    stack = list(objs)
+    while stack:
+        o = stack.pop()
+        if torch.is_tensor(o):
+            if o.is_cuda:
+                if dev is None:
+                    dev = o.device
+                elif o.device != dev:
+                    raise RuntimeError(f"pixelnerf_b200: tensors of one call live on {dev} and {o.device}")
+        elif isinstance(o, dict):
+            stack.extend(o.values())
+        elif isinstance(o, (list, tuple)):
+            stack.extend(o)
+    return dev
+
+
+def _on_device(fn):
+    """Run `fn` with its tensors' device current: the reference's callers pick a device with
+    ``util.get_cuda(args.gpu_id[0])`` and never call ``torch.cuda.set_device`` (eval/gen_video.py:66), and the
+    in-process multi-GPU wrapper drives several devices from one process."""
+    @functools.wraps(fn)
+    def call(*args, **kwargs):
+        dev = _tensor_device(args + tuple(kwargs.values()))
+        if dev is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(dev):
+            return fn(*args, **kwargs)
+    return call
 
 
 _LIN_CACHE = {}
@@ -689,3 +727,13 @@ def mlp_backward_tc(packed32, w16, feat_x, latent_nhwc, n_objects, n_views, ppo,
         off = lib().pn_mlp_backward_tc_gh0_offset(n_rows, n_views)
         return g_fz, ws[off:off + n_rows * D_HIDDEN * 2].view(torch.bfloat16).view(n_rows, D_HIDDEN)
     return g_fz
+
+
+# every entry point that launches kernels runs with its tensors' device current (see _on_device)
+for _name in ("sample_coarse", "sample_fine", "prepare_latent", "point_features", "mlp_forward_fp32",
+              "mlp_forward_fp32_train", "mlp_backward_fp32", "point_features_bwd", "depth_sample_bwd", "point_taps",
+              "prepare_latent_tables", "pack_weights_tc", "mlp_forward_tc", "composite_fwd", "composite_bwd",
+              "render_rays", "gen_rays", "encoder_latent", "frame_to_u8", "gemm_tc_rows", "gemm_tc_rows_slabs",
+              "gemm_tc_wgrad", "mlp_forward_tc_train", "pack_weights_bf16", "mlp_backward_tc"):
+    globals()[_name] = _on_device(globals()[_name])
+del _name

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
 #include <stdint.h>
+#include <atomic>
 #include <stdio.h>
 
 #include "../../include/pixelnerf_b200.h"
@@ -41,6 +42,22 @@ void count_launch(int n = 1);
   } while (0)
 
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// Kernel attributes (the dynamic shared memory opt-in) are per DEVICE: a process that renders on cuda:1 after
+// cuda:0 has to set them again there.  `seen` is one bit per device ordinal; setting an attribute twice is
+// harmless, so the check-then-mark race between two threads of one device only repeats the call.
+struct DeviceOnce {
+  std::atomic<unsigned long long> seen{0};
+  bool needed(int* dev_out) const {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { *dev_out = -1; return true; }
+    *dev_out = dev;
+    return !((seen.load(std::memory_order_acquire) >> dev) & 1ull);
+  }
+  void mark(int dev) {
+    if (dev >= 0) seen.fetch_or(1ull << dev, std::memory_order_release);
+  }
+};
 
 // ---- counter-based RNG (Philox4x32-10), used when the caller does not inject draws ----
 struct Philox {

@@ -597,12 +597,12 @@ static int gemm_tc_rows_impl(const void* a, int a_fmt, const void* b, int b_fmt,
                    (((uintptr_t)mask_f16 | (uintptr_t)acc32 | (uintptr_t)out_bf16 | (uintptr_t)resid_bf16) & 31) == 0,
                "pn_gemm_tc_rows: operands must be 16-byte, mask / outputs 32-byte aligned");
   if (n_rows == 0) return PN_OK;
-  static bool attr_set = false;
-  int rc;
-  if (!attr_set) {
+  static pn::DeviceOnce attr_set;   // per device (a second GPU of the process needs its own opt-in)
+  int rc, attr_dev;
+  if (attr_set.needed(&attr_dev)) {
     if ((rc = gemm_smem_attr(gemm_rows_kernel<false>))) return rc;
     if ((rc = gemm_smem_attr(gemm_rows_kernel<true>))) return rc;
-    attr_set = true;
+    attr_set.mark(attr_dev);
   }
   CUtensorMap ma, mb;
   if (a_slab_rows > 0) {
@@ -655,12 +655,12 @@ extern "C" int pn_gemm_tc_wgrad(const void* g, int g_fmt, int ldg, const void* x
                    ((ldo & 3) != 0 || ((uintptr_t)out & 15) == 0),
                "pn_gemm_tc_wgrad: misaligned buffer");
   if (n_rows == 0) return PN_OK;
-  static bool attr_set = false;
-  int rc;
-  if (!attr_set) {
+  static pn::DeviceOnce attr_set;
+  int rc, attr_dev;
+  if (attr_set.needed(&attr_dev)) {
     if ((rc = gemm_smem_attr(gemm_wgrad_kernel<2>))) return rc;
     if ((rc = gemm_smem_attr(gemm_wgrad_kernel<1>))) return rc;
-    attr_set = true;
+    attr_set.mark(attr_dev);
   }
   CUtensorMap ma, mb;
   if ((rc = make_map(&ma, g, (uint64_t)n_rows, (uint64_t)ldg, (uint64_t)ldg * 2, 64))) return rc;

@@ -797,11 +797,12 @@ pack_bias_kernel(pn_mlp_weights_t w, float* __restrict__ ta, float* __restrict__
 // ---- host side ----------------------------------------------------------------------------
 static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap& ms, ChainParams p,
                         cudaStream_t st) {
-  static bool attr_set = false;  // idempotent; a benign race at worst repeats the call
-  if (!attr_set) {
+  static pn::DeviceOnce attr_set;  // per device; idempotent, a benign race at worst repeats the call
+  int attr_dev;
+  if (attr_set.needed(&attr_dev)) {
     PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
     PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
-    attr_set = true;
+    attr_set.mark(attr_dev);
   }
   int dev = 0, sms = 0;
   PN_CUDA_OK(cudaGetDevice(&dev));

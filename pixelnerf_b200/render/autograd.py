@@ -56,6 +56,13 @@ class RenderFunction(torch.autograd.Function):
             ctx.stash, model._train_stash = model._train_stash, None
             renderer._keep_parts = False
         ctx.renderer, ctx.model, ctx.sb = renderer, model, sb
+        # What the backward needs of the model is captured NOW (torch's autograd captures tensors the same way): a
+        # second encode() or a parameter update between this forward and its backward must not change the camera,
+        # latent or tables the gradients are computed against.
+        tensor_core = model.mlp_precision != "fp32"
+        ctx.snap = dict(cam=model._cam, ns=ns, latent32=model.latent_nhwc(torch.float32),
+                        tables={c: model.latent_tables(c) for c in (True, False)} if tensor_core and not keep else None,
+                        versions=tuple(p._version for p in params))
         noisy = renderer.training and renderer.noise_std > 0.0 and draws is not None
         ctx.sigma_noise = (draws.get("sigma_noise_coarse"), draws.get("sigma_noise_fine")) if noisy else (None, None)
         ctx.n_params = len(params)
@@ -74,6 +81,11 @@ class RenderFunction(torch.autograd.Function):
         rays, z_c, z_f, z_dep = ctx.saved_tensors
         names = _lib.weight_names()
         coarse_p, fine_p = _flat_params(model)
+        snap = ctx.snap
+        if getattr(model, "_param_proxies", None) is None and \
+                tuple(p._version for p in coarse_p + fine_p) != snap["versions"]:
+            raise RuntimeError("one of the variables needed for gradient computation has been modified by an inplace "
+                               "operation: ResnetFC parameters changed between the render's forward and its backward")
         dev = rays.device
         want_latent = ctx.needs_input_grad[7]
         g_lat = None
@@ -98,31 +110,32 @@ class RenderFunction(torch.autograd.Function):
             g_dep = None
             if renderer.depth_sample_grad and z_dep.numel() > 0 and not all(x is None for x in (g[4], g[5], g[6])):
                 g_dep = torch.zeros(rays.shape[0], device=dev, dtype=torch.float32)
-            _backward_pass(renderer, model, False, rays, z_f, sb, g[4], g[5], g[6], grads_f, g_lat, stash,
+            _backward_pass(renderer, model, snap, False, rays, z_f, sb, g[4], g[5], g[6], grads_f, g_lat, stash,
                            z_dep=z_dep, g_dep=g_dep, sigma_noise=ctx.sigma_noise[1])
             if g_dep is not None:
                 g_depth_c = g_dep if g_depth_c is None else g_depth_c + g_dep
-        _backward_pass(renderer, model, True, rays, z_c, sb, g[0], g[1], g_depth_c, grads_c, g_lat, stash,
+        _backward_pass(renderer, model, snap, True, rays, z_c, sb, g[0], g[1], g_depth_c, grads_c, g_lat, stash,
                        sigma_noise=ctx.sigma_noise[0])
         flat = [grads_c[k] for k in names] + ([grads_f[k] for k in names] if fine_p else [])
         g_latent = g_lat.permute(0, 3, 1, 2) if want_latent else None
         return (None, None, None, None, None, None, None, g_latent, *flat)
 
 
-def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, grads, g_lat, stash=None,
+def _backward_pass(renderer, model, snap, coarse, rays, z, sb, g_w, g_rgb, g_depth, grads, g_lat, stash=None,
                    z_dep=None, g_dep=None, sigma_noise=None):
     """One pass's backward, chunk by chunk.  g_dep (R) / z_dep (R,Kd): fine pass only -- receives the gradient
-    the depth-guided sample positions carry to the coarse depth."""
+    the depth-guided sample positions carry to the coarse depth.  ``snap``: the camera block, channels-last latent
+    and lin_z tables the forward used (RenderFunction.forward)."""
     r_total, k = z.shape
     if g_w is None and g_rgb is None and g_depth is None:
         return
     b = r_total // sb
-    ns = model.num_views_per_obj
-    cam = model._cam
+    ns = snap["ns"]
+    cam = snap["cam"]
     mlp = model.mlp_coarse if coarse or model.mlp_fine is None else model.mlp_fine
     weights = {n: p.detach() for n, p in mlp.weight_dict().items()}
     packed = mlp.packed("fp32")
-    latent = model.latent_nhwc(torch.float32)
+    latent = snap["latent32"]
     if g_rgb is None:
         g_rgb = torch.zeros(r_total, 3, device=z.device)
     chunk = max(1, renderer.max_rows_train // max(1, sb * ns * k))
@@ -168,7 +181,7 @@ def _backward_pass(renderer, model, coarse, rays, z, sb, g_w, g_rgb, g_depth, gr
         return
     if tensor_core:
         packed_tc, w16 = mlp.packed(model.mlp_precision), mlp.packed("bf16_train")
-        tables = model.latent_tables(coarse)
+        tables = snap["tables"][coarse] if snap["tables"] is not None else model.latent_tables(coarse)
         _, hl, wl, _ = latent.shape
         chunk = max(1, renderer.max_rows_train_tc // max(1, sb * ns * k))
     for s in range(0, b, chunk):

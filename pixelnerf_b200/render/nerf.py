@@ -78,6 +78,10 @@ class NeRFRenderer(torch.nn.Module):
         # (nerf.py:150-161, 290-293); False treats every sample position as a constant
         self.depth_sample_grad = True
         self._keep_parts = False   # set by render/autograd.py: sample_fine also returns the unsorted depth samples
+        # multi-GPU wrappers (pixelnerf_b200/parallel.py): every shard of a call derives its draws from one call
+        # seed offset by the shard's first ray; consumed by the next forward()
+        self.seed_offset = 0
+        self.seed_override = None
 
     # ---------------------------------------------------------------- sampling
     @staticmethod
@@ -215,7 +219,13 @@ class NeRFRenderer(torch.nn.Module):
         rays = rays.reshape(-1, 8).float().contiguous()
         draws, forced = self.injected_draws, self.injected_z or {}
         self.injected_draws, self.injected_z = None, None
-        seed = 0 if (draws and "u_coarse" in draws) else self._seed()
+        if draws and "u_coarse" in draws:
+            seed = 0
+        elif self.seed_override is not None:
+            seed = int(self.seed_override)
+        else:
+            seed = self._seed() + int(self.seed_offset)
+        self.seed_override = None
         if self.training and self.noise_std > 0.0:
             # sigma noise (nerf.py:225-226): drawn once per call so that the backward sees the forward's draws
             draws = dict(draws or {})
@@ -232,6 +242,9 @@ class NeRFRenderer(torch.nn.Module):
             # training: hand-written backward behind one autograd node (render/autograd.py)
             from .autograd import RenderFunction, _flat_params
             coarse_p, fine_p = _flat_params(model)
+            proxies = getattr(model, "_param_proxies", None)
+            if proxies is not None:    # a replica of the in-process multi-GPU wrapper: gradients flow to the
+                coarse_p, fine_p = proxies   # primary's parameters through differentiable peer copies
             res = RenderFunction.apply(self, model, rays, sb, draws, forced, seed, latent, *coarse_p, *fine_p)
             coarse, fine = res[:4], (res[4:9] if self.using_fine else None)
         else:
@@ -272,10 +285,15 @@ class NeRFRenderer(torch.nn.Module):
                    sched=conf.get_list("sched", None))
 
     def bind_parallel(self, net, gpus=None, simple_output=False):
-        """Reference nerf.py:354-371.  With more than one GPU the reference wraps the module in
-        DataParallel; here multi-GPU is one process per GPU (pixelnerf_b200.parallel)."""
+        """Reference nerf.py:354-371.  With more than one GPU the reference wraps the module in DataParallel
+        (dim 1 = rays); here the rays of a call are sharded the same way over resident replicas, from one process
+        (``DeviceSharded``) or, under torchrun, one process per GPU (``RaySharded``)."""
         wrapped = _RenderWrapper(net, self, simple_output=simple_output)
         if gpus is not None and len(gpus) > 1:
-            from ..parallel import RaySharded
-            wrapped = RaySharded(wrapped)
+            import torch.distributed as dist
+            from ..parallel import DeviceSharded, RaySharded
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                wrapped = RaySharded(wrapped)           # torchrun: one process per GPU, NCCL gather
+            else:
+                wrapped = DeviceSharded(wrapped, gpus)  # one process driving all of `gpus`, like the reference
         return wrapped
