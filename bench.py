@@ -6,11 +6,18 @@
 Workload (BASELINE.json configs[1]): SRN car 128x128, 1 source view, 64 coarse + 32 fine
 (16 importance + 16 depth) samples, whole frame per step (16 384 rays, 2.62 M MLP rows),
 synthetic scene and conditioned random weights (pixelnerf_b200.synthetic).  A step is one
-frame.  With N > 1 (torchrun) every rank renders its own frame of the same scene (rays are
-independent: weak scaling, no data-path collective except the 16 B/ray result all-gather).
+frame.  With N > 1 (torchrun) one call carries N frames (N x 16 384 rays) and goes through the
+product's own multi-GPU wrapper, `renderer.bind_parallel(net, gpus)` -> `parallel.RaySharded`: contiguous ray
+ranges per rank, encoded scene broadcast from rank 0, one all-gather of rgb+depth per call (weak scaling: one
+frame's worth of rays per GPU).
 
 `--impl reference` times the CPU oracle port of the reference's torch path (oracle/, the
 reference is Python and cannot travel to the GPU box) on all host cores, same metric.
+
+Besides the contract's keys the headline line carries: `sharded` (BASELINE configs 3 and 4 -- the 40-frame NS=2
+video and the DTU 300x400 NS=3 frame -- through the same ray-sharded wrapper, strong scaling), and at N=1 `parity`
+(max-abs errors of this build against the oracle on 256 rays of the frame), `roofline_kernels` (achieved GB/s of the
+HBM-bound kernels) and `gpu_baseline` (the reference's op sequence as torch-CUDA eager on the same GPU).
 """
 import argparse
 import json
@@ -198,24 +205,7 @@ def run_torch_cuda(args):
                                                  "reference's torch op sequence on cuda:0, torch " + torch.__version__},
                           "modes": res}))
         return
-    res = {}
-    for mode in ("fp32", "tf32", "bf16_autocast"):
-        torch.backends.cuda.matmul.allow_tf32 = mode == "tf32"
-        torch.backends.cudnn.allow_tf32 = mode == "tf32"
-        ctx = torch.autocast("cuda", dtype=torch.bfloat16) if mode == "bf16_autocast" else torch.autocast("cuda", enabled=False)
-        with ctx:
-            for _ in range(max(args.warmup, 2)):
-                frame()
-            torch.cuda.synchronize()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            steps = max(1, min(args.steps, 5))
-            a.record()
-            for _ in range(steps):
-                frame()
-            b.record()
-            b.synchronize()
-        ms = a.elapsed_time(b) / steps
-        res[mode] = {"ms_per_frame": ms, "rays/s": n / (ms * 1e-3)}
+    res = time_torch_cuda_modes(frame, n, max(args.warmup, 2), max(1, min(args.steps, 5)))
     print(json.dumps({"impl": "torch-cuda-eager", "metric": "rays/sec coarse+fine", "unit": "rays/s",
                       "config": {"workload": f"{WORKLOADS[args.scene]} full frame, {n} rays, {chunk}-ray chunks",
                                  "code": "oracle port of the reference's torch op sequence on cuda:0, torch "
@@ -223,15 +213,74 @@ def run_torch_cuda(args):
                       "modes": res}))
 
 
+def time_torch_cuda_modes(frame, n, warmup, steps):
+    res = {}
+    tf32_was = torch.backends.cuda.matmul.allow_tf32
+    for mode in ("fp32", "tf32", "bf16_autocast"):
+        torch.backends.cuda.matmul.allow_tf32 = mode == "tf32"
+        torch.backends.cudnn.allow_tf32 = mode == "tf32"
+        ctx = torch.autocast("cuda", dtype=torch.bfloat16) if mode == "bf16_autocast" else torch.autocast("cuda", enabled=False)
+        with ctx:
+            for _ in range(warmup):
+                frame()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(steps):
+                frame()
+            b.record()
+            b.synchronize()
+        ms = a.elapsed_time(b) / steps
+        res[mode] = {"ms_per_frame": ms, "rays/s": n / (ms * 1e-3)}
+    torch.backends.cuda.matmul.allow_tf32 = tf32_was
+    return res
+
+
+def torch_cuda_frame(sc, scene, steps=2, warmup=1):
+    """`gpu_baseline` of the headline line: the reference's torch op sequence (oracle port) as torch-CUDA eager on
+    this GPU (cuBLAS / ATen library kernels), whole frame, fp32 / TF32 / bf16 autocast -- the existing "Blackwell path"
+    the kernels replace.  A comparator, not a product path."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import scene_camera
+    import oracle
+    from oracle import model as omodel
+    dev = torch.device("cuda", torch.cuda.current_device())
+    wc = {k: v.to(dev) for k, v in syn.mlp_weights(1).items()}
+    wf = {k: v.to(dev) for k, v in syn.mlp_weights(2).items()}
+    cam = {k: v.to(dev) for k, v in scene_camera(sc).items()}
+    lat = sc["latent"].to(dev)
+    rays = sc["rays"].to(dev)
+    n = rays.shape[0]
+    draws = {k: v.to(dev) for k, v in syn.draws(7, n, N_COARSE, N_FINE - N_DEPTH, N_DEPTH).items()}
+    chunk = 4096
+
+    def net_fn(xyz, dirs, coarse):
+        return omodel.net_forward(wc if coarse else wf, lat, cam, sc["ns"], xyz, dirs)
+
+    def frame():
+        with torch.no_grad():
+            for s0 in range(0, n, chunk):
+                d = {k: v[s0:s0 + chunk] for k, v in draws.items()}
+                oracle.render_rays(net_fn, rays[s0:s0 + chunk], 1, N_COARSE, N_FINE, N_DEPTH, d, depth_std=0.01,
+                                   white_bkgd=sc["white"])
+
+    return {"what": "reference torch op sequence (oracle port) as torch-CUDA eager on this GPU, whole frame, "
+                    f"{chunk}-ray chunks, torch {torch.__version__}; {warmup} warm-up + {steps} timed frames per mode",
+            "unit": "rays/s", "modes": time_torch_cuda_modes(frame, n, warmup, steps)}
+
+
 def run_kernels(args):
-    """--kernels: every HBM-bound kernel of the path alone at a size that exceeds L2, as achieved GB/s of
-    its ALGORITHMIC bytes against the measured copy bandwidth."""
+    torch.cuda.set_device(0)
+    print(json.dumps(kernel_table()))
+
+
+def kernel_table(r=1 << 20):
+    """Every HBM-bound kernel of the path alone at a size that exceeds L2 (2^20 rays), as achieved GB/s of its
+    ALGORITHMIC bytes against the measured copy bandwidth."""
     from pixelnerf_b200 import _lib, synthetic as syn
     from pixelnerf_b200.testing import build_net
-    dev = torch.device("cuda", 0)
-    torch.cuda.set_device(dev)
+    dev = torch.device("cuda", torch.cuda.current_device())
     pk = peaks()
-    r = 1 << 20
     g = torch.Generator(device="cpu").manual_seed(0)
     rays = torch.zeros(r, 8, device=dev)
     rays[:, 3:6] = torch.nn.functional.normalize(torch.randn(r, 3, device=dev), dim=-1)
@@ -281,143 +330,267 @@ def run_kernels(args):
     # what the tensor-core path runs instead: positional code + taps record (128 B/row), no latent traffic
     timeit("point_taps", lambda: _lib.point_taps(net._cam, lat.shape[1], lat.shape[2], rows, rays=fr, z=zf),
            rows * 128 + fr.shape[0] * (32 + 4 * k2))
-    print(json.dumps({"kernels": res, "hbm_peak_GB/s": pk["hbm"], "peak_source": pk["source"], "rays": r}))
+    del rays, z_c, z_f, w_c, d_c
+    torch.cuda.empty_cache()
+    return {"kernels": res, "hbm_peak_GB/s": pk["hbm"], "peak_source": pk["source"], "rays": r,
+            "bound": "hbm", "timing": "CUDA events around 10 back-to-back launches after 3 warm-up launches; working "
+                                      "sets of 0.3-2 GB exceed the 126 MB L2"}
 
 
-def run_gpu(args):
-    import torch.distributed as dist
-    from pixelnerf_b200 import _lib, synthetic as syn
-    from pixelnerf_b200.testing import build_net
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback; see --impl reference)"
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+def frame_rays(sc, target_az, per_ray_bounds=False):
+    """One target frame of scene `sc` at azimuth `target_az`: (H*W, 8) host tensor."""
+    from pixelnerf_b200 import synthetic as syn
+    rays = syn.gen_rays(syn.pose_spherical(target_az, -10.0, sc["radius"]), sc["w"], sc["h"], sc["focal"], sc["near"],
+                        sc["far"], sc.get("c")).reshape(-1, 8).contiguous()
+    if per_ray_bounds:   # SURVEY 8d config 4: near / far columns differ per ray
+        g = torch.Generator().manual_seed(4)
+        rays[:, 6] = 0.1 + torch.rand(rays.shape[0], generator=g) * 0.4
+        rays[:, 7] = 5.0 - torch.rand(rays.shape[0], generator=g) * 0.5
+    return rays
 
-    sc = syn.scene(args.scene, target_az=10.0 * rank)  # every rank: its own target frame, same scene
-    wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
-    net, ren = build_net(sc, wc, wf, dev, mlp_precision=args.precision)
-    if world > 1:  # encoder features come from rank 0 once per encode
-        lat = net.encoder.latent.contiguous()
-        dist.broadcast(lat, src=0)
-        net.encoder.latent = lat
-        net._refresh_camera()
-    par = ren.bind_parallel(net, [local], simple_output=True).eval()
-    n_rays = sc["rays"].shape[0]
-    rays_host = sc["rays"].reshape(1, n_rays, 8).contiguous().pin_memory()
-    rays_dev = rays_host.to(dev)
-    out_host = torch.empty(n_rays, 4).pin_memory()
-    gathered = torch.empty(world * n_rays, 4, device=dev) if world > 1 else None
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
-    def step(rays):
-        with torch.no_grad():
-            rgb, depth = par(rays)
-        res = torch.cat([rgb.reshape(-1, 3), depth.reshape(-1, 1)], -1)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, res)
-        return res
+class Job:
+    """One process-group-wide measurement context: device, ranks, timing helpers."""
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
+    def __init__(self):
+        import torch.distributed as dist
+        self.dist = dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback; see --impl reference)"
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)  # > 126 MB L2
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
-        """K steps, CUDA events on the launching stream, L2 flushed between steps (untimed)."""
+    def timed(self, fn, steps):
+        """K steps, CUDA events on the launching stream, L2 flushed between steps (untimed); MAX over ranks."""
         total = 0.0
         for _ in range(steps):
-            flush.zero_()
+            self.flush.zero_()
+            if self.world > 1:
+                self.dist.barrier()      # every step starts together: a step ends with the slowest rank's gather
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             fn()
             b.record()
             b.synchronize()
             total += a.elapsed_time(b)
-        t = torch.tensor([total], device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = torch.tensor([total], device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
+
+    def bound(self, sc, precision):
+        """Model + renderer of scene `sc` on this rank, the encoded scene coming from rank 0 only (one NCCL broadcast
+        per encode), bound over every GPU of the job through the product's own bind_parallel."""
+        from pixelnerf_b200 import parallel, synthetic as syn
+        from pixelnerf_b200.testing import build_net
+        wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
+        net, ren = build_net(sc, wc, wf, self.dev, mlp_precision=precision)
+        if self.world > 1:
+            if self.rank != 0:   # only rank 0 "encoded": wipe the others so the broadcast is what they render from
+                net.encoder.latent = torch.zeros(1, 1, 1, 1, device=self.dev)
+                net.poses = torch.zeros(1, 3, 4, device=self.dev)
+            parallel.broadcast_encoded(net, src=0)
+        gpus = list(range(self.world)) if self.world > 1 else [self.local]
+        par = ren.bind_parallel(net, gpus, simple_output=True).eval()
+        if self.world > 1:
+            assert type(par).__name__ == "RaySharded", type(par).__name__
+        return net, ren, par, (wc, wf)
+
+
+def sharded_extras(job, args):
+    """BASELINE configs 3 and 4 through the same ray-sharded wrapper, STRONG scaling (the work is fixed, every call's
+    rays are split over the job's GPUs): one DTU 300x400 NS=3 frame with per-ray bounds (120 000 rays) and the
+    40-frame SRN-chair NS=2 video (655 360 rays in one call: contiguous ranges = whole frames per GPU)."""
+    from pixelnerf_b200 import _lib, synthetic as syn
+    out = {}
+    reps = 3
+    for key, scene, n_frames in (("dtu_frame", "dtu", 1), ("srn_chair_video40", "srn_chair", 40)):
+        sc = syn.scene(scene)
+        net, ren, par, _ = job.bound(sc, args.precision)
+        az = [0.0] if n_frames == 1 else [float(a) for a in torch.linspace(-180, 180, n_frames + 1)[:-1]]
+        rays = torch.cat([frame_rays(sc, a, per_ray_bounds=(scene == "dtu")) for a in az])[None].to(job.dev)
+        n = rays.shape[1]
+        host = torch.empty(n, 3, dtype=torch.uint8).pin_memory()
+
+        def call():
+            with torch.no_grad():
+                rgb, depth = par(rays)
+            return rgb
+
+        def call_e2e():      # + the frame output path: 8-bit conversion on the device, then the copy
+            host.copy_(_lib.frame_to_u8(call()[0]), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        for _ in range(2):
+            call()
+        job.barrier()
+        ms = job.timed(call, reps) / reps
+        ms_e2e = job.timed(call_e2e, reps) / reps
+        ns = sc["ns"]
+        flop = n * (N_COARSE + N_COARSE + N_FINE) * MLP_FLOP_PER_POINT[ns]
+        out[key] = {"workload": WORKLOADS[scene] + (f" x {n_frames} frames in one call" if n_frames > 1 else ""),
+                    "rays": n, "scaling": "strong", "n_gpus": job.world, "rays_per_gpu": n // job.world,
+                    "ms_per_call": ms, "rays/s": n / (ms * 1e-3), "e2e_rays/s": n / (ms_e2e * 1e-3),
+                    "mlp_algorithmic_TFLOP/s_per_gpu": flop / (ms * 1e-3) / 1e12 / job.world, "reps": reps}
+        del net, ren, par, rays
+        torch.cuda.empty_cache()
+    return out
+
+
+def live_parity(sc, weights, precision, n_rays=256):
+    """Max-abs error of this build on `n_rays` rays of the bench frame against the CPU oracle, stage-wise (coarse
+    pass on the same draws; fine pass teacher-forced with the oracle's coarse weights / depth): rgb, weights and
+    depth in WORLD UNITS.  The checker, not the product path."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import build_net, oracle_render
+    wc, wf = weights
+    idx = torch.linspace(0, sc["rays"].shape[0] - 1, n_rays).long()
+    rays = sc["rays"][idx]
+    draws = syn.draws(11, n_rays, N_COARSE, N_FINE - N_DEPTH, N_DEPTH)
+    ref = oracle_render(sc, wc, wf, rays, draws, N_COARSE, N_FINE, N_DEPTH)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    net, ren = build_net(sc, wc, wf, dev, mlp_precision=precision)
+    ren.injected_draws = {k: v.to(dev) for k, v in draws.items()}
+    ren.injected_z = dict(w_coarse=ref["w_coarse"].to(dev), depth_coarse=ref["depth_coarse"].to(dev))
+    with torch.no_grad():
+        out = ren(net, rays[None].to(dev), want_weights=True)
+    z_c, z_f = ren.last_z
+    res = {"rays": n_rays, "against": "CPU oracle (pinned to the live reference by tests/golden)", "stagewise": True,
+           "sample_positions_bit_exact": bool(torch.equal(z_c[0].cpu(), ref["z_coarse"]) and torch.equal(z_f[0].cpu(), ref["z_fine"])),
+           "tolerance": 1e-4 if precision == "fp32" else 2e-3, "depth_unit": "world units (absolute)"}
+    for part, tag in ((out.coarse, "coarse"), (out.fine, "fine")):
+        res[f"rgb_{tag}"] = float((part.rgb[0].cpu() - ref["rgb_" + tag]).abs().max())
+        res[f"weights_{tag}"] = float((part.weights[0].cpu() - ref["w_" + tag]).abs().max())
+        res[f"depth_{tag}"] = float((part.depth[0].cpu() - ref["depth_" + tag]).abs().max())
+    return res
+
+
+def run_gpu(args):
+    from pixelnerf_b200 import _lib, synthetic as syn
+    job = Job()
+    world, rank, dev = job.world, job.rank, job.dev
+    sc = syn.scene(args.scene)
+    net, ren, par, (wc, wf) = job.bound(sc, args.precision)
+    # Headline workload: `world` target frames of the scene in ONE call (one frame's worth of rays per GPU: weak
+    # scaling), split over the GPUs by the product's own wrapper (RaySharded: contiguous ray ranges in, one
+    # all-gather of the rendered values out).  At N = 1 this is exactly BASELINE configs[1]: one 128x128 frame.
+    n_frame = sc["rays"].shape[0]
+    n_rays = world * n_frame
+    rays_host = torch.cat([frame_rays(sc, 10.0 * i, per_ray_bounds=(args.scene == "dtu")) for i in range(world)])
+    rays_host = rays_host.reshape(1, n_rays, 8).contiguous().pin_memory()
+    rays_dev = rays_host.to(dev)
+    out_host = torch.empty(n_rays, 4).pin_memory()
+
+    def step(rays):
+        with torch.no_grad():
+            rgb, depth = par(rays)
+        return rgb, depth
 
     for _ in range(max(args.warmup, 3)):
         step(rays_dev)
-    barrier()
-    sampler = ClockSampler(local)
+    job.barrier()
+    sampler = ClockSampler(job.local)
     sampler.start()
     _lib.PROFILE = {}
     launches0 = _lib.launch_count()
-    ms = timed(lambda: step(rays_dev), args.steps)
-    barrier()
+    ms = job.timed(lambda: step(rays_dev), args.steps)
+    job.barrier()
     launches = _lib.launch_count() - launches0
     prof = {k: sum(a.elapsed_time(b) for a, b in v) for k, v in _lib.PROFILE.items()}
     n_mlp = len(_lib.PROFILE.get("mlp", []))
     _lib.PROFILE = None
 
-    def e2e_step():  # public API with HOST buffers: H2D of the rays, D2H of rgb+depth, inside the timed region
-        res = step(rays_host.to(dev, non_blocking=True))
-        out_host.copy_(res, non_blocking=True)
+    def e2e_step():
+        # public API with HOST buffers: the rays start in pinned host memory (under torchrun each rank copies only
+        # its own range: RaySharded slices before the H2D copy), rgb + depth end in pinned host memory on every rank
+        rgb, depth = step(rays_host if world > 1 else rays_host.to(dev, non_blocking=True))
+        out_host[:, :3].copy_(rgb[0], non_blocking=True)
+        out_host[:, 3].copy_(depth[0], non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
     e2e_step()
-    barrier()
-    ms_e2e = timed(e2e_step, args.steps)
-    barrier()
+    job.barrier()
+    ms_e2e = job.timed(e2e_step, args.steps)
+    job.barrier()
     sampler.stop_flag = True
     sampler.join(timeout=2)
+
+    extras = sharded_extras(job, args) if (args.extras and args.scene == SCENE) else None
 
     if rank == 0:
         pk = peaks()
         ns = sc["ns"]
-        rays_total = world * n_rays * args.steps
-        flop_step = n_rays * (N_COARSE + N_COARSE + N_FINE) * MLP_FLOP_PER_POINT[ns]
+        rays_total = n_rays * args.steps
+        flop_rank = n_frame * (N_COARSE + N_COARSE + N_FINE) * MLP_FLOP_PER_POINT[ns]     # this rank's share of a step
         mlp_ms = prof.get("mlp", 0.0) / max(1, args.steps)
-        achieved = flop_step / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else 0.0
+        achieved = flop_rank / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else 0.0
         # share of the algorithmic FLOPs the fp16 chain executes as MMAs (lin_z goes through tables): MMA counts
         # per 128 rows at NS=1 (padding included), MAC counts for NS > 1
         exe = 1.0
         if args.precision == "fp16":
             exe = 686.0 / 878.0 if ns == 1 else (ns * (6 * 262144 + 21504) + 1050624) / (ns * 2380800 + 1050624)
+        launches_per_step = n_mlp // max(1, args.steps)
+        points_rank = n_frame * (N_COARSE + N_COARSE + N_FINE)
         line = {
             "metric": "rays/sec coarse+fine", "value": rays_total / (ms * 1e-3), "unit": "rays/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": {"fp32": "f32", "fp16": "f16", "bf16": "bf16"}[args.precision], "data": "synthetic",
-            "config": {"workload": f"{WORKLOADS[args.scene]} full frame: {n_rays} rays/GPU/step, {N_COARSE} coarse + "
-                                   f"{N_FINE} fine ({N_DEPTH} depth) samples, ResnetFC 5x512 x2",
-                       "mlp_precision": args.precision, "parallelism": f"ray-sharded x{world}",
+            "dtype": {"fp32": "f32", "fp16": "f16"}[args.precision], "data": "synthetic",
+            "config": {"workload": f"{WORKLOADS[args.scene]}: {world} frame(s) per step = {n_frame} rays per GPU, "
+                                   f"{N_COARSE} coarse + {N_FINE} fine ({N_DEPTH} depth) samples, ResnetFC 5x512 x2",
+                       "mlp_precision": args.precision,
+                       "parallelism": ("one call of %d rays through renderer.bind_parallel(net, gpus) -> RaySharded: "
+                                       "contiguous ray ranges per rank, encoded scene broadcast from rank 0, one "
+                                       "all_gather_into_tensor of rgb+depth per call" % n_rays) if world > 1 else
+                                      "single GPU: renderer.bind_parallel(net, [0])",
                        "cache": "256 MiB L2 flush between steps",
                        "prepared_once": "weights packed, latent transposed, per-texel lin_z tables (0.3 ms) at encode time"},
-            "e2e": {"value": rays_total / (ms_e2e * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": n_rays * 32,
-                    "d2h_bytes_per_step": n_rays * 16},
+            "e2e": {"value": rays_total / (ms_e2e * 1e-3), "unit": "rays/s",
+                    "h2d_bytes_per_step": n_rays * 32, "d2h_bytes_per_step": world * n_rays * 16,
+                    "note": "rays from pinned host memory (each rank copies its own range), rgb+depth of the whole "
+                            "call copied to pinned host memory on every rank"},
             "gpu_launches": launches,
             "clocks": sampler.summary(),
             # `achieved` counts the ALGORITHMIC FLOPs of the reference MLP (SURVEY 8d), lin_z included; the fp16
             # chain applies lin_z through per-texel tables (DESIGN 3.1) and executes 686 of those 878 MMAs per
             # 128 rows, so `achieved` can exceed the hardware peak: `executed` is what the tensor pipe really did
-            "roofline": {"bound": "tensor", "kernel": "ResnetFC chain (%s)" % args.precision, "achieved": achieved,
+            "roofline": {"bound": "tensor", "kernel": "ResnetFC chain (%s), rank 0" % args.precision, "achieved": achieved,
                          "executed": achieved * exe,
                          "executed_frac": achieved * exe / pk["tf_sustained"],
                          "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
-                         "traffic": chain_traffic(flop_step / MLP_FLOP_PER_POINT[ns] / max(1, n_mlp // max(1, args.steps)))
-                         if args.precision == "fp16" else None,
-                         "traffic_source": "profiles/r01z_chain_ncu_summary.json: ncu dram read+write bytes per MLP row of "
-                                           "one captured launch x average rows per launch of this run",
+                         "traffic": chain_traffic(ns, points_rank, launches_per_step) if args.precision == "fp16" else None,
+                         "traffic_source": "profiles/r02_chain_traffic.json: ncu dram read+write bytes of the chain "
+                                           "launches of one pass at THIS view count, per point, x points per step / "
+                                           "launches per step (a live run cannot read dram counters)",
                          "peak_source": pk["source"] + ", sustained bf16",
-                         "launches_per_step": n_mlp // max(1, args.steps), "ms_per_step": mlp_ms},
+                         "launches_per_step": launches_per_step, "ms_per_step": mlp_ms},
             "stage_ms_per_step": {k: v / args.steps for k, v in prof.items()},
         }
+        if extras is not None:
+            line["sharded"] = extras
         if world == 1 and not args.no_cpu_baseline:
             sample = 8192
             v, secs = cpu_oracle_rays_per_s(sc, wc, wf, sample)
             line["cpu_baseline"] = {"value": v, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": f"{sample} evenly spaced rays of the same frame, {secs:.1f} s, torch "
                                               f"{torch.__version__} CPU"}
+        if world == 1 and args.extras:
+            line["parity"] = live_parity(sc, (wc, wf), args.precision)
+            line["roofline_kernels"] = kernel_table()
+            line["gpu_baseline"] = torch_cuda_frame(sc, args.scene, steps=2, warmup=1)
         print(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        job.dist.destroy_process_group()
 
 
 def run_train(args):
@@ -483,13 +656,15 @@ def run_train(args):
                       "optimizer": "Adam on both MLPs", "sweep": res}))
 
 
-def chain_traffic(rows_per_launch):
-    """DRAM bytes per chain launch: measured bytes/row of the committed `ncu --set full` capture (a live run
-    cannot read dram counters) times the rows one launch of this run processes; None without the summary."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01z_chain_ncu_summary.json")
+def chain_traffic(ns, points_per_step, launches_per_step):
+    """DRAM bytes per chain launch: ncu-measured dram read + write bytes per POINT of the chain launches at this view
+    count (profiles/r02_chain_traffic.json, one `ncu --set full` capture per NS; a live run cannot read dram
+    counters) x the points one step of this run processes / its chain launches; None without the summary."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_chain_traffic.json")
     try:
         with open(path) as f:
-            return json.load(f)["dram_bytes_per_row"] * rows_per_launch
+            per_point = json.load(f)["dram_bytes_per_point"][str(ns)]
+        return per_point * points_per_step / max(1, launches_per_step)
     except (OSError, KeyError, ValueError):
         return None
 
@@ -500,8 +675,11 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "torch-cuda"])
-    ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp16"), choices=["fp32", "fp16", "bf16"])
+    ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp16"), choices=["fp32", "fp16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", dest="extras", action="store_false",
+                    help="skip the extra keys of the headline line: `sharded` (DTU frame + 40-frame video, strong "
+                         "scaling), and at N=1 `parity`, `roofline_kernels`, `gpu_baseline`")
     ap.add_argument("--scene", default=SCENE, choices=sorted(WORKLOADS),
                     help="srn_car = the headline workload (BASELINE configs[1]); the others are extra measurements")
     ap.add_argument("--kernels", action="store_true", help="per-kernel HBM roofline of the memory-bound kernels")

@@ -2,10 +2,20 @@
 // Host-side sequencing only -- every kernel lives in its own file and is reached through the same C entry
 // points a caller could use one by one; this removes the per-stage Python/ctypes/allocator work from the
 // frame (8 launches back to back on one stream, intermediates in a caller-owned workspace).
+#include <nvtx3/nvToolsExt.h>
+
 #include "pn_common.cuh"
 
 namespace pn {
 namespace render {
+
+// NVTX ranges carrying the reference's profiler names (torch.autograd.profiler.record_function at
+// src/render/nerf.py:175,264, src/model/models.py:156, src/model/encoder.py:90, src/model/resnetfc.py:139), so a
+// timeline of this path reads like one of the reference.  Header-only NVTX: a no-op unless a profiler is attached.
+struct Range {
+  explicit Range(const char* name) { nvtxRangePushA(name); }
+  ~Range() { nvtxRangePop(); }
+};
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -48,13 +58,23 @@ static int pass(const pn_camera_t* cam, const pn_render_mlp_t* mlp, int64_t n_te
                 const float* z, int k, int white, float* rgbs, void* fx, void* mlp_ws, size_t mlp_ws_bytes,
                 float* weights, float* rgb, float* depth, const pn_render_events_t* ev, int which, cudaStream_t st) {
   const int64_t ppo = n_rays / cam->n_objects * k;
-  PN_TRY(record(ev ? ev->taps[which][0] : nullptr, st));
-  PN_TRY(pn_point_taps(cam, rays, z, k, nullptr, nullptr, ppo, fx, st));
-  PN_TRY(record(ev ? ev->taps[which][1] : nullptr, st));
-  PN_TRY(record(ev ? ev->mlp[which][0] : nullptr, st));
-  PN_TRY(pn_mlp_forward_tc(mlp->packed, mlp->tables, n_texels, fx, cam->n_objects, cam->n_views, ppo, rgbs, nullptr,
-                           mlp_ws, mlp_ws_bytes, nullptr, st));
-  PN_TRY(record(ev ? ev->mlp[which][1] : nullptr, st));
+  Range r_comp("renderer_composite");
+  {
+    Range r_model("model_inference");
+    PN_TRY(record(ev ? ev->taps[which][0] : nullptr, st));
+    {
+      Range r_index("encoder_index");     // projection + taps (+ positional_enc: same kernel)
+      PN_TRY(pn_point_taps(cam, rays, z, k, nullptr, nullptr, ppo, fx, st));
+    }
+    PN_TRY(record(ev ? ev->taps[which][1] : nullptr, st));
+    PN_TRY(record(ev ? ev->mlp[which][0] : nullptr, st));
+    {
+      Range r_mlp("resnetfc_infer");
+      PN_TRY(pn_mlp_forward_tc(mlp->packed, mlp->tables, n_texels, fx, cam->n_objects, cam->n_views, ppo, rgbs, nullptr,
+                               mlp_ws, mlp_ws_bytes, nullptr, st));
+    }
+    PN_TRY(record(ev ? ev->mlp[which][1] : nullptr, st));
+  }
   PN_TRY(record(ev ? ev->composite[which][0] : nullptr, st));
   PN_TRY(pn_composite_fwd(rgbs, z, rays, weights, rgb, depth, n_rays, k, white, st));
   PN_TRY(record(ev ? ev->composite[which][1] : nullptr, st));
@@ -93,6 +113,7 @@ extern "C" int pn_render_rays(const pn_camera_t* cam, const pn_render_mlp_t* mlp
   const Layout l = layout(n_rays, cam->n_views, *cfg);
   PN_CHECK_ARG(workspace_bytes >= l.total, "pn_render_rays: workspace too small (%zu < %zu)", workspace_bytes, l.total);
   cudaStream_t st = (cudaStream_t)stream;
+  Range r_forward("renderer_forward");
   char* ws = (char*)workspace;
   const size_t mlp_bytes = l.z_c - l.mlp;
   float* z_c = out_coarse->z ? out_coarse->z : (float*)(ws + l.z_c);

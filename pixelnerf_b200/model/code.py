@@ -21,8 +21,22 @@ class PositionalEncoding(torch.nn.Module):
         self.register_buffer("_phases", phases.view(1, -1, 1))
 
     def forward(self, x):
-        raise NotImplementedError(
-            "PositionalEncoding is fused into pn_point_features; call PixelNeRFNet.forward instead")
+        """(N, 3) -> (N, 39) = [x, sin(f_k x), sin(f_k x + pi/2) ...].  Reference code.py:30-42.  The render path
+        never calls this (the code is written by pn_point_features / pn_point_taps next to the latent lookup);
+        direct callers get the same kernel through an identity camera and a dummy 2x2 latent."""
+        from .. import _lib
+        if self.num_freqs != 6 or abs(self.freq_factor - 1.5) > 1e-12 or not self.include_input or self.d_in != 3:
+            raise NotImplementedError("the kernels implement num_freqs=6, freq_factor=1.5, include_input, d_in=3")
+        if not x.is_cuda:
+            raise RuntimeError("pixelnerf_b200 kernels need CUDA tensors (there is no CPU path)")
+        dev = x.device
+        n = x.shape[0]
+        cam = dict(poses=torch.eye(3, 4, device=dev).unsqueeze(0).contiguous(), focal=torch.ones(1, 2, device=dev),
+                   c=torch.zeros(1, 2, device=dev), scale_x=1.0, scale_y=1.0, n_objects=1, n_views=1)
+        xyz = x.reshape(1, n, 3).float().contiguous()
+        _, feat_x = _lib.point_features(cam, torch.zeros(1, 2, 2, _lib.D_LATENT, device=dev), n, xyz=xyz,
+                                        viewdirs=torch.zeros_like(xyz), ldx=44)
+        return feat_x[:, : self.d_out]
 
     @classmethod
     def from_conf(cls, conf, d_in=3):

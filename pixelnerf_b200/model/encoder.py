@@ -37,7 +37,31 @@ class SpatialEncoder(nn.Module):
         self.register_buffer("latent_scaling", torch.empty(2, dtype=torch.float32), persistent=False)
 
     def index(self, uv, cam_z=None, image_size=(), z_bounds=None):
-        raise NotImplementedError("latent lookup is fused into pn_point_features; call PixelNeRFNet.forward")
+        """Bilinear latent lookup at pixel coordinates uv (B, N, 2) -> (B, L, N).  Reference encoder.py:80-109.
+        The render path never calls this (the lookup is fused into pn_point_features / the chain's tables); direct
+        callers get the same kernel through an identity camera: a point (u, v, -1) projects to uv = (u, v)."""
+        from .. import _lib
+        lat = self.latent
+        if not lat.is_cuda:
+            raise RuntimeError("pixelnerf_b200 kernels need CUDA tensors (there is no CPU path)")
+        if uv.shape[0] == 1 and lat.shape[0] > 1:
+            uv = uv.expand(lat.shape[0], -1, -1)
+        b, n, _ = uv.shape
+        dev = lat.device
+        uv = uv.to(device=dev, dtype=torch.float32)
+        if len(image_size) > 0:
+            scale = (self.latent_scaling.to(dev) / torch.as_tensor(image_size, dtype=torch.float32, device=dev)).cpu()
+        else:     # uv already normalised to [-1, 1] (encoder.py:95-101 skips the scaling): uv*1 - 1 after a shift
+            scale, uv = torch.ones(2), uv + 1.0
+        eye = torch.eye(3, 4, device=dev).unsqueeze(0).expand(b, 3, 4).contiguous()
+        cam = dict(poses=eye, focal=torch.ones(b, 2, device=dev), c=torch.zeros(b, 2, device=dev),
+                   scale_x=float(scale[0]), scale_y=float(scale[1]), n_objects=b, n_views=1)
+        xyz = torch.cat((uv, -torch.ones(b, n, 1, device=dev)), dim=-1).contiguous()
+        nhwc = lat.detach().permute(0, 2, 3, 1)
+        if not nhwc.is_contiguous():
+            nhwc = _lib.prepare_latent(lat.detach(), torch.float32)
+        feat_z, _ = _lib.point_features(cam, nhwc, n, xyz=xyz, viewdirs=torch.zeros_like(xyz), ldx=44)
+        return feat_z.reshape(b, n, -1).permute(0, 2, 1)
 
     def forward(self, x):
         """(B,3,H,W) image -> latent (B, latent_size, H/2, W/2), cached in ``self.latent``."""

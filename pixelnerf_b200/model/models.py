@@ -9,6 +9,7 @@ import warnings
 import torch
 
 from .. import _lib
+from .._prof import prof_range
 from .code import PositionalEncoding
 from .model_util import make_encoder, make_mlp
 
@@ -155,6 +156,20 @@ class PixelNeRFNet(torch.nn.Module):
             self._tables[slot] = hit
         return hit[1]
 
+    def invalidate(self):
+        """Drop every kernel-side cache (packed weights, per-texel tables, channels-last latent).  Needed only after
+        writes the version counters cannot see: ``p.data.copy_()`` / ``mul_()`` on a parameter, or a call of
+        ``self.encoder(images)`` without ``encode()`` that re-uses the latent's storage."""
+        self._latent_nhwc, self._tables = {}, {}
+        for m in (self.mlp_coarse, self.mlp_fine):
+            if m is not None:
+                m.invalidate()
+
+    def load_state_dict(self, *args, **kwargs):
+        out = super().load_state_dict(*args, **kwargs)
+        self.invalidate()
+        return out
+
     # ----------------------------------------------------------------- forward
     def _mlp(self, coarse):
         return self.mlp_coarse if coarse or self.mlp_fine is None else self.mlp_fine
@@ -163,16 +178,23 @@ class PixelNeRFNet(torch.nn.Module):
         """Feature gather + MLP + head for SB*ppo points -> (SB*ppo, 4) [rgb, sigma]."""
         if self._cam is None:
             raise RuntimeError("call encode() before forward()")
+        with prof_range("model_inference"):
+            return self._run_points(coarse, ppo, rays, z, xyz, viewdirs)
+
+    def _run_points(self, coarse, ppo, rays, z, xyz, viewdirs):
         prec = self.mlp_precision
         mlp = self._mlp(coarse)
         cam = self._cam
         if prec == "fp32":
-            fz, fx = _lib.point_features(cam, self.latent_nhwc(torch.float32), ppo, rays=rays, z=z, xyz=xyz,
-                                         viewdirs=viewdirs, ldx=44)
-            return _lib.mlp_forward_fp32(mlp.packed("fp32"), fz, fx, cam["n_objects"], cam["n_views"], ppo)
+            with prof_range("encoder_index"):
+                fz, fx = _lib.point_features(cam, self.latent_nhwc(torch.float32), ppo, rays=rays, z=z, xyz=xyz,
+                                             viewdirs=viewdirs, ldx=44)
+            with prof_range("resnetfc_infer"):
+                return _lib.mlp_forward_fp32(mlp.packed("fp32"), fz, fx, cam["n_objects"], cam["n_views"], ppo)
         tables = self.latent_tables(coarse)
         _, hl, wl, _ = self.latent_nhwc(torch.float32).shape
-        fx = _lib.point_taps(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
+        with prof_range("encoder_index"):
+            fx = _lib.point_taps(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
         stash = getattr(self, "_train_stash", None)
         if stash is not None and rays is not None:
             # training forward (render/autograd.py): keep what the tensor-core backward needs, so that it does
@@ -181,7 +203,8 @@ class PixelNeRFNet(torch.nn.Module):
             stash.append(dict(coarse=coarse, ppo=ppo, rays=rays, z=z, fx=fx, out=out, acts=acts,
                               range=getattr(self, "_stash_range", None)))
             return out
-        return _lib.mlp_forward_tc(mlp.packed(prec), tables, fx, cam["n_objects"], cam["n_views"], ppo)
+        with prof_range("resnetfc_infer"):
+            return _lib.mlp_forward_tc(mlp.packed(prec), tables, fx, cam["n_objects"], cam["n_views"], ppo)
 
     def forward(self, xyz, coarse=True, viewdirs=None, far=False):
         """(SB,B,3) world points -> (SB,B,4) [sigmoid rgb, relu sigma].  Reference models.py:146-266."""

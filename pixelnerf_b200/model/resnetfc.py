@@ -55,6 +55,17 @@ class ResnetFC(nn.Module):
         self.activation = nn.ReLU()
         self._packed = {}
 
+    def invalidate(self):
+        """Drop the kernel-side copies of the weights.  They are keyed on each parameter's (data_ptr, _version), which
+        every autograd-visible write bumps (optimiser steps, ``load_state_dict``, ``copy_`` under ``no_grad``) --
+        writes through ``p.data`` (some EMA / clipping code) do NOT: call this after such a write."""
+        self._packed = {}
+
+    def load_state_dict(self, *args, **kwargs):
+        out = super().load_state_dict(*args, **kwargs)
+        self.invalidate()
+        return out
+
     def weight_dict(self):
         return {k: v for k, v in self.state_dict(keep_vars=True).items()}
 

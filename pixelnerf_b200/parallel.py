@@ -175,8 +175,14 @@ class RaySharded(torch.nn.Module):
             # every rank draws the same call seed from its identically seeded CPU generator; offsetting it by the
             # range's first ray gives every shard its own jitter (the chunk loop offsets by ray index the same way)
             renderer.seed_offset = s
+        mine = rays[:, s:e]
+        if not mine.is_cuda and torch.cuda.is_available() and dist.get_backend(self.group) == "nccl":
+            # rays may stay in (pinned) host memory: only this rank's range crosses PCIe (1/world of the frame)
+            dev = next((q.device for q in self.wrapped.parameters() if q.is_cuda), None)
+            if dev is not None:
+                mine = mine.to(dev, non_blocking=True)
         try:
-            local = self.wrapped(rays[:, s:e].contiguous(), want_weights)
+            local = self.wrapped(mine.contiguous(), want_weights)
         finally:
             if renderer is not None and hasattr(renderer, "seed_offset"):
                 renderer.seed_offset = 0

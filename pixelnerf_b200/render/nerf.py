@@ -13,6 +13,7 @@ import os
 import torch
 
 from .. import _lib
+from .._prof import prof_range
 
 
 class DotMap(dict):
@@ -120,12 +121,13 @@ class NeRFRenderer(torch.nn.Module):
         """Model evaluation + alpha compositing.  Reference nerf.py:163-249.
         rays (B,8), z_samp (B,K) -> weights (B,K), rgb (B,3), depth (B).  sigma_noise (B,K): the standard normal
         draws of nerf.py:226 when training with noise_std > 0 (drawn here if not given)."""
-        b, k = z_samp.shape
-        n_obj = max(sb, 1)
-        rgbs = model.run_points(coarse, (b // n_obj) * k, rays=rays, z=z_samp).reshape(b, k, 4)
-        if self.training and self.noise_std > 0.0:
-            rgbs = self.noisy_sigma(rgbs, torch.randn_like(z_samp) if sigma_noise is None else sigma_noise)
-        return _lib.composite_fwd(rgbs, z_samp, rays, self.white_bkgd)
+        with prof_range("renderer_composite"):
+            b, k = z_samp.shape
+            n_obj = max(sb, 1)
+            rgbs = model.run_points(coarse, (b // n_obj) * k, rays=rays, z=z_samp).reshape(b, k, 4)
+            if self.training and self.noise_std > 0.0:
+                rgbs = self.noisy_sigma(rgbs, torch.randn_like(z_samp) if sigma_noise is None else sigma_noise)
+            return _lib.composite_fwd(rgbs, z_samp, rays, self.white_bkgd)
 
     # ----------------------------------------------------------------- forward
     def _fused_ok(self, model, forced):
@@ -209,6 +211,10 @@ class NeRFRenderer(torch.nn.Module):
 
     def forward(self, model, rays, want_weights=False):
         """rays (SB,B,8) -> DotMap{coarse:{rgb,depth[,weights]}, fine:{...}}.  Reference nerf.py:251-303."""
+        with prof_range("renderer_forward"):
+            return self._forward(model, rays, want_weights)
+
+    def _forward(self, model, rays, want_weights):
         if self.sched is not None and self.last_sched.item() > 0:
             self.n_coarse = self.sched[1][self.last_sched.item() - 1]
             self.n_fine = self.sched[2][self.last_sched.item() - 1]

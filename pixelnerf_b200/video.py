@@ -1,0 +1,36 @@
+"""Video rendering helper: the loop of eval/gen_video.py:166-237 with both ends on the device.
+
+``render_video`` builds the rays of every target pose with the ray-generation kernel (``util.gen_rays``,
+src/util/util.py:238-276), renders them in ``ray_batch_size`` chunks through a bound renderer
+(``bind_parallel(net, gpus, simple_output=True)``, eval/gen_video.py:213-217) and converts the frames with
+``pn_frame_to_u8`` (``(frames * 255).astype(np.uint8)``, eval/gen_video.py:234-236) before the device-to-host copy,
+which therefore moves 3 bytes per pixel instead of 12.
+"""
+import torch
+
+from . import _lib
+from .util import util as _util
+
+
+def render_video(render_par, poses, width, height, focal, z_near, z_far, c=None, ray_batch_size=50000,
+                 device=None, return_depth=False):
+    """poses (NV, 4, 4) camera-to-world -> uint8 frames (NV, H, W, 3) on the host (and float depth (NV, H, W) on the
+    device when asked).  ``render_par`` must have been bound with ``simple_output=True``; call ``net.encode`` first."""
+    if device is None:
+        device = next((b.device for b in render_par.buffers()), torch.device("cuda"))
+    poses = poses.to(device=device, dtype=torch.float32)
+    rays = _util.gen_rays(poses, width, height, focal, z_near, z_far, c=c).reshape(-1, 8)
+    rgb_parts, depth_parts = [], []
+    with torch.no_grad():
+        for chunk in torch.split(rays, ray_batch_size, dim=0):
+            rgb, depth = render_par(chunk[None])
+            rgb_parts.append(rgb[0])
+            if return_depth:
+                depth_parts.append(depth[0])
+    frames = _lib.frame_to_u8(torch.cat(rgb_parts)).view(-1, height, width, 3)
+    host = torch.empty(frames.shape, dtype=torch.uint8, pin_memory=True)
+    host.copy_(frames, non_blocking=True)
+    torch.cuda.current_stream(frames.device).synchronize()
+    if return_depth:
+        return host, torch.cat(depth_parts).view(-1, height, width)
+    return host

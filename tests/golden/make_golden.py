@@ -270,10 +270,107 @@ def case_sampling(NeRFRenderer, n_coarse, lindisp, seed, n_rays=1024):
                 z_coarse=z_c.numpy(), z_imp=z_i.numpy(), z_depth=z_d.numpy(), z_sorted=z_sorted.numpy())
 
 
+def rays_cases():
+    """rays_*.npz: the LIVE reference's util.gen_rays / util.pose_spherical (src/util/util.py:238-276, 309-323) on the
+    shapes of the BASELINE configs.  Poses are stored whole; of the (B, H, W, 8) ray tensor a pixel lattice (every
+    ``step``-th row / column plus the last ones) is kept, which is enough to pin the camera model."""
+    import util   # the reference's own
+    cases = [
+        dict(name="srn128", w=128, h=128, focal=131.25, c=None, rows=4, radius=1.3, elev=-10.0, near=0.8, far=1.8, step=9),
+        dict(name="dtu400x300", w=400, h=300, focal=(360.0, 355.5), c=(201.3, 148.9), rows=4, radius=2.6, elev=-30.0,
+             near=0.1, far=5.0, step=23),
+        dict(name="sn64", w=64, h=64, focal=70.0, c=None, rows=4, radius=2.6, elev=-10.0, near=1.2, far=4.0, step=5),
+        dict(name="tiny3x4", w=7, h=5, focal=3.0, c=None, rows=3, radius=1.0, elev=20.0, near=0.5, far=2.0, step=1),
+    ]
+    for cs in cases:
+        angles = np.linspace(-180, 180, 7)[:-1]
+        poses = torch.stack([util.pose_spherical(float(a), cs["elev"], cs["radius"]) for a in angles])
+        poses_in = poses[:, :cs["rows"]].contiguous()
+        focal = torch.tensor(cs["focal"], dtype=torch.float32)
+        c = None if cs["c"] is None else torch.tensor(cs["c"], dtype=torch.float32)
+        rays = util.gen_rays(poses_in, cs["w"], cs["h"], focal, cs["near"], cs["far"], c=c)
+        ys = sorted(set(list(range(0, cs["h"], cs["step"])) + [cs["h"] - 1]))
+        xs = sorted(set(list(range(0, cs["w"], cs["step"])) + [cs["w"] - 1]))
+        sub = rays[:, ys][:, :, xs].contiguous()
+        np.savez_compressed(os.path.join(HERE, f"rays_{cs['name']}.npz"), w=cs["w"], h=cs["h"],
+                            focal=np.asarray(cs["focal"], np.float32),
+                            c=np.zeros(0, np.float32) if cs["c"] is None else np.asarray(cs["c"], np.float32),
+                            near=cs["near"], far=cs["far"], angles=angles.astype(np.float64), elev=cs["elev"],
+                            radius=cs["radius"], poses=poses.numpy(), pose_rows=cs["rows"], ys=np.asarray(ys),
+                            xs=np.asarray(xs), rays=sub.numpy())
+        print("rays", cs["name"], tuple(sub.shape))
+
+
+def case_dtu_full(ConfigTree, make_model, NeRFRenderer, n_rays=2048, seed=4100, wc_seed=4101, wf_seed=4901):
+    """BASELINE config 4 at its REAL size: 300 x 400 images, three source views, the 150 x 200 latent, per-ray
+    near / far columns, rays taken from a full frame built by the reference's own util.gen_rays / pose_spherical.
+    The reference's composite() is wrapped (not modified) to record the sample positions of both passes."""
+    import util
+    from pixelnerf_b200 import synthetic as syn
+    h, w, ns = 300, 400, 3
+    conf = reference_conf(ConfigTree, use_first_pool=True, white_bkgd=False)
+    # weight seeds picked (oracle scan) so that both passes span transparent to opaque rays on this latent
+    wc, wf = syn.mlp_weights(wc_seed), syn.mlp_weights(wf_seed)
+    net = build_reference_net(ConfigTree, make_model, conf, wc, wf)
+    g = np.random.Generator(np.random.PCG64(seed + 4))
+    imgs = syn.images(seed + 3, 1, ns, h, w)
+    src_poses = torch.stack([util.pose_spherical(a, -10.0, 2.6) for a in (-20.0, 0.0, 25.0)])[None]
+    focal_t = torch.tensor([[723.0, 723.0]])
+    c_t = torch.tensor([[200.0, 150.0]])
+    with torch.no_grad():
+        net.encode(imgs, src_poses, focal_t, c=c_t)
+        enc_shape = tuple(net.encoder.latent.shape)
+        assert enc_shape == (3, 512, 150, 200), enc_shape
+        net.encoder.latent = syn.latent_maps(seed + 5, ns, 150, 200)
+    full = util.gen_rays(util.pose_spherical(8.0, -12.0, 2.6)[None], w, h, focal_t[0], 0.1, 5.0, c=c_t[0])[0]
+    full = full.reshape(-1, 8).clone()
+    u = torch.from_numpy(g.random((h * w, 2), dtype=np.float32))
+    full[:, 6] = 0.1 + u[:, 0] * 0.4
+    full[:, 7] = 5.0 - u[:, 1] * 0.5
+    # a contiguous run of rays from the middle of the frame + a strided set over the whole frame
+    start = (h // 2) * w + 37
+    pick = torch.cat([torch.arange(start, start + n_rays // 2),
+                      torch.linspace(0, h * w - 1, n_rays - n_rays // 2).long()])
+    rays = full[pick][None]
+    renderer = NeRFRenderer.from_conf(conf["renderer"], lindisp=False, eval_batch_size=50000).eval()
+    renderer.white_bkgd = False
+    seen = []
+    orig = renderer.composite
+    renderer.composite = lambda model, rr, z, coarse=True, sb=0: (seen.append(z.clone()), orig(model, rr, z, coarse=coarse, sb=sb))[1]
+    par = renderer.bind_parallel(net, [0], simple_output=False).eval()
+    d = syn.draws(seed + 6, n_rays, 64, 16, 16)
+    with torch.no_grad(), DrawInjector([d["u_coarse"], d["u_bin"], d["u_in"], d["noise"]]):
+        out = par(rays, want_weights=True)
+    z_c, z_f = seen
+    fx = dict(name="dtu_full_ns3", h=h, w=w, ns=ns, sb=1, seed=seed, wc_seed=wc_seed, wf_seed=wf_seed,
+              white=False, lindisp=False,
+              rays=rays.numpy(), pick=pick.numpy(), src_poses=src_poses.numpy(),
+              focal=focal_t.numpy(), c=c_t.numpy(),
+              cam_poses=net.poses.numpy(), cam_focal=net.focal.numpy(), cam_c=net.c.numpy(),
+              cam_image_shape=net.image_shape.numpy(), latent_shape=np.asarray(enc_shape),
+              rgb_coarse=out["coarse"]["rgb"].numpy(), depth_coarse=out["coarse"]["depth"].numpy(),
+              w_coarse=out["coarse"]["weights"].numpy(),
+              rgb_fine=out["fine"]["rgb"].numpy(), depth_fine=out["fine"]["depth"].numpy(),
+              # every 4th ray's fine sample positions / every 8th ray's fine weights keep the fixture under 1 MB
+              z_fine_sub=z_f[::4].numpy(), w_fine_sub=out["fine"]["weights"][0, ::8].numpy(),
+              z_coarse_sub=z_c[::16].numpy())
+    print(f"dtu_full_ns3: R={n_rays} mean sum(w_coarse)={float(out['coarse']['weights'].sum(-1).mean()):.3f} "
+          f"mean sum(w_fine)={float(out['fine']['weights'].sum(-1).mean()):.3f} "
+          f"depth range [{float(out['fine']['depth'].min()):.3f}, {float(out['fine']['depth'].max()):.3f}]")
+    return fx
+
+
 def main():
     torch.manual_seed(0)
     ConfigTree, make_model, NeRFRenderer = load_reference()
     args = (ConfigTree, make_model, NeRFRenderer)
+    if "--rays-only" in sys.argv:   # the rays_*.npz fixtures alone
+        rays_cases()
+        return
+    if "--dtu-full-only" in sys.argv:
+        fx = case_dtu_full(*args)
+        np.savez_compressed(os.path.join(HERE, f"full_{fx['name']}.npz"), **fx)
+        return
     if "--grad-only" in sys.argv:   # the grad_*.npz fixtures alone (the render/sampling ones are left untouched)
         grad_cases(args)
         return
@@ -294,6 +391,9 @@ def main():
     for fx in cases:
         np.savez_compressed(os.path.join(HERE, f"render_{fx['name']}.npz"), **fx)
     grad_cases(args)
+    rays_cases()
+    fx = case_dtu_full(*args)
+    np.savez_compressed(os.path.join(HERE, f"full_{fx['name']}.npz"), **fx)
 
 
 def grad_cases(args):

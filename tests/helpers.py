@@ -37,6 +37,32 @@ def render_case_inputs(fx):
     )
 
 
+def full_case_inputs(fx, rays_slice=None):
+    """Rebuild the inputs of the real-size full_*.npz fixture (BASELINE config 4: 300 x 400, NS = 3, 150 x 200 latent,
+    per-ray bounds; tests/golden/make_golden.py: case_dtu_full).  rays_slice: optional index array into its rays."""
+    seed = int(fx["seed"])
+    shape = [int(v) for v in fx["latent_shape"]]
+    rays = torch.from_numpy(fx["rays"])
+    n = rays.shape[1]
+    draws = syn.draws(seed + 6, n, 64, 16, 16)
+    if rays_slice is not None:
+        rays = rays[:, rays_slice]
+        draws = {k: v[rays_slice] for k, v in draws.items()}
+    return dict(
+        wc=syn.mlp_weights(int(fx["wc_seed"])), wf=syn.mlp_weights(int(fx["wf_seed"])),
+        latent=syn.latent_maps(seed + 5, shape[0], shape[2], shape[3]), draws=draws,
+        cam=dict(poses=torch.from_numpy(fx["cam_poses"]), focal=torch.from_numpy(fx["cam_focal"]),
+                 c=torch.from_numpy(fx["cam_c"]), image_shape=torch.from_numpy(fx["cam_image_shape"])),
+        rays=rays, sb=1, ns=int(fx["ns"]), white=bool(fx["white"]), lindisp=bool(fx["lindisp"]),
+    )
+
+
+def max_abs(a, b):
+    a = a.detach().cpu().numpy() if torch.is_tensor(a) else np.asarray(a)
+    b = b.detach().cpu().numpy() if torch.is_tensor(b) else np.asarray(b)
+    return float(np.abs(a.reshape(b.shape) - b).max())
+
+
 def make_taps(idx, wt, feat_x):
     """(N,4) texel indices + (N,4) fp32 bilinear weights, embedded like pn_point_taps does it into bytes
     [96,128) of the rows of feat_x (N,64) fp16; returns the combined (N,64) fp16 tensor."""

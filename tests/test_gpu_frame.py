@@ -5,10 +5,28 @@ import numpy as np
 import pytest
 import torch
 
+from helpers import golden_files, load
 from pixelnerf_b200 import _lib
 from pixelnerf_b200.util import util
 
 pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("path", golden_files("rays_"))
+def test_gen_rays_kernel_vs_live_reference(path):
+    """pn_gen_rays against rays_*.npz = the reference's own util.gen_rays on its own util.pose_spherical poses
+    (src/util/util.py:238-276, 309-323; tests/golden/make_golden.py: rays_cases): origins and bounds are copies (bit
+    exact), unit directions within 1e-6 (the normalisation and the 3x3 product round in a different order)."""
+    fx = load(path)
+    w, h, rows = int(fx["w"]), int(fx["h"]), int(fx["pose_rows"])
+    focal = fx["focal"].tolist() if fx["focal"].ndim else float(fx["focal"])
+    c = fx["c"].tolist() if fx["c"].size else None
+    poses = torch.from_numpy(fx["poses"])[:, :rows].contiguous().cuda()
+    got = util.gen_rays(poses, w, h, focal, float(fx["near"]), float(fx["far"]), c=c)
+    assert got.is_cuda and got.shape == (poses.shape[0], h, w, 8)
+    sub = got[:, torch.from_numpy(fx["ys"]).cuda()][:, :, torch.from_numpy(fx["xs"]).cuda()].cpu().numpy()
+    assert np.array_equal(sub[..., :3], fx["rays"][..., :3]) and np.array_equal(sub[..., 6:], fx["rays"][..., 6:])
+    assert np.abs(sub[..., 3:6] - fx["rays"][..., 3:6]).max() < 1e-6
 
 
 @pytest.mark.parametrize("w,h,focal,c,rows", [

@@ -45,11 +45,11 @@ def test_render_stagewise(path):
     # (i) coarse vs the live reference's golden outputs
     assert np.abs(out.coarse.rgb.cpu().numpy() - fx["rgb_coarse"]).max() < TOL
     assert np.abs(out.coarse.weights.cpu().numpy() - fx["w_coarse"]).max() < TOL
-    assert np.abs(out.coarse.depth.cpu().numpy() - fx["depth_coarse"]).max() < TOL * 4  # world units up to ~4
+    assert np.abs(out.coarse.depth.cpu().numpy() - fx["depth_coarse"]).max() < TOL      # world units, absolute
     # (iii) fine
     assert np.abs(out.fine.rgb.cpu().numpy() - fx["rgb_fine"]).max() < TOL
     assert np.abs(out.fine.weights.cpu().numpy() - fx["w_fine"]).max() < TOL
-    assert np.abs(out.fine.depth.cpu().numpy() - fx["depth_fine"]).max() < TOL * 4
+    assert np.abs(out.fine.depth.cpu().numpy() - fx["depth_fine"]).max() < TOL
     assert out.fine.rgb.shape == (*shp, 3) and out.fine.depth.shape == shp
 
 
@@ -63,7 +63,41 @@ def test_render_end_to_end_quantile(path):
     with torch.no_grad():
         rgb, depth = par(inp["rays"].cuda())
     err = np.abs(rgb.cpu().numpy() - fx["rgb_fine"]).max(-1).reshape(-1)
-    assert np.quantile(err, 0.9) < TOL, np.sort(err)[-5:]
+    derr = np.abs(depth.cpu().numpy() - fx["depth_fine"]).reshape(-1)
+    # >= 99.9 % of the rays inside the tolerance (hard part 12): with 40-96 rays per fixture that
+    # is every ray.  On the fp32 path a coarse-pass difference of ~1e-6 flips an importance-sampling bin with
+    # probability ~1e-5 per ray, so no flip is expected here.
+    assert np.quantile(err, 0.999) < TOL, np.sort(err)[-5:]
+    assert np.quantile(derr, 0.999) < TOL, np.sort(derr)[-5:]
+
+
+def test_render_end_to_end_fp16_on_a_frame_sample():
+    """End to end (nothing teacher-forced) on the tensor-core path, 1 024 rays of BASELINE config 2 against the
+    oracle.  The fine pass is chaotic in the coarse weights: a coarse difference of d moves an importance sample into
+    the neighbouring bin with probability ~ 64 d per draw, after which one of the 96 fine positions sits elsewhere
+    and the composite changes by up to that sample's weight.  Stated bar: the coarse pass of EVERY ray within 2e-3;
+    the fine pass within 2e-3 for at least 95 % of the rays and within 2e-2 for 99.9 % (measured: profiles/
+    r02_parity.json)."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import build_net, oracle_render
+    sc = syn.scene("srn_car")
+    wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
+    n = 1024
+    rays = sc["rays"][torch.linspace(0, sc["rays"].shape[0] - 1, n).long()]
+    draws = syn.draws(3, n, 64, 16, 16)
+    ref = oracle_render(sc, wc, wf, rays, draws)
+    net, ren = build_net(sc, wc, wf, torch.device("cuda"), mlp_precision="fp16")
+    ren.injected_draws = {k: v.cuda() for k, v in draws.items()}
+    with torch.no_grad():
+        out = ren(net, rays[None].cuda(), want_weights=True)
+    assert (out.coarse.rgb[0].cpu() - ref["rgb_coarse"]).abs().max().item() < 2e-3
+    assert (out.coarse.depth[0].cpu() - ref["depth_coarse"]).abs().max().item() < 2e-3
+    assert (out.coarse.weights[0].cpu() - ref["w_coarse"]).abs().max().item() < 2e-3
+    err = (out.fine.rgb[0].cpu() - ref["rgb_fine"]).abs().max(-1)[0].numpy()
+    derr = (out.fine.depth[0].cpu() - ref["depth_fine"]).abs().numpy()
+    for e in (err, derr):
+        assert np.mean(e < 2e-3) >= 0.95, (np.mean(e < 2e-3), np.sort(e)[-5:])
+        assert np.quantile(e, 0.999) < 2e-2, np.sort(e)[-5:]
 
 
 def test_chunked_equals_unchunked_and_wrapper_contract():

@@ -6,7 +6,7 @@ import torch
 
 import oracle
 from oracle import model as omodel
-from helpers import golden_files, load, render_case_inputs
+from helpers import full_case_inputs, golden_files, load, render_case_inputs
 
 
 @pytest.mark.parametrize("path", golden_files("sampling_"))
@@ -113,3 +113,55 @@ def test_gradients_match_reference_autograd(path):
     worst["latent"] = np.abs(lat.grad[:, ::16, ::4, ::4].numpy() - fx["g.latent"]).max() / float(fx["gmax.latent"])
     bad = {k: v for k, v in worst.items() if v > 2e-4}
     assert not bad, bad
+
+
+def test_oracle_matches_reference_on_the_real_size_dtu_slice():
+    """BASELINE config 4 at its real size (300 x 400, 150 x 200 latent, NS = 3, per-ray bounds): the oracle on 96 of
+    the fixture's 2 048 rays -- half from the contiguous run, half from the frame-wide lattice -- against the live
+    reference's outputs, sample positions bit for bit."""
+    fx = load(golden_files("full_")[0])
+    pick = np.concatenate([np.arange(0, 48), np.arange(1024, 2048, 21)[:48]])
+    inp = full_case_inputs(fx, pick)
+    rays = inp["rays"].reshape(-1, 8)
+
+    def net_fn(xyz, dirs, coarse):
+        return omodel.net_forward(inp["wc"] if coarse else inp["wf"], inp["latent"], inp["cam"], inp["ns"], xyz, dirs)
+    with torch.no_grad():
+        out = oracle.render_rays(net_fn, rays, 1, 64, 32, 16, inp["draws"], depth_std=0.01, white_bkgd=False,
+                                 lindisp=False)
+    tol = dict(rtol=0, atol=1e-5)
+    np.testing.assert_allclose(out["rgb_coarse"].numpy(), fx["rgb_coarse"][0, pick], **tol)
+    np.testing.assert_allclose(out["w_coarse"].numpy(), fx["w_coarse"][0, pick], **tol)
+    np.testing.assert_allclose(out["depth_coarse"].numpy(), fx["depth_coarse"][0, pick], **tol)
+    np.testing.assert_allclose(out["rgb_fine"].numpy(), fx["rgb_fine"][0, pick], **tol)
+    np.testing.assert_allclose(out["depth_fine"].numpy(), fx["depth_fine"][0, pick], **tol)
+    sub4 = [i for i, r in enumerate(pick) if r % 4 == 0]
+    assert np.array_equal(out["z_fine"].numpy()[sub4], fx["z_fine_sub"][pick[sub4] // 4])
+    sub16 = [i for i, r in enumerate(pick) if r % 16 == 0]
+    assert np.array_equal(out["z_coarse"].numpy()[sub16], fx["z_coarse_sub"][pick[sub16] // 16])
+
+
+@pytest.mark.parametrize("path", golden_files("rays_"))
+def test_host_ray_generation_matches_the_live_reference(path):
+    """util.gen_rays / pose_spherical (src/util/util.py:238-276, 309-323): the package's host code path and the
+    synthetic-scene builder against rays produced by the reference's own functions."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.util import util
+    fx = load(path)
+    w, h, rows = int(fx["w"]), int(fx["h"]), int(fx["pose_rows"])
+    focal = fx["focal"].tolist() if fx["focal"].ndim else float(fx["focal"])
+    c = fx["c"].tolist() if fx["c"].size else None
+    near, far = float(fx["near"]), float(fx["far"])
+    poses = torch.stack([util.pose_spherical(float(a), float(fx["elev"]), float(fx["radius"])) for a in fx["angles"]])
+    assert np.array_equal(poses.numpy(), fx["poses"])                       # same op order: bit for bit
+    rays = util.gen_rays(poses[:, :rows].contiguous(), w, h, focal, near, far, c=c)
+    sub = rays[:, fx["ys"]][:, :, fx["xs"]].numpy()
+    assert sub.shape == fx["rays"].shape
+    assert np.array_equal(sub[..., :3], fx["rays"][..., :3]) and np.array_equal(sub[..., 6:], fx["rays"][..., 6:])
+    assert np.abs(sub[..., 3:6] - fx["rays"][..., 3:6]).max() < 1e-6
+    # the synthetic scene builder (numpy poses, one pose at a time) states the same camera model
+    for i, a in enumerate(fx["angles"][:2]):
+        p = syn.pose_spherical(float(a), float(fx["elev"]), float(fx["radius"]))
+        assert np.abs(p.numpy() - fx["poses"][i]).max() < 1e-6
+        r = syn.gen_rays(p, w, h, focal if np.ndim(focal) else float(focal), near, far, c)
+        assert np.abs(r[fx["ys"]][:, fx["xs"]].numpy() - fx["rays"][i]).max() < 2e-6
