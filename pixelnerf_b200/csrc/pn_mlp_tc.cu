@@ -15,7 +15,8 @@
 // Tensor memory (512 columns per CTA, all used).  In the M=128 pair layout a 64 x 256 fp32
 // accumulator takes 128 columns: lanes 0-63 hold output features [0,128) of the block, lanes
 // 64-127 features [128,256).  Columns [0,256) hold the fp32 residual stream h (two 256-wide
-// blocks), columns [256,512) hold t = fc_0(relu(h)) (and lin_out's result).  h is never
+// blocks), columns [256,512) hold t = fc_0(relu(h)).  lin_out (4 outputs) and the head are evaluated
+// in fp32 by the epilogue warps straight from h (head_ffma).  h is never
 // rounded: fc_1 accumulates into it in place (tcgen05.mma accumulate); before blocks 0-2 the
 // epilogue adds the lin_z table blend (all biases up to there folded into the tables) with a
 // tcgen05.ld / tcgen05.st read-modify-write while h is quiescent, later biases are added as a
@@ -74,15 +75,14 @@ static_assert(kSmemAlloc <= 227 * 1024, "shared memory budget");
 
 constexpr uint32_t kColH = 0, kColT = 256;  // TMEM column bases
 constexpr uint32_t kIdesc = idesc_f16(128, 256);
-// lin_out has 8 real output rows (4 hi + 4 lo): N = 16 over the pair, i.e. the first 8 rows of each CTA's box
-constexpr uint32_t kIdescOut = idesc_f16(128, 16);
 
 // Packed weights: 15 layers of [512 features][512 K] fp16 (lin_in and lin_out zero padded).
 constexpr int kLayers = 15;
 constexpr int L_IN = 0, L_Z0 = 1, L_FC = 4, L_OUT = 14;
 constexpr size_t kPackedWeightBytes = (size_t)kLayers * 512 * 512 * 2;
-// Bias table: rows 0-5 cumulative residual bias cb_0..cb_5, rows 6-10 fc_0 biases, then b_out[4].
-constexpr int kBiasFloats = 11 * 512 + 4;
+// Bias table: rows 0-5 cumulative residual bias cb_0..cb_5, rows 6-10 fc_0 biases, row 11 b_out[4], rows 12-15 the
+// four fp32 rows of lin_out.weight (the head runs on the CUDA cores in fp32, see head_ffma).
+constexpr int kBiasFloats = 16 * 512;
 constexpr size_t kBiasBytes = ((size_t)kBiasFloats * 4 + 255) / 256 * 256;
 
 struct ChainParams {
@@ -281,12 +281,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         load_fc(L_FC + 2 * b);
         load_fc(L_FC + 2 * b + 1);
       }
-      if (has_head) {
-        load_w(S0{}, L_OUT, 0, 0, 1);
-        load_w(S1{}, L_OUT, 0, 2, 3);
-        load_w(S2{}, L_OUT, 0, 4, 5);
-        load_w(S3{}, L_OUT, 0, 6, 7);
-      }
+      // lin_out needs no weight tiles: the head is evaluated in fp32 by the epilogue warps (head_ffma)
     }
   } else if (warp == 1 && rank == 0) {
     // =============================== MMA issuer (leader CTA) ================================
@@ -300,8 +295,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // descriptor = constant high word | (address >> 4): only the low word changes per MMA
     const uint64_t desc_hi = smem_desc_k128(0);
     // One weight stage: nk K=16 steps; A steps [0,4) come from a0, [4,8) from a1 (64-wide chunks).
-    auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask,
-                    uint32_t idesc = kIdesc) {
+    auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask) {
+      constexpr uint32_t idesc = kIdesc;
       constexpr uint32_t ws = decltype(stage_c)::value;
       wait_bar<false>(bar(BAR_W_FULL + ws), (wpar >> ws) & 1u, p.err, 0x200 + ws);
       wpar ^= 1u << ws;
@@ -378,21 +373,11 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         gemm_act(kColT, true, 1);              // t = fc_0(relu(h))
         gemm_act(kColH, false, 0);             // h += fc_1(relu(t))
       }
-      if (has_head) {
-        wait_act(0);
-        item(S0{}, act, act + kChunkBytes, kColT, true, 0xFFu, kIdescOut);
-        item(S1{}, act + 2 * kChunkBytes, act + 3 * kChunkBytes, kColT, false, 0xFFu, kIdescOut);
-        wait_act(4);
-        item(S2{}, act + 4 * kChunkBytes, act + 5 * kChunkBytes, kColT, false, 0xFFu, kIdescOut);
-        item(S3{}, act + 6 * kChunkBytes, act + 7 * kChunkBytes, kColT, false, 0xFFu, kIdescOut);
-        commit(BAR_ACC + 2);
-        ++gen;
-      } else {
-        // the epilogue is still reading h out of tensor memory: wait for its drain signal
-        wait_act(0);
-        wait_act(4);
-        ++gen;
-      }
+      // The epilogue is still reading h out of tensor memory -- for the fp32 head (lin_out on the CUDA cores) or
+      // for the dump that ends a per-view segment: wait for its drain signal before the next tile's lin_in clears h.
+      wait_act(0);
+      wait_act(4);
+      ++gen;
     }
   } else if (warp >= kEpiWarp0) {
     // =============================== epilogue warps (both CTAs) =============================
@@ -696,6 +681,80 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
     };
 
+    // lin_out + head (resnetfc.py:183, models.py:257-266) in fp32 on the CUDA cores.  The four outputs are the one
+    // place where rounding the operand to fp16 shows: sigma = w . relu(h_5) sums 512 rounded activations against
+    // the largest weights of the network, an error that goes straight into alpha (a float64 ablation on the
+    // real-size DTU slice: 1.8e-3 of the 2.4e-3 depth error caused by activation rounding came from this one layer).
+    // Every epilogue thread already holds its 128 of the row's 512 values of h_5 in fp32, so it forms its part of
+    // the four dot products (512 FFMA per thread and tile against warp-uniform weight loads); the four threads of
+    // a row meet through 4 KB of the tile's x slot (free since block 2's table gather) and one of them applies
+    // sigmoid / relu and stores.  No tensor-core work, no ACT operand, no weight tiles for this layer.
+    auto head_ffma = [&](int64_t grow, uint32_t xslot) {
+      const float* bias_vec = p.bias + 5 * 512;
+      const float* w_out = p.bias + 12 * 512;
+      float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+      const bool dbg = p.debug_h != nullptr && p.debug_stage == 5;
+#pragma unroll 1
+      for (int nb = 0; nb < 2; ++nb) {
+        const int c0 = nb * 4 + 2 * hf;
+        const uint32_t tcol = tmem_base + lane_addr + kColH + nb * 128 + ch * 32;
+        wait_bar<false>(bar(BAR_ACC + nb), n_acc[nb] & 1, p.err, 0x320 + nb);
+        ++n_acc[nb];
+        tc_fence_after();
+        if (dbg) dump_block(tcol, bias_vec, nb, p.debug_h, grow);
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+          const int n0 = c0 * 64 + 64 * half + 32 * ch;
+          float x[32];
+          ld_bias32(bias_vec + n0, x);
+          uint32_t v[32];
+          tmem_ld_32x32(tcol + half * 64, v);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) x[i] += __uint_as_float(v[i]);
+          if (kSave)   // slot 10: relu(h_5), the operand of lin_out's weight gradient
+            save_relu32(&map_s, stage, lane, n0, (int64_t)10 * p.save_rows + (grow - lane), grow - lane < p.n_rows, x);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4* wj = reinterpret_cast<const float4*>(w_out + j * 512 + n0);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 w4 = __ldg(wj + i);     // warp-uniform address: one broadcast transaction
+              acc[j] = fmaf(fmaxf(x[4 * i], 0.0f), w4.x, acc[j]);
+              acc[j] = fmaf(fmaxf(x[4 * i + 1], 0.0f), w4.y, acc[j]);
+              acc[j] = fmaf(fmaxf(x[4 * i + 2], 0.0f), w4.z, acc[j]);
+              acc[j] = fmaf(fmaxf(x[4 * i + 3], 0.0f), w4.w, acc[j]);
+            }
+          }
+        }
+        // h_5 of this block is in registers: the next tile's lin_in may overwrite it
+        tc_fence_before();
+        signal_chunk(c0);
+        signal_chunk(c0 + 1);
+      }
+      const uint32_t slot4 = xslot + (uint32_t)(((hf * 2 + ch) * kRows + r) * 16);
+      st_shared_v4(slot4, __float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
+      asm volatile("bar.sync 1, 256;" ::: "memory");     // the eight epilogue warps of this CTA
+      if (hf == 0 && ch == 0) {
+        float s[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {    // fixed order: deterministic from run to run
+          const uint4 t = ld_shared_v4(xslot + (uint32_t)((g * kRows + r) * 16));
+          s[0] += __uint_as_float(t.x); s[1] += __uint_as_float(t.y);
+          s[2] += __uint_as_float(t.z); s[3] += __uint_as_float(t.w);
+        }
+        if (grow < p.n_rows) {
+          const float4 bo = __ldg(reinterpret_cast<const float4*>(p.bias + 11 * 512));
+          const float s0 = s[0] + bo.x, s1 = s[1] + bo.y, s2 = s[2] + bo.z, s3 = s[3] + bo.w;
+          if (p.pre) p.pre[grow] = make_float4(s0, s1, s2, s3);
+          p.out[grow] = make_float4(1.0f / (1.0f + expf(-s0)), 1.0f / (1.0f + expf(-s1)),
+                                    1.0f / (1.0f + expf(-s2)), fmaxf(s3, 0.0f));
+        }
+      }
+      // the slot is refilled by TMA two tiles from now: order these generic-proxy accesses in front of it
+      fence_proxy_async_smem();
+    };
+
     uint32_t xs = 0;   // x slot of the current tile (the producer fills the slots round robin)
     for (int tile = cluster_id; tile < tile_end; tile += n_clusters) {
       const int64_t grow = (int64_t)tile * kTileRows + rank * kRows + r;
@@ -708,28 +767,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         epi(1, p.bias + (6 + b) * 512, -1, 0u, 0, grow, false, 2 * b + 1);
       }
       if (has_head) {
-        epi(0, p.bias + 5 * 512, -1, 0u, 0, grow, p.debug_h != nullptr && p.debug_stage == 5, 10);
-        // lin_out result: features 0-3 of block 0 = lanes 0-63, columns kColT..+3
-        wait_bar<false>(bar(BAR_ACC + 2), n_acc[2] & 1, p.err, 0x310);
-        ++n_acc[2];
-        tc_fence_after();
-        if (hf == 0 && ch == 0) {
-          uint32_t v[8];   // columns 0-3: x W_hi, 4-7: x (W - W_hi) * 2^10
-          tmem_ld_32x8(tmem_base + lane_addr + kColT, v);
-          tmem_wait_ld();
-          if (grow < p.n_rows) {
-            const float4 bo = __ldg(reinterpret_cast<const float4*>(p.bias + 11 * 512));
-            const float k = 1.0f / 1024.0f;
-            const float s0 = (__uint_as_float(v[0]) + k * __uint_as_float(v[4])) + bo.x;
-            const float s1 = (__uint_as_float(v[1]) + k * __uint_as_float(v[5])) + bo.y;
-            const float s2 = (__uint_as_float(v[2]) + k * __uint_as_float(v[6])) + bo.z;
-            const float s3 = (__uint_as_float(v[3]) + k * __uint_as_float(v[7])) + bo.w;
-            if (p.pre) p.pre[grow] = make_float4(s0, s1, s2, s3);
-            p.out[grow] = make_float4(1.0f / (1.0f + expf(-s0)), 1.0f / (1.0f + expf(-s1)),
-                                      1.0f / (1.0f + expf(-s2)), fmaxf(s3, 0.0f));
-          }
-        }
-        tc_fence_before();
+        head_ffma(grow, xslot);
       } else {
         epi(0, p.bias + p.last_block * 512, -1, 0u, 1, grow, false, -1);
       }
@@ -749,10 +787,10 @@ pack_weights_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
   if (i >= (int64_t)kLayers * 512 * 512) return;
   const int layer = (int)(i / (512 * 512));
   const int n = (int)((i / 512) % 512), k = (int)(i % 512);
-  // fp16 rounding of the weights is the one error that is coherent over all samples of a ray (the same
-  // perturbed network everywhere); lin_in and lin_out carry 60 % of it and are the two
-  // cheap layers, so they are stored as hi + lo: lin_in's lo part in K columns [64, 64+42) (the x chunk is
-  // multiplied by both), lin_out's lo part, scaled by 2^10 into the normal range, in the spare output rows 4-7.
+  // fp16 rounding of the weights is an error that is coherent over all samples of a ray (the same perturbed
+  // network everywhere); lin_in is cheap and carries a large share of it, so it is stored as
+  // hi + lo: the lo part in K columns [64, 64+42) (the x chunk is multiplied by both).  lin_out no longer runs on
+  // the tensor cores at all (fp32 head on the CUDA cores, head_ffma); its slot of the packed buffer is unused.
   float v = 0.0f;
   if (layer == L_IN) {
     if (k < PN_D_CODE) {
@@ -791,7 +829,8 @@ pack_bias_kernel(pn_mlp_weights_t w, float* __restrict__ ta, float* __restrict__
   tb[4 * 512 + n] = w.fc1_b[3][n];
   tb[5 * 512 + n] = w.fc1_b[3][n] + w.fc1_b[4][n];
   for (int b = 0; b < 5; ++b) ta[(6 + b) * 512 + n] = tb[(6 + b) * 512 + n] = w.fc0_b[b][n];
-  if (n < 4) ta[11 * 512 + n] = tb[11 * 512 + n] = w.lin_out_b[n];
+  ta[11 * 512 + n] = tb[11 * 512 + n] = n < 4 ? w.lin_out_b[n] : 0.0f;
+  for (int j = 0; j < 4; ++j) ta[(12 + j) * 512 + n] = tb[(12 + j) * 512 + n] = w.lin_out_w[j * 512 + n];
 }
 
 // ---- host side ----------------------------------------------------------------------------

@@ -14,7 +14,7 @@ import torch
 
 import oracle
 from oracle import model as omodel
-from helpers import emulate_tc_chain, golden_files, load, make_taps, render_case_inputs
+from helpers import emulate_tc_chain, golden_files, load, make_taps, render_case_inputs, tc_depth_tol
 from test_gpu_model import _net_for
 
 pytestmark = pytest.mark.gpu
@@ -123,7 +123,8 @@ def test_render_stagewise_fp16(path):
     for part, tag in ((out.coarse, "coarse"), (out.fine, "fine")):
         assert np.abs(part.rgb.cpu().numpy() - fx["rgb_" + tag]).max() < TC_TOL, tag
         assert np.abs(part.weights.cpu().numpy() - fx["w_" + tag]).max() < TC_TOL, tag
-        assert np.abs(part.depth.cpu().numpy() - fx["depth_" + tag]).max() < TC_TOL, tag     # world units, absolute
+        # world units, absolute; 2e-3 except the stated DTU-class deviation (helpers.TC_DEPTH_TOL_DTU)
+        assert np.abs(part.depth.cpu().numpy() - fx["depth_" + tag]).max() < tc_depth_tol(fx["name"]), tag
 
 
 def test_unimplemented_operand_format_raises():
