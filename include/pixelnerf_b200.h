@@ -227,6 +227,25 @@ PN_API int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t n_t
                       float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                       const pn_mlp_tc_debug_t* dbg, pn_stream_t stream);
 
+/* pn_mlp_forward_tc for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and arithmetic as pn_mlp_forward_tc (bit-identical results), but the workspace is a
+ * file-scope device array of PN_STATIC_SCRATCH_BYTES inside the library (csrc/pn_noalloc.cu) instead of a caller
+ * buffer; the call performs no cudaMalloc / cudaFree and calls no allocating routine.  The caller still provides
+ * every input and output buffer.
+ *   - Limit: pn_mlp_tc_workspace_bytes(n_rows, n_views) must be <= PN_STATIC_SCRATCH_BYTES (32 MiB), i.e. any row
+ *     count when n_views == 1 (256 bytes of scratch) and at most 32 767 (view, point) rows when n_views > 1 (1 KB
+ *     per row); beyond that the call returns PN_ERR_INVALID with the sizes in pn_last_error().
+ *   - Cost: every GPU that loads the library holds the 32 MiB until the process exits.
+ *   - Sharing: all calls on a device use the same array, which keeps the previous call's contents; the call clears
+ *     what must start at zero (the watchdog error word) itself.  Calls that overlap on the GPU (different streams
+ *     or host threads on one device) RACE on the array: serialise them.  The launch uses the current device. */
+#define PN_STATIC_SCRATCH_BYTES (32u << 20)
+PN_API size_t pn_static_scratch_bytes(void);
+PN_API int pn_mlp_forward_tc_static(const void* packed, const void* tables, int64_t n_texels,
+                             const void* feat_x, int n_objects, int n_views, int64_t points_per_object,
+                             float* out, float* pre_act, pn_stream_t stream);
+
 /* ---- (3c) tensor-core GEMMs of the training path (dgrad / wgrad of the 512-wide linears) -- */
 
 /* D[rows, n] = scale * A[rows, k] x B[k, n]  (both row-major 16-bit of the SAME format, 0 = fp16 or 1 = bf16; k % 64 == 0,

@@ -89,6 +89,9 @@ _SIGNATURES = {
     "pn_prepare_weights": (_int, [C.POINTER(MlpWeights), _vp, _sz, _vp]),
     "pn_mlp_tc_workspace_bytes": (_sz, [_i64, _int]),
     "pn_mlp_forward_tc": (_int, [_vp, _vp, _i64, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp, _vp]),
+    # no-allocation variant of pn_mlp_forward_tc (scratch in a static device array, csrc/pn_noalloc.cu)
+    "pn_static_scratch_bytes": (_sz, []),
+    "pn_mlp_forward_tc_static": (_int, [_vp, _vp, _i64, _vp, _int, _int, _i64, _vp, _vp, _vp]),
     "pn_point_taps": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp]),
     "pn_latent_tables_bytes": (_sz, [_i64]),
     "pn_prepare_latent_tables": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp, _sz, _vp]),
