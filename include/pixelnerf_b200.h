@@ -227,6 +227,28 @@ PN_API int pn_mlp_forward_tc(const void* packed, const void* tables, int64_t n_t
                       float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                       const pn_mlp_tc_debug_t* dbg, pn_stream_t stream);
 
+/* n_views > 1 in ONE launch, with the view mean (combine_interleaved, src/util/util.py:461-466, at block 3,
+ * src/model/resnetfc.py:152-172) taken on chip.  pn_point_taps_grouped writes the rows of pn_point_taps in GROUPED
+ * order: points are numbered object-major (SB * points_per_object of them); super-tile S holds points [128 S, 128 S + 128)
+ * as one 128-row block per view -- row (S * n_views + v) * 128 + m = view v of point 128 S + m; rows of points past the
+ * end are zero.  feat_x_grouped holds pn_point_taps_grouped_rows(n_points, n_views) rows of 128 bytes.
+ * pn_mlp_forward_tc_grouped runs blocks 0-2 on the n_views blocks of a super-tile one after the other; row m of every
+ * block is point m, so each epilogue thread keeps a running fp32 sum of its row's h over the views (in view order, like
+ * torch.mean's sum; parked in the workspace between blocks, 128 KB per CTA, L2 resident), divides by n_views, rounds
+ * the mean to fp16 ONCE (the two-launch form rounds every view's h to fp16 before the mean) and continues with blocks
+ * 3-4 and the head on the same 128 rows, now one per point: no per-row HBM hand-off, no second launch.  out / pre_act (SB*P, 4) as pn_mlp_forward_tc.
+ * workspace: pn_mlp_tc_grouped_workspace_bytes(), 256-byte aligned.  Inference only (the training forward keeps the
+ * two-launch form whose saved operands the backward reads). */
+PN_API int64_t pn_point_taps_grouped_rows(int64_t n_points, int n_views);
+PN_API int pn_point_taps_grouped(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
+                          const float* xyz, const float* viewdirs, int64_t points_per_object,
+                          void* feat_x_grouped, pn_stream_t stream);
+PN_API size_t pn_mlp_tc_grouped_workspace_bytes(void);
+PN_API int pn_mlp_forward_tc_grouped(const void* packed, const void* tables, int64_t n_texels,
+                              const void* feat_x_grouped, int n_objects, int n_views, int64_t points_per_object,
+                              float* out, float* pre_act, void* workspace, size_t workspace_bytes,
+                              pn_stream_t stream);
+
 /* pn_mlp_forward_tc for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
  * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
  * Same inputs, outputs and arithmetic as pn_mlp_forward_tc (bit-identical results), but the workspace is a

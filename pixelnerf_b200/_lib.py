@@ -92,6 +92,11 @@ _SIGNATURES = {
     # no-allocation variant of pn_mlp_forward_tc (scratch in a static device array, csrc/pn_noalloc.cu)
     "pn_static_scratch_bytes": (_sz, []),
     "pn_mlp_forward_tc_static": (_int, [_vp, _vp, _i64, _vp, _int, _int, _i64, _vp, _vp, _vp]),
+    # n_views > 1 in one launch: grouped row order + on-chip view mean
+    "pn_point_taps_grouped_rows": (_i64, [_i64, _int]),
+    "pn_point_taps_grouped": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp]),
+    "pn_mlp_tc_grouped_workspace_bytes": (_sz, []),
+    "pn_mlp_forward_tc_grouped": (_int, [_vp, _vp, _i64, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp]),
     "pn_point_taps": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp]),
     "pn_latent_tables_bytes": (_sz, [_i64]),
     "pn_prepare_latent_tables": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp, _sz, _vp]),
@@ -428,6 +433,41 @@ def point_taps(cam_bufs, hl, wl, ppo, *, rays=None, z=None, xyz=None, viewdirs=N
     return feat_x
 
 
+def point_taps_grouped(cam_bufs, hl, wl, ppo, *, rays=None, z=None, xyz=None, viewdirs=None):
+    """point_taps in GROUPED row order for mlp_forward_tc_grouped (n_views > 1): row (S * n_views + v) * 128 + m =
+    view v of point 128 S + m of the flattened (object, point) index (include/pixelnerf_b200.h)."""
+    cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
+                 cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
+    n_rows = int(lib().pn_point_taps_grouped_rows(cam.n_objects * ppo, cam.n_views))
+    feat_x = torch.empty(n_rows, 64, device=cam_bufs["poses"].device, dtype=torch.float16)
+    rays, z, xyz, viewdirs = _f32c(rays), _f32c(z), _f32c(xyz), _f32c(viewdirs)
+    k = 0 if z is None else z.shape[-1]
+    with _Timed("features"):
+        _check(lib().pn_point_taps_grouped(C.byref(cam), _ptr(rays), _ptr(z), k, _ptr(xyz), _ptr(viewdirs), ppo,
+                                           feat_x.data_ptr(), _stream()), "pn_point_taps_grouped")
+    return feat_x
+
+
+def mlp_forward_tc_grouped(packed, tables, feat_x_grouped, n_objects, n_views, ppo, want_pre=False):
+    """The tensor-core chain for n_views > 1 in one launch (view mean on chip); feat_x_grouped from
+    point_taps_grouped.  -> (SB*ppo, 4) [sigmoid rgb, relu sigma]."""
+    dev = feat_x_grouped.device
+    n_rows = int(lib().pn_point_taps_grouped_rows(n_objects * ppo, n_views))
+    if feat_x_grouped.shape != (n_rows, 64) or feat_x_grouped.dtype != torch.float16 or not feat_x_grouped.is_contiguous():
+        raise RuntimeError("grouped tensor-core MLP needs contiguous fp16 feat_x of shape (grouped rows, 64)")
+    if tables.dtype != torch.float16 or tables.dim() != 3 or tables.shape[0] != COMBINE_LAYER or not tables.is_contiguous():
+        raise RuntimeError("tensor-core MLP needs contiguous fp16 lin_z tables of shape (3, texels, 512)")
+    out = torch.empty(n_objects * ppo, 4, device=dev, dtype=torch.float32)
+    pre = torch.empty_like(out) if want_pre else None
+    nbytes = lib().pn_mlp_tc_grouped_workspace_bytes()
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    with _Timed("mlp"):
+        _check(lib().pn_mlp_forward_tc_grouped(packed.data_ptr(), tables.data_ptr(), tables.shape[1],
+                                               _ptr(feat_x_grouped, torch.float16), n_objects, n_views, ppo, _ptr(out),
+                                               _ptr(pre), ws.data_ptr(), nbytes, _stream()), "pn_mlp_forward_tc_grouped")
+    return (out, pre) if want_pre else out
+
+
 def prepare_latent_tables(w, latent_nhwc):
     """Per-texel lin_z tables (3, V*Hl*Wl, 512) fp16 of one MLP for the tensor-core chain.  fp32 NHWC latent: the
     fp32 CUDA-core product (once per encode: inference); fp16 NHWC latent: the tensor-core product with hi + lo
@@ -736,7 +776,7 @@ def mlp_backward_tc(packed32, w16, feat_x, latent_nhwc, n_objects, n_views, ppo,
 for _name in ("sample_coarse", "sample_fine", "prepare_latent", "point_features", "mlp_forward_fp32",
               "mlp_forward_fp32_train", "mlp_backward_fp32", "point_features_bwd", "depth_sample_bwd", "point_taps",
               "prepare_latent_tables", "pack_weights_tc", "mlp_forward_tc", "composite_fwd", "composite_bwd",
-              "render_rays", "gen_rays", "encoder_latent", "frame_to_u8", "gemm_tc_rows", "gemm_tc_rows_slabs",
+              "point_taps_grouped", "mlp_forward_tc_grouped", "render_rays", "gen_rays", "encoder_latent", "frame_to_u8", "gemm_tc_rows", "gemm_tc_rows_slabs",
               "gemm_tc_wgrad", "mlp_forward_tc_train", "pack_weights_bf16", "mlp_backward_tc"):
     globals()[_name] = _on_device(globals()[_name])
 del _name

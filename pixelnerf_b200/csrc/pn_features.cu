@@ -123,20 +123,36 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
                       const float* __restrict__ rays, const float* __restrict__ zs, int n_samples,
                       const float* __restrict__ xyz_in, const float* __restrict__ dirs_in,
                       int64_t ppo, OutT* __restrict__ feat_z, OutT* __restrict__ feat_x, int ldx,
-                      int64_t n_rows, uint4* __restrict__ taps) {
+                      int64_t n_rows, uint4* __restrict__ taps, int group = 0) {
   __shared__ __align__(16) unsigned char stage_all[kTaps ? kFeatWarps * 32 * kTapsPitch : 16];
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5)) * 32;
   if (row0 >= n_rows) return;
   const int64_t row = row0 + lane;
-  const bool valid = row < n_rows;
+  bool valid = row < n_rows;
   unsigned char* stage = stage_all + (kTaps ? (threadIdx.x >> 5) * 32 * kTapsPitch : 0);
   uint32_t o00 = 0, o01 = 0, o10 = 0, o11 = 0;
   float w00 = 0.f, w01 = 0.f, w10 = 0.f, w11 = 0.f;
+  // row = (obj * NS + view) * P + p ...
+  int64_t ov = row / ppo;
+  int64_t p = row - ov * ppo;
+  if (kTaps && group > 0) {
+    // ... or, grouped order (pn_point_taps_grouped, for the chain's on-chip view mean): super-tile S = 128 points
+    // [128 S, 128 S + 128) of the flattened (object, point) index, one 128-row block per view:
+    // row (S * n_views + v) * 128 + m = view v of point 128 S + m; points past the end are zero rows (zero taps weights)
+    const int64_t blk = row >> 7;
+    const int v = (int)(blk % cam.n_views);
+    const int64_t q = (blk / cam.n_views) * 128 + (row & 127);
+    valid = q < (int64_t)cam.n_objects * ppo;
+    const int64_t obj_q = q / ppo;
+    p = q - obj_q * ppo;
+    ov = obj_q * cam.n_views + v;
+    if (!valid) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(stage + lane * kTapsPitch + 16 * i) = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
   if (valid) {
-    // row = (obj * NS + view) * P + p
-    const int64_t ov = row / ppo;
-    const int64_t p = row - ov * ppo;
     const int view = (int)ov;
     const int obj = view / cam.n_views;
     float x, y, z, dx, dy, dz;
@@ -576,6 +592,32 @@ extern "C" int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc
         *cam, (const __half*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
         (__half*)feat_z, (__half*)feat_x, ldx, n_rows, nullptr);
   PN_LAUNCH_OK("point_features_kernel");
+  pn::count_launch();
+  return PN_OK;
+}
+
+extern "C" int64_t pn_point_taps_grouped_rows(int64_t n_points, int n_views) {
+  if (n_points <= 0 || n_views < 1) return 0;
+  return (n_points + 127) / 128 * 128 * n_views;
+}
+
+extern "C" int pn_point_taps_grouped(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
+                                     const float* xyz, const float* viewdirs, int64_t points_per_object,
+                                     void* feat_x, pn_stream_t stream) {
+  PN_CHECK_ARG(cam && feat_x, "pn_point_taps_grouped: null pointer");
+  PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_taps_grouped: camera buffers missing (call encode first)");
+  PN_CHECK_ARG((rays && z && n_samples > 0) || xyz, "pn_point_taps_grouped: need rays+z or xyz");
+  PN_CHECK_ARG(!rays || points_per_object % n_samples == 0, "pn_point_taps_grouped: P must be a multiple of K");
+  PN_CHECK_ARG(cam->hl > 1 && cam->wl > 1 && cam->n_objects > 0 && cam->n_views > 0, "pn_point_taps_grouped: bad camera sizes");
+  PN_CHECK_ARG((int64_t)cam->n_objects * cam->n_views * cam->hl * cam->wl < (1ll << 31), "pn_point_taps_grouped: too many texels");
+  PN_CHECK_ARG(((uintptr_t)feat_x & 127) == 0, "pn_point_taps_grouped: feat_x must be 128-byte aligned");
+  const int64_t n_rows = pn_point_taps_grouped_rows((int64_t)cam->n_objects * points_per_object, cam->n_views);
+  if (n_rows == 0) return PN_OK;
+  const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
+  pn::point_features_kernel<__half, __half, true><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+      *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
+      (uint4*)feat_x, 1);
+  PN_LAUNCH_OK("point_features_kernel(taps, grouped)");
   pn::count_launch();
   return PN_OK;
 }

@@ -74,6 +74,8 @@ constexpr int kSmemAlloc = kSmemBytes + 1024;  // slack for the manual 1024-byte
 static_assert(kSmemAlloc <= 227 * 1024, "shared memory budget");
 
 constexpr uint32_t kColH = 0, kColT = 256;  // TMEM column bases
+constexpr int kParkCtas = 192;              // fused view mean: CTAs the park buffer (64 KB each) is sized for
+constexpr size_t kParkBytesPerCta = 128 * 1024;   // 256 epilogue threads x 128 fp32
 constexpr uint32_t kIdesc = idesc_f16(128, 256);
 
 // Packed weights: 15 layers of [512 features][512 K] fp16 (lin_in and lin_out zero padded).
@@ -103,6 +105,13 @@ struct ChainParams {
   int first_block, last_block;   // [0,5] full chain, [0,3) and [3,5] when NS > 1
   int n_views;
   int debug_stage;
+  // fused view mean (kFuse, n_views > 1, pn_mlp_forward_tc_grouped): x rows arrive in grouped order (pn_point_taps_grouped:
+  // rows (S * n_views + v) * 128 + m = view v of point S * 128 + m); a "tile" of the persistent loop is a super-tile =
+  // n_views sub-tiles of blocks 0-2 (one per view, same 128 points) followed by ONE merged tile of blocks 3-4 + head
+  int group;             // != 0: fused mode
+  int64_t n_points;      // SB * ppo
+  const float* bias2;    // bias table of the merged phase (cumulative from block 3)
+  float* park;           // 128 KB per CTA: the running fp32 sum of h over the views done so far (L2 resident)
 };
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -148,7 +157,7 @@ __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
   return d;
 }
 
-template <bool kSave>
+template <bool kSave, bool kFuse = false>
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
                  const __grid_constant__ CUtensorMap map_s, const ChainParams p) {
@@ -271,6 +280,26 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
       }
       __syncwarp();
+      if constexpr (kFuse) {
+        // super-tile: n_views sub-tiles of (x, lin_in, blocks 0-2), then the merged tile's blocks 3-4
+#pragma unroll 1
+        for (int k = 0; k < p.n_views; ++k) {
+          load_a(&map_x, 0, ((tile * p.n_views + k) * 2 + (int)rank) * kRows);
+          load_w(S0{}, L_IN, 0, 0, 1);
+          load_w(S1{}, L_IN, 1, 0, 1);
+#pragma unroll 1
+          for (int b = 0; b < 3; ++b) {
+            load_fc(L_FC + 2 * b);
+            load_fc(L_FC + 2 * b + 1);
+          }
+        }
+#pragma unroll 1
+        for (int b = 3; b < 5; ++b) {
+          load_fc(L_FC + 2 * b);
+          load_fc(L_FC + 2 * b + 1);
+        }
+        continue;
+      }
       if (full_front) {
         load_a(&map_x, 0, row0);
         load_w(S0{}, L_IN, 0, 0, 1);           // hi and lo halves of lin_in
@@ -359,6 +388,40 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     };
 #pragma unroll 1
     for (int tile = cluster_id; tile < tile_end; tile += n_clusters) {
+      if constexpr (kFuse) {
+#pragma unroll 1
+        for (int k = 0; k < p.n_views; ++k) {
+          const uint32_t xa = take_a();
+          tc_fence_after();
+          item(S0{}, xa, xa, kColH, true, 0x77u);
+          item(S1{}, xa, xa, kColH + 128, true, 0x77u);
+          release_a(xa);
+          commit(BAR_ACC + 0);
+          commit(BAR_ACC + 1);
+#pragma unroll 1
+          for (int b = 0; b < 3; ++b) {
+            gemm_act(kColT, true, 1);
+            gemm_act(kColH, false, 0);
+          }
+          if (k + 1 < p.n_views) {
+            // the merge epilogue reads this sub-tile's h (and parks its view means): wait for its drain signal
+            // before the next sub-tile's lin_in clears h.  After the LAST sub-tile the merge epilogue's signals are
+            // the operand-ready signals of block 3's fc_0 instead (consumed by gemm_act below).
+            wait_act(0);
+            wait_act(4);
+            ++gen;
+          }
+        }
+#pragma unroll 1
+        for (int b = 3; b < 5; ++b) {
+          gemm_act(kColT, true, 1);
+          gemm_act(kColH, false, 0);
+        }
+        wait_act(0);     // the fp32 head has read h
+        wait_act(4);
+        ++gen;
+        continue;
+      }
       if (full_front) {
         const uint32_t xa = take_a();
         tc_fence_after();
@@ -689,9 +752,9 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // the four dot products (512 FFMA per thread and tile against warp-uniform weight loads); the four threads of
     // a row meet through 4 KB of the tile's x slot (free since block 2's table gather) and one of them applies
     // sigmoid / relu and stores.  No tensor-core work, no ACT operand, no weight tiles for this layer.
-    auto head_ffma = [&](int64_t grow, uint32_t xslot) {
-      const float* bias_vec = p.bias + 5 * 512;
-      const float* w_out = p.bias + 12 * 512;
+    auto head_ffma = [&](int64_t grow, uint32_t xslot, const float* tbl) {
+      const float* bias_vec = tbl + 5 * 512;
+      const float* w_out = tbl + 12 * 512;
       float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
       const bool dbg = p.debug_h != nullptr && p.debug_stage == 5;
 #pragma unroll 1
@@ -744,7 +807,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           s[2] += __uint_as_float(t.z); s[3] += __uint_as_float(t.w);
         }
         if (grow < p.n_rows) {
-          const float4 bo = __ldg(reinterpret_cast<const float4*>(p.bias + 11 * 512));
+          const float4 bo = __ldg(reinterpret_cast<const float4*>(tbl + 11 * 512));
           const float s0 = s[0] + bo.x, s1 = s[1] + bo.y, s2 = s[2] + bo.z, s3 = s[3] + bo.w;
           if (p.pre) p.pre[grow] = make_float4(s0, s1, s2, s3);
           p.out[grow] = make_float4(1.0f / (1.0f + expf(-s0)), 1.0f / (1.0f + expf(-s1)),
@@ -755,8 +818,108 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       fence_proxy_async_smem();
     };
 
+    // Fused view mean (kFuse; resnetfc.py:152-172, util.py:461-466), at the end of block 2 of sub-tile k_cur.
+    // Sub-tile v of a super-tile is VIEW v of the super-tile's 128 points (row m of every sub-tile = point m), so the
+    // sum over views is a per-thread running sum across sub-tiles: after sub-tile 0 the thread parks its h (fp32, 128
+    // values, written and later read by the SAME thread, piece-major so that a warp's 16-byte accesses are contiguous;
+    // L2 resident), after sub-tile v it adds its h to the parked sum -- in view order, like torch.mean's sum -- and
+    // after the last one divides by n_views, rounds the mean to fp16 once, writes it to tensor memory as the merged
+    // tile's residual stream and relu(mean) to the ACT operand: block 3 starts on the same 128 rows, now one per point.
+    auto merge = [&](int k_cur) {
+      const bool first = k_cur == 0, last = k_cur == p.n_views - 1;
+      const float* bias_vec = p.bias + 3 * 512;   // fc_1 bias of block 2 (everything earlier sits in the tables)
+      const float inv = (float)p.n_views;
+      float4* park = reinterpret_cast<float4*>(p.park) + ((size_t)blockIdx.x * 8 + (size_t)(warp - kEpiWarp0)) * (32 * 32) + lane;
+#pragma unroll 1
+      for (int nb = 0; nb < 2; ++nb) {
+        const int c0 = nb * 4 + 2 * hf;
+        const uint32_t tcol = tmem_base + lane_addr + kColH + nb * 128 + ch * 32;
+        wait_bar<false>(bar(BAR_ACC + nb), n_acc[nb] & 1, p.err, 0x330 + nb);
+        ++n_acc[nb];
+        tc_fence_after();
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+          const int piece = nb * 2 + half;
+          const int n0 = c0 * 64 + 64 * half + 32 * ch;
+          float4* pp = park + piece * 8 * 32;
+          float x[32];
+          if (first) {
+            ld_bias32(bias_vec + n0, x);
+          } else {   // the running sum of views 0 .. k_cur-1 (their biases included), requested before the accumulator
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 t4 = __ldcg(pp + i * 32);
+              x[4 * i] = t4.x; x[4 * i + 1] = t4.y; x[4 * i + 2] = t4.z; x[4 * i + 3] = t4.w;
+            }
+          }
+          uint32_t v[32];
+          tmem_ld_32x32(tcol + half * 64, v);
+          tmem_wait_ld();
+          if (first) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) x[i] += __uint_as_float(v[i]);
+          } else {
+            float bv[32];
+            ld_bias32(bias_vec + n0, bv);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) x[i] += __uint_as_float(v[i]) + bv[i];     // sum_so_far + (h_v + bias)
+          }
+          if (!last) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) __stcg(pp + i * 32, make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]));
+            continue;
+          }
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {   // mean, one fp16 rounding
+            const float2 t2 = __half22float2(__floats2half2_rn(x[2 * i] / inv, x[2 * i + 1] / inv));
+            f[2 * i] = t2.x; f[2 * i + 1] = t2.y;
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(f[i]);
+          tmem_st_32x32(tcol + half * 64, v);
+          const uint32_t dst = smem_base + kOffAct + (c0 + half) * kChunkBytes + row_off;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            st_shared_v4(dst + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
+                         pack_relu_h2(f[8 * i + 0], f[8 * i + 1]), pack_relu_h2(f[8 * i + 2], f[8 * i + 3]),
+                         pack_relu_h2(f[8 * i + 4], f[8 * i + 5]), pack_relu_h2(f[8 * i + 6], f[8 * i + 7]));
+          tmem_wait_st();
+          fence_proxy_async_smem();
+          tc_fence_before();
+          signal_chunk(c0 + half);
+        }
+        if (!last) {   // h of this block is consumed: the next sub-tile's lin_in may clear it
+          tc_fence_before();
+          signal_chunk(c0);
+          signal_chunk(c0 + 1);
+        }
+      }
+    };
+
     uint32_t xs = 0;   // x slot of the current tile (the producer fills the slots round robin)
     for (int tile = cluster_id; tile < tile_end; tile += n_clusters) {
+      if constexpr (kFuse) {
+        const int64_t none = p.n_rows;      // no per-row side outputs (debug dump, saved operands) in this mode
+        uint32_t xslot = 0;
+#pragma unroll 1
+        for (int k = 0; k < p.n_views; ++k) {
+          xslot = smem_base + kOffA + xs * kChunkBytes;
+          if (++xs == kASlots) xs = 0;
+#pragma unroll 1
+          for (int b = 0; b < 3; ++b) {
+            epi(0, p.bias + b * 512, b, xslot, 0, none, false, 2 * b);
+            epi(1, p.bias + (6 + b) * 512, -1, 0u, 0, none, false, 2 * b + 1);
+          }
+          merge(k);
+        }
+        epi(1, p.bias2 + (6 + 3) * 512, -1, 0u, 0, none, false, 7);
+        epi(0, p.bias2 + 4 * 512, -1, 0u, 0, none, false, 8);
+        epi(1, p.bias2 + (6 + 4) * 512, -1, 0u, 0, none, false, 9);
+        // row m of the merged tile = point m of the super-tile
+        head_ffma((int64_t)tile * kTileRows + rank * kRows + r, xslot, p.bias2);
+        continue;
+      }
       const int64_t grow = (int64_t)tile * kTileRows + rank * kRows + r;
       const uint32_t xslot = smem_base + kOffA + xs * kChunkBytes;
       if (++xs == kASlots) xs = 0;
@@ -767,7 +930,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         epi(1, p.bias + (6 + b) * 512, -1, 0u, 0, grow, false, 2 * b + 1);
       }
       if (has_head) {
-        head_ffma(grow, xslot);
+        head_ffma(grow, xslot, p.bias);
       } else {
         epi(0, p.bias + p.last_block * 512, -1, 0u, 1, grow, false, -1);
       }
@@ -841,15 +1004,19 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, const CUte
   if (attr_set.needed(&attr_dev)) {
     PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
     PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
+    PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
     attr_set.mark(attr_dev);
   }
   int dev = 0, sms = 0;
   PN_CUDA_OK(cudaGetDevice(&dev));
   PN_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   p.n_tiles = (int)((p.n_rows + kTileRows - 1) / kTileRows);
+  if (p.group > 0)   // fused view mean: the persistent loop runs over super-tiles of 128 points
+    p.n_tiles = (int)((p.n_points + kTileRows - 1) / kTileRows);
   // One CTA per SM, in groups of four where the GPU can co-schedule four (preferred cluster dimension) and
   // pairs elsewhere; no more groups than the tiles need.
-  const int max_groups = sms / 4;
+  int max_groups = sms / 4;
+  if (p.group > 0 && max_groups > kParkCtas / 4) max_groups = kParkCtas / 4;   // the park buffer is sized for kParkCtas CTAs
   const int want = (p.n_tiles + 1) / 2;
   const int groups = want < max_groups ? want : max_groups;
   cudaLaunchConfig_t cfg = {};
@@ -864,7 +1031,8 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, const CUte
   attrs[1].val.preferredClusterDim.x = 4; attrs[1].val.preferredClusterDim.y = 1; attrs[1].val.preferredClusterDim.z = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 2;
-  if (p.save) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<true>, mw, mx, ms, p));
+  if (p.group > 0) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false, true>, mw, mx, ms, p));
+  else if (p.save) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<true>, mw, mx, ms, p));
   else PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false>, mw, mx, ms, p));
   PN_LAUNCH_OK("mlp_chain_kernel");
   count_launch();
@@ -983,4 +1151,53 @@ static int mlp_forward_tc_impl(const void* packed, const void* tables, int64_t n
   p.bias = tb; p.n_rows = n_pts; p.first_block = 3; p.last_block = 5;
   p.debug_h = (dbg && dbg->stage >= 4) ? dbg->h : nullptr;
   return launch_chain(mw, mx, ms, p, st);
+}
+
+// ---- fused view mean: one launch for n_views > 1 -----------------------------------------------------------------
+extern "C" size_t pn_mlp_tc_grouped_workspace_bytes(void) {
+  // watchdog word + the park buffer (each CTA's running sum of h over the views of its super-tile)
+  return 256 + (size_t)pn::tc::kParkCtas * pn::tc::kParkBytesPerCta;
+}
+
+extern "C" int pn_mlp_forward_tc_grouped(const void* packed, const void* tables, int64_t n_texels,
+                                         const void* feat_x_grouped, int n_objects, int n_views,
+                                         int64_t points_per_object, float* out, float* pre_act, void* workspace,
+                                         size_t workspace_bytes, pn_stream_t stream) {
+  using namespace pn::tc;
+  PN_CHECK_ARG(packed && tables && feat_x_grouped && out && workspace, "pn_mlp_forward_tc_grouped: null pointer");
+  PN_CHECK_ARG(n_texels > 0, "pn_mlp_forward_tc_grouped: no texels");
+  PN_CHECK_ARG(n_objects > 0 && n_views > 1 && n_views <= 64 && points_per_object >= 0,
+               "pn_mlp_forward_tc_grouped: bad sizes (2 to 64 views; one view: pn_mlp_forward_tc)");
+  const int64_t n_pts = (int64_t)n_objects * points_per_object;
+  if (n_pts == 0) return PN_OK;
+  const int64_t n_rows = pn_point_taps_grouped_rows(n_pts, n_views);
+  PN_CHECK_ARG(n_rows < (1ll << 31) - 4096, "pn_mlp_forward_tc_grouped: too many rows for one launch");
+  PN_CHECK_ARG(workspace_bytes >= pn_mlp_tc_grouped_workspace_bytes(), "pn_mlp_forward_tc_grouped: workspace too small");
+  PN_CHECK_ARG(((uintptr_t)workspace & 255) == 0 && ((uintptr_t)tables & 15) == 0 && ((uintptr_t)feat_x_grouped & 15) == 0,
+               "pn_mlp_forward_tc_grouped: misaligned buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUtensorMap mw, mx;
+  int rc;
+  if ((rc = make_map(&mw, packed, (uint64_t)kLayers * 512, 512, 1024, 128))) return rc;
+  if ((rc = make_map(&mx, feat_x_grouped, (uint64_t)n_rows, 64, 128, kRows))) return rc;
+  unsigned int* err = (unsigned int*)workspace;
+  PN_CUDA_OK(cudaMemsetAsync(err, 0, 4, st));
+  ChainParams p = {};
+  p.out = (float4*)out;
+  p.pre = (float4*)pre_act;
+  p.err = err;
+  p.tables = (const __half*)tables;
+  p.table_stride = n_texels * 512;
+  p.ppo = points_per_object;
+  p.n_views = n_views;
+  p.debug_stage = -1;
+  p.bias = (const float*)((const char*)packed + kPackedWeightBytes);
+  p.bias2 = (const float*)((const char*)packed + kPackedWeightBytes + kBiasBytes);
+  p.group = 1;
+  p.n_points = n_pts;
+  p.n_rows = n_pts;          // what the head's row check compares against
+  p.first_block = 0;
+  p.last_block = 5;
+  p.park = (float*)((char*)workspace + 256);
+  return launch_chain(mw, mx, mw, p, st);
 }

@@ -30,13 +30,16 @@ static Layout layout(int64_t n_rays, int n_views, const pn_render_config_t& c) {
   const int64_t r = n_rays > 0 ? n_rays : 0;
   Layout l;
   size_t off = 0;
-  l.mlp = off;  off += align256(pn_mlp_tc_workspace_bytes(r * n_views * k_max, n_views));
+  // one view: the chain's watchdog word; several views: the grouped chain's park buffer (view mean on chip)
+  l.mlp = off;  off += align256(n_views > 1 ? pn_mlp_tc_grouped_workspace_bytes()
+                                            : pn_mlp_tc_workspace_bytes(r * n_views * k_max, n_views));
   l.z_c = off;  off += align256((size_t)r * c.n_coarse * 4);
   l.w_c = off;  off += align256((size_t)r * c.n_coarse * 4);
   l.z_f = off;  off += align256((size_t)r * (k_f > 0 ? k2 : 0) * 4);
   l.w_f = off;  off += align256((size_t)r * (k_f > 0 ? k2 : 0) * 4);
   l.rgbs = off; off += align256((size_t)r * k_max * 16);
-  l.fx = off;   off += align256((size_t)r * n_views * k_max * 128);
+  l.fx = off;   off += align256((size_t)(n_views > 1 ? pn_point_taps_grouped_rows(r * k_max, n_views)
+                                                       : r * n_views * k_max) * 128);
   l.total = off;
   return l;
 }
@@ -62,16 +65,22 @@ static int pass(const pn_camera_t* cam, const pn_render_mlp_t* mlp, int64_t n_te
   {
     Range r_model("model_inference");
     PN_TRY(record(ev ? ev->taps[which][0] : nullptr, st));
+    const bool grouped = cam->n_views > 1;   // several views: grouped row order + on-chip view mean, one chain launch
     {
       Range r_index("encoder_index");     // projection + taps (+ positional_enc: same kernel)
-      PN_TRY(pn_point_taps(cam, rays, z, k, nullptr, nullptr, ppo, fx, st));
+      if (grouped) PN_TRY(pn_point_taps_grouped(cam, rays, z, k, nullptr, nullptr, ppo, fx, st));
+      else PN_TRY(pn_point_taps(cam, rays, z, k, nullptr, nullptr, ppo, fx, st));
     }
     PN_TRY(record(ev ? ev->taps[which][1] : nullptr, st));
     PN_TRY(record(ev ? ev->mlp[which][0] : nullptr, st));
     {
       Range r_mlp("resnetfc_infer");
-      PN_TRY(pn_mlp_forward_tc(mlp->packed, mlp->tables, n_texels, fx, cam->n_objects, cam->n_views, ppo, rgbs, nullptr,
-                               mlp_ws, mlp_ws_bytes, nullptr, st));
+      if (grouped)
+        PN_TRY(pn_mlp_forward_tc_grouped(mlp->packed, mlp->tables, n_texels, fx, cam->n_objects, cam->n_views, ppo, rgbs,
+                                         nullptr, mlp_ws, mlp_ws_bytes, st));
+      else
+        PN_TRY(pn_mlp_forward_tc(mlp->packed, mlp->tables, n_texels, fx, cam->n_objects, cam->n_views, ppo, rgbs, nullptr,
+                                 mlp_ws, mlp_ws_bytes, nullptr, st));
     }
     PN_TRY(record(ev ? ev->mlp[which][1] : nullptr, st));
   }

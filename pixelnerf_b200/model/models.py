@@ -193,9 +193,17 @@ class PixelNeRFNet(torch.nn.Module):
                 return _lib.mlp_forward_fp32(mlp.packed("fp32"), fz, fx, cam["n_objects"], cam["n_views"], ppo)
         tables = self.latent_tables(coarse)
         _, hl, wl, _ = self.latent_nhwc(torch.float32).shape
+        stash = getattr(self, "_train_stash", None)
+        if cam["n_views"] > 1 and not self.training and not (stash is not None and rays is not None) and \
+                os.environ.get("PIXELNERF_B200_TWO_LAUNCH") != "1":
+            # several views, inference (eval mode): rows in grouped order, view mean on chip, one chain launch.
+            # Training mode keeps the two-launch form, whose saved operands / recomputation the backward uses.
+            with prof_range("encoder_index"):
+                fx = _lib.point_taps_grouped(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
+            with prof_range("resnetfc_infer"):
+                return _lib.mlp_forward_tc_grouped(mlp.packed(prec), tables, fx, cam["n_objects"], cam["n_views"], ppo)
         with prof_range("encoder_index"):
             fx = _lib.point_taps(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
-        stash = getattr(self, "_train_stash", None)
         if stash is not None and rays is not None:
             # training forward (render/autograd.py): keep what the tensor-core backward needs, so that it does
             # not have to re-run the chain

@@ -69,7 +69,8 @@ class NeRFRenderer(torch.nn.Module):
         # in-kernel draws (the reference's four torch.rand* calls, nerf.py:111,135,141,158).
         self.injected_draws = None
         self.injected_z = None  # teacher forcing: dict(z_coarse=..., z_fine=...)
-        self.max_rows_per_launch = 1 << 22   # MLP rows per chunk: 0.5 GB of code rows, 4.3 GB of fp16 hand-off when NS > 1
+        self.max_rows_per_launch = 1 << 22   # MLP rows per chunk: 0.5 GB of code rows (the two-launch NS > 1 form of the
+                                             # training forward adds 4.3 GB of fp16 hand-off; inference has none)
         self.max_rows_train = 1 << 16  # rows whose 11 fp32 activation tensors are kept at once (1.4 GB)
         self.max_rows_train_tc = 1 << 20  # tensor-core training path: ~20 KB per row of activations + workspace
         # tensor-core training path: the forward keeps its GEMM operands (11.3 KB per MLP row) for the backward

@@ -88,7 +88,29 @@ def make_taps(idx, wt, feat_x):
     return out
 
 
-def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo):
+def grouped_row_index(sb, ns, ppo):
+    """Row permutation of pn_point_taps_grouped (include/pixelnerf_b200.h): for every grouped row, the index of the
+    same (object, view, point) row in the ordinary (object, view, point) order, or -1 for a zero row.  Super-tile S holds
+    points [128 S, 128 S + 128) of the flattened (object, point) index, one 128-row block per view:
+    grouped row (S * ns + v) * 128 + m = view v of point 128 S + m."""
+    n_pts = sb * ppo
+    n_st = (n_pts + 127) // 128
+    q = (torch.arange(n_st)[:, None, None] * 128 + torch.arange(128)[None, None, :]).expand(n_st, ns, 128)
+    v = torch.arange(ns)[None, :, None].expand(n_st, ns, 128)
+    obj, pt = q // ppo, q % ppo
+    old = (obj * ns + v) * ppo + pt
+    return torch.where(q < n_pts, old, torch.full_like(old, -1)).reshape(-1)
+
+
+def to_grouped(rows, sb, ns, ppo):
+    """Reorder (sb*ns*ppo, ...) rows from (object, view, point) order into the grouped order (zero rows where unused)."""
+    idx = grouped_row_index(sb, ns, ppo).to(rows.device)
+    out = rows.new_zeros(idx.shape[0], *rows.shape[1:])
+    out[idx >= 0] = rows[idx[idx >= 0]]
+    return out
+
+
+def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo, fused_mean=False):
     """float64 restatement of the tensor-core ResnetFC chain with its roundings: fc / lin_out weights and
     GEMM inputs rounded to fp16 (lin_in / lin_out weights as an fp16 hi + lo pair), exact accumulation,
     fp32-exact residual stream; lin_z through per-texel tables rounded to fp16 (biases folded as in
@@ -119,7 +141,10 @@ def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo):
     h = x @ W("lin_in").T
     stages = []
     for b in range(5):
-        if b == 3 and ns > 1:
+        if b == 3 and ns > 1 and fused_mean:
+            # one-launch form (pn_mlp_forward_tc_grouped): mean of the fp32 h over the views, rounded to fp16 once
+            h = h.reshape(-1, ns, ppo, 512).sum(1).div(ns).float().half().double().reshape(-1, 512)
+        elif b == 3 and ns > 1:
             # the per-view h crosses the two launches as fp16, the mean is taken in fp32 (sum in view order, divide)
             h = h.float().half().double().reshape(-1, ns, ppo, 512).sum(1).div(ns).reshape(-1, 512)
         if b < 3:

@@ -14,7 +14,7 @@ import torch
 
 import oracle
 from oracle import model as omodel
-from helpers import emulate_tc_chain, golden_files, load, make_taps, render_case_inputs, tc_depth_tol
+from helpers import emulate_tc_chain, golden_files, grouped_row_index, load, make_taps, render_case_inputs, tc_depth_tol, to_grouped
 from test_gpu_model import _net_for
 
 pytestmark = pytest.mark.gpu
@@ -197,3 +197,62 @@ def test_training_mode_uses_tensor_core_tables_and_stays_in_tolerance():
         assert (outs[mode].coarse.weights[0].cpu() - ref["w_coarse"]).abs().max().item() < 2e-3
     assert not torch.equal(outs["eval"].coarse.weights, outs["train"].coarse.weights)   # different table builds
     net.eval()
+
+
+@pytest.mark.parametrize("ns,ppo,sb", [(2, 130, 2), (2, 1, 1), (3, 77, 1), (3, 1301, 2), (4, 500, 1), (5, 97, 1),
+                                       (2, 64 * 150 + 5, 1), (3, 40 * 74 * 2 + 11, 1)])
+def test_grouped_chain_vs_emulation_and_two_launch_form(ns, ppo, sb):
+    """n_views > 1 in ONE launch (view mean on chip, pn_mlp_forward_tc_grouped): against the float64 emulation of its
+    arithmetic (mean of the fp32 h over the views, one fp16 rounding) and against the two-launch form (which rounds
+    every view's h to fp16 before the mean).  Ragged point counts, view counts that do and do not divide 32, several
+    objects, more super-tiles than CTA pairs; repeated launches agree bit for bit."""
+    from pixelnerf_b200 import _lib, synthetic as syn
+    w = syn.mlp_weights(42)
+    packed = _lib.pack_weights_tc({k: v.cuda() for k, v in w.items()})
+    n = sb * ns * ppo
+    idx, wt, latent, fx = _inputs(n, seed=ns)
+    tables = _tables(w, latent)
+    rows = make_taps(idx, wt, fx)                       # (object, view, point) order
+    grouped = to_grouped(rows, sb, ns, ppo).cuda()
+    assert grouped.shape[0] == int(_lib.lib().pn_point_taps_grouped_rows(sb * ppo, ns))
+    out, pre = _lib.mlp_forward_tc_grouped(packed, tables, grouped, sb, ns, ppo, want_pre=True)
+    torch.cuda.synchronize()
+    assert torch.isfinite(pre).all() and pre.shape == (sb * ppo, 4)
+    if n <= 20000:
+        refs = []
+        for o in range(sb):
+            sl = slice(o * ns * ppo, (o + 1) * ns * ppo)
+            refs.append(emulate_tc_chain(w, idx[sl], wt[sl], latent, fx[sl].float(), ns, ppo, fused_mean=True)[1])
+        ref = torch.cat(refs)
+        scale = max(8.0, ref.abs().max().item())
+        assert (pre.cpu().double() - ref).abs().max().item() < 1.5e-3 * scale
+        assert (out.cpu()[:, :3].double() - torch.sigmoid(ref[:, :3])).abs().max().item() < 1e-3
+    two, pre_two = _lib.mlp_forward_tc(packed, tables, rows.cuda(), sb, ns, ppo, want_pre=True)
+    scale = max(8.0, pre_two.abs().max().item())
+    assert (pre - pre_two).abs().max().item() < 3e-3 * scale       # same arithmetic up to where the fp16 rounding of h sits
+    assert (out[:, :3] - two[:, :3]).abs().max().item() < 2e-3
+    for _ in range(6):
+        again = _lib.mlp_forward_tc_grouped(packed, tables, grouped, sb, ns, ppo, want_pre=True)[1]
+        assert torch.equal(again, pre)
+
+
+@pytest.mark.parametrize("name", ["srn_chair", "dtu"])
+def test_grouped_taps_are_a_permutation_of_the_ordinary_taps(name):
+    """pn_point_taps_grouped writes exactly the rows of pn_point_taps, in grouped order, zero rows elsewhere."""
+    from pixelnerf_b200 import _lib, synthetic as syn
+    from pixelnerf_b200.testing import build_net
+    sc = syn.scene(name)
+    net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), torch.device("cuda"), mlp_precision="fp16")
+    n_rays, k = 333, 96
+    rays = sc["rays"][torch.linspace(0, sc["rays"].shape[0] - 1, n_rays).long()].cuda()
+    z = ren.sample_coarse(rays, u=torch.rand(n_rays, 64, device="cuda"))
+    z = torch.sort(torch.cat([z, z[:, :32] + 1e-3], -1), -1)[0].contiguous()
+    _, hl, wl, _ = net.latent_nhwc(torch.float32).shape
+    ppo = n_rays * k
+    plain = _lib.point_taps(net._cam, hl, wl, ppo, rays=rays, z=z)
+    grouped = _lib.point_taps_grouped(net._cam, hl, wl, ppo, rays=rays, z=z)
+    idx = grouped_row_index(1, sc["ns"], ppo).cuda()
+    assert grouped.shape[0] == idx.shape[0]
+    got = grouped.view(torch.int32)
+    assert torch.equal(got[idx >= 0], plain.view(torch.int32)[idx[idx >= 0]])
+    assert int(got[idx < 0].abs().sum()) == 0
