@@ -419,6 +419,27 @@ PN_API int pn_render_rays(const pn_camera_t* cam, const pn_render_mlp_t* mlp_coa
                    const pn_render_out_t* out_coarse, const pn_render_out_t* out_fine,
                    void* workspace, size_t workspace_bytes, const pn_render_events_t* events, pn_stream_t stream);
 
+/* SURVEY 8f.1 -- ray generation fused into the renderer (util.gen_rays / unproj_map, src/util/util.py:113-143, 238-276,
+ * feeding the loop of eval/gen_video.py:176-217): pn_render_rays with the rays of the call defined by FRAMES instead of
+ * an (R, 8) tensor.  Ray r of the call is pixel first_ray + r of the concatenated (n_frames, height, width) grid; its
+ * origin / unit direction are computed inside the kernels that need them from the frame's camera-to-world pose and the
+ * intrinsics, with the arithmetic of pn_gen_rays (bit-identical results), near / far are the two constants.  A frame
+ * costs 48-64 bytes of input instead of 32 bytes per ray.  One encoded object (cam->n_objects == 1).  Outputs are
+ * indexed by r.  Workspace: pn_render_rays_workspace_bytes(n_rays, ...). */
+typedef struct pn_frames {
+  const float* poses;   /* DEVICE (n_frames, pose_stride) row-major camera-to-world, rows of 4 floats */
+  int pose_stride;      /* 12 (3x4) or 16 (4x4) */
+  int n_frames;
+  int width, height;
+  float fx, fy, cx, cy; /* focal lengths and principal point in pixels (util.unproj_map) */
+  float z_near, z_far;
+} pn_frames_t;
+PN_API int pn_render_frames(const pn_camera_t* cam, const pn_render_mlp_t* mlp_coarse, const pn_render_mlp_t* mlp_fine,
+                     int64_t n_texels, const pn_frames_t* frames, int64_t first_ray, int64_t n_rays,
+                     const float* lin, const pn_render_config_t* cfg, const pn_render_draws_t* draws,
+                     const pn_render_out_t* out_coarse, const pn_render_out_t* out_fine, void* workspace,
+                     size_t workspace_bytes, const pn_render_events_t* events, pn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

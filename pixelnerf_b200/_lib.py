@@ -57,6 +57,11 @@ class RenderOut(C.Structure):
     _fields_ = [("rgb", _vp), ("depth", _vp), ("weights", _vp), ("z", _vp)]
 
 
+class Frames(C.Structure):
+    _fields_ = [("poses", _vp), ("pose_stride", _int), ("n_frames", _int), ("width", _int), ("height", _int),
+                ("fx", _f32), ("fy", _f32), ("cx", _f32), ("cy", _f32), ("z_near", _f32), ("z_far", _f32)]
+
+
 class RenderEvents(C.Structure):
     _fields_ = [("taps", (_vp * 2) * 2), ("mlp", (_vp * 2) * 2), ("composite", (_vp * 2) * 2),
                 ("sample", (_vp * 2) * 2)]
@@ -119,6 +124,9 @@ _SIGNATURES = {
     "pn_frame_to_u8": (_int, [_vp, _vp, _i64, _vp]),
     "pn_encoder_latent": (_int, [_vp, _vp, _vp, _vp, _int, _int, _vp, _int, _vp]),
     "pn_render_rays_workspace_bytes": (_sz, [_i64, _int, C.POINTER(RenderConfig)]),
+    "pn_render_frames": (_int, [C.POINTER(Camera), C.POINTER(RenderMlp), C.POINTER(RenderMlp), _i64, C.POINTER(Frames),
+                                _i64, _i64, _vp, C.POINTER(RenderConfig), C.POINTER(RenderDraws), C.POINTER(RenderOut),
+                                C.POINTER(RenderOut), _vp, _sz, C.POINTER(RenderEvents), _vp]),
     "pn_render_rays": (_int, [C.POINTER(Camera), C.POINTER(RenderMlp), C.POINTER(RenderMlp), _i64, _vp, _i64, _vp,
                               C.POINTER(RenderConfig), C.POINTER(RenderDraws), C.POINTER(RenderOut),
                               C.POINTER(RenderOut), _vp, _sz, C.POINTER(RenderEvents), _vp]),
@@ -563,14 +571,36 @@ def _new_event():
     return e
 
 
+def frames_struct(poses, width, height, focal, z_near, z_far, c=None):
+    """(Frames, keep-alive) for pn_render_frames: poses (NV, 3|4, 4) CUDA camera-to-world; focal scalar or (fx, fy);
+    c None (image centre) or (cx, cy) -- the arguments of util.gen_rays (src/util/util.py:238-276)."""
+    poses = _f32c(poses)
+    if poses.dim() != 3 or poses.shape[1] not in (3, 4) or poses.shape[2] != 4:
+        raise ValueError(f"poses must be (B, 3|4, 4), got {tuple(poses.shape)}")
+    f = torch.as_tensor(focal, dtype=torch.float32).reshape(-1)
+    fx, fy = float(f[0]), float(f[-1])
+    if c is None:
+        cx, cy = width * 0.5, height * 0.5
+    else:
+        c = torch.as_tensor(c).reshape(-1)
+        cx, cy = float(c[0]), float(c[1])
+    return Frames(_ptr(poses), poses.shape[1] * 4, poses.shape[0], int(width), int(height), fx, fy, cx, cy,
+                  float(z_near), float(z_far)), poses
+
+
 def render_rays(cam_bufs, hl, wl, mlp_coarse, mlp_fine, rays, n_coarse, n_imp, n_depth, depth_std, lindisp,
-                white_bkgd, seed=0, draws=None):
+                white_bkgd, seed=0, draws=None, frames=None, first_ray=0, n_rays=None):
     """The whole no-grad render in one C call (pn_render_rays): mlp_* = (packed, tables) pairs of the tensor-core
     chain, mlp_fine None = the fine pass uses mlp_coarse.  rays (R,8) ordered (object, ray).  Returns
-    (weights, rgb, depth, z) for the coarse pass and the same tuple (or None) for the fine pass."""
-    rays = _f32c(rays)
-    r = rays.shape[0]
-    dev = rays.device
+    (weights, rgb, depth, z) for the coarse pass and the same tuple (or None) for the fine pass.
+    With ``frames`` (a frames_struct pair) instead of rays: pn_render_frames on pixels [first_ray, first_ray + n_rays)
+    of the frames -- the rays are generated inside the kernels."""
+    if frames is None:
+        rays = _f32c(rays)
+        r = rays.shape[0]
+        dev = rays.device
+    else:
+        r, dev = int(n_rays), frames[1].device
     cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
                  cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
     cfg = RenderConfig(n_coarse, n_imp, n_depth, float(depth_std), int(bool(lindisp)), int(bool(white_bkgd)), seed)
@@ -601,6 +631,12 @@ def render_rays(cam_bufs, hl, wl, mlp_coarse, mlp_fine, rays, n_coarse, n_imp, n
                 pair = (_new_event(), _new_event())
                 getattr(ev, name)[p][0], getattr(ev, name)[p][1] = pair[0].cuda_event, pair[1].cuda_event
                 PROFILE.setdefault(key, []).append(pair)
+    if frames is not None:
+        _check(lib().pn_render_frames(C.byref(cam), C.byref(mc), C.byref(mf) if mf is not None else None, n_tex,
+                                      C.byref(frames[0]), int(first_ray), r, _ptr(_linspace(n_coarse, dev)), C.byref(cfg),
+                                      C.byref(dr), C.byref(oc), C.byref(of) if of is not None else None, ws.data_ptr(),
+                                      nbytes, C.byref(ev) if ev is not None else None, _stream()), "pn_render_frames")
+        return coarse, fine
     _check(lib().pn_render_rays(C.byref(cam), C.byref(mc), C.byref(mf) if mf is not None else None, n_tex, _ptr(rays),
                                 r, _ptr(_linspace(n_coarse, dev)), C.byref(cfg), C.byref(dr), C.byref(oc),
                                 C.byref(of) if of is not None else None, ws.data_ptr(), nbytes,

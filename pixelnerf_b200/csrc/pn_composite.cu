@@ -94,14 +94,14 @@ __device__ __forceinline__ void load_samples(const float4* __restrict__ crow, co
 template <int G, int CMAX>
 __global__ void __launch_bounds__(kCompWarpsFwd * 32, CMAX <= 8 ? PN_COMP_FWD_MINB : 2)
 composite_fwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ z,
-                     const float* __restrict__ rays, float* __restrict__ weights,
+                     const RaySrc rays, float* __restrict__ weights,
                      float* __restrict__ rgb, float* __restrict__ depth, int64_t n_rays, int k,
                      int rounds, bool white) {
   const int lane = threadIdx.x & 31, gl = lane % G;
   const int64_t r_raw = ((int64_t)blockIdx.x * kCompWarpsFwd + (threadIdx.x >> 5)) * (32 / G) + lane / G;
   const bool live = r_raw < n_rays;
   const int64_t r = live ? r_raw : n_rays - 1;   // dead groups recompute the last ray and store nothing
-  const float far = rays[r * 8 + 7];
+  const float far = ray_far(rays, r);
   float4 c[CMAX];
   float zz[CMAX], zn[CMAX];
   load_samples<G, CMAX>(rgbs + r * k, z + r * k, k, rounds, gl, far, c, zz, zn);
@@ -225,11 +225,11 @@ composite_bwd_kernel(const float4* __restrict__ rgbs, const float* __restrict__ 
 static int comp_lanes(int k) { return k <= 64 ? 8 : k <= 128 ? 16 : 32; }
 static int composite_args_ok(int64_t n_rays, int k) { return n_rays >= 0 && k > 0 && k <= 512; }
 
-extern "C" int pn_composite_fwd(const float* rgb_sigma, const float* z, const float* rays,
+int pn::composite_fwd_src(const float* rgb_sigma, const float* z, const pn::RaySrc& rays,
                                 float* weights, float* rgb, float* depth, int64_t n_rays,
                                 int n_samples, int white_bkgd, pn_stream_t stream) {
   if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers
-  PN_CHECK_ARG(rgb_sigma && z && rays && weights && rgb && depth, "pn_composite_fwd: null pointer");
+  PN_CHECK_ARG(rgb_sigma && z && (rays.rays || rays.poses) && weights && rgb && depth, "pn_composite_fwd: null pointer");
   PN_CHECK_ARG(composite_args_ok(n_rays, n_samples), "pn_composite_fwd: need 1 <= K <= 512, got K=%d", n_samples);
   const int g = comp_lanes(n_samples);
   const int per_lane = (n_samples + g - 1) / g;
@@ -241,6 +241,14 @@ extern "C" int pn_composite_fwd(const float* rgb_sigma, const float* z, const fl
   PN_LAUNCH_OK("composite_fwd_kernel");
   pn::count_launch();
   return PN_OK;
+}
+
+extern "C" int pn_composite_fwd(const float* rgb_sigma, const float* z, const float* rays,
+                                float* weights, float* rgb, float* depth, int64_t n_rays,
+                                int n_samples, int white_bkgd, pn_stream_t stream) {
+  if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers
+  PN_CHECK_ARG(rays, "pn_composite_fwd: null pointer");
+  return pn::composite_fwd_src(rgb_sigma, z, pn::ray_src(rays), weights, rgb, depth, n_rays, n_samples, white_bkgd, stream);
 }
 
 extern "C" int pn_composite_bwd(const float* rgb_sigma, const float* z, const float* rays,

@@ -120,7 +120,7 @@ constexpr int kTapsPitch = 144;
 template <typename LatT, typename OutT, bool kTaps>
 __global__ void __launch_bounds__(kFeatWarps * 32)
 point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
-                      const float* __restrict__ rays, const float* __restrict__ zs, int n_samples,
+                      const RaySrc rays, const float* __restrict__ zs, int n_samples,
                       const float* __restrict__ xyz_in, const float* __restrict__ dirs_in,
                       int64_t ppo, OutT* __restrict__ feat_z, OutT* __restrict__ feat_x, int ldx,
                       int64_t n_rows, uint4* __restrict__ taps, int group = 0) {
@@ -156,10 +156,10 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     const int view = (int)ov;
     const int obj = view / cam.n_views;
     float x, y, z, dx, dy, dz;
-    if (rays) {  // x = o + z d  (src/render/nerf.py:185), separate mul and add like torch
+    if (rays.rays || rays.poses) {  // x = o + z d  (src/render/nerf.py:185), separate mul and add like torch
       const int64_t ray = obj * (ppo / n_samples) + p / n_samples;
-      const float4 r0 = __ldg(reinterpret_cast<const float4*>(rays + ray * 8));
-      const float4 r1 = __ldg(reinterpret_cast<const float4*>(rays + ray * 8 + 4));
+      float4 r0, r1;
+      ray_load(rays, ray, r0, r1);
       const float zz = zs[ray * n_samples + (p % n_samples)];
       dx = r0.w; dy = r1.x; dz = r1.y;
       x = __fadd_rn(r0.x, __fmul_rn(zz, dx));
@@ -585,11 +585,11 @@ extern "C" int pn_point_features(const pn_camera_t* cam, const void* latent_nhwc
   const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
   if (out_dtype == PN_DTYPE_F32)
     pn::point_features_kernel<float, float, false><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
-        *cam, (const float*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
+        *cam, (const float*)latent_nhwc, pn::ray_src(rays), z, n_samples, xyz, viewdirs, points_per_object,
         (float*)feat_z, (float*)feat_x, ldx, n_rows, nullptr);
   else
     pn::point_features_kernel<__half, __half, false><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
-        *cam, (const __half*)latent_nhwc, rays, z, n_samples, xyz, viewdirs, points_per_object,
+        *cam, (const __half*)latent_nhwc, pn::ray_src(rays), z, n_samples, xyz, viewdirs, points_per_object,
         (__half*)feat_z, (__half*)feat_x, ldx, n_rows, nullptr);
   PN_LAUNCH_OK("point_features_kernel");
   pn::count_launch();
@@ -601,44 +601,37 @@ extern "C" int64_t pn_point_taps_grouped_rows(int64_t n_points, int n_views) {
   return (n_points + 127) / 128 * 128 * n_views;
 }
 
-extern "C" int pn_point_taps_grouped(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
-                                     const float* xyz, const float* viewdirs, int64_t points_per_object,
-                                     void* feat_x, pn_stream_t stream) {
-  PN_CHECK_ARG(cam && feat_x, "pn_point_taps_grouped: null pointer");
-  PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_taps_grouped: camera buffers missing (call encode first)");
-  PN_CHECK_ARG((rays && z && n_samples > 0) || xyz, "pn_point_taps_grouped: need rays+z or xyz");
-  PN_CHECK_ARG(!rays || points_per_object % n_samples == 0, "pn_point_taps_grouped: P must be a multiple of K");
-  PN_CHECK_ARG(cam->hl > 1 && cam->wl > 1 && cam->n_objects > 0 && cam->n_views > 0, "pn_point_taps_grouped: bad camera sizes");
-  PN_CHECK_ARG((int64_t)cam->n_objects * cam->n_views * cam->hl * cam->wl < (1ll << 31), "pn_point_taps_grouped: too many texels");
-  PN_CHECK_ARG(((uintptr_t)feat_x & 127) == 0, "pn_point_taps_grouped: feat_x must be 128-byte aligned");
-  const int64_t n_rows = pn_point_taps_grouped_rows((int64_t)cam->n_objects * points_per_object, cam->n_views);
+// pn_point_taps / pn_point_taps_grouped with the rays coming from any RaySrc (an explicit tensor, or frames)
+int pn::point_taps_src(const pn_camera_t* cam, const pn::RaySrc& rays, const float* z, int n_samples, const float* xyz,
+                       const float* viewdirs, int64_t points_per_object, void* feat_x, bool grouped, pn_stream_t stream) {
+  const bool have_rays = rays.rays || rays.poses;
+  PN_CHECK_ARG(cam && feat_x, "pn_point_taps: null pointer");
+  PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_taps: camera buffers missing (call encode first)");
+  PN_CHECK_ARG((have_rays && z && n_samples > 0) || xyz, "pn_point_taps: need rays+z or xyz");
+  PN_CHECK_ARG(!have_rays || points_per_object % n_samples == 0, "pn_point_taps: P must be a multiple of K");
+  PN_CHECK_ARG(cam->hl > 1 && cam->wl > 1 && cam->n_objects > 0 && cam->n_views > 0, "pn_point_taps: bad camera sizes");
+  PN_CHECK_ARG((int64_t)cam->n_objects * cam->n_views * cam->hl * cam->wl < (1ll << 31), "pn_point_taps: too many texels");
+  PN_CHECK_ARG(((uintptr_t)feat_x & 127) == 0, "pn_point_taps: feat_x must be 128-byte aligned");
+  const int64_t n_rows = grouped ? pn_point_taps_grouped_rows((int64_t)cam->n_objects * points_per_object, cam->n_views)
+                                 : (int64_t)cam->n_objects * cam->n_views * points_per_object;
   if (n_rows == 0) return PN_OK;
   const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
   pn::point_features_kernel<__half, __half, true><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
       *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
-      (uint4*)feat_x, 1);
-  PN_LAUNCH_OK("point_features_kernel(taps, grouped)");
+      (uint4*)feat_x, grouped ? 1 : 0);
+  PN_LAUNCH_OK("point_features_kernel(taps)");
   pn::count_launch();
   return PN_OK;
+}
+
+extern "C" int pn_point_taps_grouped(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
+                                     const float* xyz, const float* viewdirs, int64_t points_per_object,
+                                     void* feat_x, pn_stream_t stream) {
+  return pn::point_taps_src(cam, pn::ray_src(rays), z, n_samples, xyz, viewdirs, points_per_object, feat_x, true, stream);
 }
 
 extern "C" int pn_point_taps(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
                              const float* xyz, const float* viewdirs, int64_t points_per_object,
                              void* feat_x, pn_stream_t stream) {
-  PN_CHECK_ARG(cam && feat_x, "pn_point_taps: null pointer");
-  PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_taps: camera buffers missing (call encode first)");
-  PN_CHECK_ARG((rays && z && n_samples > 0) || xyz, "pn_point_taps: need rays+z or xyz");
-  PN_CHECK_ARG(!rays || points_per_object % n_samples == 0, "pn_point_taps: P must be a multiple of K");
-  PN_CHECK_ARG(cam->hl > 1 && cam->wl > 1 && cam->n_objects > 0 && cam->n_views > 0, "pn_point_taps: bad camera sizes");
-  PN_CHECK_ARG((int64_t)cam->n_objects * cam->n_views * cam->hl * cam->wl < (1ll << 31), "pn_point_taps: too many texels");
-  PN_CHECK_ARG(((uintptr_t)feat_x & 127) == 0, "pn_point_taps: feat_x must be 128-byte aligned");
-  const int64_t n_rows = (int64_t)cam->n_objects * cam->n_views * points_per_object;
-  if (n_rows == 0) return PN_OK;
-  const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
-  pn::point_features_kernel<__half, __half, true><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
-      *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
-      (uint4*)feat_x);
-  PN_LAUNCH_OK("point_features_kernel(taps)");
-  pn::count_launch();
-  return PN_OK;
+  return pn::point_taps_src(cam, pn::ray_src(rays), z, n_samples, xyz, viewdirs, points_per_object, feat_x, false, stream);
 }

@@ -12,21 +12,14 @@ gen_rays_kernel(const float* __restrict__ poses, int pose_stride, int n_images, 
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t per = (int64_t)width * height;
   if (i >= per * n_images) return;
-  const int img = (int)(i / per);
-  const int pix = (int)(i - (int64_t)img * per);
-  const int py = pix / width, px = pix - py * width;
-  // unproj_map: ((x - cx) / fx, -(y - cy) / fy, -1), normalised
-  const float X = __fdiv_rn((float)px - cx, fx);
-  const float Y = -__fdiv_rn((float)py - cy, fy);
-  const float Z = -1.0f;
-  const float n = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(X, X), __fmul_rn(Y, Y)), 1.0f));
-  const float ux = __fdiv_rn(X, n), uy = __fdiv_rn(Y, n), uz = __fdiv_rn(Z, n);
-  const float* P = poses + (size_t)img * pose_stride;   // row-major camera-to-world, 4 floats per row
-  const float dx = P[0] * ux + P[1] * uy + P[2] * uz;
-  const float dy = P[4] * ux + P[5] * uy + P[6] * uz;
-  const float dz = P[8] * ux + P[9] * uy + P[10] * uz;
-  rays[i * 2] = make_float4(P[3], P[7], P[11], dx);
-  rays[i * 2 + 1] = make_float4(dy, dz, z_near, z_far);
+  // one definition of the camera model for the stand-alone kernel and the fused ray source (pn_common.cuh: ray_load)
+  RaySrc src = {};
+  src.poses = poses; src.pose_stride = pose_stride; src.width = width; src.height = height;
+  src.fx = fx; src.fy = fy; src.cx = cx; src.cy = cy; src.z_near = z_near; src.z_far = z_far; src.first_ray = 0;
+  float4 a4, b4;
+  ray_load(src, i, a4, b4);
+  rays[i * 2] = a4;
+  rays[i * 2 + 1] = b4;
 }
 
 __global__ void __launch_bounds__(256)

@@ -57,7 +57,7 @@ static inline int record(void* ev, cudaStream_t st) {
   } while (0)
 
 // taps -> chain -> composite for one pass
-static int pass(const pn_camera_t* cam, const pn_render_mlp_t* mlp, int64_t n_texels, const float* rays, int64_t n_rays,
+static int pass(const pn_camera_t* cam, const pn_render_mlp_t* mlp, int64_t n_texels, const RaySrc& rays, int64_t n_rays,
                 const float* z, int k, int white, float* rgbs, void* fx, void* mlp_ws, size_t mlp_ws_bytes,
                 float* weights, float* rgb, float* depth, const pn_render_events_t* ev, int which, cudaStream_t st) {
   const int64_t ppo = n_rays / cam->n_objects * k;
@@ -68,8 +68,7 @@ static int pass(const pn_camera_t* cam, const pn_render_mlp_t* mlp, int64_t n_te
     const bool grouped = cam->n_views > 1;   // several views: grouped row order + on-chip view mean, one chain launch
     {
       Range r_index("encoder_index");     // projection + taps (+ positional_enc: same kernel)
-      if (grouped) PN_TRY(pn_point_taps_grouped(cam, rays, z, k, nullptr, nullptr, ppo, fx, st));
-      else PN_TRY(pn_point_taps(cam, rays, z, k, nullptr, nullptr, ppo, fx, st));
+      PN_TRY(point_taps_src(cam, rays, z, k, nullptr, nullptr, ppo, fx, grouped, st));
     }
     PN_TRY(record(ev ? ev->taps[which][1] : nullptr, st));
     PN_TRY(record(ev ? ev->mlp[which][0] : nullptr, st));
@@ -85,7 +84,7 @@ static int pass(const pn_camera_t* cam, const pn_render_mlp_t* mlp, int64_t n_te
     PN_TRY(record(ev ? ev->mlp[which][1] : nullptr, st));
   }
   PN_TRY(record(ev ? ev->composite[which][0] : nullptr, st));
-  PN_TRY(pn_composite_fwd(rgbs, z, rays, weights, rgb, depth, n_rays, k, white, st));
+  PN_TRY(composite_fwd_src(rgbs, z, rays, weights, rgb, depth, n_rays, k, white, st));
   PN_TRY(record(ev ? ev->composite[which][1] : nullptr, st));
   return PN_OK;
 }
@@ -98,12 +97,13 @@ extern "C" size_t pn_render_rays_workspace_bytes(int64_t n_rays, int n_views, co
   return pn::render::layout(n_rays, n_views, *cfg).total;
 }
 
-extern "C" int pn_render_rays(const pn_camera_t* cam, const pn_render_mlp_t* mlp_coarse, const pn_render_mlp_t* mlp_fine,
-                              int64_t n_texels, const float* rays, int64_t n_rays, const float* lin,
-                              const pn_render_config_t* cfg, const pn_render_draws_t* draws,
-                              const pn_render_out_t* out_coarse, const pn_render_out_t* out_fine, void* workspace,
-                              size_t workspace_bytes, const pn_render_events_t* events, pn_stream_t stream) {
+static int render_impl(const pn_camera_t* cam, const pn_render_mlp_t* mlp_coarse, const pn_render_mlp_t* mlp_fine,
+                       int64_t n_texels, const pn::RaySrc& rays, int64_t n_rays, const float* lin,
+                       const pn_render_config_t* cfg, const pn_render_draws_t* draws,
+                       const pn_render_out_t* out_coarse, const pn_render_out_t* out_fine, void* workspace,
+                       size_t workspace_bytes, const pn_render_events_t* events, pn_stream_t stream) {
   using namespace pn::render;
+  using namespace pn;
   PN_CHECK_ARG(cam && mlp_coarse && cfg && out_coarse, "pn_render_rays: null pointer");
   PN_CHECK_ARG(cfg->n_coarse > 0 && cfg->n_imp >= 0 && cfg->n_depth >= 0, "pn_render_rays: bad sample counts");
   PN_CHECK_ARG(cam->n_objects > 0 && cam->n_views > 0, "pn_render_rays: bad camera sizes");
@@ -112,7 +112,7 @@ extern "C" int pn_render_rays(const pn_camera_t* cam, const pn_render_mlp_t* mlp
   if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers (nerf.py:23-27)
   const int k_f = cfg->n_imp + cfg->n_depth;
   const int k2 = cfg->n_coarse + k_f;
-  PN_CHECK_ARG(rays && lin && workspace, "pn_render_rays: null pointer");
+  PN_CHECK_ARG((rays.rays || rays.poses) && lin && workspace, "pn_render_rays: null pointer");
   PN_CHECK_ARG(mlp_coarse->packed && mlp_coarse->tables, "pn_render_rays: coarse MLP not prepared");
   PN_CHECK_ARG(!mlp_fine || (mlp_fine->packed && mlp_fine->tables), "pn_render_rays: fine MLP not prepared");
   PN_CHECK_ARG(out_coarse->rgb && out_coarse->depth, "pn_render_rays: coarse rgb/depth outputs are required");
@@ -131,8 +131,8 @@ extern "C" int pn_render_rays(const pn_camera_t* cam, const pn_render_mlp_t* mlp
   void* fx = ws + l.fx;
 
   PN_TRY(record(events ? events->sample[0][0] : nullptr, st));
-  PN_TRY(pn_sample_coarse(rays, draws ? draws->u_coarse : nullptr, lin, z_c, n_rays, cfg->n_coarse, cfg->lindisp,
-                          cfg->seed, st));
+  PN_TRY(sample_coarse_src(rays, draws ? draws->u_coarse : nullptr, lin, z_c, n_rays, cfg->n_coarse, cfg->lindisp,
+                           cfg->seed, st));
   PN_TRY(record(events ? events->sample[0][1] : nullptr, st));
   PN_TRY(pass(cam, mlp_coarse, n_texels, rays, n_rays, z_c, cfg->n_coarse, cfg->white_bkgd, rgbs, fx, ws + l.mlp,
               mlp_bytes, w_c, out_coarse->rgb, out_coarse->depth, events, 0, st));
@@ -141,11 +141,47 @@ extern "C" int pn_render_rays(const pn_camera_t* cam, const pn_render_mlp_t* mlp
   float* z_f = out_fine->z ? out_fine->z : (float*)(ws + l.z_f);
   float* w_f = out_fine->weights ? out_fine->weights : (float*)(ws + l.w_f);
   PN_TRY(record(events ? events->sample[1][0] : nullptr, st));
-  PN_TRY(pn_sample_fine(rays, z_c, w_c, out_coarse->depth, draws ? draws->u_bin : nullptr,
-                        draws ? draws->u_in : nullptr, draws ? draws->noise : nullptr, z_f, nullptr, nullptr, n_rays,
-                        cfg->n_coarse, cfg->n_imp, cfg->n_depth, cfg->depth_std, cfg->lindisp, cfg->seed, st));
+  PN_TRY(sample_fine_src(rays, z_c, w_c, out_coarse->depth, draws ? draws->u_bin : nullptr,
+                         draws ? draws->u_in : nullptr, draws ? draws->noise : nullptr, z_f, nullptr, nullptr, n_rays,
+                         cfg->n_coarse, cfg->n_imp, cfg->n_depth, cfg->depth_std, cfg->lindisp, cfg->seed, st));
   PN_TRY(record(events ? events->sample[1][1] : nullptr, st));
   PN_TRY(pass(cam, mlp_fine ? mlp_fine : mlp_coarse, n_texels, rays, n_rays, z_f, k2, cfg->white_bkgd, rgbs, fx,
               ws + l.mlp, mlp_bytes, w_f, out_fine->rgb, out_fine->depth, events, 1, st));
   return PN_OK;
+}
+
+extern "C" int pn_render_rays(const pn_camera_t* cam, const pn_render_mlp_t* mlp_coarse, const pn_render_mlp_t* mlp_fine,
+                              int64_t n_texels, const float* rays, int64_t n_rays, const float* lin,
+                              const pn_render_config_t* cfg, const pn_render_draws_t* draws,
+                              const pn_render_out_t* out_coarse, const pn_render_out_t* out_fine, void* workspace,
+                              size_t workspace_bytes, const pn_render_events_t* events, pn_stream_t stream) {
+  PN_CHECK_ARG(rays || n_rays == 0, "pn_render_rays: null pointer");
+  return render_impl(cam, mlp_coarse, mlp_fine, n_texels, pn::ray_src(rays), n_rays, lin, cfg, draws, out_coarse, out_fine,
+                     workspace, workspace_bytes, events, stream);
+}
+
+// ray generation fused into the renderer.  The rays of the call are pixels [first_ray, first_ray + n_rays)
+// of the concatenated (n_frames, H, W) grid of `frames`; every kernel that needs a ray computes it from the frame's pose
+// and the intrinsics (pn_common.cuh: ray_load, the arithmetic of pn_gen_rays), so no (H, W, 8) tensor exists.
+extern "C" int pn_render_frames(const pn_camera_t* cam, const pn_render_mlp_t* mlp_coarse, const pn_render_mlp_t* mlp_fine,
+                                int64_t n_texels, const pn_frames_t* frames, int64_t first_ray, int64_t n_rays,
+                                const float* lin, const pn_render_config_t* cfg, const pn_render_draws_t* draws,
+                                const pn_render_out_t* out_coarse, const pn_render_out_t* out_fine, void* workspace,
+                                size_t workspace_bytes, const pn_render_events_t* events, pn_stream_t stream) {
+  PN_CHECK_ARG(frames && frames->poses, "pn_render_frames: null pointer");
+  PN_CHECK_ARG(frames->pose_stride == 12 || frames->pose_stride == 16, "pn_render_frames: poses must be (n, 3|4, 4) row-major");
+  PN_CHECK_ARG(frames->n_frames > 0 && frames->width > 0 && frames->height > 0, "pn_render_frames: bad frame sizes");
+  PN_CHECK_ARG(frames->fx != 0.0f && frames->fy != 0.0f, "pn_render_frames: zero focal length");
+  PN_CHECK_ARG(cam && cam->n_objects == 1, "pn_render_frames: one encoded object (a video of one scene)");
+  const int64_t total = (int64_t)frames->n_frames * frames->width * frames->height;
+  PN_CHECK_ARG(first_ray >= 0 && n_rays >= 0 && first_ray + n_rays <= total,
+               "pn_render_frames: rays [%lld, %lld) outside the %lld pixels of the frames", (long long)first_ray,
+               (long long)(first_ray + n_rays), (long long)total);
+  pn::RaySrc src = {};
+  src.poses = frames->poses; src.pose_stride = frames->pose_stride;
+  src.width = frames->width; src.height = frames->height;
+  src.fx = frames->fx; src.fy = frames->fy; src.cx = frames->cx; src.cy = frames->cy;
+  src.z_near = frames->z_near; src.z_far = frames->z_far; src.first_ray = first_ray;
+  return render_impl(cam, mlp_coarse, mlp_fine, n_texels, src, n_rays, lin, cfg, draws, out_coarse, out_fine, workspace,
+                     workspace_bytes, events, stream);
 }

@@ -20,7 +20,7 @@ __device__ __forceinline__ float lerp_depth(float near, float far, float zs, boo
 // One thread per 4 consecutive samples (one Philox call yields their 4 draws, one 16-byte store);
 // consecutive threads write consecutive z: fully coalesced.  Kc % 4 == 0 takes this path.
 __global__ void __launch_bounds__(256)
-sample_coarse4_kernel(const float* __restrict__ rays, const float* __restrict__ u,
+sample_coarse4_kernel(const RaySrc rays, const float* __restrict__ u,
                       const float* __restrict__ lin, float* __restrict__ z, int64_t total4, int kc,
                       float step, bool lindisp, uint64_t seed) {
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -36,7 +36,7 @@ sample_coarse4_kernel(const float* __restrict__ rays, const float* __restrict__ 
     uu = make_float4(u01(rnd.x), u01(rnd.y), u01(rnd.z), u01(rnd.w));
   }
   const float4 ln = *reinterpret_cast<const float4*>(lin + k);
-  const float2 nf = *reinterpret_cast<const float2*>(rays + r * 8 + 6);
+  const float2 nf = ray_near_far(rays, r);
   float4 o;
   o.x = lerp_depth(nf.x, nf.y, __fadd_rn(ln.x, __fmul_rn(uu.x, step)), lindisp);
   o.y = lerp_depth(nf.x, nf.y, __fadd_rn(ln.y, __fmul_rn(uu.y, step)), lindisp);
@@ -47,7 +47,7 @@ sample_coarse4_kernel(const float* __restrict__ rays, const float* __restrict__ 
 
 // General Kc: one thread per sample.
 __global__ void __launch_bounds__(256)
-sample_coarse_kernel(const float* __restrict__ rays, const float* __restrict__ u,
+sample_coarse_kernel(const RaySrc rays, const float* __restrict__ u,
                      const float* __restrict__ lin, float* __restrict__ z, int64_t total, int kc,
                      float step, bool lindisp, uint64_t seed) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -56,7 +56,7 @@ sample_coarse_kernel(const float* __restrict__ rays, const float* __restrict__ u
   int k = (int)(i - r * kc);
   float uu = u ? u[i] : rand_uniform(seed, PN_STREAM_COARSE, (uint64_t)i);
   float zs = __fadd_rn(lin[k], __fmul_rn(uu, step));
-  float2 nf = *reinterpret_cast<const float2*>(rays + r * 8 + 6);
+  float2 nf = ray_near_far(rays, r);
   z[i] = lerp_depth(nf.x, nf.y, zs, lindisp);
 }
 
@@ -140,7 +140,7 @@ constexpr int kFineWarps = 4;
 #define PN_FINE_MINB 10   // 48 registers: 1.62 ms per 2^20 rays against 1.78 ms at 72 (tests/fine_sweep.sh); instruction bound either way
 #endif
 __global__ void __launch_bounds__(kFineWarps * 32, PN_FINE_MINB)
-sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_coarse,
+sample_fine_kernel(const RaySrc rays, const float* __restrict__ z_coarse,
                    const float* __restrict__ weights, const float* __restrict__ depth,
                    const float* __restrict__ u_bin, const float* __restrict__ u_in,
                    const float* __restrict__ noise, float* __restrict__ z_sorted,
@@ -155,7 +155,7 @@ sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_c
   const int k2 = kc + kf + kd;
 
   for (int64_t r = (int64_t)blockIdx.x * kFineWarps + warp; r < n_rays; r += (int64_t)gridDim.x * kFineWarps) {
-    const float2 nf = *reinterpret_cast<const float2*>(rays + r * 8 + 6);
+    const float2 nf = ray_near_far(rays, r);
     for (int k = lane; k < kc; k += 32) srt[k] = z_coarse[r * kc + k];
     if (kf > 0) {
       for (int k = lane; k < kc; k += 32) w[k] = __fadd_rn(weights[r * kc + k], 1e-5f);
@@ -303,13 +303,11 @@ sample_fine_kernel(const float* __restrict__ rays, const float* __restrict__ z_c
   }
 }
 
-}  // namespace pn
-
-extern "C" int pn_sample_coarse(const float* rays, const float* u, const float* lin, float* z,
-                                int64_t n_rays, int n_coarse, int lindisp, uint64_t seed,
-                                pn_stream_t stream) {
+// The entry points below with the rays coming from any RaySrc (an explicit tensor, or frames: pn_render_frames).
+int sample_coarse_src(const RaySrc& rays, const float* u, const float* lin, float* z, int64_t n_rays, int n_coarse,
+                      int lindisp, uint64_t seed, pn_stream_t stream) {
   if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers
-  PN_CHECK_ARG(rays && lin && z, "pn_sample_coarse: null pointer");
+  PN_CHECK_ARG((rays.rays || rays.poses) && lin && z, "pn_sample_coarse: null pointer");
   PN_CHECK_ARG(n_rays >= 0 && n_coarse > 0, "pn_sample_coarse: bad sizes R=%lld Kc=%d", (long long)n_rays, n_coarse);
   if (n_rays == 0) return PN_OK;
   const int64_t total = n_rays * n_coarse;
@@ -327,13 +325,12 @@ extern "C" int pn_sample_coarse(const float* rays, const float* u, const float* 
   return PN_OK;
 }
 
-extern "C" int pn_sample_fine(const float* rays, const float* z_coarse, const float* weights,
-                              const float* depth, const float* u_bin, const float* u_in,
-                              const float* noise, float* z_sorted, float* z_imp, float* z_depth,
-                              int64_t n_rays, int n_coarse, int n_imp, int n_depth, float depth_std,
-                              int lindisp, uint64_t seed, pn_stream_t stream) {
+int sample_fine_src(const RaySrc& rays, const float* z_coarse, const float* weights, const float* depth,
+                    const float* u_bin, const float* u_in, const float* noise, float* z_sorted, float* z_imp,
+                    float* z_depth, int64_t n_rays, int n_coarse, int n_imp, int n_depth, float depth_std, int lindisp,
+                    uint64_t seed, pn_stream_t stream) {
   if (n_rays == 0) return PN_OK;  // empty batches carry null data pointers
-  PN_CHECK_ARG(rays && z_coarse && z_sorted, "pn_sample_fine: null pointer");
+  PN_CHECK_ARG((rays.rays || rays.poses) && z_coarse && z_sorted, "pn_sample_fine: null pointer");
   PN_CHECK_ARG(n_imp == 0 || weights, "pn_sample_fine: importance samples need coarse weights");
   PN_CHECK_ARG(n_depth == 0 || depth, "pn_sample_fine: depth samples need coarse depth");
   PN_CHECK_ARG(n_rays >= 0 && n_coarse > 0 && n_imp >= 0 && n_depth >= 0, "pn_sample_fine: bad sizes");
@@ -352,4 +349,21 @@ extern "C" int pn_sample_fine(const float* rays, const float* z_coarse, const fl
   PN_LAUNCH_OK("sample_fine_kernel");
   pn::count_launch();
   return PN_OK;
+}
+
+}  // namespace pn
+
+extern "C" int pn_sample_coarse(const float* rays, const float* u, const float* lin, float* z,
+                                int64_t n_rays, int n_coarse, int lindisp, uint64_t seed,
+                                pn_stream_t stream) {
+  return pn::sample_coarse_src(pn::ray_src(rays), u, lin, z, n_rays, n_coarse, lindisp, seed, stream);
+}
+
+extern "C" int pn_sample_fine(const float* rays, const float* z_coarse, const float* weights,
+                              const float* depth, const float* u_bin, const float* u_in,
+                              const float* noise, float* z_sorted, float* z_imp, float* z_depth,
+                              int64_t n_rays, int n_coarse, int n_imp, int n_depth, float depth_std,
+                              int lindisp, uint64_t seed, pn_stream_t stream) {
+  return pn::sample_fine_src(pn::ray_src(rays), z_coarse, weights, depth, u_bin, u_in, noise, z_sorted, z_imp, z_depth,
+                             n_rays, n_coarse, n_imp, n_depth, depth_std, lindisp, seed, stream);
 }

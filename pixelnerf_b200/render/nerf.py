@@ -154,6 +154,51 @@ class NeRFRenderer(torch.nn.Module):
             fine = fine + (fine[3].new_zeros(rays.shape[0], 0),)
         return coarse, fine
 
+    def render_frames(self, model, poses, width, height, focal, z_near, z_far, c=None, draws=None):
+        """SURVEY 8f.1 -- ray generation fused into the renderer: render every pixel of the target frames given by
+        camera-to-world ``poses`` (NV, 3|4, 4) and the intrinsics -- the arguments of ``util.gen_rays``
+        (src/util/util.py:238-276) -- without ever building the (NV, H, W, 8) ray tensor: the kernels compute each ray
+        from the pose where they need it (pn_render_frames).  Same result, bit for bit, as
+        ``self(model, util.gen_rays(poses, ...).reshape(1, -1, 8))`` with the same draws / seed and chunking.  Eval-mode
+        tensor-core path only (one encoded object).  Returns DotMap{coarse:{rgb (NV,H,W,3), depth (NV,H,W)}, fine:{...}}."""
+        if model.mlp_precision == "fp32" or (torch.is_grad_enabled() and self.training):
+            raise NotImplementedError("render_frames: the no-grad tensor-core path only; build rays with util.gen_rays")
+        if model._cam is None:
+            raise RuntimeError("call encode() before render_frames()")
+        if model._cam["n_objects"] != 1:
+            raise NotImplementedError("render_frames renders target views of ONE encoded object")
+        with prof_range("renderer_forward"), torch.no_grad():
+            frames = _lib.frames_struct(poses.to(model.poses.device), width, height, focal, z_near, z_far, c=c)
+            nv = frames[1].shape[0]
+            n = nv * height * width
+            ns = model.num_views_per_obj
+            k_max = self.n_coarse + (self.n_fine if self.using_fine else 0)
+            chunk = max(1, self.max_rows_per_launch // max(1, ns * k_max))
+            seed = 0 if (draws and "u_coarse" in draws) else self._seed() + int(self.seed_offset)
+            prec = model.mlp_precision
+            _, hl, wl, _ = model.latent_nhwc(torch.float32).shape
+            mc = (model.mlp_coarse.packed(prec), model.latent_tables(True))
+            fine_mlp = model._mlp(False)
+            mf = None if fine_mlp is model.mlp_coarse else (fine_mlp.packed(prec), model.latent_tables(False))
+            n_dep = self.n_fine_depth if self.using_fine else 0
+            n_imp = self.n_fine - n_dep if self.using_fine else 0
+            parts = []
+            for s in range(0, n, chunk):
+                e = min(n, s + chunk)
+                dr = {k: v[s:e].contiguous() for k, v in draws.items()} if draws else None
+                parts.append(_lib.render_rays(model._cam, hl, wl, mc, mf, None, self.n_coarse, n_imp, n_dep,
+                                              self.depth_std, self.lindisp, self.white_bkgd, seed=seed + s, draws=dr,
+                                              frames=frames, first_ray=s, n_rays=e - s))
+
+            def fmt(which):
+                rgb = torch.cat([p[which][1] for p in parts]) if len(parts) > 1 else parts[0][which][1]
+                dep = torch.cat([p[which][2] for p in parts]) if len(parts) > 1 else parts[0][which][2]
+                return DotMap(rgb=rgb.reshape(nv, height, width, 3), depth=dep.reshape(nv, height, width))
+            out = DotMap(coarse=fmt(0))
+            if self.using_fine:
+                out.fine = fmt(1)
+            return out
+
     def _render_chunk(self, model, rays, sb, draws, forced, want_weights, seed):
         if self._fused_ok(model, forced):
             return self._render_fused(model, rays, draws, seed)

@@ -19,18 +19,30 @@ def render_video(render_par, poses, width, height, focal, z_near, z_far, c=None,
     if device is None:
         device = next((b.device for b in render_par.buffers()), torch.device("cuda"))
     poses = poses.to(device=device, dtype=torch.float32)
-    rays = _util.gen_rays(poses, width, height, focal, z_near, z_far, c=c).reshape(-1, 8)
-    rgb_parts, depth_parts = [], []
-    with torch.no_grad():
-        for chunk in torch.split(rays, ray_batch_size, dim=0):
-            rgb, depth = render_par(chunk[None])
-            rgb_parts.append(rgb[0])
-            if return_depth:
-                depth_parts.append(depth[0])
-    frames = _lib.frame_to_u8(torch.cat(rgb_parts)).view(-1, height, width, 3)
+    renderer, net = getattr(render_par, "renderer", None), getattr(render_par, "net", None)
+    fused = (renderer is not None and net is not None and getattr(net, "mlp_precision", "fp32") != "fp32"
+             and getattr(net, "_cam", None) is not None and net._cam["n_objects"] == 1 and not renderer.training)
+    if fused:
+        # one GPU, tensor-core path: the rays are generated inside the render kernels (NeRFRenderer.render_frames),
+        # a frame costs 64 bytes of input instead of 32 bytes per ray
+        out = renderer.render_frames(net, poses, width, height, focal, z_near, z_far, c=c)
+        part = out.fine if renderer.using_fine else out.coarse
+        rgb_all, depth_all = part.rgb.reshape(-1, 3), part.depth.reshape(-1)
+    else:
+        rays = _util.gen_rays(poses, width, height, focal, z_near, z_far, c=c).reshape(-1, 8)
+        rgb_parts, depth_parts = [], []
+        with torch.no_grad():
+            for chunk in torch.split(rays, ray_batch_size, dim=0):
+                rgb, depth = render_par(chunk[None])
+                rgb_parts.append(rgb[0])
+                if return_depth:
+                    depth_parts.append(depth[0])
+        rgb_all = torch.cat(rgb_parts)
+        depth_all = torch.cat(depth_parts) if return_depth else None
+    frames = _lib.frame_to_u8(rgb_all).view(-1, height, width, 3)
     host = torch.empty(frames.shape, dtype=torch.uint8, pin_memory=True)
     host.copy_(frames, non_blocking=True)
     torch.cuda.current_stream(frames.device).synchronize()
     if return_depth:
-        return host, torch.cat(depth_parts).view(-1, height, width)
+        return host, depth_all.view(-1, height, width)
     return host

@@ -65,3 +65,56 @@ def test_frame_to_u8_vs_numpy(n):
     if n > 8:      # unaligned start: the vector path must not be taken
         got = _lib.frame_to_u8(x.cuda()[1:])
         assert np.array_equal(got.cpu().numpy(), ref[1:])
+
+
+@pytest.mark.parametrize("scene,rows,c,chunk_rays", [
+    ("sn64", 4, None, None),                 # NS = 1, whole call in one chunk
+    ("sn64", 3, (30.5, 33.25), 3000),        # 3x4 poses, off-centre principal point, chunk boundaries inside a frame
+    ("srn_chair", 4, None, 5000),            # NS = 2: grouped taps + one-launch chain under the fused ray source
+])
+def test_render_frames_equals_rendering_generated_rays(scene, rows, c, chunk_rays):
+    """SURVEY 8f.1 -- ray generation fused into the renderer (NeRFRenderer.render_frames -> pn_render_frames): rendering
+    target frames from (pose, focal, c, near, far) without a ray tensor must equal, BIT FOR BIT, rendering the tensor
+    util.gen_rays builds (pinned to the live reference by test_gen_rays_kernel_vs_live_reference) through the ordinary
+    path, with injected draws and with in-kernel draws of the same seed."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import build_net
+    sc = syn.scene(scene)
+    dev = torch.device("cuda")
+    net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), dev, mlp_precision="fp16")
+    w = h = 40 if scene == "sn64" else 48
+    focal = sc["focal"] * w / sc["w"]
+    poses = torch.stack([util.pose_spherical(a, -15.0, sc["radius"]) for a in (-70.0, 5.0, 140.0)])[:, :rows].contiguous().to(dev)
+    n = poses.shape[0] * h * w
+    rays = util.gen_rays(poses, w, h, focal, sc["near"], sc["far"], c=c).reshape(1, n, 8)
+    if chunk_rays is not None:
+        ren.max_rows_per_launch = chunk_rays * sc["ns"] * 96
+    for injected in (True, False):
+        draws = {k: v.to(dev) for k, v in syn.draws(9, n, 64, 16, 16).items()} if injected else None
+        with torch.no_grad():
+            torch.manual_seed(123)
+            ren.injected_draws = dict(draws) if draws else None
+            ref = ren(net, rays, want_weights=False)
+            torch.manual_seed(123)
+            got = ren.render_frames(net, poses, w, h, focal, sc["near"], sc["far"], c=c, draws=draws)
+        for part in ("coarse", "fine"):
+            assert got[part].rgb.shape == (poses.shape[0], h, w, 3) and got[part].depth.shape == (poses.shape[0], h, w)
+            assert torch.equal(got[part].rgb.reshape(-1, 3), ref[part].rgb.reshape(-1, 3)), (scene, part, injected)
+            assert torch.equal(got[part].depth.reshape(-1), ref[part].depth.reshape(-1)), (scene, part, injected)
+    assert torch.isfinite(got.fine.rgb).all() and float(got.fine.rgb.std()) > 1e-3      # not a constant image
+
+
+def test_render_frames_rejects_what_it_does_not_cover():
+    from pixelnerf_b200 import _lib, synthetic as syn
+    from pixelnerf_b200.testing import build_net
+    sc = syn.scene("sn64")
+    net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), torch.device("cuda"), mlp_precision="fp32")
+    poses = util.pose_spherical(0.0, -10.0, 2.6)[None].cuda()
+    with pytest.raises(NotImplementedError):
+        ren.render_frames(net, poses, 8, 8, 10.0, 1.2, 4.0)
+    net.mlp_precision = "fp16"
+    with pytest.raises(RuntimeError, match="outside"):      # more rays than the frames have pixels
+        fr = _lib.frames_struct(poses, 8, 8, 10.0, 1.2, 4.0)
+        _, hl, wl, _ = net.latent_nhwc(torch.float32).shape
+        mc = (net.mlp_coarse.packed("fp16"), net.latent_tables(True))
+        _lib.render_rays(net._cam, hl, wl, mc, None, None, 64, 16, 16, 0.01, False, True, frames=fr, first_ray=10, n_rays=64)
