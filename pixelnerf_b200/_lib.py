@@ -97,6 +97,12 @@ _SIGNATURES = {
     # no-allocation variant of pn_mlp_forward_tc (scratch in a static device array, csrc/pn_noalloc.cu)
     "pn_static_scratch_bytes": (_sz, []),
     "pn_mlp_forward_tc_static": (_int, [_vp, _vp, _i64, _vp, _int, _int, _i64, _vp, _vp, _vp]),
+    # precise tensor-core chain (mlp_precision = fp16x3)
+    "pn_prepare_latent_tables_f32": (_int, [C.POINTER(MlpWeights), _vp, _i64, _vp, _vp]),
+    "pn_point_taps_f32": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp, _int, _vp]),
+    "pn_mlp_tc_packed_x3_bytes": (_sz, []),
+    "pn_prepare_weights_x3": (_int, [C.POINTER(MlpWeights), _vp, _sz, _vp]),
+    "pn_mlp_forward_tc_x3": (_int, [_vp, _vp, _i64, _vp, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp]),
     # n_views > 1 in one launch: grouped row order + on-chip view mean
     "pn_point_taps_grouped_rows": (_i64, [_i64, _int]),
     "pn_point_taps_grouped": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp]),
@@ -476,6 +482,66 @@ def mlp_forward_tc_grouped(packed, tables, feat_x_grouped, n_objects, n_views, p
     return (out, pre) if want_pre else out
 
 
+def prepare_latent_tables_f32(w, latent_nhwc):
+    """Per-texel lin_z tables (3, V*Hl*Wl, 512) in fp32 for the precise chain (mlp_precision = fp16x3)."""
+    s, keep = pack_weights_fp32(w)
+    if latent_nhwc.dtype != torch.float32:
+        raise RuntimeError("prepare_latent_tables_f32 needs the fp32 channels-last latent")
+    v, hl, wl, ch = latent_nhwc.shape
+    n_tex = v * hl * wl
+    tables = torch.empty(COMBINE_LAYER, n_tex, D_HIDDEN, device=latent_nhwc.device, dtype=torch.float32)
+    _check(lib().pn_prepare_latent_tables_f32(C.byref(s), _ptr(latent_nhwc), n_tex, _ptr(tables), _stream()),
+           "pn_prepare_latent_tables_f32")
+    return tables
+
+
+def pack_weights_x3(w):
+    """Packed buffer of the precise chain: fp16 hi + lo layers, bias tables, lin_in.weight^T in fp32."""
+    s, keep = pack_weights_fp32(w)
+    nbytes = lib().pn_mlp_tc_packed_x3_bytes()
+    packed = torch.empty(nbytes, device=keep["lin_in.weight"].device, dtype=torch.uint8)
+    _check(lib().pn_prepare_weights_x3(C.byref(s), packed.data_ptr(), nbytes, _stream()), "pn_prepare_weights_x3")
+    return packed
+
+
+def point_taps_f32(cam_bufs, hl, wl, ppo, *, rays=None, z=None, xyz=None, viewdirs=None):
+    """point_taps (n_views == 1) / point_taps_grouped (n_views > 1) plus the UNROUNDED positional code: returns
+    (feat_x (rows, 64) fp16, code32 (rows, 44) fp32) in the same row order."""
+    cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
+                 cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
+    grouped = cam.n_views > 1
+    n_rows = int(lib().pn_point_taps_grouped_rows(cam.n_objects * ppo, cam.n_views)) if grouped else cam.n_objects * ppo
+    dev = cam_bufs["poses"].device
+    feat_x = torch.empty(n_rows, 64, device=dev, dtype=torch.float16)
+    code32 = torch.empty(n_rows, 44, device=dev, dtype=torch.float32)
+    rays, z, xyz, viewdirs = _f32c(rays), _f32c(z), _f32c(xyz), _f32c(viewdirs)
+    k = 0 if z is None else z.shape[-1]
+    with _Timed("features"):
+        _check(lib().pn_point_taps_f32(C.byref(cam), _ptr(rays), _ptr(z), k, _ptr(xyz), _ptr(viewdirs), ppo,
+                                       feat_x.data_ptr(), _ptr(code32), int(grouped), _stream()), "pn_point_taps_f32")
+    return feat_x, code32
+
+
+def mlp_forward_tc_x3(packed_x3, tables32, feat_x, code32, n_objects, n_views, ppo, want_pre=False):
+    """The precise tensor-core chain (three fp16 hi/lo operand passes per GEMM, everything else fp32); inputs from
+    pack_weights_x3 / prepare_latent_tables_f32 / point_taps_f32.  -> (SB*ppo, 4) [sigmoid rgb, relu sigma]."""
+    dev = feat_x.device
+    if tables32.dtype != torch.float32 or tables32.dim() != 3 or tables32.shape[0] != COMBINE_LAYER or not tables32.is_contiguous():
+        raise RuntimeError("precise tensor-core MLP needs contiguous fp32 lin_z tables of shape (3, texels, 512)")
+    if feat_x.dtype != torch.float16 or feat_x.shape[1] != 64 or code32.shape != (feat_x.shape[0], 44) \
+            or not feat_x.is_contiguous() or not code32.is_contiguous():
+        raise RuntimeError("precise tensor-core MLP needs feat_x (rows, 64) fp16 and code32 (rows, 44) fp32 from point_taps_f32")
+    out = torch.empty(n_objects * ppo, 4, device=dev, dtype=torch.float32)
+    pre = torch.empty_like(out) if want_pre else None
+    nbytes = lib().pn_mlp_tc_grouped_workspace_bytes()
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    with _Timed("mlp"):
+        _check(lib().pn_mlp_forward_tc_x3(packed_x3.data_ptr(), _ptr(tables32), tables32.shape[1],
+                                          _ptr(feat_x, torch.float16), _ptr(code32), n_objects, n_views, ppo, _ptr(out),
+                                          _ptr(pre), ws.data_ptr(), nbytes, _stream()), "pn_mlp_forward_tc_x3")
+    return (out, pre) if want_pre else out
+
+
 def prepare_latent_tables(w, latent_nhwc):
     """Per-texel lin_z tables (3, V*Hl*Wl, 512) fp16 of one MLP for the tensor-core chain.  fp32 NHWC latent: the
     fp32 CUDA-core product (once per encode: inference); fp16 NHWC latent: the tensor-core product with hi + lo
@@ -812,7 +878,8 @@ def mlp_backward_tc(packed32, w16, feat_x, latent_nhwc, n_objects, n_views, ppo,
 for _name in ("sample_coarse", "sample_fine", "prepare_latent", "point_features", "mlp_forward_fp32",
               "mlp_forward_fp32_train", "mlp_backward_fp32", "point_features_bwd", "depth_sample_bwd", "point_taps",
               "prepare_latent_tables", "pack_weights_tc", "mlp_forward_tc", "composite_fwd", "composite_bwd",
-              "point_taps_grouped", "mlp_forward_tc_grouped", "render_rays", "gen_rays", "encoder_latent", "frame_to_u8", "gemm_tc_rows", "gemm_tc_rows_slabs",
+              "point_taps_grouped", "mlp_forward_tc_grouped", "prepare_latent_tables_f32", "pack_weights_x3",
+              "point_taps_f32", "mlp_forward_tc_x3", "render_rays", "gen_rays", "encoder_latent", "frame_to_u8", "gemm_tc_rows", "gemm_tc_rows_slabs",
               "gemm_tc_wgrad", "mlp_forward_tc_train", "pack_weights_bf16", "mlp_backward_tc"):
     globals()[_name] = _on_device(globals()[_name])
 del _name

@@ -118,7 +118,8 @@ int sample_fine_src(const RaySrc& rays, const float* z_coarse, const float* weig
                     float* z_depth, int64_t n_rays, int n_coarse, int n_imp, int n_depth, float depth_std, int lindisp,
                     uint64_t seed, pn_stream_t stream);
 int point_taps_src(const pn_camera_t* cam, const RaySrc& rays, const float* z, int n_samples, const float* xyz,
-                   const float* viewdirs, int64_t points_per_object, void* feat_x, bool grouped, pn_stream_t stream);
+                   const float* viewdirs, int64_t points_per_object, void* feat_x, bool grouped, pn_stream_t stream,
+                   float* code32 = nullptr);
 int composite_fwd_src(const float* rgb_sigma, const float* z, const RaySrc& rays, float* weights, float* rgb, float* depth,
                       int64_t n_rays, int n_samples, int white_bkgd, pn_stream_t stream);
 

@@ -123,7 +123,7 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
                       const RaySrc rays, const float* __restrict__ zs, int n_samples,
                       const float* __restrict__ xyz_in, const float* __restrict__ dirs_in,
                       int64_t ppo, OutT* __restrict__ feat_z, OutT* __restrict__ feat_x, int ldx,
-                      int64_t n_rows, uint4* __restrict__ taps, int group = 0) {
+                      int64_t n_rows, uint4* __restrict__ taps, int group = 0, float* __restrict__ code32 = nullptr) {
   __shared__ __align__(16) unsigned char stage_all[kTaps ? kFeatWarps * 32 * kTapsPitch : 16];
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5)) * 32;
@@ -150,6 +150,10 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     if (!valid) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(stage + lane * kTapsPitch + 16 * i) = make_uint4(0u, 0u, 0u, 0u);
+      if (code32 && row < n_rows) {
+#pragma unroll
+        for (int i = 0; i < 11; ++i) *reinterpret_cast<float4*>(code32 + (size_t)row * 44 + 4 * i) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
     }
   }
   if (valid) {
@@ -234,6 +238,8 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
         }
         q[i] = val;
       }
+      if (kTaps && code32)   // precise chain (fp16x3): the code also leaves unrounded, 44 floats per row
+        *reinterpret_cast<float4*>(code32 + (size_t)row * 44 + e0) = make_float4(q[0], q[1], q[2], q[3]);
       if (sizeof(OutT) == 4) {
         *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(q[0], q[1], q[2], q[3]);
       } else {
@@ -603,7 +609,8 @@ extern "C" int64_t pn_point_taps_grouped_rows(int64_t n_points, int n_views) {
 
 // pn_point_taps / pn_point_taps_grouped with the rays coming from any RaySrc (an explicit tensor, or frames)
 int pn::point_taps_src(const pn_camera_t* cam, const pn::RaySrc& rays, const float* z, int n_samples, const float* xyz,
-                       const float* viewdirs, int64_t points_per_object, void* feat_x, bool grouped, pn_stream_t stream) {
+                       const float* viewdirs, int64_t points_per_object, void* feat_x, bool grouped, pn_stream_t stream,
+                       float* code32) {
   const bool have_rays = rays.rays || rays.poses;
   PN_CHECK_ARG(cam && feat_x, "pn_point_taps: null pointer");
   PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_taps: camera buffers missing (call encode first)");
@@ -618,7 +625,7 @@ int pn::point_taps_src(const pn_camera_t* cam, const pn::RaySrc& rays, const flo
   const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
   pn::point_features_kernel<__half, __half, true><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
       *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
-      (uint4*)feat_x, grouped ? 1 : 0);
+      (uint4*)feat_x, grouped ? 1 : 0, code32);
   PN_LAUNCH_OK("point_features_kernel(taps)");
   pn::count_launch();
   return PN_OK;
@@ -634,4 +641,14 @@ extern "C" int pn_point_taps(const pn_camera_t* cam, const float* rays, const fl
                              const float* xyz, const float* viewdirs, int64_t points_per_object,
                              void* feat_x, pn_stream_t stream) {
   return pn::point_taps_src(cam, pn::ray_src(rays), z, n_samples, xyz, viewdirs, points_per_object, feat_x, false, stream);
+}
+
+// pn_point_taps / pn_point_taps_grouped that also write the positional code unrounded: code32 (rows, 44) fp32 in the
+// same row order as feat_x (columns [42,44) zero) -- the input of the precise chain's fp32 lin_in.
+extern "C" int pn_point_taps_f32(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
+                                 const float* xyz, const float* viewdirs, int64_t points_per_object,
+                                 void* feat_x, float* code32, int grouped, pn_stream_t stream) {
+  PN_CHECK_ARG(code32 && ((uintptr_t)code32 & 15) == 0, "pn_point_taps_f32: code32 missing or misaligned");
+  return pn::point_taps_src(cam, pn::ray_src(rays), z, n_samples, xyz, viewdirs, points_per_object, feat_x, grouped != 0,
+                            stream, code32);
 }

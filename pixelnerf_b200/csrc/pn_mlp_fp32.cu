@@ -471,6 +471,43 @@ extern "C" int pn_prepare_latent_tables(const pn_mlp_weights_t* w, const float* 
   return PN_OK;
 }
 
+// The same tables kept in fp32 (2 KB per texel and layer) for the precise tensor-core chain (mlp_precision = fp16x3),
+// where nothing but the 512-wide GEMM operands may be rounded.
+namespace pn {
+__global__ void __launch_bounds__(256)
+table_bias_kernel(float4* __restrict__ t, const float* __restrict__ c0, const float* __restrict__ c1, int64_t total4) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total4) return;
+  const int n = (int)(i % (PN_D_HIDDEN / 4)) * 4;
+  float4 v = t[i];
+  v.x += c0[n] + c1[n]; v.y += c0[n + 1] + c1[n + 1]; v.z += c0[n + 2] + c1[n + 2]; v.w += c0[n + 3] + c1[n + 3];
+  t[i] = v;
+}
+}  // namespace pn
+
+extern "C" int pn_prepare_latent_tables_f32(const pn_mlp_weights_t* w, const float* latent_nhwc, int64_t n_texels,
+                                            float* tables32, pn_stream_t stream) {
+  using namespace pn;
+  PN_CHECK_ARG(w && latent_nhwc && tables32, "pn_prepare_latent_tables_f32: null pointer");
+  PN_CHECK_ARG(n_texels > 0, "pn_prepare_latent_tables_f32: no texels");
+  PN_CHECK_ARG(((uintptr_t)tables32 & 15) == 0, "pn_prepare_latent_tables_f32: misaligned buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t total4 = n_texels * (PN_D_HIDDEN / 4);
+  int rc;
+  for (int b = 0; b < PN_COMBINE_LAYER; ++b) {
+    float* dst = tables32 + (size_t)b * n_texels * PN_D_HIDDEN;
+    if ((rc = launch_linear<false, false>(latent_nhwc, PN_D_LATENT, w->lin_z_w[b], PN_D_LATENT, nullptr, dst, n_texels,
+                                          PN_D_LATENT, st))) return rc;
+    // the same constants are folded in as in the fp16 tables (lin_in.bias into table 0, fc_1 biases of blocks 0-1 into
+    // tables 1-2), so the chain's bias tables serve both precisions
+    const float* folded = b == 0 ? w->lin_in_b : w->fc1_b[b - 1];
+    table_bias_kernel<<<ceil_div(total4, 256), 256, 0, st>>>((float4*)dst, w->lin_z_b[b], folded, total4);
+    PN_LAUNCH_OK("table_bias_kernel");
+    count_launch();
+  }
+  return PN_OK;
+}
+
 // Training mode rebuilds the tables every step (the lin_z weights change): the same product on the tensor cores.
 // latent16 = the fp16 channels-last latent; lin_z[b].weight enters as an fp16 pair hi + lo * 2^-10 (two GEMMs into
 // the fp32 workspace), so the one coherent error source of DESIGN 3.1 -- weight rounding -- stays out of the tables;

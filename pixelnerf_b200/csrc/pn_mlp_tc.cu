@@ -112,6 +112,12 @@ struct ChainParams {
   int64_t n_points;      // SB * ppo
   const float* bias2;    // bias table of the merged phase (cumulative from block 3)
   float* park;           // 128 KB per CTA: the running fp32 sum of h over the views done so far (L2 resident)
+  // precise chain (kX3, mlp_precision = fp16x3): every 512-wide GEMM runs as three operand passes a_hi w_hi +
+  // a_hi w_lo + a_lo w_hi (fp16 pairs, fp32 accumulate); everything else stays in fp32
+  const float* tables32; // [3][n_texels][512] fp32 lin_z tables
+  const float* code32;   // (x_rows, 44) fp32 positional code, same row order as x
+  int64_t x_rows;
+  const float* w_in_t;   // lin_in.weight^T fp32 [44][512]
 };
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -157,7 +163,7 @@ __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
   return d;
 }
 
-template <bool kSave, bool kFuse = false>
+template <bool kSave, bool kFuse = false, bool kX3 = false>
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
                  const __grid_constant__ CUtensorMap map_s, const ChainParams p) {
@@ -220,7 +226,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     uint32_t as = 0, aph = 0;   // operand-chunk ring slot / phase
     // Weight tile for K-chunks kc0 and kc1 of block nb of `layer`: two boxes of [128 out x 64 in].
     auto load_w = [&](auto stage_c, int layer, int nb, int kc0, int kc1) {
-      constexpr uint32_t ws = decltype(stage_c)::value;
+      // precise chain: a two-stage ring (stages 2-3 of the ring hold the lo half of the ACT operand)
+      constexpr uint32_t ws = kX3 ? (decltype(stage_c)::value & 1u) : decltype(stage_c)::value;
       wait_bar<false>(bar(BAR_W_EMPTY + ws), ((wpar >> ws) & 1u) ^ 1u, p.err, 0x100 + ws);
       wpar ^= 1u << ws;
       if (elect_one()) {
@@ -256,13 +263,17 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     using S1 = std::integral_constant<uint32_t, 1>;
     using S2 = std::integral_constant<uint32_t, 2>;
     using S3 = std::integral_constant<uint32_t, 3>;
-    auto load_fc = [&](int layer) {   // quarter order, two K=128 items per quarter: K-chunks (h, h+2) of the group
+    auto load_fc = [&](int layer0) {   // quarter order, two K=128 items per quarter: K-chunks (h, h+2) of the group
 #pragma unroll 1
-      for (int kg = 0; kg < 2; ++kg) {
-        load_w(S0{}, layer, 0, kg * 4 + 0, kg * 4 + 2);
-        load_w(S1{}, layer, 0, kg * 4 + 1, kg * 4 + 3);
-        load_w(S2{}, layer, 1, kg * 4 + 0, kg * 4 + 2);
-        load_w(S3{}, layer, 1, kg * 4 + 1, kg * 4 + 3);
+      for (int ps = 0; ps < (kX3 ? 3 : 1); ++ps) {   // precise chain: W_hi, W_lo, W_hi (against a_hi, a_hi, a_lo)
+        const int layer = ps == 1 ? layer0 + kLayers : layer0;
+#pragma unroll 1
+        for (int kg = 0; kg < 2; ++kg) {
+          load_w(S0{}, layer, 0, kg * 4 + 0, kg * 4 + 2);
+          load_w(S1{}, layer, 0, kg * 4 + 1, kg * 4 + 3);
+          load_w(S2{}, layer, 1, kg * 4 + 0, kg * 4 + 2);
+          load_w(S3{}, layer, 1, kg * 4 + 1, kg * 4 + 3);
+        }
       }
     };
 #pragma unroll 1
@@ -326,7 +337,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // One weight stage: nk K=16 steps; A steps [0,4) come from a0, [4,8) from a1 (64-wide chunks).
     auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask) {
       constexpr uint32_t idesc = kIdesc;
-      constexpr uint32_t ws = decltype(stage_c)::value;
+      constexpr uint32_t ws = kX3 ? (decltype(stage_c)::value & 1u) : decltype(stage_c)::value;
       wait_bar<false>(bar(BAR_W_FULL + ws), (wpar >> ws) & 1u, p.err, 0x200 + ws);
       wpar ^= 1u << ws;
       tc_fence_after();
@@ -364,25 +375,33 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     };
     auto release_a = [&](uint32_t addr) { commit(BAR_A_EMPTY + (int)((addr - (smem_base + kOffA)) / kChunkBytes)); };
     const uint32_t act = smem_base + kOffAct;
+    const uint32_t act_lo = smem_base + kOffW + 2 * kWStageBytes;   // precise chain only: lo half of the operand
     // 512x512 GEMM from the ACT operand, quarter order (see header), D = 2 blocks at d_col.
     auto gemm_act = [&](uint32_t d_col, bool clear, int commit_region) {
 #pragma unroll 1
-      for (int kg = 0; kg < 2; ++kg) {
-        // K-chunks (h, h+2) of the group: the epilogue finishes chunks 0 and 2 of a block first
-        const uint32_t a = act + kg * 4 * kChunkBytes;
-        const bool clr = clear && kg == 0;
-        wait_chunk(kg * 4 + 0);
-        wait_chunk(kg * 4 + 2);
-        tc_fence_after();
-        item(S0{}, a, a + 2 * kChunkBytes, d_col, clr, 0xFFu);
-        wait_chunk(kg * 4 + 1);
-        wait_chunk(kg * 4 + 3);
-        tc_fence_after();
-        item(S1{}, a + kChunkBytes, a + 3 * kChunkBytes, d_col, false, 0xFFu);
-        if (kg == 1) commit(BAR_ACC + commit_region * 2);
-        item(S2{}, a, a + 2 * kChunkBytes, d_col + 128, clr, 0xFFu);
-        item(S3{}, a + kChunkBytes, a + 3 * kChunkBytes, d_col + 128, false, 0xFFu);
-        if (kg == 1) commit(BAR_ACC + commit_region * 2 + 1);
+      for (int ps = 0; ps < (kX3 ? 3 : 1); ++ps) {
+        // precise chain: three operand passes into the same accumulator -- a_hi W_hi, a_hi W_lo, a_lo W_hi (the
+        // producer streams W_hi, W_lo, W_hi); the accumulators are complete, and committed, in the last pass only
+        const uint32_t abase = ps == 2 ? act_lo : act;
+        const bool fin = !kX3 || ps == 2;
+#pragma unroll 1
+        for (int kg = 0; kg < 2; ++kg) {
+          // K-chunks (h, h+2) of the group: the epilogue finishes chunks 0 and 2 of a block first
+          const uint32_t a = abase + kg * 4 * kChunkBytes;
+          const bool clr = clear && kg == 0 && ps == 0;
+          wait_chunk(kg * 4 + 0);
+          wait_chunk(kg * 4 + 2);
+          tc_fence_after();
+          item(S0{}, a, a + 2 * kChunkBytes, d_col, clr, 0xFFu);
+          wait_chunk(kg * 4 + 1);
+          wait_chunk(kg * 4 + 3);
+          tc_fence_after();
+          item(S1{}, a + kChunkBytes, a + 3 * kChunkBytes, d_col, false, 0xFFu);
+          if (kg == 1 && fin) commit(BAR_ACC + commit_region * 2);
+          item(S2{}, a, a + 2 * kChunkBytes, d_col + 128, clr, 0xFFu);
+          item(S3{}, a + kChunkBytes, a + 3 * kChunkBytes, d_col + 128, false, 0xFFu);
+          if (kg == 1 && fin) commit(BAR_ACC + commit_region * 2 + 1);
+        }
       }
       ++gen;
     };
@@ -541,6 +560,80 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         __syncwarp();
       }
     };
+    // ---- precise chain (kX3) helpers ----
+    // 32 consecutive features of this thread's row -> the 64 bytes of its ACT chunk row: relu + fp16, and for the
+    // precise chain also the lo half fp16(relu(x) - hi) into the second operand buffer.
+    constexpr uint32_t kActLoOff = (uint32_t)(kOffW + 2 * kWStageBytes - kOffAct);
+    auto store_act = [&](uint32_t dst, const float (&b)[32]) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t at = dst + (((uint32_t)(ch * 4 + i) ^ sw) << 4);
+        if constexpr (!kX3) {
+          st_shared_v4(at, pack_relu_h2(b[8 * i + 0], b[8 * i + 1]), pack_relu_h2(b[8 * i + 2], b[8 * i + 3]),
+                       pack_relu_h2(b[8 * i + 4], b[8 * i + 5]), pack_relu_h2(b[8 * i + 6], b[8 * i + 7]));
+        } else {
+          uint32_t hi[4], lo[4];
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const float ra = fmaxf(b[8 * i + 2 * jj], 0.0f), rb = fmaxf(b[8 * i + 2 * jj + 1], 0.0f);
+            const __half2 h2 = __floats2half2_rn(ra, rb);
+            const float2 back = __half22float2(h2);
+            const __half2 l2 = __floats2half2_rn(ra - back.x, rb - back.y);
+            hi[jj] = *reinterpret_cast<const uint32_t*>(&h2);
+            lo[jj] = *reinterpret_cast<const uint32_t*>(&l2);
+          }
+          st_shared_v4(at, hi[0], hi[1], hi[2], hi[3]);
+          st_shared_v4(at + kActLoOff, lo[0], lo[1], lo[2], lo[3]);
+        }
+      }
+    };
+    // fp32 table blend of this lane's row, both 32-feature halves (tab32, tab32 + 64): every lane reads its own four
+    // texel rows straight from the fp32 tables (32 lines per load instruction -- the slow, simple form; the precise
+    // chain is bound by its 3x tensor work, not by this)
+    auto gather_block_x3 = [&](const float* tab32, uint32_t xslot, float (&g0)[32], float (&g1)[32]) {
+      const uint32_t rc = (uint32_t)((lq & 1) * 32 + lane);
+      const uint4 ti = ld_shared_v4(xslot + rc * 128 + ((6u ^ (rc & 7u)) << 4));
+      const uint4 tw = ld_shared_v4(xslot + rc * 128 + ((7u ^ (rc & 7u)) << 4));
+      const uint32_t idx[4] = {ti.x, ti.y, ti.z, ti.w};
+      const float wt[4] = {__uint_as_float(tw.x), __uint_as_float(tw.y), __uint_as_float(tw.z), __uint_as_float(tw.w)};
+#pragma unroll
+      for (int i = 0; i < 32; ++i) g0[i] = g1[i] = 0.0f;
+#pragma unroll 1
+      for (int k = 0; k < 4; ++k) {
+        const float4* src = reinterpret_cast<const float4*>(tab32 + (size_t)idx[k] * 512);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 a = __ldg(src + i), b = __ldg(src + 16 + i);
+          g0[4 * i] = fmaf(wt[k], a.x, g0[4 * i]); g0[4 * i + 1] = fmaf(wt[k], a.y, g0[4 * i + 1]);
+          g0[4 * i + 2] = fmaf(wt[k], a.z, g0[4 * i + 2]); g0[4 * i + 3] = fmaf(wt[k], a.w, g0[4 * i + 3]);
+          g1[4 * i] = fmaf(wt[k], b.x, g1[4 * i]); g1[4 * i + 1] = fmaf(wt[k], b.y, g1[4 * i + 1]);
+          g1[4 * i + 2] = fmaf(wt[k], b.z, g1[4 * i + 2]); g1[4 * i + 3] = fmaf(wt[k], b.w, g1[4 * i + 3]);
+        }
+      }
+    };
+    // lin_in (resnetfc.py:141-146: h = lin_in(x), K = 42) in fp32 on the CUDA cores for this lane's row: 32 features
+    // starting at n0, added to acc.  x = the unrounded positional code of the row (code32), weights = lin_in.weight^T
+    // (warp-uniform float4 loads).  The tensor-core lin_in of the fast chain still runs -- its commit is what tells
+    // both CTAs' epilogue warps that the tile's x (and taps) have landed -- but its fp16-input result is discarded.
+    auto lin_in_ffma = [&](int64_t xrow, int n0, float (&acc)[32]) {
+      if (xrow >= p.x_rows) return;     // rows of a dummy / ragged tile past the end of the input
+      const float4* xr = reinterpret_cast<const float4*>(p.code32 + (size_t)xrow * 44);
+#pragma unroll 1
+      for (int k4 = 0; k4 < 11; ++k4) {
+        const float4 xv = __ldg(xr + k4);
+        const float xs4[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const float4* wr = reinterpret_cast<const float4*>(p.w_in_t + (size_t)(k4 * 4 + kk) * 512 + n0);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 w4 = __ldg(wr + i);
+            acc[4 * i] = fmaf(xs4[kk], w4.x, acc[4 * i]); acc[4 * i + 1] = fmaf(xs4[kk], w4.y, acc[4 * i + 1]);
+            acc[4 * i + 2] = fmaf(xs4[kk], w4.z, acc[4 * i + 2]); acc[4 * i + 3] = fmaf(xs4[kk], w4.w, acc[4 * i + 3]);
+          }
+        }
+      }
+    };
     // fp32 dump of (accumulator + bias) of one block: segment end (h_io) and the debug tap
     auto dump_block = [&](uint32_t tcol, const float* bias_vec, int nb, float* dst, int64_t grow) {
 #pragma unroll 1
@@ -595,7 +688,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // gather_b >= 0 (h before blocks 0-2): add the lin_z[gather_b] table blend instead of a bias vector and
     // write the sum back to tensor memory, so the residual stream carries it from here on.
     auto epi = [&](int region, const float* bias_vec, int gather_b, uint32_t xslot, int mode, int64_t grow, bool dbg,
-                   int slot) {
+                   int slot, int64_t xrow = 0) {
 #pragma unroll 1
       for (int nb = 0; nb < 2; ++nb) {
         const int a = region * 2 + nb;
@@ -625,7 +718,10 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             if (lane == 0) bulk_wait_read0();
             __syncwarp();
           }
-          gather_block(p.tables + (size_t)gather_b * p.table_stride + c0 * 64 + 32 * ch, xslot, b0, b1);
+          if constexpr (kX3)
+            gather_block_x3(p.tables32 + (size_t)gather_b * p.table_stride + c0 * 64 + 32 * ch, xslot, b0, b1);
+          else
+            gather_block(p.tables + (size_t)gather_b * p.table_stride + c0 * 64 + 32 * ch, xslot, b0, b1);
         } else {
           ld_bias32(bias_vec + c0 * 64 + 32 * ch, b0);
           ld_bias32(bias_vec + c0 * 64 + 64 + 32 * ch, b1);
@@ -642,14 +738,20 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           continue;
         }
         uint32_t v0[32], v1[32];
-        tmem_ld_32x32(tcol, v0);
-        tmem_ld_32x32(tcol + 64, v1);
-        tmem_wait_ld();
         const uint32_t dst = smem_base + kOffAct + c0 * kChunkBytes + row_off;
+        if (kX3 && gather_b == 0) {
+          // precise chain: h_0 = lin_in(x) in fp32 (+ the table blend); the accumulator holds the discarded fp16 form
+          lin_in_ffma(xrow, c0 * 64 + 32 * ch, b0);
+          lin_in_ffma(xrow, c0 * 64 + 64 + 32 * ch, b1);
+        } else {
+          tmem_ld_32x32(tcol, v0);
+          tmem_ld_32x32(tcol + 64, v1);
+          tmem_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          b0[i] += __uint_as_float(v0[i]);
-          b1[i] += __uint_as_float(v1[i]);
+          for (int i = 0; i < 32; ++i) {
+            b0[i] += __uint_as_float(v0[i]);
+            b1[i] += __uint_as_float(v1[i]);
+          }
         }
         if (gather_b >= 0) {   // h <- h + blend: read-modify-write while no MMA touches h
 #pragma unroll
@@ -668,11 +770,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             }
           }
         }
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          st_shared_v4(dst + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
-                       pack_relu_h2(b0[8 * i + 0], b0[8 * i + 1]), pack_relu_h2(b0[8 * i + 2], b0[8 * i + 3]),
-                       pack_relu_h2(b0[8 * i + 4], b0[8 * i + 5]), pack_relu_h2(b0[8 * i + 6], b0[8 * i + 7]));
+        store_act(dst, b0);
         fence_proxy_async_smem();
         if (gather_b >= 0) tmem_wait_st();
         tc_fence_before();
@@ -680,11 +778,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         if (kSave)
           save_relu32(&map_s, stage, lane, c0 * 64 + 32 * ch, (int64_t)slot * p.save_rows + (grow - lane),
                       grow - lane < p.n_rows, b0);
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          st_shared_v4(dst + kChunkBytes + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
-                       pack_relu_h2(b1[8 * i + 0], b1[8 * i + 1]), pack_relu_h2(b1[8 * i + 2], b1[8 * i + 3]),
-                       pack_relu_h2(b1[8 * i + 4], b1[8 * i + 5]), pack_relu_h2(b1[8 * i + 6], b1[8 * i + 7]));
+        store_act(dst + kChunkBytes, b1);
         fence_proxy_async_smem();
         signal_chunk(c0 + 1);
         if (kSave)
@@ -871,19 +965,18 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           }
           float f[32];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {   // mean, one fp16 rounding
-            const float2 t2 = __half22float2(__floats2half2_rn(x[2 * i] / inv, x[2 * i + 1] / inv));
-            f[2 * i] = t2.x; f[2 * i + 1] = t2.y;
+          for (int i = 0; i < 16; ++i) {   // mean; one fp16 rounding in the fast chain, none in the precise one
+            if constexpr (kX3) {
+              f[2 * i] = x[2 * i] / inv; f[2 * i + 1] = x[2 * i + 1] / inv;
+            } else {
+              const float2 t2 = __half22float2(__floats2half2_rn(x[2 * i] / inv, x[2 * i + 1] / inv));
+              f[2 * i] = t2.x; f[2 * i + 1] = t2.y;
+            }
           }
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(f[i]);
           tmem_st_32x32(tcol + half * 64, v);
-          const uint32_t dst = smem_base + kOffAct + (c0 + half) * kChunkBytes + row_off;
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            st_shared_v4(dst + (((uint32_t)(ch * 4 + i) ^ sw) << 4),
-                         pack_relu_h2(f[8 * i + 0], f[8 * i + 1]), pack_relu_h2(f[8 * i + 2], f[8 * i + 3]),
-                         pack_relu_h2(f[8 * i + 4], f[8 * i + 5]), pack_relu_h2(f[8 * i + 6], f[8 * i + 7]));
+          store_act(smem_base + kOffAct + (c0 + half) * kChunkBytes + row_off, f);
           tmem_wait_st();
           fence_proxy_async_smem();
           tc_fence_before();
@@ -908,7 +1001,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           if (++xs == kASlots) xs = 0;
 #pragma unroll 1
           for (int b = 0; b < 3; ++b) {
-            epi(0, p.bias + b * 512, b, xslot, 0, none, false, 2 * b);
+            epi(0, p.bias + b * 512, b, xslot, 0, none, false, 2 * b,
+                ((int64_t)tile * p.n_views + k) * kTileRows + rank * kRows + r);
             epi(1, p.bias + (6 + b) * 512, -1, 0u, 0, none, false, 2 * b + 1);
           }
           merge(k);
@@ -926,7 +1020,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       if (!full_front) epi_load(grow);
       for (int b = p.first_block; b < p.last_block; ++b) {
         if (b > p.first_block || full_front)
-          epi(0, p.bias + b * 512, b < 3 ? b : -1, xslot, 0, grow, p.debug_h != nullptr && p.debug_stage == b, 2 * b);
+          epi(0, p.bias + b * 512, b < 3 ? b : -1, xslot, 0, grow, p.debug_h != nullptr && p.debug_stage == b, 2 * b, grow);
         epi(1, p.bias + (6 + b) * 512, -1, 0u, 0, grow, false, 2 * b + 1);
       }
       if (has_head) {
@@ -976,6 +1070,27 @@ pack_weights_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
   dst[i] = __float2half_rn(v);
 }
 
+// Precise chain (fp16x3): the lo halves of the ten 512x512 matrices, W_lo = fp16(W - fp16(W)), as layers
+// [kLayers + L_FC, kLayers + L_OUT) of the packed buffer (the other slots of the second half stay unused), and
+// lin_in.weight transposed in fp32 ([k][n], n contiguous) for the CUDA-core lin_in.
+__global__ void __launch_bounds__(256)
+pack_weights_lo_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)(L_OUT - L_FC) * 512 * 512) return;
+  const int layer = L_FC + (int)(i / (512 * 512));
+  const int n = (int)((i / 512) % 512), k = (int)(i % 512);
+  const int b = (layer - L_FC) >> 1;
+  const float v = ((layer - L_FC) & 1) ? w.fc1_w[b][n * 512 + k] : w.fc0_w[b][n * 512 + k];
+  dst[((size_t)(kLayers + layer) * 512 + n) * 512 + k] = __float2half_rn(v - __half2float(__float2half_rn(v)));
+}
+__global__ void __launch_bounds__(256)
+pack_lin_in_t_kernel(pn_mlp_weights_t w, float* __restrict__ dst) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 44 * 512) return;
+  const int k = i / 512, n = i % 512;
+  dst[i] = k < PN_D_CODE ? w.lin_in_w[n * PN_D_CODE + k] : 0.0f;
+}
+
 // table A: cumulative from lin_in; table B: cumulative from block 3 (h handed over with biases in).
 __global__ void __launch_bounds__(512)
 pack_bias_kernel(pn_mlp_weights_t w, float* __restrict__ ta, float* __restrict__ tb) {
@@ -1005,6 +1120,8 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, const CUte
     PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
     PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
     PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
+    PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
+    PN_CUDA_OK(cudaFuncSetAttribute(mlp_chain_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemAlloc));
     attr_set.mark(attr_dev);
   }
   int dev = 0, sms = 0;
@@ -1031,7 +1148,9 @@ static int launch_chain(const CUtensorMap& mw, const CUtensorMap& mx, const CUte
   attrs[1].val.preferredClusterDim.x = 4; attrs[1].val.preferredClusterDim.y = 1; attrs[1].val.preferredClusterDim.z = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 2;
-  if (p.group > 0) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false, true>, mw, mx, ms, p));
+  if (p.tables32 && p.group > 0) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false, true, true>, mw, mx, ms, p));
+  else if (p.tables32) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false, false, true>, mw, mx, ms, p));
+  else if (p.group > 0) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false, true>, mw, mx, ms, p));
   else if (p.save) PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<true>, mw, mx, ms, p));
   else PN_CUDA_OK(cudaLaunchKernelEx(&cfg, mlp_chain_kernel<false>, mw, mx, ms, p));
   PN_LAUNCH_OK("mlp_chain_kernel");
@@ -1060,6 +1179,31 @@ extern "C" int pn_prepare_weights(const pn_mlp_weights_t* w, void* packed, size_
   pack_bias_kernel<<<1, 512, 0, st>>>(*w, ta, tb);
   PN_LAUNCH_OK("pack_bias_kernel");
   pn::count_launch(2);
+  return PN_OK;
+}
+
+// packed buffer of the precise chain: [hi layers][lo layers][bias table A][bias table B][lin_in.weight^T fp32 (44 x 512)]
+constexpr size_t kX3BiasOff = 2 * pn::tc::kPackedWeightBytes;
+constexpr size_t kX3WinOff = kX3BiasOff + 2 * pn::tc::kBiasBytes;
+extern "C" size_t pn_mlp_tc_packed_x3_bytes(void) { return kX3WinOff + 44 * 512 * sizeof(float); }
+
+extern "C" int pn_prepare_weights_x3(const pn_mlp_weights_t* w, void* packed, size_t packed_bytes, pn_stream_t stream) {
+  using namespace pn::tc;
+  PN_CHECK_ARG(w && packed, "pn_prepare_weights_x3: null pointer");
+  PN_CHECK_ARG(packed_bytes >= pn_mlp_tc_packed_x3_bytes(), "pn_prepare_weights_x3: buffer too small");
+  PN_CHECK_ARG(((uintptr_t)packed & 255) == 0, "pn_prepare_weights_x3: buffer must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t total = (int64_t)kLayers * 512 * 512;
+  pack_weights_kernel<<<pn::ceil_div(total, 256), 256, 0, st>>>(*w, (__half*)packed);
+  PN_LAUNCH_OK("pack_weights_kernel");
+  PN_CUDA_OK(cudaMemsetAsync((char*)packed + kPackedWeightBytes, 0, kPackedWeightBytes, st));
+  pack_weights_lo_kernel<<<pn::ceil_div((int64_t)(L_OUT - L_FC) * 512 * 512, 256), 256, 0, st>>>(*w, (__half*)packed);
+  PN_LAUNCH_OK("pack_weights_lo_kernel");
+  pack_bias_kernel<<<1, 512, 0, st>>>(*w, (float*)((char*)packed + kX3BiasOff), (float*)((char*)packed + kX3BiasOff + kBiasBytes));
+  PN_LAUNCH_OK("pack_bias_kernel");
+  pack_lin_in_t_kernel<<<pn::ceil_div(44 * 512, 256), 256, 0, st>>>(*w, (float*)((char*)packed + kX3WinOff));
+  PN_LAUNCH_OK("pack_lin_in_t_kernel");
+  pn::count_launch(4);
   return PN_OK;
 }
 
@@ -1196,6 +1340,54 @@ extern "C" int pn_mlp_forward_tc_grouped(const void* packed, const void* tables,
   p.group = 1;
   p.n_points = n_pts;
   p.n_rows = n_pts;          // what the head's row check compares against
+  p.first_block = 0;
+  p.last_block = 5;
+  p.park = (float*)((char*)workspace + 256);
+  return launch_chain(mw, mx, mw, p, st);
+}
+
+// ---- precise chain: mlp_precision = fp16x3 ------------------------------------------------------------------------
+extern "C" int pn_mlp_forward_tc_x3(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
+                                    const float* code32, int n_objects, int n_views, int64_t points_per_object,
+                                    float* out, float* pre_act, void* workspace, size_t workspace_bytes,
+                                    pn_stream_t stream) {
+  using namespace pn::tc;
+  PN_CHECK_ARG(packed_x3 && tables32 && feat_x && code32 && out && workspace, "pn_mlp_forward_tc_x3: null pointer");
+  PN_CHECK_ARG(n_texels > 0, "pn_mlp_forward_tc_x3: no texels");
+  PN_CHECK_ARG(n_objects > 0 && n_views > 0 && n_views <= 64 && points_per_object >= 0, "pn_mlp_forward_tc_x3: bad sizes");
+  const int64_t n_pts = (int64_t)n_objects * points_per_object;
+  if (n_pts == 0) return PN_OK;
+  const bool fused = n_views > 1;
+  const int64_t x_rows = fused ? pn_point_taps_grouped_rows(n_pts, n_views) : n_pts;
+  PN_CHECK_ARG(x_rows < (1ll << 31) - 4096, "pn_mlp_forward_tc_x3: too many rows for one launch");
+  PN_CHECK_ARG(workspace_bytes >= pn_mlp_tc_grouped_workspace_bytes(), "pn_mlp_forward_tc_x3: workspace too small");
+  PN_CHECK_ARG(((uintptr_t)workspace & 255) == 0 && ((uintptr_t)tables32 & 15) == 0 && ((uintptr_t)feat_x & 15) == 0 &&
+                   ((uintptr_t)code32 & 15) == 0 && ((uintptr_t)packed_x3 & 255) == 0,
+               "pn_mlp_forward_tc_x3: misaligned buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUtensorMap mw, mx;
+  int rc;
+  if ((rc = make_map(&mw, packed_x3, (uint64_t)2 * kLayers * 512, 512, 1024, 128))) return rc;
+  if ((rc = make_map(&mx, feat_x, (uint64_t)x_rows, 64, 128, kRows))) return rc;
+  unsigned int* err = (unsigned int*)workspace;
+  PN_CUDA_OK(cudaMemsetAsync(err, 0, 4, st));
+  ChainParams p = {};
+  p.out = (float4*)out;
+  p.pre = (float4*)pre_act;
+  p.err = err;
+  p.table_stride = n_texels * 512;
+  p.tables32 = tables32;
+  p.code32 = code32;
+  p.x_rows = x_rows;
+  p.w_in_t = (const float*)((const char*)packed_x3 + kX3WinOff);
+  p.ppo = points_per_object;
+  p.n_views = n_views;
+  p.debug_stage = -1;
+  p.bias = (const float*)((const char*)packed_x3 + kX3BiasOff);
+  p.bias2 = (const float*)((const char*)packed_x3 + kX3BiasOff + kBiasBytes);
+  p.n_points = n_pts;
+  p.n_rows = n_pts;
+  p.group = fused ? 1 : 0;
   p.first_block = 0;
   p.last_block = 5;
   p.park = (float*)((char*)workspace + 256);

@@ -13,7 +13,7 @@ from .._prof import prof_range
 from .code import PositionalEncoding
 from .model_util import make_encoder, make_mlp
 
-_PRECISIONS = ("fp32", "fp16", "bf16")
+_PRECISIONS = ("fp32", "fp16", "fp16x3", "bf16")
 
 
 class PixelNeRFNet(torch.nn.Module):
@@ -54,7 +54,9 @@ class PixelNeRFNet(torch.nn.Module):
         self.register_buffer("c", torch.empty(1, 2), persistent=False)
         self.num_objs = 0
         self.num_views_per_obj = 1
-        # "fp16" (default): tcgen05 chain, 2e-3 parity -- the product path.  "fp32": 1e-4 parity path.
+        # "fp16" (default): tcgen05 chain, 2e-3 parity -- the product path.  "fp16x3": the precise tcgen05 chain (three
+        # hi/lo operand passes per GEMM, everything else fp32), 1e-4 parity; inference -- in training mode it runs the
+        # fp32 kernels.  "fp32": the CUDA-core 1e-4 parity path.
         # Not a reference conf key: the reference's conf files never set it, so they get the tensor-core chain.
         self.mlp_precision = conf.get_string("mlp_precision", os.environ.get("PIXELNERF_B200_MLP", "fp16"))
         assert self.mlp_precision in _PRECISIONS, self.mlp_precision
@@ -139,20 +141,21 @@ class PixelNeRFNet(torch.nn.Module):
             self._latent_nhwc[dtype] = hit = (key, t)
         return hit[1]
 
-    def latent_tables(self, coarse):
+    def latent_tables(self, coarse, fp32=False):
         """Per-texel lin_z tables of one MLP for the tensor-core chain (lin_z of a bilinear blend = blend of
         lin_z of the texels, resnetfc.py:174-180 after encoder.py:102-108): rebuilt when the latent or any
         parameter of that MLP changed."""
         mlp = self._mlp(coarse)
         # training mode rebuilds the tables every optimiser step: tensor-core product from the fp16 latent
         # (hi + lo weights); eval mode builds them once per encode in fp32
-        lat = self.latent_nhwc(torch.float16 if self.training else torch.float32)
+        lat = self.latent_nhwc(torch.float16 if (self.training and not fp32) else torch.float32)
         params = mlp.weight_dict()
         key = (self._latent_nhwc[lat.dtype][0], lat.dtype, tuple((q.data_ptr(), q._version) for q in params.values()))
-        slot = "coarse" if mlp is self.mlp_coarse else "fine"
+        slot = ("coarse" if mlp is self.mlp_coarse else "fine") + ("32" if fp32 else "")
         hit = self._tables.get(slot)
         if hit is None or hit[0] != key:
-            hit = (key, _lib.prepare_latent_tables({k: v.detach() for k, v in params.items()}, lat))
+            build = _lib.prepare_latent_tables_f32 if fp32 else _lib.prepare_latent_tables
+            hit = (key, build({k: v.detach() for k, v in params.items()}, lat))
             self._tables[slot] = hit
         return hit[1]
 
@@ -183,6 +186,8 @@ class PixelNeRFNet(torch.nn.Module):
 
     def _run_points(self, coarse, ppo, rays, z, xyz, viewdirs):
         prec = self.mlp_precision
+        if prec == "fp16x3" and (self.training or getattr(self, "_train_stash", None) is not None):
+            prec = "fp32"      # the precise chain is an inference path; training uses the fp32 kernels (fwd and bwd)
         mlp = self._mlp(coarse)
         cam = self._cam
         if prec == "fp32":
@@ -191,8 +196,14 @@ class PixelNeRFNet(torch.nn.Module):
                                              viewdirs=viewdirs, ldx=44)
             with prof_range("resnetfc_infer"):
                 return _lib.mlp_forward_fp32(mlp.packed("fp32"), fz, fx, cam["n_objects"], cam["n_views"], ppo)
-        tables = self.latent_tables(coarse)
         _, hl, wl, _ = self.latent_nhwc(torch.float32).shape
+        if prec == "fp16x3":
+            with prof_range("encoder_index"):
+                fx, code32 = _lib.point_taps_f32(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
+            with prof_range("resnetfc_infer"):
+                return _lib.mlp_forward_tc_x3(mlp.packed("fp16x3"), self.latent_tables(coarse, fp32=True), fx, code32,
+                                              cam["n_objects"], cam["n_views"], ppo)
+        tables = self.latent_tables(coarse)
         stash = getattr(self, "_train_stash", None)
         if cam["n_views"] > 1 and not self.training and not (stash is not None and rays is not None) and \
                 os.environ.get("PIXELNERF_B200_TWO_LAUNCH") != "1":

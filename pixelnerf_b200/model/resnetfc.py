@@ -77,6 +77,8 @@ class ResnetFC(nn.Module):
         if hit is None or hit[0] != key:
             if precision == "fp32":
                 hit = (key, _lib.pack_weights_fp32(params))
+            elif precision == "fp16x3":       # precise chain: fp16 hi + lo layers, fp32 lin_in
+                hit = (key, _lib.pack_weights_x3(params))
             elif precision == "bf16_train":   # row-major bf16 copies for the tensor-core backward
                 hit = (key, _lib.pack_weights_bf16(params))
             else:

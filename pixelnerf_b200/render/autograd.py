@@ -46,7 +46,7 @@ class RenderFunction(torch.autograd.Function):
         ns = getattr(model, "num_views_per_obj", 1)
         k_all = renderer.n_coarse + ((renderer.n_coarse + renderer.n_fine) if renderer.using_fine else 0)
         stash_bytes = rays.shape[0] * ns * k_all * (11 * 1024 + 160)
-        keep = model.mlp_precision != "fp32" and stash_bytes <= renderer.train_stash_bytes
+        keep = model.mlp_precision == "fp16" and stash_bytes <= renderer.train_stash_bytes
         model._train_stash = [] if keep else None
         renderer._keep_parts = bool(renderer.depth_sample_grad and renderer.n_fine_depth > 0)
         try:
@@ -59,7 +59,7 @@ class RenderFunction(torch.autograd.Function):
         # What the backward needs of the model is captured NOW (torch's autograd captures tensors the same way): a
         # second encode() or a parameter update between this forward and its backward must not change the camera,
         # latent or tables the gradients are computed against.
-        tensor_core = model.mlp_precision != "fp32"
+        tensor_core = model.mlp_precision == "fp16"
         ctx.snap = dict(cam=model._cam, ns=ns, latent32=model.latent_nhwc(torch.float32),
                         tables={c: model.latent_tables(c) for c in (True, False)} if tensor_core and not keep else None,
                         versions=tuple(p._version for p in params))
@@ -160,7 +160,7 @@ def _backward_pass(renderer, model, snap, coarse, rays, z, sb, g_w, g_rgb, g_dep
         _lib.depth_sample_bwd(cam, latent, rr, zz, cut(z_dep, s, e), g_z, g_h0, g_fz, w_in, part)
         g_dep.view(sb, b)[:, s:e] += part.view(sb, e - s)
 
-    tensor_core = model.mlp_precision != "fp32"
+    tensor_core = model.mlp_precision == "fp16"
     if stash is not None:
         # the forward kept its operands: one backward per forward chunk, nothing is recomputed
         w16 = mlp.packed("bf16_train")

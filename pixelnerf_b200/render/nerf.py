@@ -134,7 +134,7 @@ class NeRFRenderer(torch.nn.Module):
     def _fused_ok(self, model, forced):
         """The whole chunk can go through pn_render_rays: tensor-core MLP, nothing teacher-forced, and no
         training forward that has to keep intermediates for the backward."""
-        return (model.mlp_precision != "fp32" and not forced and not self._keep_parts
+        return (model.mlp_precision == "fp16" and not forced and not self._keep_parts
                 and not (self.training and self.noise_std > 0.0)
                 and getattr(model, "_train_stash", None) is None and os.environ.get("PIXELNERF_B200_STAGED") != "1")
 
@@ -161,7 +161,7 @@ class NeRFRenderer(torch.nn.Module):
         from the pose where they need it (pn_render_frames).  Same result, bit for bit, as
         ``self(model, util.gen_rays(poses, ...).reshape(1, -1, 8))`` with the same draws / seed and chunking.  Eval-mode
         tensor-core path only (one encoded object).  Returns DotMap{coarse:{rgb (NV,H,W,3), depth (NV,H,W)}, fine:{...}}."""
-        if model.mlp_precision == "fp32" or (torch.is_grad_enabled() and self.training):
+        if model.mlp_precision != "fp16" or (torch.is_grad_enabled() and self.training):
             raise NotImplementedError("render_frames: the no-grad tensor-core path only; build rays with util.gen_rays")
         if model._cam is None:
             raise RuntimeError("call encode() before render_frames()")

@@ -20,7 +20,7 @@ def render_video(render_par, poses, width, height, focal, z_near, z_far, c=None,
         device = next((b.device for b in render_par.buffers()), torch.device("cuda"))
     poses = poses.to(device=device, dtype=torch.float32)
     renderer, net = getattr(render_par, "renderer", None), getattr(render_par, "net", None)
-    fused = (renderer is not None and net is not None and getattr(net, "mlp_precision", "fp32") != "fp32"
+    fused = (renderer is not None and net is not None and getattr(net, "mlp_precision", "fp32") == "fp16"
              and getattr(net, "_cam", None) is not None and net._cam["n_objects"] == 1 and not renderer.training)
     if fused:
         # one GPU, tensor-core path: the rays are generated inside the render kernels (NeRFRenderer.render_frames),
