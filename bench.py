@@ -571,7 +571,7 @@ def run_gpu(args):
                          "executed_frac": achieved * exe / pk["tf_sustained"],
                          "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
                          "traffic": chain_traffic(ns, points_rank, launches_per_step) if args.precision == "fp16" else None,
-                         "traffic_source": "profiles/r02_chain_traffic.json: ncu dram read+write bytes of the chain "
+                         "traffic_source": "profiles/r02_chain_traffic.json (from profiles/r02m_chain_ncu_summary.json): ncu dram read+write bytes of the chain "
                                            "launches of one pass at THIS view count, per point, x points per step / "
                                            "launches per step (a live run cannot read dram counters)",
                          "peak_source": pk["source"] + ", sustained bf16",
