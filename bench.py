@@ -595,6 +595,51 @@ def run_gpu(args):
         job.dist.destroy_process_group()
 
 
+def run_in_process(args):
+    """--in-process: ONE process driving `--gpus N` devices through renderer.bind_parallel(net, [0..N-1]) ->
+    parallel.DeviceSharded -- what the reference's scripts do with several --gpu_id values (eval/gen_video.py:110: a
+    single process, DataParallel in the reference).  Same workloads as the torchrun form: N SRN-car frames per call
+    (weak), one DTU frame and the 40-frame NS=2 video (strong).  Wall-clock around a synchronise of every device (the
+    devices are driven by host threads; CUDA events of one stream do not span them).  Not the headline line."""
+    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200.testing import build_net
+    n_dev = args.gpus
+    assert torch.cuda.device_count() >= n_dev, f"--in-process --gpus {n_dev} needs {n_dev} visible devices"
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+
+    def sync_all():
+        for i in range(n_dev):
+            torch.cuda.synchronize(i)
+
+    out = {}
+    for key, scene, n_frames in (("srn_car_frames", "srn_car", n_dev), ("dtu_frame", "dtu", 1), ("srn_chair_video40", "srn_chair", 40)):
+        sc = syn.scene(scene)
+        net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), dev, mlp_precision=args.precision)
+        par = ren.bind_parallel(net, list(range(n_dev)), simple_output=True).eval()
+        az = [10.0 * i for i in range(n_frames)] if scene != "srn_chair" else [float(a) for a in torch.linspace(-180, 180, n_frames + 1)[:-1]]
+        rays = torch.cat([frame_rays(sc, a, per_ray_bounds=(scene == "dtu")) for a in az])[None].to(dev)
+        n = rays.shape[1]
+        with torch.no_grad():
+            for _ in range(3):
+                par(rays)
+            sync_all()
+            reps = max(3, min(args.steps, 10))
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                rgb, depth = par(rays)
+            sync_all()
+            dt = (time.perf_counter() - t0) / reps
+        assert rgb.device == dev and torch.isfinite(rgb).all()
+        out[key] = {"workload": WORKLOADS[scene] + f" x {n_frames} frame(s) in one call", "rays": n, "n_gpus": n_dev,
+                    "ms_per_call": dt * 1e3, "rays/s": n / dt, "reps": reps}
+        del net, ren, par, rays
+        torch.cuda.empty_cache()
+    print(json.dumps({"metric": "rays/sec coarse+fine, one process driving N GPUs (bind_parallel(net, gpu_ids) -> DeviceSharded)",
+                      "unit": "rays/s", "n_gpus": n_dev, "timing": "wall clock around a synchronise of every device",
+                      "mlp_precision": args.precision, "workloads": out}))
+
+
 def run_train(args):
     """--train: BASELINE config 5, one training step = render 4 objects x `--train-rays` rays (want_weights, train
     mode) -> MSE on coarse+fine rgb vs U(0,1) targets -> backward through composite / ResnetFC / latent gather
@@ -685,10 +730,14 @@ def main():
     ap.add_argument("--scene", default=SCENE, choices=sorted(WORKLOADS),
                     help="srn_car = the headline workload (BASELINE configs[1]); the others are extra measurements")
     ap.add_argument("--kernels", action="store_true", help="per-kernel HBM roofline of the memory-bound kernels")
+    ap.add_argument("--in-process", action="store_true",
+                    help="one process driving --gpus N devices through bind_parallel(net, gpu_ids) (DeviceSharded); not the headline")
     ap.add_argument("--train", action="store_true", help="training-step timing (BASELINE config 5), not the headline")
     ap.add_argument("--train-rays", type=int, nargs="+", default=[128, 4096], help="rays per object for --train")
     args = ap.parse_args()
-    if args.kernels:
+    if args.in_process:
+        run_in_process(args)
+    elif args.kernels:
         run_kernels(args)
     elif args.train and args.impl == "torch-cuda":
         run_torch_cuda(args)

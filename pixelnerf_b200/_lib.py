@@ -597,7 +597,7 @@ def mlp_forward_tc(packed, tables, feat_x, n_objects, n_views, ppo, want_pre=Fal
         dbg_h = torch.zeros(rows, D_HIDDEN, device=dev, dtype=torch.float32)
         dbg = C.byref(MlpTcDebug(dbg_h.data_ptr(), int(debug_stage)))
     if os.environ.get("PN_TC_EXPERIMENT"):   # timing experiments (wrong results), see pn_mlp_tc.cu
-        dbg = C.byref(MlpTcDebug(None, {"no_epilogue": -99, "no_gather": -98}[os.environ["PN_TC_EXPERIMENT"]]))
+        dbg = C.byref(MlpTcDebug(None, {"no_epilogue": -99, "no_gather": -98, "gather_loads_only": -97, "gather_no_loads": -96}[os.environ["PN_TC_EXPERIMENT"]]))
     with _Timed("mlp"):
         _check(lib().pn_mlp_forward_tc(packed.data_ptr(), tables.data_ptr(), tables.shape[1],
                                        _ptr(feat_x, torch.float16), n_objects, n_views, ppo, _ptr(out), _ptr(pre), ws.data_ptr(), nbytes, dbg,

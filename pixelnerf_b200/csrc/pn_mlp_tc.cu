@@ -507,12 +507,32 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       for (int half = 0; half < 2; ++half) {
         const uint4* src = reinterpret_cast<const uint4*>(tab + half * 64) + (lane & 3);
         uint4 t[4][4];   // every global load of the half is in flight before the first is consumed
+        if (p.debug_stage == -96) {   // timing experiment only (wrong results): blend + staging without the loads
 #pragma unroll
-        for (int it = 0; it < 4; ++it) {
-          t[it][0] = __ldg(src + (size_t)ti[it].x * 64);
-          t[it][1] = __ldg(src + (size_t)ti[it].y * 64);
-          t[it][2] = __ldg(src + (size_t)ti[it].z * 64);
-          t[it][3] = __ldg(src + (size_t)ti[it].w * 64);
+          for (int it = 0; it < 4; ++it)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) t[it][k] = make_uint4(ti[it].x, ti[it].y, ti[it].z, ti[it].w);
+        } else {
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            t[it][0] = __ldg(src + (size_t)ti[it].x * 64);
+            t[it][1] = __ldg(src + (size_t)ti[it].y * 64);
+            t[it][2] = __ldg(src + (size_t)ti[it].z * 64);
+            t[it][3] = __ldg(src + (size_t)ti[it].w * 64);
+          }
+        }
+        if (p.debug_stage == -97) {   // timing experiment only (wrong results): the loads without blend and staging
+          uint32_t keep = 0;
+#pragma unroll
+          for (int it = 0; it < 4; ++it)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) keep ^= t[it][k].x ^ t[it][k].y ^ t[it][k].z ^ t[it][k].w;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            if (half == 0) g0[i] = __uint_as_float(keep & 0x3f800000u);
+            else g1[i] = __uint_as_float(keep & 0x3f800000u);
+          }
+          continue;
         }
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
