@@ -134,9 +134,27 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
   uint32_t o00 = 0, o01 = 0, o10 = 0, o11 = 0;
   float w00 = 0.f, w01 = 0.f, w10 = 0.f, w11 = 0.f;
   // row = (obj * NS + view) * P + p ...
-  int64_t ov = row / ppo;
-  int64_t p = row - ov * ppo;
-  if (kTaps && group > 0) {
+  // (index arithmetic in 32 bits whenever the launch fits -- warp uniform; a 64-bit division is ~50 instructions and
+  // this kernel is instruction bound: eight of them were a quarter of the taps kernel)
+  const bool idx32 = n_rows <= 0x7fffffffll && (int64_t)cam.n_objects * ppo <= 0x7fffffffll;
+  int64_t ov, p;
+  if (idx32) {
+    const uint32_t o32 = (uint32_t)row / (uint32_t)ppo;
+    ov = o32;
+    p = (uint32_t)row - o32 * (uint32_t)ppo;
+  } else {
+    ov = row / ppo;
+    p = row - ov * ppo;
+  }
+  if (kTaps && group > 0 && idx32) {
+    const uint32_t blk = (uint32_t)row >> 7, nv = (uint32_t)cam.n_views;
+    const uint32_t s = blk / nv, v = blk - s * nv;
+    const uint32_t q = s * 128u + ((uint32_t)row & 127u);
+    valid = q < (uint32_t)cam.n_objects * (uint32_t)ppo;
+    const uint32_t obj_q = q / (uint32_t)ppo;
+    p = q - obj_q * (uint32_t)ppo;
+    ov = obj_q * nv + v;
+  } else if (kTaps && group > 0) {
     // ... or, grouped order (pn_point_taps_grouped, for the chain's on-chip view mean): super-tile S = 128 points
     // [128 S, 128 S + 128) of the flattened (object, point) index, one 128-row block per view:
     // row (S * n_views + v) * 128 + m = view v of point 128 S + m; points past the end are zero rows (zero taps weights)
@@ -147,6 +165,8 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     const int64_t obj_q = q / ppo;
     p = q - obj_q * ppo;
     ov = obj_q * cam.n_views + v;
+  }
+  if (kTaps && group > 0) {
     if (!valid) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(stage + lane * kTapsPitch + 16 * i) = make_uint4(0u, 0u, 0u, 0u);
@@ -161,10 +181,19 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     const int obj = view / cam.n_views;
     float x, y, z, dx, dy, dz;
     if (rays.rays || rays.poses) {  // x = o + z d  (src/render/nerf.py:185), separate mul and add like torch
-      const int64_t ray = obj * (ppo / n_samples) + p / n_samples;
+      int64_t ray;
+      int ks;
+      if (idx32) {
+        const uint32_t ns32 = (uint32_t)n_samples, pr = (uint32_t)p / ns32;
+        ks = (int)((uint32_t)p - pr * ns32);
+        ray = (int64_t)((uint32_t)obj * ((uint32_t)ppo / ns32) + pr);
+      } else {
+        ray = obj * (ppo / n_samples) + p / n_samples;
+        ks = (int)(p % n_samples);
+      }
       float4 r0, r1;
       ray_load(rays, ray, r0, r1);
-      const float zz = zs[ray * n_samples + (p % n_samples)];
+      const float zz = zs[ray * n_samples + ks];
       dx = r0.w; dy = r1.x; dz = r1.y;
       x = __fadd_rn(r0.x, __fmul_rn(zz, dx));
       y = __fadd_rn(r0.y, __fmul_rn(zz, dy));
@@ -232,7 +261,13 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
           const int j = (e - 3) / 3, d = (e - 3) - j * 3;
           const float freq = 1.5f * (float)(1 << (j >> 1));      // freq_factor * 2^k (conf/default.conf:19-23)
           const float phase = (j & 1) ? 1.57079637050628662109375f : 0.0f;  // float32(pi/2) (code.py:24-28)
-          val = sinf(__fadd_rn(phase, __fmul_rn(comp[d], freq)));  // addcmul then sin (code.py:38)
+          const float arg = __fadd_rn(phase, __fmul_rn(comp[d], freq));   // addcmul then sin (code.py:38)
+          // The fp16 code (tensor-core paths: taps and the materialised training features, which must agree bit for
+          // bit -- tests/test_gpu_guards.py; rounded to 2^-11 relative right below) takes the SFU sine:
+          // |error| <= |arg| * 2^-24 + 2^-21.4 (arguments reach ~100: 6e-6), a fortieth of the fp16 quantum, against
+          // ~25 instructions for sinf -- 36 of them per row were two thirds of this kernel.  The fp32 code (parity
+          // path, and code32 of the precise chain) keeps sinf.
+          val = (sizeof(OutT) == 2 && !(kTaps && code32)) ? __sinf(arg) : sinf(arg);
         } else if (e < 42) {
           val = rd[e - 39];
         }

@@ -19,15 +19,28 @@ __device__ __forceinline__ float lerp_depth(float near, float far, float zs, boo
 
 // One thread per 4 consecutive samples (one Philox call yields their 4 draws, one 16-byte store);
 // consecutive threads write consecutive z: fully coalesced.  Kc % 4 == 0 takes this path.
+// The kernel is instruction bound (Philox4x32-10 is ~70 of its ~110 instructions per thread), so `lindisp` is a
+// template parameter (its three IEEE divisions per sample stay out of the linear instantiation) and the index split is
+// 32-bit when the launch fits.
+template <bool kLindisp>
 __global__ void __launch_bounds__(256)
 sample_coarse4_kernel(const RaySrc rays, const float* __restrict__ u,
                       const float* __restrict__ lin, float* __restrict__ z, int64_t total4, int kc,
-                      float step, bool lindisp, uint64_t seed) {
+                      float step, uint64_t seed) {
+  constexpr bool lindisp = kLindisp;
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= total4) return;
   const int64_t i = q * 4;
-  const int64_t r = i / kc;
-  const int k = (int)(i - r * kc);
+  int64_t r;
+  int k;
+  if (total4 <= 0x3fffffffll) {   // uniform
+    const uint32_t kc4 = (uint32_t)kc >> 2, r32 = (uint32_t)q / kc4;
+    r = r32;
+    k = (int)(((uint32_t)q - r32 * kc4) << 2);
+  } else {
+    r = i / kc;
+    k = (int)(i - r * kc);
+  }
   float4 uu;
   if (u) {
     uu = *reinterpret_cast<const float4*>(u + i);
@@ -314,9 +327,12 @@ int sample_coarse_src(const RaySrc& rays, const float* u, const float* lin, floa
   const float step = (float)(1.0 / (double)n_coarse);
   const bool vec = n_coarse % 4 == 0 && ((uintptr_t)z & 15) == 0 && ((uintptr_t)lin & 15) == 0 &&
                    (!u || ((uintptr_t)u & 15) == 0);
-  if (vec)
-    pn::sample_coarse4_kernel<<<pn::ceil_div(total / 4, 256), 256, 0, (cudaStream_t)stream>>>(
-        rays, u, lin, z, total / 4, n_coarse, step, lindisp != 0, seed);
+  if (vec && lindisp)
+    pn::sample_coarse4_kernel<true><<<pn::ceil_div(total / 4, 256), 256, 0, (cudaStream_t)stream>>>(
+        rays, u, lin, z, total / 4, n_coarse, step, seed);
+  else if (vec)
+    pn::sample_coarse4_kernel<false><<<pn::ceil_div(total / 4, 256), 256, 0, (cudaStream_t)stream>>>(
+        rays, u, lin, z, total / 4, n_coarse, step, seed);
   else
     pn::sample_coarse_kernel<<<pn::ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
         rays, u, lin, z, total, n_coarse, step, lindisp != 0, seed);
