@@ -658,7 +658,10 @@ def run_train(args):
     ren.train()
     for q in net.parameters():
         q.requires_grad_(True)
-    opt = torch.optim.Adam([q for n, q in net.named_parameters() if n.startswith("mlp_")], lr=1e-4)
+    opt = torch.optim.Adam([q for n, q in net.named_parameters() if n.startswith("mlp_")], lr=1e-4,
+                           capturable=bool(args.graph))
+    if args.graph:
+        ren.use_device_seed(dev)      # the draws' call seed in device memory, advanced by a captured add
     res = []
     for n_obj_rays in args.train_rays:
         g = torch.Generator().manual_seed(n_obj_rays)
@@ -696,6 +699,37 @@ def run_train(args):
         _lib.PROFILE = None
         res.append({"rays_per_step": n, "ms_per_step": ms, "rays/s": n / (ms * 1e-3), "mlp_TFLOP/s_fwd+bwd": flop / (ms * 1e-3) / 1e12,
                     "loss": float(loss), "kernel_ms": fam})
+        if args.graph:
+            import gc
+            # the same step captured once in a CUDA graph and replayed (tests/test_gpu_graph.py: same loss curve).
+            # The eager steps' autograd graph must be gone first: it keeps the parameters' gradient accumulators alive,
+            # and those remember the (legacy default) stream they were made on, which may not be touched while capturing
+            loss = None
+            gc.collect()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    step()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                g_loss = step()
+            for _ in range(3):
+                graph.replay()
+            torch.cuda.synchronize()
+            reps = max(5, steps)
+            a.record()
+            for _ in range(reps):
+                graph.replay()
+            b.record()
+            b.synchronize()
+            g_ms = a.elapsed_time(b) / reps
+            res[-1]["cuda_graph"] = {"ms_per_step": g_ms, "rays/s": n / (g_ms * 1e-3), "loss": float(g_loss),
+                                     "speedup_vs_eager": ms / g_ms}
+            del graph
+            net.invalidate()
     backward = ("tcgen05 dgrad/wgrad GEMMs, bf16 gradients, forward chain re-run per chunk keeping its operands"
                 if args.precision != "fp32" else "fp32 CUDA-core kernels, recompute per chunk")
     print(json.dumps({"metric": "training step rays/sec (config 5)", "unit": "rays/s", "objects": sb,
@@ -734,6 +768,8 @@ def main():
                     help="one process driving --gpus N devices through bind_parallel(net, gpu_ids) (DeviceSharded); not the headline")
     ap.add_argument("--train", action="store_true", help="training-step timing (BASELINE config 5), not the headline")
     ap.add_argument("--train-rays", type=int, nargs="+", default=[128, 4096], help="rays per object for --train")
+    ap.add_argument("--graph", action="store_true",
+                    help="--train: also capture the step in a CUDA graph (device-resident call seed) and time replays")
     args = ap.parse_args()
     if args.in_process:
         run_in_process(args)

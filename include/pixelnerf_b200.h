@@ -55,6 +55,15 @@ PN_API uint64_t pn_launch_count(void);
 
 /* ---- (1) ray sampling ---------------------------------------------------------------- */
 
+/* Device-resident seed word for the in-kernel draws (no counterpart in the reference, whose draws come from torch's
+ * generator on the host: src/render/nerf.py:112,139,158).  The sampling launches made by the CALLING HOST THREAD after
+ * this call (pn_sample_coarse, pn_sample_fine, pn_render_rays, pn_render_frames) use seed + *seed_dev; NULL (the
+ * default) restores the host seed alone.  For CUDA graphs: a captured launch has its arguments baked in, so a replayed
+ * training step would repeat one jitter pattern; with the word in device memory the owner advances it by a captured
+ * device-side add and every replay draws anew.  The pointer must stay valid for as long as launches that saw it
+ * may run. */
+PN_API void pn_set_device_seed(const uint64_t* seed_dev);
+
 /* NeRFRenderer.sample_coarse, src/render/nerf.py:98-118.  rays (R,8) =
  * [origin, dir, near, far]; host-made table lin = torch.linspace(0, 1-1/Kc, Kc);
  * u (R,Kc) uniform draws or NULL to draw in-kernel from (seed).  Every fp32

@@ -71,6 +71,7 @@ _SIGNATURES = {
     "pn_version": (_int, []),
     "pn_last_error": (C.c_char_p, []),
     "pn_launch_count": (_u64, []),
+    "pn_set_device_seed": (None, [_vp]),
     "pn_sample_coarse": (_int, [_vp, _vp, _vp, _vp, _i64, _int, _int, _u64, _vp]),
     "pn_sample_fine": (_int, [_vp] * 10 + [_i64, _int, _int, _int, _f32, _int, _u64, _vp]),
     "pn_prepare_latent": (_int, [_vp, _vp, _int, _int, _int, _int, _int, _vp]),
@@ -182,6 +183,14 @@ def lib():
 
 def launch_count():
     return int(lib().pn_launch_count())
+
+
+def set_device_seed(word):
+    """Sampling launches made by this host thread from now on add the int64 device word to their host seed
+    (include/pixelnerf_b200.h: pn_set_device_seed); None restores the host seed alone."""
+    if word is not None and (word.dtype != torch.int64 or word.numel() != 1 or not word.is_cuda):
+        raise RuntimeError("device seed must be a one-element int64 CUDA tensor")
+    lib().pn_set_device_seed(None if word is None else word.data_ptr())
 
 
 def _check(rc, what):

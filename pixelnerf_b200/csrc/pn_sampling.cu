@@ -10,6 +10,14 @@
 
 namespace pn {
 
+// pn_set_device_seed: a device-resident seed word that the sampling launches of THIS host thread add to their host
+// seed (NULL = none).  A captured CUDA graph bakes kernel arguments in; with the seed in device memory a replayed
+// training step still draws new jitter every time (the owner advances the word with a captured device-side add).
+static thread_local const uint64_t* g_seed_dev = nullptr;
+__device__ __forceinline__ uint64_t eff_seed(uint64_t seed, const uint64_t* seed_dev) {
+  return seed_dev ? seed + __ldg(seed_dev) : seed;
+}
+
 __device__ __forceinline__ float lerp_depth(float near, float far, float zs, bool lindisp) {
   float a = __fsub_rn(1.0f, zs);
   if (!lindisp) return __fadd_rn(__fmul_rn(near, a), __fmul_rn(far, zs));
@@ -26,8 +34,9 @@ template <bool kLindisp>
 __global__ void __launch_bounds__(256)
 sample_coarse4_kernel(const RaySrc rays, const float* __restrict__ u,
                       const float* __restrict__ lin, float* __restrict__ z, int64_t total4, int kc,
-                      float step, uint64_t seed) {
+                      float step, uint64_t seed, const uint64_t* __restrict__ seed_dev) {
   constexpr bool lindisp = kLindisp;
+  seed = eff_seed(seed, seed_dev);
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= total4) return;
   const int64_t i = q * 4;
@@ -62,9 +71,10 @@ sample_coarse4_kernel(const RaySrc rays, const float* __restrict__ u,
 __global__ void __launch_bounds__(256)
 sample_coarse_kernel(const RaySrc rays, const float* __restrict__ u,
                      const float* __restrict__ lin, float* __restrict__ z, int64_t total, int kc,
-                     float step, bool lindisp, uint64_t seed) {
+                     float step, bool lindisp, uint64_t seed, const uint64_t* __restrict__ seed_dev) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
+  seed = eff_seed(seed, seed_dev);
   int64_t r = i / kc;
   int k = (int)(i - r * kc);
   float uu = u ? u[i] : rand_uniform(seed, PN_STREAM_COARSE, (uint64_t)i);
@@ -158,8 +168,10 @@ sample_fine_kernel(const RaySrc rays, const float* __restrict__ z_coarse,
                    const float* __restrict__ u_bin, const float* __restrict__ u_in,
                    const float* __restrict__ noise, float* __restrict__ z_sorted,
                    float* __restrict__ z_imp, float* __restrict__ z_depth, int64_t n_rays, int kc,
-                   int kf, int kd, int sort_n, float depth_std, bool lindisp, uint64_t seed) {
+                   int kf, int kd, int sort_n, float depth_std, bool lindisp, uint64_t seed,
+                   const uint64_t* __restrict__ seed_dev) {
   extern __shared__ float smem[];
+  seed = eff_seed(seed, seed_dev);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int per_warp = kc + (kc + 1) + sort_n;
   float* w = smem + warp * per_warp;
@@ -329,13 +341,13 @@ int sample_coarse_src(const RaySrc& rays, const float* u, const float* lin, floa
                    (!u || ((uintptr_t)u & 15) == 0);
   if (vec && lindisp)
     pn::sample_coarse4_kernel<true><<<pn::ceil_div(total / 4, 256), 256, 0, (cudaStream_t)stream>>>(
-        rays, u, lin, z, total / 4, n_coarse, step, seed);
+        rays, u, lin, z, total / 4, n_coarse, step, seed, pn::g_seed_dev);
   else if (vec)
     pn::sample_coarse4_kernel<false><<<pn::ceil_div(total / 4, 256), 256, 0, (cudaStream_t)stream>>>(
-        rays, u, lin, z, total / 4, n_coarse, step, seed);
+        rays, u, lin, z, total / 4, n_coarse, step, seed, pn::g_seed_dev);
   else
     pn::sample_coarse_kernel<<<pn::ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
-        rays, u, lin, z, total, n_coarse, step, lindisp != 0, seed);
+        rays, u, lin, z, total, n_coarse, step, lindisp != 0, seed, pn::g_seed_dev);
   PN_LAUNCH_OK("sample_coarse_kernel");
   pn::count_launch();
   return PN_OK;
@@ -361,13 +373,15 @@ int sample_fine_src(const RaySrc& rays, const float* z_coarse, const float* weig
   const int blocks = (int)((n_rays + pn::kFineWarps - 1) / pn::kFineWarps);
   pn::sample_fine_kernel<<<blocks < 148 * 16 ? blocks : 148 * 16, pn::kFineWarps * 32, smem, (cudaStream_t)stream>>>(
       rays, z_coarse, weights, depth, u_bin, u_in, noise, z_sorted, z_imp, z_depth, n_rays, n_coarse,
-      n_imp, n_depth, sort_n, depth_std, lindisp != 0, seed);
+      n_imp, n_depth, sort_n, depth_std, lindisp != 0, seed, pn::g_seed_dev);
   PN_LAUNCH_OK("sample_fine_kernel");
   pn::count_launch();
   return PN_OK;
 }
 
 }  // namespace pn
+
+extern "C" void pn_set_device_seed(const uint64_t* seed_dev) { pn::g_seed_dev = seed_dev; }
 
 extern "C" int pn_sample_coarse(const float* rays, const float* u, const float* lin, float* z,
                                 int64_t n_rays, int n_coarse, int lindisp, uint64_t seed,

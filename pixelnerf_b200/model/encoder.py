@@ -14,6 +14,14 @@ from torch import nn
 from .. import util
 
 
+def latent_scaling_host(wl, hl):
+    """[W_l, H_l] / ([W_l, H_l] - 1) * 2 with fp32 rounding, as python floats (reference encoder.py:131-133)."""
+    import numpy as np
+    w, h = np.float32(wl), np.float32(hl)
+    one, two = np.float32(1.0), np.float32(2.0)
+    return float(w / (w - one) * two), float(h / (h - one) * two)
+
+
 class SpatialEncoder(nn.Module):
     def __init__(self, backbone="resnet34", pretrained=True, num_layers=4, index_interp="bilinear",
                  index_padding="border", upsample_interp="bilinear", feature_scale=1.0,
@@ -95,9 +103,13 @@ class SpatialEncoder(nn.Module):
             size = latents[0].shape[-2:]
             latents = [F.interpolate(l, size, mode=self.upsample_interp, align_corners=True) for l in latents]
             self.latent = torch.cat(latents, dim=1)
-        ls = torch.tensor([self.latent.shape[-1], self.latent.shape[-2]], dtype=torch.float32,
-                          device=self.latent.device)
-        self.latent_scaling = ls / (ls - 1) * 2.0
+        # latent_scaling = [W_l, H_l] / ([W_l, H_l] - 1) * 2 in fp32 (encoder.py:131-133), evaluated on the host and
+        # written with two fills: no host -> device copy, so a training step can be captured in a CUDA graph
+        self._latent_scaling_host = latent_scaling_host(self.latent.shape[-1], self.latent.shape[-2])
+        ls = torch.empty(2, dtype=torch.float32, device=self.latent.device)
+        ls[0].fill_(self._latent_scaling_host[0])
+        ls[1].fill_(self._latent_scaling_host[1])
+        self.latent_scaling = ls
         return self.latent
 
     @classmethod

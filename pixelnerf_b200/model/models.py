@@ -84,8 +84,8 @@ class PixelNeRFNet(torch.nn.Module):
         rot = poses[:, :3, :3].transpose(1, 2)
         trans = -torch.bmm(rot, poses[:, :3, 3:])
         self.poses = torch.cat((rot, trans), dim=-1)
-        self.image_shape[0] = images.shape[-1]
-        self.image_shape[1] = images.shape[-2]
+        self.image_shape[0].fill_(images.shape[-1])     # fills, not scalar copies: capturable in a CUDA graph
+        self.image_shape[1].fill_(images.shape[-2])
         if len(focal.shape) == 0:
             focal = focal[None, None].repeat((1, 2))
         elif len(focal.shape) == 1:
@@ -101,10 +101,18 @@ class PixelNeRFNet(torch.nn.Module):
         elif len(c.shape) == 1:
             c = c.unsqueeze(-1).repeat((1, 2))
         self.c = c
-        self._refresh_camera()
+        # the uv -> texel scale from host-side shapes (no device read: the step stays capturable in a CUDA graph)
+        import numpy as np
+        ls = getattr(self.encoder, "_latent_scaling_host", None)
+        host = None
+        if ls is not None:
+            host = (float(np.float32(ls[0]) / np.float32(images.shape[-1])),
+                    float(np.float32(ls[1]) / np.float32(images.shape[-2])))
+        self._refresh_camera(host)
 
-    def _refresh_camera(self):
-        """Kernel-side camera block: per-view expanded focal / c and the uv -> texel scale."""
+    def _refresh_camera(self, host_scale=None):
+        """Kernel-side camera block: per-view expanded focal / c and the uv -> texel scale (`host_scale`: that scale
+        when the caller already has it on the host; otherwise it is read back from the device buffers)."""
         n_views_total = self.poses.shape[0]
         ns = self.num_views_per_obj
         dev = self.poses.device
@@ -115,9 +123,12 @@ class PixelNeRFNet(torch.nn.Module):
                 return t.expand(n_views_total, 2).contiguous()
             return t.unsqueeze(1).expand(-1, ns, 2).reshape(-1, 2).contiguous()
 
-        ls = self.encoder.latent_scaling.float().cpu()
-        img = self.image_shape.float().cpu()
-        scale = ls / img  # encoder.py:98: latent_scaling / image_size, fp32 like the reference
+        if host_scale is not None:
+            scale = host_scale
+        else:
+            ls = self.encoder.latent_scaling.float().cpu()
+            img = self.image_shape.float().cpu()
+            scale = ls / img  # encoder.py:98: latent_scaling / image_size, fp32 like the reference
         self._cam = dict(poses=self.poses.float().contiguous(), focal=per_view(self.focal), c=per_view(self.c),
                          scale_x=float(scale[0]), scale_y=float(scale[1]),
                          n_objects=n_views_total // ns, n_views=ns)

@@ -84,6 +84,23 @@ class NeRFRenderer(torch.nn.Module):
         # seed offset by the shard's first ray; consumed by the next forward()
         self.seed_offset = 0
         self.seed_override = None
+        # CUDA-graph capture of a training step (use_device_seed): the call seed lives in device memory and is
+        # advanced by a device-side add at the start of every forward, so a replayed graph draws new jitter
+        self.device_seed = None
+
+    _SEED_STRIDE = -7046029254386353131    # 0x9E3779B97F4A7C15 as int64: consecutive calls land far apart
+
+    def use_device_seed(self, device=None, enable=True):
+        """Keep the call seed of the in-kernel draws in device memory (one int64 word, initialised from torch's CPU
+        generator like `_seed`).  Needed to capture a training step in a CUDA graph: the reference draws with
+        torch.rand_like / randn_like (src/render/nerf.py:112,139,158), whose generator state torch advances across
+        graph replays; the equivalent here is this word plus a captured `add_`."""
+        if not enable:
+            self.device_seed = None
+            return self
+        device = device if device is not None else self.last_sched.device
+        self.device_seed = torch.full((1,), self._seed(), dtype=torch.int64, device=device)
+        return self
 
     # ---------------------------------------------------------------- sampling
     @staticmethod
@@ -271,13 +288,27 @@ class NeRFRenderer(torch.nn.Module):
         rays = rays.reshape(-1, 8).float().contiguous()
         draws, forced = self.injected_draws, self.injected_z or {}
         self.injected_draws, self.injected_z = None, None
+        dev_seed = None
         if draws and "u_coarse" in draws:
             seed = 0
         elif self.seed_override is not None:
             seed = int(self.seed_override)
+        elif self.device_seed is not None:
+            if self.device_seed.device != rays.device:
+                raise RuntimeError("use_device_seed() was set up on another device than the rays")
+            dev_seed = self.device_seed
+            dev_seed.add_(self._SEED_STRIDE)       # a device op: captured with the step, replayed with it
+            seed = int(self.seed_offset)
         else:
             seed = self._seed() + int(self.seed_offset)
         self.seed_override = None
+        _lib.set_device_seed(dev_seed)
+        try:
+            return self._forward_seeded(model, rays, sb, b, draws, forced, seed, want_weights)
+        finally:
+            _lib.set_device_seed(None)
+
+    def _forward_seeded(self, model, rays, sb, b, draws, forced, seed, want_weights):
         if self.training and self.noise_std > 0.0:
             # sigma noise (nerf.py:225-226): drawn once per call so that the backward sees the forward's draws
             draws = dict(draws or {})
