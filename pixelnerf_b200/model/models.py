@@ -160,11 +160,11 @@ class PixelNeRFNet(torch.nn.Module):
         # training mode rebuilds the tables every optimiser step: tensor-core product from the fp16 latent
         # (hi + lo weights); eval mode builds them once per encode in fp32
         lat = self.latent_nhwc(torch.float16 if (self.training and not fp32) else torch.float32)
-        params = mlp.weight_dict()
-        key = (self._latent_nhwc[lat.dtype][0], lat.dtype, tuple((q.data_ptr(), q._version) for q in params.values()))
+        key = (self._latent_nhwc[lat.dtype][0], lat.dtype, mlp.version_key())
         slot = ("coarse" if mlp is self.mlp_coarse else "fine") + ("32" if fp32 else "")
         hit = self._tables.get(slot)
         if hit is None or hit[0] != key:
+            params = mlp.weight_dict()
             build = _lib.prepare_latent_tables_f32 if fp32 else _lib.prepare_latent_tables
             hit = (key, build({k: v.detach() for k, v in params.items()}, lat))
             self._tables[slot] = hit
