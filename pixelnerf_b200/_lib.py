@@ -4,6 +4,7 @@ There is deliberately no fallback: if the shared library is missing or a tensor 
 not on a CUDA device the call raises.  torch is used only to own device memory and
 to supply the current stream.
 """
+import collections
 import ctypes as C
 import functools
 import os
@@ -324,8 +325,26 @@ def point_features(cam_bufs, latent_nhwc, ppo, *, rays=None, z=None, xyz=None, v
     return feat_z, feat_x
 
 
+_PACK32_CACHE = collections.OrderedDict()
+
+
 def pack_weights_fp32(w):
-    """dict of un-prefixed ResnetFC tensors (CUDA fp32 contiguous) -> (MlpWeights, keepalive)."""
+    """dict of un-prefixed ResnetFC tensors (CUDA fp32 contiguous) -> (MlpWeights, keepalive).  The last few results
+    are kept, keyed on every tensor's (data_ptr, _version): a training step asks for the same struct eight times
+    (tables, forward, backward of both MLPs) and building it is ~100 torch calls."""
+    key = tuple((v.data_ptr(), v._version, v.dtype) for v in w.values())
+    hit = _PACK32_CACHE.get(key)
+    if hit is not None:
+        _PACK32_CACHE.move_to_end(key)
+        return hit
+    hit = _pack_weights_fp32(w)
+    _PACK32_CACHE[key] = hit       # the keepalive dict pins the storages, so a cached data_ptr cannot be recycled
+    while len(_PACK32_CACHE) > 8:
+        _PACK32_CACHE.popitem(last=False)
+    return hit
+
+
+def _pack_weights_fp32(w):
     keep = {k: _f32c(v) for k, v in w.items()}
     s = MlpWeights()
     s.lin_in_w, s.lin_in_b = _ptr(keep["lin_in.weight"]), _ptr(keep["lin_in.bias"])

@@ -66,24 +66,30 @@ class ResnetFC(nn.Module):
         self.invalidate()
         return out
 
-    def weight_dict(self):
-        return {k: v for k, v in self.state_dict(keep_vars=True).items()}
-
-    def version_key(self):
-        """(data_ptr, _version) of every parameter: the cache key of everything derived from the weights.  The list
-        of (module, name, parameter) is kept between calls and re-validated by identity against each module's
-        ``_parameters`` (a re-assigned Parameter rebuilds it) -- ``state_dict()`` / ``parameters()`` cost 50-90 us per
-        call, four calls per frame, which was half of the host time of a frame."""
+    def _param_list(self):
+        """[(state_dict name, module, attribute, parameter)] in ``state_dict()`` order, kept between calls and
+        re-validated by identity against each module's ``_parameters`` (a re-assigned Parameter rebuilds it).
+        ``state_dict()`` / ``parameters()`` cost 50-90 us per call -- four calls per rendered frame, fourteen per
+        training step -- which was half of the host time of a frame."""
         plist = self.__dict__.get("_plist")
         if plist is not None:
-            for m, n, p in plist:
+            for _, m, n, p in plist:
                 if m._parameters.get(n) is not p:
                     plist = None
                     break
         if plist is None:
-            plist = [(m, n, p) for m in self.modules() for n, p in m._parameters.items() if p is not None]
+            plist = [((prefix + "." if prefix else "") + n, m, n, p) for prefix, m in self.named_modules()
+                     for n, p in m._parameters.items() if p is not None]
             self.__dict__["_plist"] = plist
-        return tuple((p.data_ptr(), p._version) for _, _, p in plist)
+        return plist
+
+    def weight_dict(self):
+        """{state_dict name: Parameter}, same keys and order as ``state_dict(keep_vars=True)``."""
+        return {k: p for k, _, _, p in self._param_list()}
+
+    def version_key(self):
+        """(data_ptr, _version) of every parameter: the cache key of everything derived from the weights."""
+        return tuple((p.data_ptr(), p._version) for _, _, _, p in self._param_list())
 
     def packed(self, precision):
         """Kernel-side view of the weights, rebuilt when any parameter changed."""

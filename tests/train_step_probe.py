@@ -76,3 +76,13 @@ cpu = sorted([(e.self_cpu_time_total / 5, e.count / 5, e.key) for e in ev], reve
 print("top CPU self time per step:")
 for t, c, k in cpu[:12]:
     print(f"  {t:9.1f} us  x{c:5.1f}  {k[:90]}")
+# host side only: python-level profile of the step (where the launch gaps come from)
+import cProfile  # noqa: E402
+import pstats  # noqa: E402
+pr = cProfile.Profile()
+pr.enable()
+for _ in range(20):
+    step()
+pr.disable()
+torch.cuda.synchronize()
+pstats.Stats(pr).sort_stats("tottime").print_stats(22)
