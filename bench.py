@@ -644,10 +644,20 @@ def run_train(args):
     """--train: BASELINE config 5, one training step = render 4 objects x `--train-rays` rays (want_weights, train
     mode) -> MSE on coarse+fine rgb vs U(0,1) targets -> backward through composite / ResnetFC / latent gather
     (hand-written kernels behind torch.autograd.Function) -> Adam step on both MLPs.  Not the headline line."""
-    from pixelnerf_b200 import synthetic as syn
+    from pixelnerf_b200 import parallel, synthetic as syn
     from pixelnerf_b200.testing import build_net, scene_camera, set_encoded
-    dev = torch.device("cuda", 0)
+    # under torchrun (--gpus N): the same batch ray-sharded over N GPUs (RaySharded: every rank renders and
+    # back-propagates its own ray range), weight gradients summed by parallel.allreduce_gradients (one flat NCCL
+    # all-reduce per dtype), the same Adam step on every rank -- strong scaling of one training step
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+        assert not args.graph, "--graph is the single-GPU form"
     sb = 4
     sc = syn.scene(SCENE)
     net, ren = build_net(sc, syn.mlp_weights(1), syn.mlp_weights(2), dev, mlp_precision=args.precision)
@@ -668,12 +678,19 @@ def run_train(args):
         idx = torch.randint(0, sc["rays"].shape[0], (sb, n_obj_rays), generator=g)
         rays = sc["rays"][idx].to(dev)                       # (SB, B, 8)
         target = torch.rand(sb, n_obj_rays, 3, generator=g).to(dev)
+        par = ren.bind_parallel(net, list(range(world))) if world > 1 else None
 
         def step():
             opt.zero_grad(set_to_none=True)
-            out = ren(net, rays, want_weights=True)
-            loss = ((out.coarse.rgb - target) ** 2).mean() + ((out.fine.rgb - target) ** 2).mean()
-            loss.backward()
+            if par is not None:
+                out = par(rays, want_weights=True)
+                loss = ((out["coarse"]["rgb"] - target) ** 2).mean() + ((out["fine"]["rgb"] - target) ** 2).mean()
+                loss.backward()
+                parallel.allreduce_gradients([net.mlp_coarse, net.mlp_fine])
+            else:
+                out = ren(net, rays, want_weights=True)
+                loss = ((out.coarse.rgb - target) ** 2).mean() + ((out.fine.rgb - target) ** 2).mean()
+                loss.backward()
             opt.step()
             return loss
 
@@ -682,12 +699,19 @@ def run_train(args):
         torch.cuda.synchronize()
         steps = max(1, min(args.steps, 5))
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
         a.record()
         for _ in range(steps):
             loss = step()
         b.record()
         b.synchronize()
         ms = a.elapsed_time(b) / steps
+        if world > 1:      # the slowest rank's time
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
         n = sb * n_obj_rays
         flop = 3.0 * n * (N_COARSE + N_COARSE + N_FINE) * MLP_FLOP_PER_POINT[1]
         # one more step with CUDA events around every kernel family (not part of the timed region)
@@ -732,7 +756,14 @@ def run_train(args):
             net.invalidate()
     backward = ("tcgen05 dgrad/wgrad GEMMs, bf16 gradients, forward chain re-run per chunk keeping its operands"
                 if args.precision != "fp32" else "fp32 CUDA-core kernels, recompute per chunk")
-    print(json.dumps({"metric": "training step rays/sec (config 5)", "unit": "rays/s", "objects": sb,
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+        if rank != 0:
+            return
+    print(json.dumps({"metric": "training step rays/sec (config 5)", "unit": "rays/s", "objects": sb, "n_gpus": world,
+                      "parallelism": "single GPU" if world == 1 else
+                      f"one batch ray-sharded over {world} GPUs (RaySharded), gradients all-reduced, strong scaling",
                       "forward": "%s chain" % args.precision, "backward": backward,
                       "optimizer": "Adam on both MLPs", "sweep": res}))
 
