@@ -467,7 +467,7 @@ def live_parity(sc, weights, precision, n_rays=256):
     z_c, z_f = ren.last_z
     res = {"rays": n_rays, "against": "CPU oracle (pinned to the live reference by tests/golden)", "stagewise": True,
            "sample_positions_bit_exact": bool(torch.equal(z_c[0].cpu(), ref["z_coarse"]) and torch.equal(z_f[0].cpu(), ref["z_fine"])),
-           "tolerance": 2e-3 if precision == "fp16" else 1e-4, "depth_unit": "world units (absolute)"}
+           "tolerance": 2e-3 if precision in ("fp16", "fp16x2") else 1e-4, "depth_unit": "world units (absolute)"}
     for part, tag in ((out.coarse, "coarse"), (out.fine, "fine")):
         res[f"rgb_{tag}"] = float((part.rgb[0].cpu() - ref["rgb_" + tag]).abs().max())
         res[f"weights_{tag}"] = float((part.weights[0].cpu() - ref["w_" + tag]).abs().max())
@@ -539,6 +539,8 @@ def run_gpu(args):
         exe = 1.0
         if args.precision == "fp16x3":      # three MMAs per product of the ten 512-wide GEMMs (+ the discarded lin_in)
             exe = 3.0 * (ns * 6 * 262144 + 4 * 262144) / (ns * 2380800 + 1050624)
+        if args.precision == "fp16x2":      # two MMAs per product of the ten 512-wide GEMMs
+            exe = 2.0 * (ns * 6 * 262144 + 4 * 262144) / (ns * 2380800 + 1050624)
         if args.precision == "fp16":
             exe = 686.0 / 878.0 if ns == 1 else (ns * (6 * 262144 + 21504) + 1050624) / (ns * 2380800 + 1050624)
         launches_per_step = n_mlp // max(1, args.steps)
@@ -547,7 +549,7 @@ def run_gpu(args):
             "metric": "rays/sec coarse+fine", "value": rays_total / (ms * 1e-3), "unit": "rays/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": {"fp32": "f32", "fp16": "f16", "fp16x3": "f16x3"}[args.precision], "data": "synthetic",
+            "dtype": {"fp32": "f32", "fp16": "f16", "fp16x2": "f16x2", "fp16x3": "f16x3"}[args.precision], "data": "synthetic",
             "config": {"workload": f"{WORKLOADS[args.scene]}: {world} frame(s) per step = {n_frame} rays per GPU, "
                                    f"{N_COARSE} coarse + {N_FINE} fine ({N_DEPTH} depth) samples, ResnetFC 5x512 x2",
                        "mlp_precision": args.precision,
@@ -787,7 +789,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "torch-cuda"])
-    ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp16"), choices=["fp32", "fp16", "fp16x3"])
+    ap.add_argument("--precision", default=os.environ.get("PIXELNERF_B200_MLP", "fp16"), choices=["fp32", "fp16", "fp16x2", "fp16x3"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", dest="extras", action="store_false",
                     help="skip the extra keys of the headline line: `sharded` (DTU frame + 40-frame video, strong "

@@ -278,6 +278,17 @@ PN_API int pn_mlp_forward_tc_x3(const void* packed_x3, const float* tables32, in
                          const float* code32, int n_objects, int n_views, int64_t points_per_object,
                          float* out, float* pre_act, void* workspace, size_t workspace_bytes, pn_stream_t stream);
 
+/* The TWO-PASS chain (mlp_precision = fp16x2): pn_mlp_forward_tc_x3 without its third operand pass -- every 512-wide
+ * GEMM as a_hi w_hi + a_hi w_lo (weights as fp16 pairs, activations rounded to fp16 once), lin_z tables, lin_in and the
+ * head in fp32 as in the precise chain.  Weight rounding and fp16 tables are the fast chain's two errors that are
+ * coherent along a ray (the same perturbed network at every sample); activation rounding is independent per sample and
+ * averages out in the composite.  This form stays within north_star's 2e-3 on every BASELINE config, DTU depth
+ * included (measured <= 1.7e-3), for two thirds of the precise chain's tensor work.  Same arguments as
+ * pn_mlp_forward_tc_x3.  Inference only. */
+PN_API int pn_mlp_forward_tc_x2(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
+                         const float* code32, int n_objects, int n_views, int64_t points_per_object, float* out,
+                         float* pre_act, void* workspace, size_t workspace_bytes, pn_stream_t stream);
+
 /* pn_mlp_forward_tc for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
  * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
  * Same inputs, outputs and arithmetic as pn_mlp_forward_tc (bit-identical results), but the workspace is a

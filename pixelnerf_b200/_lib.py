@@ -105,6 +105,7 @@ _SIGNATURES = {
     "pn_mlp_tc_packed_x3_bytes": (_sz, []),
     "pn_prepare_weights_x3": (_int, [C.POINTER(MlpWeights), _vp, _sz, _vp]),
     "pn_mlp_forward_tc_x3": (_int, [_vp, _vp, _i64, _vp, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp]),
+    "pn_mlp_forward_tc_x2": (_int, [_vp, _vp, _i64, _vp, _vp, _int, _int, _i64, _vp, _vp, _vp, _sz, _vp]),
     # n_views > 1 in one launch: grouped row order + on-chip view mean
     "pn_point_taps_grouped_rows": (_i64, [_i64, _int]),
     "pn_point_taps_grouped": (_int, [C.POINTER(Camera), _vp, _vp, _int, _vp, _vp, _i64, _vp, _vp]),
@@ -550,9 +551,13 @@ def point_taps_f32(cam_bufs, hl, wl, ppo, *, rays=None, z=None, xyz=None, viewdi
     return feat_x, code32
 
 
-def mlp_forward_tc_x3(packed_x3, tables32, feat_x, code32, n_objects, n_views, ppo, want_pre=False):
+def mlp_forward_tc_x3(packed_x3, tables32, feat_x, code32, n_objects, n_views, ppo, want_pre=False, passes=3):
     """The precise tensor-core chain (three fp16 hi/lo operand passes per GEMM, everything else fp32); inputs from
-    pack_weights_x3 / prepare_latent_tables_f32 / point_taps_f32.  -> (SB*ppo, 4) [sigmoid rgb, relu sigma]."""
+    pack_weights_x3 / prepare_latent_tables_f32 / point_taps_f32.  -> (SB*ppo, 4) [sigmoid rgb, relu sigma].
+    passes=2: the two-pass form (mlp_precision = fp16x2, pn_mlp_forward_tc_x2): no a_lo pass."""
+    assert passes in (2, 3)
+    entry, what = (lib().pn_mlp_forward_tc_x3, "pn_mlp_forward_tc_x3") if passes == 3 else \
+        (lib().pn_mlp_forward_tc_x2, "pn_mlp_forward_tc_x2")
     dev = feat_x.device
     if tables32.dtype != torch.float32 or tables32.dim() != 3 or tables32.shape[0] != COMBINE_LAYER or not tables32.is_contiguous():
         raise RuntimeError("precise tensor-core MLP needs contiguous fp32 lin_z tables of shape (3, texels, 512)")
@@ -564,9 +569,8 @@ def mlp_forward_tc_x3(packed_x3, tables32, feat_x, code32, n_objects, n_views, p
     nbytes = lib().pn_mlp_tc_grouped_workspace_bytes()
     ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
     with _Timed("mlp"):
-        _check(lib().pn_mlp_forward_tc_x3(packed_x3.data_ptr(), _ptr(tables32), tables32.shape[1],
-                                          _ptr(feat_x, torch.float16), _ptr(code32), n_objects, n_views, ppo, _ptr(out),
-                                          _ptr(pre), ws.data_ptr(), nbytes, _stream()), "pn_mlp_forward_tc_x3")
+        _check(entry(packed_x3.data_ptr(), _ptr(tables32), tables32.shape[1], _ptr(feat_x, torch.float16), _ptr(code32),
+                     n_objects, n_views, ppo, _ptr(out), _ptr(pre), ws.data_ptr(), nbytes, _stream()), what)
     return (out, pre) if want_pre else out
 
 

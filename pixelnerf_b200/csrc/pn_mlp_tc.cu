@@ -118,6 +118,9 @@ struct ChainParams {
   const float* code32;   // (x_rows, 44) fp32 positional code, same row order as x
   int64_t x_rows;
   const float* w_in_t;   // lin_in.weight^T fp32 [44][512]
+  // two-pass chain (mlp_precision = fp16x2, pn_mlp_forward_tc_x2): the precise chain without its third pass --
+  // a_hi W_hi + a_hi W_lo: weights as fp16 pairs, activations single fp16, tables / lin_in / head in fp32
+  int drop_a_lo;         // 0 (three passes) or 1
 };
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -264,8 +267,9 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     using S2 = std::integral_constant<uint32_t, 2>;
     using S3 = std::integral_constant<uint32_t, 3>;
     auto load_fc = [&](int layer0) {   // quarter order, two K=128 items per quarter: K-chunks (h, h+2) of the group
+      const int n_ps = kX3 ? 3 - p.drop_a_lo : 1;
 #pragma unroll 1
-      for (int ps = 0; ps < (kX3 ? 3 : 1); ++ps) {   // precise chain: W_hi, W_lo, W_hi (against a_hi, a_hi, a_lo)
+      for (int ps = 0; ps < n_ps; ++ps) {   // precise chain: W_hi, W_lo, W_hi (against a_hi, a_hi, a_lo); two-pass form: W_hi, W_lo
         const int layer = ps == 1 ? layer0 + kLayers : layer0;
 #pragma unroll 1
         for (int kg = 0; kg < 2; ++kg) {
@@ -378,12 +382,14 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     const uint32_t act_lo = smem_base + kOffW + 2 * kWStageBytes;   // precise chain only: lo half of the operand
     // 512x512 GEMM from the ACT operand, quarter order (see header), D = 2 blocks at d_col.
     auto gemm_act = [&](uint32_t d_col, bool clear, int commit_region) {
+      const int n_ps = kX3 ? 3 - p.drop_a_lo : 1;
 #pragma unroll 1
-      for (int ps = 0; ps < (kX3 ? 3 : 1); ++ps) {
+      for (int ps = 0; ps < n_ps; ++ps) {
         // precise chain: three operand passes into the same accumulator -- a_hi W_hi, a_hi W_lo, a_lo W_hi (the
-        // producer streams W_hi, W_lo, W_hi); the accumulators are complete, and committed, in the last pass only
-        const uint32_t abase = ps == 2 ? act_lo : act;
-        const bool fin = !kX3 || ps == 2;
+        // producer streams W_hi, W_lo, W_hi); the two-pass form stops after the second.  The accumulators are
+        // complete, and committed, in the last pass only
+        const uint32_t abase = (kX3 && ps == 2) ? act_lo : act;
+        const bool fin = ps == n_ps - 1;
 #pragma unroll 1
         for (int kg = 0; kg < 2; ++kg) {
           // K-chunks (h, h+2) of the group: the epilogue finishes chunks 0 and 2 of a block first
@@ -589,6 +595,9 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       for (int i = 0; i < 4; ++i) {
         const uint32_t at = dst + (((uint32_t)(ch * 4 + i) ^ sw) << 4);
         if constexpr (!kX3) {
+          st_shared_v4(at, pack_relu_h2(b[8 * i + 0], b[8 * i + 1]), pack_relu_h2(b[8 * i + 2], b[8 * i + 3]),
+                       pack_relu_h2(b[8 * i + 4], b[8 * i + 5]), pack_relu_h2(b[8 * i + 6], b[8 * i + 7]));
+        } else if (p.drop_a_lo) {   // two-pass form: no a_lo operand
           st_shared_v4(at, pack_relu_h2(b[8 * i + 0], b[8 * i + 1]), pack_relu_h2(b[8 * i + 2], b[8 * i + 3]),
                        pack_relu_h2(b[8 * i + 4], b[8 * i + 5]), pack_relu_h2(b[8 * i + 6], b[8 * i + 7]));
         } else {
@@ -1367,10 +1376,10 @@ extern "C" int pn_mlp_forward_tc_grouped(const void* packed, const void* tables,
 }
 
 // ---- precise chain: mlp_precision = fp16x3 ------------------------------------------------------------------------
-extern "C" int pn_mlp_forward_tc_x3(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
-                                    const float* code32, int n_objects, int n_views, int64_t points_per_object,
-                                    float* out, float* pre_act, void* workspace, size_t workspace_bytes,
-                                    pn_stream_t stream) {
+static int mlp_forward_tc_pairs(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
+                                const float* code32, int n_objects, int n_views, int64_t points_per_object,
+                                float* out, float* pre_act, void* workspace, size_t workspace_bytes, int drop_a_lo,
+                                pn_stream_t stream) {
   using namespace pn::tc;
   PN_CHECK_ARG(packed_x3 && tables32 && feat_x && code32 && out && workspace, "pn_mlp_forward_tc_x3: null pointer");
   PN_CHECK_ARG(n_texels > 0, "pn_mlp_forward_tc_x3: no texels");
@@ -1411,5 +1420,24 @@ extern "C" int pn_mlp_forward_tc_x3(const void* packed_x3, const float* tables32
   p.first_block = 0;
   p.last_block = 5;
   p.park = (float*)((char*)workspace + 256);
+  p.drop_a_lo = drop_a_lo;
   return launch_chain(mw, mx, mw, p, st);
+}
+
+extern "C" int pn_mlp_forward_tc_x3(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
+                                    const float* code32, int n_objects, int n_views, int64_t points_per_object,
+                                    float* out, float* pre_act, void* workspace, size_t workspace_bytes,
+                                    pn_stream_t stream) {
+  return mlp_forward_tc_pairs(packed_x3, tables32, n_texels, feat_x, code32, n_objects, n_views, points_per_object, out,
+                              pre_act, workspace, workspace_bytes, 0, stream);
+}
+
+// mlp_precision = fp16x2: the precise chain without its third operand pass (a_lo W_hi).  Weight rounding and the fp16
+// tables are the fast chain's errors that do not average out along a ray; activation rounding does.
+extern "C" int pn_mlp_forward_tc_x2(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
+                                    const float* code32, int n_objects, int n_views, int64_t points_per_object,
+                                    float* out, float* pre_act, void* workspace, size_t workspace_bytes,
+                                    pn_stream_t stream) {
+  return mlp_forward_tc_pairs(packed_x3, tables32, n_texels, feat_x, code32, n_objects, n_views, points_per_object, out,
+                              pre_act, workspace, workspace_bytes, 1, stream);
 }

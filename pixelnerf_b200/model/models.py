@@ -13,7 +13,7 @@ from .._prof import prof_range
 from .code import PositionalEncoding
 from .model_util import make_encoder, make_mlp
 
-_PRECISIONS = ("fp32", "fp16", "fp16x3", "bf16")
+_PRECISIONS = ("fp32", "fp16", "fp16x2", "fp16x3", "bf16")
 
 
 class PixelNeRFNet(torch.nn.Module):
@@ -56,7 +56,9 @@ class PixelNeRFNet(torch.nn.Module):
         self.num_views_per_obj = 1
         # "fp16" (default): tcgen05 chain, 2e-3 parity -- the product path.  "fp16x3": the precise tcgen05 chain (three
         # hi/lo operand passes per GEMM, everything else fp32), 1e-4 parity; inference -- in training mode it runs the
-        # fp32 kernels.  "fp32": the CUDA-core 1e-4 parity path.
+        # fp32 kernels.  "fp16x2": the precise chain without its third pass (weights as fp16 pairs, activations single
+        # fp16): 2e-3 parity on every scene class incl. DTU depth; inference -- training mode runs the fp16 path.
+        # "fp32": the CUDA-core 1e-4 parity path.
         # Not a reference conf key: the reference's conf files never set it, so they get the tensor-core chain.
         self.mlp_precision = conf.get_string("mlp_precision", os.environ.get("PIXELNERF_B200_MLP", "fp16"))
         assert self.mlp_precision in _PRECISIONS, self.mlp_precision
@@ -199,6 +201,8 @@ class PixelNeRFNet(torch.nn.Module):
         prec = self.mlp_precision
         if prec == "fp16x3" and (self.training or getattr(self, "_train_stash", None) is not None):
             prec = "fp32"      # the precise chain is an inference path; training uses the fp32 kernels (fwd and bwd)
+        if prec == "fp16x2" and (self.training or getattr(self, "_train_stash", None) is not None):
+            prec = "fp16"      # the two-pass chain is an inference path; training uses the tensor-core fp16 path
         mlp = self._mlp(coarse)
         cam = self._cam
         if prec == "fp32":
@@ -208,12 +212,12 @@ class PixelNeRFNet(torch.nn.Module):
             with prof_range("resnetfc_infer"):
                 return _lib.mlp_forward_fp32(mlp.packed("fp32"), fz, fx, cam["n_objects"], cam["n_views"], ppo)
         _, hl, wl, _ = self.latent_nhwc(torch.float32).shape
-        if prec == "fp16x3":
+        if prec in ("fp16x3", "fp16x2"):     # fp16x2: the same chain without its third operand pass
             with prof_range("encoder_index"):
                 fx, code32 = _lib.point_taps_f32(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
             with prof_range("resnetfc_infer"):
                 return _lib.mlp_forward_tc_x3(mlp.packed("fp16x3"), self.latent_tables(coarse, fp32=True), fx, code32,
-                                              cam["n_objects"], cam["n_views"], ppo)
+                                              cam["n_objects"], cam["n_views"], ppo, passes=3 if prec == "fp16x3" else 2)
         tables = self.latent_tables(coarse)
         stash = getattr(self, "_train_stash", None)
         if cam["n_views"] > 1 and not self.training and not (stash is not None and rays is not None) and \

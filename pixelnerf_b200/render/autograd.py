@@ -40,13 +40,18 @@ def _flat_params(model):
     return coarse, fine
 
 
+# precisions whose TRAINING path is the tensor-core one (fp16 forward keeping its operands, bf16 dgrad / wgrad GEMMs);
+# the two-pass chain (fp16x2) is an inference form of the same path.  fp32 and fp16x3 train with the fp32 kernels.
+_TC_TRAIN = ("fp16", "fp16x2")
+
+
 class RenderFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, renderer, model, rays, sb, draws, forced, seed, latent, *params):
         ns = getattr(model, "num_views_per_obj", 1)
         k_all = renderer.n_coarse + ((renderer.n_coarse + renderer.n_fine) if renderer.using_fine else 0)
         stash_bytes = rays.shape[0] * ns * k_all * (11 * 1024 + 160)
-        keep = model.mlp_precision == "fp16" and stash_bytes <= renderer.train_stash_bytes
+        keep = model.mlp_precision in _TC_TRAIN and stash_bytes <= renderer.train_stash_bytes
         model._train_stash = [] if keep else None
         renderer._keep_parts = bool(renderer.depth_sample_grad and renderer.n_fine_depth > 0)
         try:
@@ -59,7 +64,7 @@ class RenderFunction(torch.autograd.Function):
         # What the backward needs of the model is captured NOW (torch's autograd captures tensors the same way): a
         # second encode() or a parameter update between this forward and its backward must not change the camera,
         # latent or tables the gradients are computed against.
-        tensor_core = model.mlp_precision == "fp16"
+        tensor_core = model.mlp_precision in _TC_TRAIN
         ctx.snap = dict(cam=model._cam, ns=ns, latent32=model.latent_nhwc(torch.float32),
                         tables={c: model.latent_tables(c) for c in (True, False)} if tensor_core and not keep else None,
                         versions=tuple(p._version for p in params))
@@ -160,7 +165,7 @@ def _backward_pass(renderer, model, snap, coarse, rays, z, sb, g_w, g_rgb, g_dep
         _lib.depth_sample_bwd(cam, latent, rr, zz, cut(z_dep, s, e), g_z, g_h0, g_fz, w_in, part)
         g_dep.view(sb, b)[:, s:e] += part.view(sb, e - s)
 
-    tensor_core = model.mlp_precision == "fp16"
+    tensor_core = model.mlp_precision in _TC_TRAIN
     if stash is not None:
         # the forward kept its operands: one backward per forward chunk, nothing is recomputed
         w16 = mlp.packed("bf16_train")
@@ -180,7 +185,7 @@ def _backward_pass(renderer, model, snap, coarse, rays, z, sb, g_w, g_rgb, g_dep
             ent.clear()     # release this chunk's activations
         return
     if tensor_core:
-        packed_tc, w16 = mlp.packed(model.mlp_precision), mlp.packed("bf16_train")
+        packed_tc, w16 = mlp.packed("fp16"), mlp.packed("bf16_train")
         tables = snap["tables"][coarse] if snap["tables"] is not None else model.latent_tables(coarse)
         _, hl, wl, _ = latent.shape
         chunk = max(1, renderer.max_rows_train_tc // max(1, sb * ns * k))

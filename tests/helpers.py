@@ -110,17 +110,19 @@ def to_grouped(rows, sb, ns, ppo):
     return out
 
 
-def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo, fused_mean=False):
+def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo, fused_mean=False, weight_pairs=False, fp32_front=False):
     """float64 restatement of the tensor-core ResnetFC chain with its roundings: fc / lin_out weights and
     GEMM inputs rounded to fp16 (lin_in / lin_out weights as an fp16 hi + lo pair), exact accumulation,
     fp32-exact residual stream; lin_z through per-texel tables rounded to fp16 (biases folded as in
     pn_prepare_latent_tables), blended with the row's four taps and rounded to fp16 once more.
     idx, wt (N,4): texel indices / bilinear weights; latent (T,512) fp32; feat_x (N,>=42) fp16-valued.
+    weight_pairs + fp32_front: the two-pass chain (mlp_precision = fp16x2) -- every fc weight as an fp16 hi + lo pair,
+    and lin_in / the lin_z tables exact (fp32 on the CUDA cores from the unrounded code `feat_x` / fp32 tables).
     Returns (list of h at stages 0..5 incl. biases, raw lin_out outputs (N/ns, 4))."""
     def W(k):
         t = w[k + ".weight"]
         hi = t.half()
-        if k == "lin_in":      # stored hi + lo (lo in the second K chunk)
+        if k == "lin_in" or weight_pairs:      # stored hi + lo (lin_in: lo in the second K chunk)
             return hi.double() + (t - hi.float()).half().double()
         return hi.double()
 
@@ -133,17 +135,22 @@ def emulate_tc_chain(w, idx, wt, latent, feat_x, ns, ppo, fused_mean=False):
     def table_blend(b):
         folded = B("lin_in") if b == 0 else B(f"blocks.{b - 1}.fc_1")
         tab = latent.double() @ w[f"lin_z.{b}.weight"].double().T + B(f"lin_z.{b}") + folded
+        if fp32_front:
+            return (tab[idx.long()] * wt.double().unsqueeze(-1)).sum(1)
         tab = tab.float().half().double()
         # blended in fp32, handed to the tensor-memory layout through an fp16 staging buffer
         return (tab[idx.long()] * wt.double().unsqueeze(-1)).sum(1).float().half().double()
 
     x = feat_x[:, :42].double()
-    h = x @ W("lin_in").T
+    h = x @ (w["lin_in.weight"].double().T if fp32_front else W("lin_in").T)
     stages = []
     for b in range(5):
         if b == 3 and ns > 1 and fused_mean:
             # one-launch form (pn_mlp_forward_tc_grouped): mean of the fp32 h over the views, rounded to fp16 once
-            h = h.reshape(-1, ns, ppo, 512).sum(1).div(ns).float().half().double().reshape(-1, 512)
+            h = h.reshape(-1, ns, ppo, 512).sum(1).div(ns)
+            if not fp32_front:     # the precise / two-pass chains keep the mean in fp32
+                h = h.float().half().double()
+            h = h.reshape(-1, 512)
         elif b == 3 and ns > 1:
             # the per-view h crosses the two launches as fp16, the mean is taken in fp32 (sum in view order, divide)
             h = h.float().half().double().reshape(-1, ns, ppo, 512).sum(1).div(ns).reshape(-1, 512)

@@ -26,7 +26,7 @@ from pixelnerf_b200 import synthetic as syn  # noqa: E402
 from pixelnerf_b200.testing import build_net, oracle_render  # noqa: E402
 from test_gpu_model import _net_for  # noqa: E402
 
-TOL = {"fp32": 1e-4, "fp16x3": 1e-4, "fp16": 2e-3}
+TOL = {"fp32": 1e-4, "fp16x3": 1e-4, "fp16x2": 2e-3, "fp16": 2e-3}
 
 
 def stagewise(net, ren, rays, draws, ref):
@@ -74,7 +74,7 @@ def main():
         inp = render_case_inputs(fx)
         ref = {k: fx[k] for k in ("rgb_coarse", "w_coarse", "depth_coarse", "rgb_fine", "w_fine", "depth_fine")}
         span = float((inp["rays"][..., 7] - inp["rays"][..., 6]).max())
-        for prec in ("fp32", "fp16x3", "fp16"):
+        for prec in ("fp32", "fp16x3", "fp16x2", "fp16"):
             net, ren = _net_for(fx, inp, precision=prec)
             r = stagewise(net, ren, inp["rays"], inp["draws"], ref)
             r["e2e"] = end_to_end(net, ren, inp["rays"], inp["draws"], ref, TOL[prec])
@@ -85,7 +85,7 @@ def main():
     fx = load(golden_files("full_")[0])
     inp = full_case_inputs(fx)
     ref = {k: fx[k] for k in ("rgb_coarse", "w_coarse", "depth_coarse", "rgb_fine", "depth_fine")}
-    for prec in ("fp32", "fp16x3", "fp16"):
+    for prec in ("fp32", "fp16x3", "fp16x2", "fp16"):
         net, ren = _net_for(fx, inp, precision=prec)
         r = stagewise(net, ren, inp["rays"], inp["draws"], ref)
         r["e2e"] = end_to_end(net, ren, inp["rays"], inp["draws"], ref, TOL[prec])
@@ -104,7 +104,7 @@ def main():
         wc, wf = syn.mlp_weights(1), syn.mlp_weights(2)
         draws = syn.draws(3, args.rays, 64, 16, 16)
         ref = oracle_render(sc, wc, wf, rays, draws)
-        for prec in ("fp32", "fp16x3", "fp16"):
+        for prec in ("fp32", "fp16x3", "fp16x2", "fp16"):
             net, ren = build_net(sc, wc, wf, torch.device("cuda"), mlp_precision=prec)
             r = stagewise(net, ren, rays[None], draws, ref)
             r["e2e"] = end_to_end(net, ren, rays[None], draws, ref, TOL[prec])

@@ -102,14 +102,14 @@ def test_dense_point_query_chunks():
     assert float((outs["fp16"][..., 3] - sig).abs().max()) < 2e-3 * max(1.0, float(sig.max()))
 
 
-@pytest.mark.parametrize("prec,tol", [("fp32", 1e-4), ("fp16x3", 1e-4), ("fp16", 2e-3)])
+@pytest.mark.parametrize("prec,tol", [("fp32", 1e-4), ("fp16x3", 1e-4), ("fp16x2", 2e-3), ("fp16", 2e-3)])
 def test_real_size_dtu_slice_vs_live_reference(prec, tol):
     """BASELINE config 4 at its REAL size against the live reference (tests/golden/full_dtu_full_ns3.npz: 300 x 400
     images, 150 x 200 latent, three views, per-ray near / far, 2 048 rays = a contiguous run + a frame-wide
     lattice), stage-wise with teacher forcing, in two chunks whose boundary falls inside the ray range
     (``max_rows_per_launch`` splits at NS = 3): sample positions bit exact, rgb / weights / depth (world units) within
     north_star's tolerance of the path -- except fp16 depth on this scene class, asserted at its measured, stated
-    value (helpers.TC_DEPTH_TOL_DTU; BASELINE.md "Parity")."""
+    value (helpers.TC_DEPTH_TOL_DTU; BASELINE.md "Parity"); the two-pass chain (fp16x2) meets 2e-3 here too."""
     import numpy as np
     from helpers import full_case_inputs, golden_files, load, max_abs
     from test_gpu_model import _net_for
