@@ -229,8 +229,9 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     uint32_t as = 0, aph = 0;   // operand-chunk ring slot / phase
     // Weight tile for K-chunks kc0 and kc1 of block nb of `layer`: two boxes of [128 out x 64 in].
     auto load_w = [&](auto stage_c, int layer, int nb, int kc0, int kc1) {
-      // precise chain: a two-stage ring (stages 2-3 of the ring hold the lo half of the ACT operand)
-      constexpr uint32_t ws = kX3 ? (decltype(stage_c)::value & 1u) : decltype(stage_c)::value;
+      // precise chain: a two-stage ring (stages 2-3 of the ring hold the lo half of the ACT operand); its two-pass
+      // form has no lo half and keeps all four stages
+      const uint32_t ws = (kX3 && !p.drop_a_lo) ? (decltype(stage_c)::value & 1u) : decltype(stage_c)::value;
       wait_bar<false>(bar(BAR_W_EMPTY + ws), ((wpar >> ws) & 1u) ^ 1u, p.err, 0x100 + ws);
       wpar ^= 1u << ws;
       if (elect_one()) {
@@ -341,7 +342,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // One weight stage: nk K=16 steps; A steps [0,4) come from a0, [4,8) from a1 (64-wide chunks).
     auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask) {
       constexpr uint32_t idesc = kIdesc;
-      constexpr uint32_t ws = kX3 ? (decltype(stage_c)::value & 1u) : decltype(stage_c)::value;
+      const uint32_t ws = (kX3 && !p.drop_a_lo) ? (decltype(stage_c)::value & 1u) : decltype(stage_c)::value;
       wait_bar<false>(bar(BAR_W_FULL + ws), (wpar >> ws) & 1u, p.err, 0x200 + ws);
       wpar ^= 1u << ws;
       tc_fence_after();
@@ -616,28 +617,60 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
       }
     };
-    // fp32 table blend of this lane's row, both 32-feature halves (tab32, tab32 + 64): every lane reads its own four
-    // texel rows straight from the fp32 tables (32 lines per load instruction -- the slow, simple form; the precise
-    // chain is bound by its 3x tensor work, not by this)
+    // fp32 table blend of this warp's 32 rows, both 32-feature halves (tab32, tab32 + 64), for the precise / two-pass
+    // chains.  Same cooperative form as gather_block, in fp32 throughout: one 16-byte load instruction covers 8 rows x
+    // 64 contiguous bytes (lane = (row in group, 16-byte piece = 4 floats)), each lane blends the four taps of its
+    // piece, and the 2 KB staging buffer transposes 32 rows x 16 features at a time to the tensor-memory layout (lane =
+    // row), so a 32-feature half takes two passes.  (The first version had every lane read its own four table rows:
+    // 32 L1 lines per load instruction for 16 useful bytes each, 4x the wavefronts of this form.)
     auto gather_block_x3 = [&](const float* tab32, uint32_t xslot, float (&g0)[32], float (&g1)[32]) {
-      const uint32_t rc = (uint32_t)((lq & 1) * 32 + lane);
-      const uint4 ti = ld_shared_v4(xslot + rc * 128 + ((6u ^ (rc & 7u)) << 4));
-      const uint4 tw = ld_shared_v4(xslot + rc * 128 + ((7u ^ (rc & 7u)) << 4));
-      const uint32_t idx[4] = {ti.x, ti.y, ti.z, ti.w};
-      const float wt[4] = {__uint_as_float(tw.x), __uint_as_float(tw.y), __uint_as_float(tw.z), __uint_as_float(tw.w)};
+      uint4 ti[4];
 #pragma unroll
-      for (int i = 0; i < 32; ++i) g0[i] = g1[i] = 0.0f;
-#pragma unroll 1
-      for (int k = 0; k < 4; ++k) {
-        const float4* src = reinterpret_cast<const float4*>(tab32 + (size_t)idx[k] * 512);
+      for (int it = 0; it < 4; ++it) {
+        const uint32_t rc = (uint32_t)((lq & 1) * 32 + it * 8 + (lane >> 2));   // row within the CTA
+        ti[it] = ld_shared_v4(xslot + rc * 128 + ((6u ^ (rc & 7u)) << 4));
+      }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float4 a = __ldg(src + i), b = __ldg(src + 16 + i);
-          g0[4 * i] = fmaf(wt[k], a.x, g0[4 * i]); g0[4 * i + 1] = fmaf(wt[k], a.y, g0[4 * i + 1]);
-          g0[4 * i + 2] = fmaf(wt[k], a.z, g0[4 * i + 2]); g0[4 * i + 3] = fmaf(wt[k], a.w, g0[4 * i + 3]);
-          g1[4 * i] = fmaf(wt[k], b.x, g1[4 * i]); g1[4 * i + 1] = fmaf(wt[k], b.y, g1[4 * i + 1]);
-          g1[4 * i + 2] = fmaf(wt[k], b.z, g1[4 * i + 2]); g1[4 * i + 3] = fmaf(wt[k], b.w, g1[4 * i + 3]);
+      for (int pass = 0; pass < 4; ++pass) {      // (half, 16-feature quarter)
+        const int half = pass >> 1, q = pass & 1;
+        const float4* src = reinterpret_cast<const float4*>(tab32 + half * 64 + q * 16) + (lane & 3);
+        float4 t[4][4];   // every global load of the pass is in flight before the first is consumed
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          t[it][0] = __ldg(src + (size_t)ti[it].x * 128);
+          t[it][1] = __ldg(src + (size_t)ti[it].y * 128);
+          t[it][2] = __ldg(src + (size_t)ti[it].z * 128);
+          t[it][3] = __ldg(src + (size_t)ti[it].w * 128);
         }
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int rr = it * 8 + (lane >> 2);
+          const uint32_t rc = (uint32_t)((lq & 1) * 32 + rr);
+          const uint4 tw = ld_shared_v4(xslot + rc * 128 + ((7u ^ (rc & 7u)) << 4));
+          const float wt[4] = {__uint_as_float(tw.x), __uint_as_float(tw.y), __uint_as_float(tw.z), __uint_as_float(tw.w)};
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            acc.x = fmaf(wt[k], t[it][k].x, acc.x);
+            acc.y = fmaf(wt[k], t[it][k].y, acc.y);
+            acc.z = fmaf(wt[k], t[it][k].z, acc.z);
+            acc.w = fmaf(wt[k], t[it][k].w, acc.w);
+          }
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};"
+                       ::"r"(stage + rr * 64 + ((uint32_t)((lane & 3) ^ ((rr >> 1) & 3)) << 4)),
+                         "f"(acc.x), "f"(acc.y), "f"(acc.z), "f"(acc.w));
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float4 v;
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                       : "r"(stage + lane * 64 + ((uint32_t)(j ^ ((lane >> 1) & 3)) << 4)));
+          if (half == 0) { g0[q * 16 + 4 * j] = v.x; g0[q * 16 + 4 * j + 1] = v.y; g0[q * 16 + 4 * j + 2] = v.z; g0[q * 16 + 4 * j + 3] = v.w; }
+          else { g1[q * 16 + 4 * j] = v.x; g1[q * 16 + 4 * j + 1] = v.y; g1[q * 16 + 4 * j + 2] = v.z; g1[q * 16 + 4 * j + 3] = v.w; }
+        }
+        __syncwarp();
       }
     };
     // lin_in (resnetfc.py:141-146: h = lin_in(x), K = 42) in fp32 on the CUDA cores for this lane's row: 32 features
