@@ -262,31 +262,33 @@ PN_API int pn_mlp_forward_tc_grouped(const void* packed, const void* tables, int
  * src/model/models.py:257-266) within the fp32 path's 1e-4 of the reference, on the tensor cores.  Every 512-wide
  * GEMM runs as three operand passes a_hi w_hi + a_hi w_lo + a_lo w_hi with a = a_hi + a_lo, w = w_hi + w_lo split into
  * fp16 pairs (22 significand bits each), fp32 accumulation and fp32 residual stream in tensor memory as in the fast
- * chain; everything else stays in fp32: lin_in (K = 42) and lin_out + head on the CUDA cores from the UNROUNDED
- * positional code (code32, written by pn_point_taps_f32 next to the usual taps rows) and fp32 weights, the lin_z
- * tables in fp32 (pn_prepare_latent_tables_f32: [3][n_texels][512] floats, same folded constants as the fp16 tables),
+ * chain.  lin_in (K = 42) runs the same way on an fp16 PAIR of the positional code: pn_point_taps_f32 writes, next
+ * to the usual taps rows feat_x (code rounded to fp16 = x_hi), a second (rows, 64) fp16 tensor feat_x_lo with the
+ * remainder x_lo = fp16(x - x_hi) in columns [0,42) and zeros elsewhere (same row order), and the chain issues
+ * x_hi w_hi + x_hi w_lo + x_lo w_hi.  lin_out + head are evaluated in fp32 on the CUDA cores, the lin_z tables stay
+ * in fp32 (pn_prepare_latent_tables_f32: [3][n_texels][512] floats, same folded constants as the fp16 tables),
  * the view mean (n_views > 1: rows in GROUPED order, one launch) unrounded.  packed_x3: pn_prepare_weights_x3 into
  * pn_mlp_tc_packed_x3_bytes() bytes.  workspace: pn_mlp_tc_grouped_workspace_bytes().  Inference only. */
 PN_API int pn_prepare_latent_tables_f32(const pn_mlp_weights_t* w, const float* latent_nhwc, int64_t n_texels,
                                  float* tables32, pn_stream_t stream);
 PN_API int pn_point_taps_f32(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
                       const float* xyz, const float* viewdirs, int64_t points_per_object,
-                      void* feat_x, float* code32, int grouped, pn_stream_t stream);
+                      void* feat_x, void* feat_x_lo, int grouped, pn_stream_t stream);
 PN_API size_t pn_mlp_tc_packed_x3_bytes(void);
 PN_API int pn_prepare_weights_x3(const pn_mlp_weights_t* w, void* packed, size_t packed_bytes, pn_stream_t stream);
 PN_API int pn_mlp_forward_tc_x3(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
-                         const float* code32, int n_objects, int n_views, int64_t points_per_object,
+                         const void* feat_x_lo, int n_objects, int n_views, int64_t points_per_object,
                          float* out, float* pre_act, void* workspace, size_t workspace_bytes, pn_stream_t stream);
 
 /* The TWO-PASS chain (mlp_precision = fp16x2): pn_mlp_forward_tc_x3 without its third operand pass -- every 512-wide
- * GEMM as a_hi w_hi + a_hi w_lo (weights as fp16 pairs, activations rounded to fp16 once), lin_z tables, lin_in and the
- * head in fp32 as in the precise chain.  Weight rounding and fp16 tables are the fast chain's two errors that are
+ * GEMM as a_hi w_hi + a_hi w_lo (weights as fp16 pairs, activations rounded to fp16 once), lin_z tables and head in
+ * fp32 and lin_in on the fp16 pair of the code as in the precise chain.  Weight rounding and fp16 tables are the fast chain's two errors that are
  * coherent along a ray (the same perturbed network at every sample); activation rounding is independent per sample and
  * averages out in the composite.  This form stays within north_star's 2e-3 on every BASELINE config, DTU depth
  * included (measured <= 1.7e-3), for two thirds of the precise chain's tensor work.  Same arguments as
  * pn_mlp_forward_tc_x3.  Inference only. */
 PN_API int pn_mlp_forward_tc_x2(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
-                         const float* code32, int n_objects, int n_views, int64_t points_per_object, float* out,
+                         const void* feat_x_lo, int n_objects, int n_views, int64_t points_per_object, float* out,
                          float* pre_act, void* workspace, size_t workspace_bytes, pn_stream_t stream);
 
 /* pn_mlp_forward_tc for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses

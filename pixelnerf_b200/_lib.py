@@ -534,26 +534,28 @@ def pack_weights_x3(w):
 
 
 def point_taps_f32(cam_bufs, hl, wl, ppo, *, rays=None, z=None, xyz=None, viewdirs=None):
-    """point_taps (n_views == 1) / point_taps_grouped (n_views > 1) plus the UNROUNDED positional code: returns
-    (feat_x (rows, 64) fp16, code32 (rows, 44) fp32) in the same row order."""
+    """point_taps (n_views == 1) / point_taps_grouped (n_views > 1) plus the fp16 remainder of the positional code:
+    returns (feat_x (rows, 64) fp16, feat_x_lo (rows, 64) fp16) in the same row order; columns [0, 42) of the two are
+    the fp16 pair x_hi + x_lo of the unrounded code (the rest of feat_x_lo is zero)."""
     cam = Camera(_ptr(cam_bufs["poses"]), _ptr(cam_bufs["focal"]), _ptr(cam_bufs["c"]),
                  cam_bufs["scale_x"], cam_bufs["scale_y"], hl, wl, cam_bufs["n_objects"], cam_bufs["n_views"])
     grouped = cam.n_views > 1
     n_rows = int(lib().pn_point_taps_grouped_rows(cam.n_objects * ppo, cam.n_views)) if grouped else cam.n_objects * ppo
     dev = cam_bufs["poses"].device
     feat_x = torch.empty(n_rows, 64, device=dev, dtype=torch.float16)
-    code32 = torch.empty(n_rows, 44, device=dev, dtype=torch.float32)
+    feat_x_lo = torch.empty(n_rows, 64, device=dev, dtype=torch.float16)
     rays, z, xyz, viewdirs = _f32c(rays), _f32c(z), _f32c(xyz), _f32c(viewdirs)
     k = 0 if z is None else z.shape[-1]
     with _Timed("features"):
         _check(lib().pn_point_taps_f32(C.byref(cam), _ptr(rays), _ptr(z), k, _ptr(xyz), _ptr(viewdirs), ppo,
-                                       feat_x.data_ptr(), _ptr(code32), int(grouped), _stream()), "pn_point_taps_f32")
-    return feat_x, code32
+                                       feat_x.data_ptr(), feat_x_lo.data_ptr(), int(grouped), _stream()), "pn_point_taps_f32")
+    return feat_x, feat_x_lo
 
 
-def mlp_forward_tc_x3(packed_x3, tables32, feat_x, code32, n_objects, n_views, ppo, want_pre=False, passes=3):
-    """The precise tensor-core chain (three fp16 hi/lo operand passes per GEMM, everything else fp32); inputs from
-    pack_weights_x3 / prepare_latent_tables_f32 / point_taps_f32.  -> (SB*ppo, 4) [sigmoid rgb, relu sigma].
+def mlp_forward_tc_x3(packed_x3, tables32, feat_x, feat_x_lo, n_objects, n_views, ppo, want_pre=False, passes=3):
+    """The precise tensor-core chain (three fp16 hi/lo operand passes per GEMM, lin_in on the fp16 pair of the code,
+    tables and head fp32); inputs from pack_weights_x3 / prepare_latent_tables_f32 / point_taps_f32.
+    -> (SB*ppo, 4) [sigmoid rgb, relu sigma].
     passes=2: the two-pass form (mlp_precision = fp16x2, pn_mlp_forward_tc_x2): no a_lo pass."""
     assert passes in (2, 3)
     entry, what = (lib().pn_mlp_forward_tc_x3, "pn_mlp_forward_tc_x3") if passes == 3 else \
@@ -561,15 +563,16 @@ def mlp_forward_tc_x3(packed_x3, tables32, feat_x, code32, n_objects, n_views, p
     dev = feat_x.device
     if tables32.dtype != torch.float32 or tables32.dim() != 3 or tables32.shape[0] != COMBINE_LAYER or not tables32.is_contiguous():
         raise RuntimeError("precise tensor-core MLP needs contiguous fp32 lin_z tables of shape (3, texels, 512)")
-    if feat_x.dtype != torch.float16 or feat_x.shape[1] != 64 or code32.shape != (feat_x.shape[0], 44) \
-            or not feat_x.is_contiguous() or not code32.is_contiguous():
-        raise RuntimeError("precise tensor-core MLP needs feat_x (rows, 64) fp16 and code32 (rows, 44) fp32 from point_taps_f32")
+    if feat_x.dtype != torch.float16 or feat_x.shape[1] != 64 or feat_x_lo.shape != feat_x.shape \
+            or feat_x_lo.dtype != torch.float16 or not feat_x.is_contiguous() or not feat_x_lo.is_contiguous():
+        raise RuntimeError("precise tensor-core MLP needs feat_x and feat_x_lo, both (rows, 64) fp16, from point_taps_f32")
     out = torch.empty(n_objects * ppo, 4, device=dev, dtype=torch.float32)
     pre = torch.empty_like(out) if want_pre else None
     nbytes = lib().pn_mlp_tc_grouped_workspace_bytes()
     ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
     with _Timed("mlp"):
-        _check(entry(packed_x3.data_ptr(), _ptr(tables32), tables32.shape[1], _ptr(feat_x, torch.float16), _ptr(code32),
+        _check(entry(packed_x3.data_ptr(), _ptr(tables32), tables32.shape[1], _ptr(feat_x, torch.float16),
+                     _ptr(feat_x_lo, torch.float16),
                      n_objects, n_views, ppo, _ptr(out), _ptr(pre), ws.data_ptr(), nbytes, _stream()), what)
     return (out, pre) if want_pre else out
 

@@ -119,7 +119,7 @@ int sample_fine_src(const RaySrc& rays, const float* z_coarse, const float* weig
                     uint64_t seed, pn_stream_t stream);
 int point_taps_src(const pn_camera_t* cam, const RaySrc& rays, const float* z, int n_samples, const float* xyz,
                    const float* viewdirs, int64_t points_per_object, void* feat_x, bool grouped, pn_stream_t stream,
-                   float* code32 = nullptr);
+                   void* feat_x_lo = nullptr);
 int composite_fwd_src(const float* rgb_sigma, const float* z, const RaySrc& rays, float* weights, float* rgb, float* depth,
                       int64_t n_rays, int n_samples, int white_bkgd, pn_stream_t stream);
 

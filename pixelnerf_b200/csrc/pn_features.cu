@@ -123,7 +123,7 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
                       const RaySrc rays, const float* __restrict__ zs, int n_samples,
                       const float* __restrict__ xyz_in, const float* __restrict__ dirs_in,
                       int64_t ppo, OutT* __restrict__ feat_z, OutT* __restrict__ feat_x, int ldx,
-                      int64_t n_rows, uint4* __restrict__ taps, int group = 0, float* __restrict__ code32 = nullptr) {
+                      int64_t n_rows, uint4* __restrict__ taps, int group = 0, __half* __restrict__ xlo = nullptr) {
   __shared__ __align__(16) unsigned char stage_all[kTaps ? kFeatWarps * 32 * kTapsPitch : 16];
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kFeatWarps + (threadIdx.x >> 5)) * 32;
@@ -170,9 +170,9 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     if (!valid) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(stage + lane * kTapsPitch + 16 * i) = make_uint4(0u, 0u, 0u, 0u);
-      if (code32 && row < n_rows) {
+      if (xlo && row < n_rows) {
 #pragma unroll
-        for (int i = 0; i < 11; ++i) *reinterpret_cast<float4*>(code32 + (size_t)row * 44 + 4 * i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(xlo + (size_t)row * 64 + 8 * i) = make_uint4(0u, 0u, 0u, 0u);
       }
     }
   }
@@ -266,15 +266,21 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
           // bit -- tests/test_gpu_guards.py; rounded to 2^-11 relative right below) takes the SFU sine:
           // |error| <= |arg| * 2^-24 + 2^-21.4 (arguments reach ~100: 6e-6), a fortieth of the fp16 quantum, against
           // ~25 instructions for sinf -- 36 of them per row were two thirds of this kernel.  The fp32 code (parity
-          // path, and code32 of the precise chain) keeps sinf.
-          val = (sizeof(OutT) == 2 && !(kTaps && code32)) ? __sinf(arg) : sinf(arg);
+          // path, and the fp16 hi + lo pair of the precise chains) keeps sinf.
+          val = (sizeof(OutT) == 2 && !(kTaps && xlo)) ? __sinf(arg) : sinf(arg);
         } else if (e < 42) {
           val = rd[e - 39];
         }
         q[i] = val;
       }
-      if (kTaps && code32)   // precise chain (fp16x3): the code also leaves unrounded, 44 floats per row
-        *reinterpret_cast<float4*>(code32 + (size_t)row * 44 + e0) = make_float4(q[0], q[1], q[2], q[3]);
+      if (kTaps && xlo) {   // precise chains: the fp16 remainder of the code, x_lo = fp16(x - fp16(x)), as a second row
+        float l[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) l[i] = q[i] - __half2float(__float2half_rn(q[i]));
+        const __half2 la = __floats2half2_rn(l[0], l[1]), lb = __floats2half2_rn(l[2], l[3]);
+        *reinterpret_cast<uint2*>(xlo + (size_t)row * 64 + e0) =
+            make_uint2(*reinterpret_cast<const uint32_t*>(&la), *reinterpret_cast<const uint32_t*>(&lb));
+      }
       if (sizeof(OutT) == 4) {
         *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(q[0], q[1], q[2], q[3]);
       } else {
@@ -282,6 +288,10 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
         *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ox) + e0) =
             make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
       }
+    }
+    if (kTaps && xlo) {
+#pragma unroll
+      for (int e0 = 44; e0 < 64; e0 += 4) *reinterpret_cast<uint2*>(xlo + (size_t)row * 64 + e0) = make_uint2(0u, 0u);
     }
     for (int e0 = 44; e0 < (kTaps ? 48 : ldx); e0 += 4) {  // zero padding up to ldx (up to the taps record)
       if (sizeof(OutT) == 4) *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -645,7 +655,7 @@ extern "C" int64_t pn_point_taps_grouped_rows(int64_t n_points, int n_views) {
 // pn_point_taps / pn_point_taps_grouped with the rays coming from any RaySrc (an explicit tensor, or frames)
 int pn::point_taps_src(const pn_camera_t* cam, const pn::RaySrc& rays, const float* z, int n_samples, const float* xyz,
                        const float* viewdirs, int64_t points_per_object, void* feat_x, bool grouped, pn_stream_t stream,
-                       float* code32) {
+                       void* feat_x_lo) {
   const bool have_rays = rays.rays || rays.poses;
   PN_CHECK_ARG(cam && feat_x, "pn_point_taps: null pointer");
   PN_CHECK_ARG(cam->poses && cam->focal && cam->c, "pn_point_taps: camera buffers missing (call encode first)");
@@ -660,7 +670,7 @@ int pn::point_taps_src(const pn_camera_t* cam, const pn::RaySrc& rays, const flo
   const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
   pn::point_features_kernel<__half, __half, true><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
       *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
-      (uint4*)feat_x, grouped ? 1 : 0, code32);
+      (uint4*)feat_x, grouped ? 1 : 0, (__half*)feat_x_lo);
   PN_LAUNCH_OK("point_features_kernel(taps)");
   pn::count_launch();
   return PN_OK;
@@ -678,12 +688,13 @@ extern "C" int pn_point_taps(const pn_camera_t* cam, const float* rays, const fl
   return pn::point_taps_src(cam, pn::ray_src(rays), z, n_samples, xyz, viewdirs, points_per_object, feat_x, false, stream);
 }
 
-// pn_point_taps / pn_point_taps_grouped that also write the positional code unrounded: code32 (rows, 44) fp32 in the
-// same row order as feat_x (columns [42,44) zero) -- the input of the precise chain's fp32 lin_in.
+// pn_point_taps / pn_point_taps_grouped that also write the fp16 REMAINDER of the positional code: feat_x_lo (rows, 64)
+// fp16 in the same row order as feat_x, x_lo = fp16(x - fp16(x)) in columns [0,42), zeros elsewhere -- with feat_x the
+// fp16 pair (22 significand bits) that the precise chains' tensor-core lin_in multiplies.
 extern "C" int pn_point_taps_f32(const pn_camera_t* cam, const float* rays, const float* z, int n_samples,
                                  const float* xyz, const float* viewdirs, int64_t points_per_object,
-                                 void* feat_x, float* code32, int grouped, pn_stream_t stream) {
-  PN_CHECK_ARG(code32 && ((uintptr_t)code32 & 15) == 0, "pn_point_taps_f32: code32 missing or misaligned");
+                                 void* feat_x, void* feat_x_lo, int grouped, pn_stream_t stream) {
+  PN_CHECK_ARG(feat_x_lo && ((uintptr_t)feat_x_lo & 127) == 0, "pn_point_taps_f32: feat_x_lo missing or misaligned");
   return pn::point_taps_src(cam, pn::ray_src(rays), z, n_samples, xyz, viewdirs, points_per_object, feat_x, grouped != 0,
-                            stream, code32);
+                            stream, feat_x_lo);
 }

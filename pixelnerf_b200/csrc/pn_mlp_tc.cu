@@ -64,8 +64,11 @@ enum {
   BAR_A_EMPTY = 2 * kStages + kASlots,
   BAR_ACT = 2 * kStages + 2 * kASlots,   // 8: operand chunk c of the current generation is in shared memory
   BAR_ACC = BAR_ACT + 8,                 // 4: accumulator (region, block) complete
-  BAR_COUNT = BAR_ACC + 4
+  BAR_XLO_FULL = BAR_ACC + 4,            // precise chains: the x_lo chunk of the coming lin_in has landed (in ACT chunk 7)
+  BAR_XLO_FREE = BAR_XLO_FULL + 1,       //   the last GEMM before that lin_in is complete: ACT may be overwritten
+  BAR_COUNT = BAR_XLO_FREE + 1
 };
+constexpr int kOffXlo = kOffAct + 7 * kChunkBytes;
 constexpr int kOffTmemPtr = kOffBar + BAR_COUNT * 8;
 constexpr int kOffStage = (kOffTmemPtr + 16 + 511) / 512 * 512;   // per epilogue warp: [32 rows x 32 x 16 bit], 64-byte swizzle: table-blend staging and TMA-store source
 constexpr int kStageBytes = 32 * 64;
@@ -115,9 +118,6 @@ struct ChainParams {
   // precise chain (kX3, mlp_precision = fp16x3): every 512-wide GEMM runs as three operand passes a_hi w_hi +
   // a_hi w_lo + a_lo w_hi (fp16 pairs, fp32 accumulate); everything else stays in fp32
   const float* tables32; // [3][n_texels][512] fp32 lin_z tables
-  const float* code32;   // (x_rows, 44) fp32 positional code, same row order as x
-  int64_t x_rows;
-  const float* w_in_t;   // lin_in.weight^T fp32 [44][512]
   // two-pass chain (mlp_precision = fp16x2, pn_mlp_forward_tc_x2): the precise chain without its third pass --
   // a_hi W_hi + a_hi W_lo: weights as fp16 pairs, activations single fp16, tables / lin_in / head in fp32
   int drop_a_lo;         // 0 (three passes) or 1
@@ -195,7 +195,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&map_w);
     prefetch_tensormap(&map_x);
-    if (kSave) prefetch_tensormap(&map_s);
+    if (kSave || kX3) prefetch_tensormap(&map_s);   // kSave: store map of the saved operands; kX3: the x_lo rows
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -208,6 +208,8 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     }
     for (int c = 0; c < 8; ++c) mbar_init(bar(BAR_ACT + c), 8);  // 4 warps per chunk per CTA
     for (int a = 0; a < 4; ++a) mbar_init(bar(BAR_ACC + a), 1);
+    mbar_init(bar(BAR_XLO_FULL), 1);
+    mbar_init(bar(BAR_XLO_FREE), 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc_pair(smem_base + kOffTmemPtr, 512);
@@ -263,6 +265,23 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       __syncwarp();
       if (++as == kASlots) { as = 0; aph ^= 1; }
     };
+    // Precise chains: the fp16 REMAINDER of the positional code, x_lo = fp16(x - fp16(x)) (pn_point_taps_f32 writes it
+    // as a second [rows x 64] fp16 tensor), so that lin_in runs on the tensor cores as x_hi W_hi + x_hi W_lo + x_lo W_hi,
+    // exact to 2^-22.  Shared memory has no room for a third operand slot; the chunk borrows ACT chunk 7, which is idle
+    // between the last GEMM before a lin_in (its MMAs complete: BAR_XLO_FREE, committed by the issuer) and that
+    // lin_in's epilogue (which first waits for the lin_in accumulators, i.e. for the MMAs that read the chunk).  The
+    // load overlaps the head / merge epilogue of the previous tile.
+    uint32_t xlo_ph = 0;
+    auto load_xlo = [&](int row0) {
+      wait_bar<false>(bar(BAR_XLO_FREE), xlo_ph ^ 1, p.err, 0x120);
+      xlo_ph ^= 1;
+      if (elect_one()) {
+        const uint32_t full = bar(BAR_XLO_FULL);
+        if (rank == 0) mbar_arrive_expect_tx(full, 2 * kChunkBytes);
+        tma_load_2d_pair(smem_base + kOffXlo, &map_s, full, 0, row0);
+      }
+      __syncwarp();
+    };
     using S0 = std::integral_constant<uint32_t, 0>;
     using S1 = std::integral_constant<uint32_t, 1>;
     using S2 = std::integral_constant<uint32_t, 2>;
@@ -301,6 +320,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll 1
         for (int k = 0; k < p.n_views; ++k) {
           load_a(&map_x, 0, ((tile * p.n_views + k) * 2 + (int)rank) * kRows);
+          if constexpr (kX3) load_xlo(((tile * p.n_views + k) * 2 + (int)rank) * kRows);
           load_w(S0{}, L_IN, 0, 0, 1);
           load_w(S1{}, L_IN, 1, 0, 1);
 #pragma unroll 1
@@ -318,6 +338,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       if (full_front) {
         load_a(&map_x, 0, row0);
+        if constexpr (kX3) load_xlo(row0);
         load_w(S0{}, L_IN, 0, 0, 1);           // hi and lo halves of lin_in
         load_w(S1{}, L_IN, 1, 0, 1);
       }
@@ -340,7 +361,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // descriptor = constant high word | (address >> 4): only the low word changes per MMA
     const uint64_t desc_hi = smem_desc_k128(0);
     // One weight stage: nk K=16 steps; A steps [0,4) come from a0, [4,8) from a1 (64-wide chunks).
-    auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask) {
+    auto item = [&](auto stage_c, uint32_t a0, uint32_t a1, uint32_t d_col, bool clear, uint32_t kmask, uint32_t a2 = 0) {
       constexpr uint32_t idesc = kIdesc;
       const uint32_t ws = (kX3 && !p.drop_a_lo) ? (decltype(stage_c)::value & 1u) : decltype(stage_c)::value;
       wait_bar<false>(bar(BAR_W_FULL + ws), (wpar >> ws) & 1u, p.err, 0x200 + ws);
@@ -357,6 +378,12 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)a_lo, desc_hi | (uint64_t)bj, idesc,
                           (clear && j == 0) ? 0u : 1u);
           }
+        if (a2) {   // lin_in of the precise chains: + x_lo W_hi (K steps 0-2 of the first box)
+#pragma unroll
+          for (int j = 0; j < 3; ++j)
+            umma_f16_pair(tmem_base + d_col, desc_hi | (uint64_t)((a2 >> 4) + 2 * j), desc_hi | (uint64_t)(b_lo + 2 * j),
+                          idesc, 1u);
+        }
         umma_commit_pair(bar(BAR_W_EMPTY + ws), quad ? 0xF : 0x3);   // frees the stage in every CTA of the cluster
       }
       __syncwarp();
@@ -364,6 +391,13 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     auto commit = [&](int b) {
       if (elect_one()) umma_commit_pair(bar(b), pair_mask);
       __syncwarp();
+    };
+    uint32_t xlo_fph = 0;
+    auto take_xlo = [&]() -> uint32_t {     // precise chains: the x_lo chunk of this lin_in (0 otherwise)
+      if constexpr (!kX3) return 0u;
+      wait_bar<false>(bar(BAR_XLO_FULL), xlo_fph, p.err, 0x230);
+      xlo_fph ^= 1;
+      return smem_base + kOffXlo;
     };
     auto wait_chunk = [&](int c) { wait_bar<false>(bar(BAR_ACT + c), gen & 1, p.err, 0x210 + c); };
     auto wait_act = [&](int c0) {
@@ -418,9 +452,10 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll 1
         for (int k = 0; k < p.n_views; ++k) {
           const uint32_t xa = take_a();
+          const uint32_t xl = take_xlo();
           tc_fence_after();
-          item(S0{}, xa, xa, kColH, true, 0x77u);
-          item(S1{}, xa, xa, kColH + 128, true, 0x77u);
+          item(S0{}, xa, xa, kColH, true, 0x77u, xl);
+          item(S1{}, xa, xa, kColH + 128, true, 0x77u, xl);
           release_a(xa);
           commit(BAR_ACC + 0);
           commit(BAR_ACC + 1);
@@ -430,6 +465,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             gemm_act(kColH, false, 0);
           }
           if (k + 1 < p.n_views) {
+            if constexpr (kX3) commit(BAR_XLO_FREE);   // the next sub-tile's x_lo may land in ACT chunk 7
             // the merge epilogue reads this sub-tile's h (and parks its view means): wait for its drain signal
             // before the next sub-tile's lin_in clears h.  After the LAST sub-tile the merge epilogue's signals are
             // the operand-ready signals of block 3's fc_0 instead (consumed by gemm_act below).
@@ -443,6 +479,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           gemm_act(kColT, true, 1);
           gemm_act(kColH, false, 0);
         }
+        if constexpr (kX3) commit(BAR_XLO_FREE);
         wait_act(0);     // the fp32 head has read h
         wait_act(4);
         ++gen;
@@ -450,9 +487,10 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       if (full_front) {
         const uint32_t xa = take_a();
+        const uint32_t xl = take_xlo();
         tc_fence_after();
-        item(S0{}, xa, xa, kColH, true, 0x77u);      // lin_in: x (K = 48 of the zero-padded 64) times W_hi, then W_lo
-        item(S1{}, xa, xa, kColH + 128, true, 0x77u);
+        item(S0{}, xa, xa, kColH, true, 0x77u, xl);  // lin_in: x (K = 48 of the zero-padded 64) times W_hi, then W_lo
+        item(S1{}, xa, xa, kColH + 128, true, 0x77u, xl);
         release_a(xa);
         commit(BAR_ACC + 0);                   // the h_0 epilogue adds the lin_z[0] table blend
         commit(BAR_ACC + 1);
@@ -462,6 +500,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         gemm_act(kColT, true, 1);              // t = fc_0(relu(h))
         gemm_act(kColH, false, 0);             // h += fc_1(relu(t))
       }
+      if constexpr (kX3) commit(BAR_XLO_FREE);   // the next tile's x_lo may land in ACT chunk 7
       // The epilogue is still reading h out of tensor memory -- for the fp32 head (lin_out on the CUDA cores) or
       // for the dump that ends a per-view segment: wait for its drain signal before the next tile's lin_in clears h.
       wait_act(0);
@@ -673,29 +712,6 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         __syncwarp();
       }
     };
-    // lin_in (resnetfc.py:141-146: h = lin_in(x), K = 42) in fp32 on the CUDA cores for this lane's row: 32 features
-    // starting at n0, added to acc.  x = the unrounded positional code of the row (code32), weights = lin_in.weight^T
-    // (warp-uniform float4 loads).  The tensor-core lin_in of the fast chain still runs -- its commit is what tells
-    // both CTAs' epilogue warps that the tile's x (and taps) have landed -- but its fp16-input result is discarded.
-    auto lin_in_ffma = [&](int64_t xrow, int n0, float (&acc)[32]) {
-      if (xrow >= p.x_rows) return;     // rows of a dummy / ragged tile past the end of the input
-      const float4* xr = reinterpret_cast<const float4*>(p.code32 + (size_t)xrow * 44);
-#pragma unroll 1
-      for (int k4 = 0; k4 < 11; ++k4) {
-        const float4 xv = __ldg(xr + k4);
-        const float xs4[4] = {xv.x, xv.y, xv.z, xv.w};
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          const float4* wr = reinterpret_cast<const float4*>(p.w_in_t + (size_t)(k4 * 4 + kk) * 512 + n0);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float4 w4 = __ldg(wr + i);
-            acc[4 * i] = fmaf(xs4[kk], w4.x, acc[4 * i]); acc[4 * i + 1] = fmaf(xs4[kk], w4.y, acc[4 * i + 1]);
-            acc[4 * i + 2] = fmaf(xs4[kk], w4.z, acc[4 * i + 2]); acc[4 * i + 3] = fmaf(xs4[kk], w4.w, acc[4 * i + 3]);
-          }
-        }
-      }
-    };
     // fp32 dump of (accumulator + bias) of one block: segment end (h_io) and the debug tap
     auto dump_block = [&](uint32_t tcol, const float* bias_vec, int nb, float* dst, int64_t grow) {
 #pragma unroll 1
@@ -801,11 +817,7 @@ mlp_chain_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
         uint32_t v0[32], v1[32];
         const uint32_t dst = smem_base + kOffAct + c0 * kChunkBytes + row_off;
-        if (kX3 && gather_b == 0) {
-          // precise chain: h_0 = lin_in(x) in fp32 (+ the table blend); the accumulator holds the discarded fp16 form
-          lin_in_ffma(xrow, c0 * 64 + 32 * ch, b0);
-          lin_in_ffma(xrow, c0 * 64 + 64 + 32 * ch, b1);
-        } else {
+        {
           tmem_ld_32x32(tcol, v0);
           tmem_ld_32x32(tcol + 64, v1);
           tmem_wait_ld();
@@ -1133,8 +1145,7 @@ pack_weights_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
 }
 
 // Precise chain (fp16x3): the lo halves of the ten 512x512 matrices, W_lo = fp16(W - fp16(W)), as layers
-// [kLayers + L_FC, kLayers + L_OUT) of the packed buffer (the other slots of the second half stay unused), and
-// lin_in.weight transposed in fp32 ([k][n], n contiguous) for the CUDA-core lin_in.
+// [kLayers + L_FC, kLayers + L_OUT) of the packed buffer (the other slots of the second half stay unused).
 __global__ void __launch_bounds__(256)
 pack_weights_lo_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1145,13 +1156,7 @@ pack_weights_lo_kernel(pn_mlp_weights_t w, __half* __restrict__ dst) {
   const float v = ((layer - L_FC) & 1) ? w.fc1_w[b][n * 512 + k] : w.fc0_w[b][n * 512 + k];
   dst[((size_t)(kLayers + layer) * 512 + n) * 512 + k] = __float2half_rn(v - __half2float(__float2half_rn(v)));
 }
-__global__ void __launch_bounds__(256)
-pack_lin_in_t_kernel(pn_mlp_weights_t w, float* __restrict__ dst) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 44 * 512) return;
-  const int k = i / 512, n = i % 512;
-  dst[i] = k < PN_D_CODE ? w.lin_in_w[n * PN_D_CODE + k] : 0.0f;
-}
+
 
 // table A: cumulative from lin_in; table B: cumulative from block 3 (h handed over with biases in).
 __global__ void __launch_bounds__(512)
@@ -1244,10 +1249,9 @@ extern "C" int pn_prepare_weights(const pn_mlp_weights_t* w, void* packed, size_
   return PN_OK;
 }
 
-// packed buffer of the precise chain: [hi layers][lo layers][bias table A][bias table B][lin_in.weight^T fp32 (44 x 512)]
+// packed buffer of the precise chain: [hi layers][lo layers][bias table A][bias table B]
 constexpr size_t kX3BiasOff = 2 * pn::tc::kPackedWeightBytes;
-constexpr size_t kX3WinOff = kX3BiasOff + 2 * pn::tc::kBiasBytes;
-extern "C" size_t pn_mlp_tc_packed_x3_bytes(void) { return kX3WinOff + 44 * 512 * sizeof(float); }
+extern "C" size_t pn_mlp_tc_packed_x3_bytes(void) { return kX3BiasOff + 2 * pn::tc::kBiasBytes; }
 
 extern "C" int pn_prepare_weights_x3(const pn_mlp_weights_t* w, void* packed, size_t packed_bytes, pn_stream_t stream) {
   using namespace pn::tc;
@@ -1263,9 +1267,7 @@ extern "C" int pn_prepare_weights_x3(const pn_mlp_weights_t* w, void* packed, si
   PN_LAUNCH_OK("pack_weights_lo_kernel");
   pack_bias_kernel<<<1, 512, 0, st>>>(*w, (float*)((char*)packed + kX3BiasOff), (float*)((char*)packed + kX3BiasOff + kBiasBytes));
   PN_LAUNCH_OK("pack_bias_kernel");
-  pack_lin_in_t_kernel<<<pn::ceil_div(44 * 512, 256), 256, 0, st>>>(*w, (float*)((char*)packed + kX3WinOff));
-  PN_LAUNCH_OK("pack_lin_in_t_kernel");
-  pn::count_launch(4);
+  pn::count_launch(3);
   return PN_OK;
 }
 
@@ -1410,11 +1412,11 @@ extern "C" int pn_mlp_forward_tc_grouped(const void* packed, const void* tables,
 
 // ---- precise chain: mlp_precision = fp16x3 ------------------------------------------------------------------------
 static int mlp_forward_tc_pairs(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
-                                const float* code32, int n_objects, int n_views, int64_t points_per_object,
+                                const void* feat_x_lo, int n_objects, int n_views, int64_t points_per_object,
                                 float* out, float* pre_act, void* workspace, size_t workspace_bytes, int drop_a_lo,
                                 pn_stream_t stream) {
   using namespace pn::tc;
-  PN_CHECK_ARG(packed_x3 && tables32 && feat_x && code32 && out && workspace, "pn_mlp_forward_tc_x3: null pointer");
+  PN_CHECK_ARG(packed_x3 && tables32 && feat_x && feat_x_lo && out && workspace, "pn_mlp_forward_tc_x3: null pointer");
   PN_CHECK_ARG(n_texels > 0, "pn_mlp_forward_tc_x3: no texels");
   PN_CHECK_ARG(n_objects > 0 && n_views > 0 && n_views <= 64 && points_per_object >= 0, "pn_mlp_forward_tc_x3: bad sizes");
   const int64_t n_pts = (int64_t)n_objects * points_per_object;
@@ -1424,13 +1426,15 @@ static int mlp_forward_tc_pairs(const void* packed_x3, const float* tables32, in
   PN_CHECK_ARG(x_rows < (1ll << 31) - 4096, "pn_mlp_forward_tc_x3: too many rows for one launch");
   PN_CHECK_ARG(workspace_bytes >= pn_mlp_tc_grouped_workspace_bytes(), "pn_mlp_forward_tc_x3: workspace too small");
   PN_CHECK_ARG(((uintptr_t)workspace & 255) == 0 && ((uintptr_t)tables32 & 15) == 0 && ((uintptr_t)feat_x & 15) == 0 &&
-                   ((uintptr_t)code32 & 15) == 0 && ((uintptr_t)packed_x3 & 255) == 0,
+                   ((uintptr_t)feat_x_lo & 15) == 0 && ((uintptr_t)packed_x3 & 255) == 0,
                "pn_mlp_forward_tc_x3: misaligned buffer");
   cudaStream_t st = (cudaStream_t)stream;
   CUtensorMap mw, mx;
   int rc;
   if ((rc = make_map(&mw, packed_x3, (uint64_t)2 * kLayers * 512, 512, 1024, 128))) return rc;
   if ((rc = make_map(&mx, feat_x, (uint64_t)x_rows, 64, 128, kRows))) return rc;
+  CUtensorMap ml;
+  if ((rc = make_map(&ml, feat_x_lo, (uint64_t)x_rows, 64, 128, kRows))) return rc;
   unsigned int* err = (unsigned int*)workspace;
   PN_CUDA_OK(cudaMemsetAsync(err, 0, 4, st));
   ChainParams p = {};
@@ -1439,9 +1443,6 @@ static int mlp_forward_tc_pairs(const void* packed_x3, const float* tables32, in
   p.err = err;
   p.table_stride = n_texels * 512;
   p.tables32 = tables32;
-  p.code32 = code32;
-  p.x_rows = x_rows;
-  p.w_in_t = (const float*)((const char*)packed_x3 + kX3WinOff);
   p.ppo = points_per_object;
   p.n_views = n_views;
   p.debug_stage = -1;
@@ -1454,23 +1455,23 @@ static int mlp_forward_tc_pairs(const void* packed_x3, const float* tables32, in
   p.last_block = 5;
   p.park = (float*)((char*)workspace + 256);
   p.drop_a_lo = drop_a_lo;
-  return launch_chain(mw, mx, mw, p, st);
+  return launch_chain(mw, mx, ml, p, st);
 }
 
 extern "C" int pn_mlp_forward_tc_x3(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
-                                    const float* code32, int n_objects, int n_views, int64_t points_per_object,
+                                    const void* feat_x_lo, int n_objects, int n_views, int64_t points_per_object,
                                     float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                                     pn_stream_t stream) {
-  return mlp_forward_tc_pairs(packed_x3, tables32, n_texels, feat_x, code32, n_objects, n_views, points_per_object, out,
+  return mlp_forward_tc_pairs(packed_x3, tables32, n_texels, feat_x, feat_x_lo, n_objects, n_views, points_per_object, out,
                               pre_act, workspace, workspace_bytes, 0, stream);
 }
 
 // mlp_precision = fp16x2: the precise chain without its third operand pass (a_lo W_hi).  Weight rounding and the fp16
 // tables are the fast chain's errors that do not average out along a ray; activation rounding does.
 extern "C" int pn_mlp_forward_tc_x2(const void* packed_x3, const float* tables32, int64_t n_texels, const void* feat_x,
-                                    const float* code32, int n_objects, int n_views, int64_t points_per_object,
+                                    const void* feat_x_lo, int n_objects, int n_views, int64_t points_per_object,
                                     float* out, float* pre_act, void* workspace, size_t workspace_bytes,
                                     pn_stream_t stream) {
-  return mlp_forward_tc_pairs(packed_x3, tables32, n_texels, feat_x, code32, n_objects, n_views, points_per_object, out,
+  return mlp_forward_tc_pairs(packed_x3, tables32, n_texels, feat_x, feat_x_lo, n_objects, n_views, points_per_object, out,
                               pre_act, workspace, workspace_bytes, 1, stream);
 }

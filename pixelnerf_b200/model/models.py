@@ -214,9 +214,9 @@ class PixelNeRFNet(torch.nn.Module):
         _, hl, wl, _ = self.latent_nhwc(torch.float32).shape
         if prec in ("fp16x3", "fp16x2"):     # fp16x2: the same chain without its third operand pass
             with prof_range("encoder_index"):
-                fx, code32 = _lib.point_taps_f32(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
+                fx, fx_lo = _lib.point_taps_f32(cam, hl, wl, ppo, rays=rays, z=z, xyz=xyz, viewdirs=viewdirs)
             with prof_range("resnetfc_infer"):
-                return _lib.mlp_forward_tc_x3(mlp.packed("fp16x3"), self.latent_tables(coarse, fp32=True), fx, code32,
+                return _lib.mlp_forward_tc_x3(mlp.packed("fp16x3"), self.latent_tables(coarse, fp32=True), fx, fx_lo,
                                               cam["n_objects"], cam["n_views"], ppo, passes=3 if prec == "fp16x3" else 2)
         tables = self.latent_tables(coarse)
         stash = getattr(self, "_train_stash", None)

@@ -1,7 +1,9 @@
-# round-2: bench of the two-pass and precise chains on the three scene classes (final kernels)
+# round-2: final kernels -- whole GPU suite, bench of the two-pass and precise chains on the three scene classes, parity report
 set -x
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
+timeout 1800 python -m pytest tests -m gpu -x -q > gpurun_out/r02z_gpu_tests.log 2>&1; echo "tests rc=$?"
+tail -3 gpurun_out/r02z_gpu_tests.log
 for PR in fp16x2 fp16x3; do
 for SC in srn_car srn_chair dtu; do
   timeout 600 python bench.py --precision $PR --scene $SC --steps 5 --no-extras --no-cpu-baseline > gpurun_out/r02z_bench_${PR}_$SC.json 2> gpurun_out/r02z_bench_${PR}_$SC.err; echo "bench $PR $SC rc=$?"
@@ -12,3 +14,5 @@ print("PS $PR $SC", round(d["value"]), round(d["e2e"]["value"]), round(d["ms_per
 PY
 done
 done
+timeout 600 python tests/parity_report.py --out gpurun_out/r02_parity.json > gpurun_out/r02z_parity.log 2>&1; echo "parity rc=$?"
+grep "fp16x2\|fp16x3" gpurun_out/r02z_parity.log | cut -c1-230

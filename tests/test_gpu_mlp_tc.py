@@ -37,6 +37,13 @@ def _inputs(n, seed=0):
     return idx, wt, latent, fx.half()
 
 
+def _xlo_rows(code, fx16):
+    """The second operand row of the precise chains: x_lo = fp16(x - fp16(x)) in columns [0, 42) of a (n, 64) fp16 row."""
+    lo = torch.zeros(code.shape[0], 64, dtype=torch.float16)
+    lo[:, :42] = (code[:, :42] - fx16[:, :42].float()).half()
+    return lo
+
+
 def _tables(w, latent):
     from pixelnerf_b200 import _lib
     return _lib.prepare_latent_tables({k: v.cuda() for k, v in w.items()}, latent.reshape(1, 8, 24, 512).cuda())
@@ -282,10 +289,11 @@ def test_two_pass_chain_vs_emulation(ns, ppo, sb):
     fx[:, :42] = code[:, :42].half()
     rows = make_taps(idx, wt, fx)
     tables32 = _lib.prepare_latent_tables_f32(wd, latent.reshape(1, 8, 24, 512).cuda())
+    xlo = _xlo_rows(code, fx)
     if ns > 1:
-        rows_dev, code_dev = to_grouped(rows, sb, ns, ppo).cuda(), to_grouped(code, sb, ns, ppo).cuda().contiguous()
+        rows_dev, code_dev = to_grouped(rows, sb, ns, ppo).cuda(), to_grouped(xlo, sb, ns, ppo).cuda().contiguous()
     else:
-        rows_dev, code_dev = rows.cuda(), code.cuda()
+        rows_dev, code_dev = rows.cuda(), xlo.cuda()
     out, pre = _lib.mlp_forward_tc_x3(packed, tables32, rows_dev, code_dev, sb, ns, ppo, want_pre=True, passes=2)
     torch.cuda.synchronize()
     assert torch.isfinite(pre).all() and pre.shape == (sb * ppo, 4)
@@ -330,10 +338,11 @@ def test_precise_chain_vs_float64(ns, ppo, sb):
     fx[:, :42] = code[:, :42].half()
     rows = make_taps(idx, wt, fx)
     tables32 = _lib.prepare_latent_tables_f32(wd, latent.reshape(1, 8, 24, 512).cuda())
+    xlo = _xlo_rows(code, fx)
     if ns > 1:
-        rows_dev, code_dev = to_grouped(rows, sb, ns, ppo).cuda(), to_grouped(code, sb, ns, ppo).cuda().contiguous()
+        rows_dev, code_dev = to_grouped(rows, sb, ns, ppo).cuda(), to_grouped(xlo, sb, ns, ppo).cuda().contiguous()
     else:
-        rows_dev, code_dev = rows.cuda(), code.cuda()
+        rows_dev, code_dev = rows.cuda(), xlo.cuda()
     out, pre = _lib.mlp_forward_tc_x3(packed, tables32, rows_dev, code_dev, sb, ns, ppo, want_pre=True)
     torch.cuda.synchronize()
     assert torch.isfinite(pre).all()
