@@ -117,7 +117,7 @@ template <> struct Vec16<__half> {
 // one lane storing its own row directly touches 32 lines for 8 bytes each per instruction.
 constexpr int kTapsPitch = 144;
 
-template <typename LatT, typename OutT, bool kTaps>
+template <typename LatT, typename OutT, bool kTaps, bool kLo = false>   // kLo: also the x_lo rows (precise chains)
 __global__ void __launch_bounds__(kFeatWarps * 32)
 point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
                       const RaySrc rays, const float* __restrict__ zs, int n_samples,
@@ -133,6 +133,9 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
   unsigned char* stage = stage_all + (kTaps ? (threadIdx.x >> 5) * 32 * kTapsPitch : 0);
   uint32_t o00 = 0, o01 = 0, o10 = 0, o11 = 0;
   float w00 = 0.f, w01 = 0.f, w10 = 0.f, w11 = 0.f;
+  uint2 lo_keep[kLo ? 11 : 1];     // precise chains: this lane's x_lo row (44 fp16), zero for rows that are not written
+#pragma unroll
+  for (int i = 0; i < (kLo ? 11 : 1); ++i) lo_keep[i] = make_uint2(0u, 0u);
   // row = (obj * NS + view) * P + p ...
   // (index arithmetic in 32 bits whenever the launch fits -- warp uniform; a 64-bit division is ~50 instructions and
   // this kernel is instruction bound: eight of them were a quarter of the taps kernel)
@@ -170,10 +173,7 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
     if (!valid) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(stage + lane * kTapsPitch + 16 * i) = make_uint4(0u, 0u, 0u, 0u);
-      if (xlo && row < n_rows) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(xlo + (size_t)row * 64 + 8 * i) = make_uint4(0u, 0u, 0u, 0u);
-      }
+
     }
   }
   if (valid) {
@@ -267,19 +267,18 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
           // |error| <= |arg| * 2^-24 + 2^-21.4 (arguments reach ~100: 6e-6), a fortieth of the fp16 quantum, against
           // ~25 instructions for sinf -- 36 of them per row were two thirds of this kernel.  The fp32 code (parity
           // path, and the fp16 hi + lo pair of the precise chains) keeps sinf.
-          val = (sizeof(OutT) == 2 && !(kTaps && xlo)) ? __sinf(arg) : sinf(arg);
+          val = (sizeof(OutT) == 2 && !kLo) ? __sinf(arg) : sinf(arg);
         } else if (e < 42) {
           val = rd[e - 39];
         }
         q[i] = val;
       }
-      if (kTaps && xlo) {   // precise chains: the fp16 remainder of the code, x_lo = fp16(x - fp16(x)), as a second row
-        float l[4];
+      if constexpr (kLo) {  // precise chains: the fp16 remainder of the code, x_lo = fp16(x - fp16(x)), as a second row
+        float l[4];           // (kept in registers: it leaves through the staging buffer after the first row has)
 #pragma unroll
         for (int i = 0; i < 4; ++i) l[i] = q[i] - __half2float(__float2half_rn(q[i]));
         const __half2 la = __floats2half2_rn(l[0], l[1]), lb = __floats2half2_rn(l[2], l[3]);
-        *reinterpret_cast<uint2*>(xlo + (size_t)row * 64 + e0) =
-            make_uint2(*reinterpret_cast<const uint32_t*>(&la), *reinterpret_cast<const uint32_t*>(&lb));
+        lo_keep[e0 >> 2] = make_uint2(*reinterpret_cast<const uint32_t*>(&la), *reinterpret_cast<const uint32_t*>(&lb));
       }
       if (sizeof(OutT) == 4) {
         *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(q[0], q[1], q[2], q[3]);
@@ -288,10 +287,6 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
         *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ox) + e0) =
             make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
       }
-    }
-    if (kTaps && xlo) {
-#pragma unroll
-      for (int e0 = 44; e0 < 64; e0 += 4) *reinterpret_cast<uint2*>(xlo + (size_t)row * 64 + e0) = make_uint2(0u, 0u);
     }
     for (int e0 = 44; e0 < (kTaps ? 48 : ldx); e0 += 4) {  // zero padding up to ldx (up to the taps record)
       if (sizeof(OutT) == 4) *reinterpret_cast<float4*>(reinterpret_cast<float*>(ox) + e0) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -305,6 +300,21 @@ point_features_kernel(pn_camera_t cam, const LatT* __restrict__ latent,
       const int j = it * 32 + lane, rr = j >> 3, piece = j & 7;
       if (row0 + rr < n_rows)
         taps[(row0 + rr) * 8 + piece] = *reinterpret_cast<const uint4*>(stage + rr * kTapsPitch + piece * 16);
+    }
+    if constexpr (kLo) {   // the x_lo rows take the same way out: staged, then coalesced 16-byte stores (zero rows stay zero)
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 11; ++i) *reinterpret_cast<uint2*>(stage + lane * kTapsPitch + 8 * i) = lo_keep[i];
+#pragma unroll
+      for (int i = 11; i < 16; ++i) *reinterpret_cast<uint2*>(stage + lane * kTapsPitch + 8 * i) = make_uint2(0u, 0u);
+      __syncwarp();
+      uint4* dst = reinterpret_cast<uint4*>(xlo);
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int j = it * 32 + lane, rr = j >> 3, piece = j & 7;
+        if (row0 + rr < n_rows)
+          dst[(row0 + rr) * 8 + piece] = *reinterpret_cast<const uint4*>(stage + rr * kTapsPitch + piece * 16);
+      }
     }
     return;
   }
@@ -668,9 +678,14 @@ int pn::point_taps_src(const pn_camera_t* cam, const pn::RaySrc& rays, const flo
                                  : (int64_t)cam->n_objects * cam->n_views * points_per_object;
   if (n_rows == 0) return PN_OK;
   const int blocks = pn::ceil_div(n_rows, pn::kFeatWarps * 32);
-  pn::point_features_kernel<__half, __half, true><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
-      *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
-      (uint4*)feat_x, grouped ? 1 : 0, (__half*)feat_x_lo);
+  if (feat_x_lo)
+    pn::point_features_kernel<__half, __half, true, true><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+        *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
+        (uint4*)feat_x, grouped ? 1 : 0, (__half*)feat_x_lo);
+  else
+    pn::point_features_kernel<__half, __half, true, false><<<blocks, pn::kFeatWarps * 32, 0, (cudaStream_t)stream>>>(
+        *cam, nullptr, rays, z, n_samples, xyz, viewdirs, points_per_object, nullptr, (__half*)feat_x, 64, n_rows,
+        (uint4*)feat_x, grouped ? 1 : 0, nullptr);
   PN_LAUNCH_OK("point_features_kernel(taps)");
   pn::count_launch();
   return PN_OK;
