@@ -99,7 +99,7 @@ class ResnetFC(nn.Module):
             params = self.weight_dict()
             if precision == "fp32":
                 hit = (key, _lib.pack_weights_fp32(params))
-            elif precision == "fp16x3":       # precise chain: fp16 hi + lo layers, fp32 lin_in
+            elif precision == "fp16x3":       # precise / two-pass chains: fp16 hi + lo layers
                 hit = (key, _lib.pack_weights_x3(params))
             elif precision == "bf16_train":   # row-major bf16 copies for the tensor-core backward
                 hit = (key, _lib.pack_weights_bf16(params))
